@@ -1,0 +1,153 @@
+"""Operator front-end: every op dispatches to the sm_100a kernel library for CUDA
+tensors and to the pure-torch oracle (:mod:`.reference`) otherwise.
+
+There is exactly one device code path (no multi-backend dispatch): a CUDA tensor
+either runs the hand-written kernel or raises -- it never silently falls back to
+cuDNN/ATen.  ``PICD_FORCE_TORCH=1`` is an explicit debugging switch that runs the
+oracle on the GPU for A/B comparison.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from . import reference as ref
+from ._lib import lib_available, lib_path, require_lib  # noqa: F401
+
+
+def _force_torch() -> bool:
+    return os.environ.get("PICD_FORCE_TORCH", "0") == "1"
+
+
+def use_native(x: torch.Tensor) -> bool:
+    """True when ``x`` must go through libpicd_b200.so (fails loudly if it is absent)."""
+    if not x.is_cuda or _force_torch():
+        return False
+    require_lib()
+    return True
+
+
+# ---------------------------------------------------------------------- CNN ops
+def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, padding=0, groups=1,
+                training=True, momentum=0.1, eps=1e-5, act="relu", residual=None, sync_group=False):
+    if use_native(x) and groups == 1:
+        from . import native
+        return native.conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride,
+                                  padding=padding, training=training, momentum=momentum, eps=eps,
+                                  act=act, residual=residual, sync_group=sync_group)
+    if x.is_cuda and not _force_torch() and groups != 1:
+        # depthwise convs (EfficientNet) keep the library conv but use the native BN/act kernels
+        from . import native
+        y = ref.conv2d(x, w, None, stride, padding, groups)
+        return native.bn_act(y, gamma, beta, running_mean, running_var, training=training,
+                             momentum=momentum, eps=eps, act=act, residual=residual,
+                             sync_group=sync_group)
+    return ref.conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride,
+                           padding=padding, groups=groups, training=training, momentum=momentum,
+                           eps=eps, act=act, residual=residual, sync_group=sync_group)
+
+
+def conv2d(x, w, bias=None, stride=1, padding=0, groups=1):
+    if use_native(x) and groups == 1:
+        from . import native
+        return native.conv2d(x, w, bias, stride, padding)
+    return ref.conv2d(x, w, bias, stride, padding, groups)
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum, eps, sync_group=False,
+               act=None, residual=None):
+    if use_native(x) and x.dim() == 4:
+        from . import native
+        return native.bn_act(x, gamma, beta, running_mean, running_var, training=training,
+                             momentum=momentum, eps=eps, act=act or "none", residual=residual,
+                             sync_group=sync_group)
+    z = ref.batch_norm(x, gamma, beta, running_mean, running_var, training, momentum, eps, sync_group)
+    if residual is not None:
+        z = z + residual
+    return ref.activation(z, act)
+
+
+def linear(x, w, b=None, act: Optional[str] = None):
+    if use_native(x):
+        from . import native
+        return native.linear(x, w, b, act)
+    return ref.linear(x, w, b, act)
+
+
+def activation(x, act):
+    if act in (None, "none"):
+        return x
+    if use_native(x):
+        from . import native
+        return native.activation(x, act)
+    return ref.activation(x, act)
+
+
+def max_pool2d(x, kernel_size, stride, padding=0, ceil_mode=False):
+    if use_native(x) and not ceil_mode:
+        from . import native
+        return native.pool2d(x, kernel_size, stride, padding, mode="max")
+    return ref.max_pool2d(x, kernel_size, stride, padding, ceil_mode)
+
+
+def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True):
+    if use_native(x) and count_include_pad:
+        from . import native
+        return native.pool2d(x, kernel_size, stride, padding, mode="avg")
+    return ref.avg_pool2d(x, kernel_size, stride, padding, count_include_pad)
+
+
+def global_avg_pool(x):
+    if use_native(x):
+        from . import native
+        return native.global_avg_pool(x)
+    return ref.global_avg_pool(x)
+
+
+def cross_entropy(logits, labels, weight=None):
+    if use_native(logits):
+        from . import native
+        return native.cross_entropy(logits, labels, weight)
+    return ref.cross_entropy(logits, labels, weight)
+
+
+def layer_norm(x, gamma, beta, eps=1e-6):
+    if use_native(x):
+        from . import native
+        return native.layer_norm(x, gamma, beta, eps)
+    return ref.layer_norm(x, gamma, beta, eps)
+
+
+def attention(q, k, v, scale=None):
+    if use_native(q):
+        from . import native
+        return native.attention(q, k, v, scale)
+    return ref.attention(q, k, v, scale)
+
+
+def dropout(x, p, training):
+    if not training or p == 0.0:
+        return x
+    if use_native(x):
+        from . import native
+        return native.dropout(x, p)
+    return ref.dropout(x, p, training)
+
+
+def synthetic_batch(batch, channels, height, width, num_classes, seed, step, device="cpu",
+                    dtype=torch.float32):
+    dev = torch.device(device)
+    if dev.type == "cuda" and not _force_torch():
+        require_lib()
+        from . import native
+        return native.synthetic_batch(batch, channels, height, width, num_classes, seed, step, dev, dtype)
+    return ref.synthetic_batch(batch, channels, height, width, num_classes, seed, step, dev, dtype)
+
+
+def normalize_u8(images_u8, dtype=torch.float32):
+    if use_native(images_u8):
+        from . import native
+        return native.normalize_u8(images_u8, dtype)
+    return ref.normalize_u8(images_u8, dtype)
