@@ -1,0 +1,194 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 classifier training throughput (images/sec) at 224x224, bf16, SGD-momentum,
+data-parallel over N GPUs of one node (BASELINE.json: "images/sec at 224^2 bf16 (device-timed, max over ranks)").
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 \
+        bench.py --gpus 8 --steps 20 --warmup 5
+    python bench.py --impl reference ...        # the unmodified reference (baseline/_ref) on the same config
+
+Protocol: W untimed warm-up steps, then exactly K steps bracketed by barrier + torch.cuda.synchronize() and a pair
+of CUDA events on the compute stream; the reported time is the MAX over ranks.  Weak scaling: the per-GPU batch is
+fixed, `value` is the whole-job images/sec.  Every step touches >1 GB of activations, i.e. inputs far larger than
+the 126 MB L2, so no explicit L2 flush is needed between iterations.  SM clocks / throttle reasons are sampled with
+nvidia-smi during the timed region.  `e2e` repeats the measurement through the public training API with the batch
+crossing PCIe from pinned host memory every step and the loss read back to the host every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+NUM_CLASSES = 7                           # the reference hard-codes 7 class weights (train.py:157)
+CLASS_WEIGHTS = [3, 3, 10, 1, 4, 4, 5]
+LR, MOMENTUM, WEIGHT_DECAY = 0.1, 0.9, 1e-4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch", type=int, default=256, help="per-GPU batch")
+    ap.add_argument("--image-size", type=int, default=224)
+    ap.add_argument("--sync-bn", action="store_true")
+    ap.add_argument("--optimizer", default="sgd")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--local_rank", "--local-rank", type=int, default=0)
+    return ap.parse_args()
+
+
+def published_baseline():
+    try:
+        with open(os.path.join(ROOT, "BASELINE.json")) as f:
+            pub = json.load(f).get("published", {})
+        for v in pub.values():
+            if isinstance(v, (int, float)):
+                return float(v)
+    except Exception:
+        pass
+    return None
+
+
+def timed_region(run_steps, steps, device, rank):
+    """barrier+sync, events around `steps` steps, barrier+sync; returns max-over-ranks milliseconds + clocks."""
+    import torch
+    import torch.distributed as dist
+    from picd_b200.utils.clocks import ClockSampler
+    multi = dist.is_available() and dist.is_initialized()
+    if multi:
+        dist.barrier(device_ids=[device.index])
+    torch.cuda.synchronize()
+    sampler = ClockSampler(device.index).start() if rank == 0 else None
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    run_steps(steps)
+    b.record()
+    torch.cuda.synchronize()
+    if multi:
+        dist.barrier(device_ids=[device.index])
+    ms = torch.tensor([a.elapsed_time(b)], device=device)
+    if multi:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    clocks = sampler.stop() if sampler is not None else None
+    return float(ms.item()), clocks
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def run_b200(args):
+    import torch
+    from picd_b200.data import SyntheticDeviceLoader, SyntheticHostLoader
+    from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
+    from picd_b200.models import Classifier, convert_sync_batchnorm
+    from picd_b200.ops import require_lib
+    from picd_b200.parallel import dist as D
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+
+    local_rank = D.init_distributed("b200", args.local_rank)
+    device = torch.device("cuda", torch.cuda.current_device())
+    rank, world = D.get_rank(), D.get_world_size()
+    lib = require_lib()
+    lib.picd_launch_count.restype = __import__("ctypes").c_ulonglong
+    torch.manual_seed(0)
+    model = Classifier(args.model, NUM_CLASSES, image_size=args.image_size)
+    if args.sync_bn:
+        convert_sync_batchnorm(model)
+    model = model.to(device)
+    spec = OptimizerSpec(kind=args.optimizer, lr=LR if args.optimizer == "sgd" else 1e-3, momentum=MOMENTUM,
+                         weight_decay=WEIGHT_DECAY)
+    dp = FusedDataParallel(model, spec)
+    dp.train()
+    loss_fn = WeightedCrossEntropy(torch.tensor(CLASS_WEIGHTS, dtype=torch.float32, device=device))
+    dev_loader = SyntheticDeviceLoader(args.batch, args.image_size, NUM_CLASSES, 1 << 30, device, seed=0)
+    counter = {"i": 0}
+    last = {}
+
+    def step(images, labels):
+        out = dp(images)
+        loss, _ = compute_loss(out, labels, loss_fn)
+        dp.optimizer.zero_grad()
+        loss.backward()
+        dp.optimizer.step()
+        return loss
+
+    def run_device(n):
+        for _ in range(n):
+            images, labels = dev_loader.batch(counter["i"])      # generated + normalised on the device
+            counter["i"] += 1
+            last["loss"] = step(images, labels)
+
+    run_device(args.warmup)
+    l0 = lib.picd_launch_count()
+    ms, clocks = timed_region(run_device, args.steps, device, rank)
+    launches = int(lib.picd_launch_count() - l0)
+    final_loss = float(last["loss"].item())
+    value = args.batch * world * args.steps / (ms / 1e3)
+
+    e2e = None
+    if not args.no_e2e:
+        host_loader = SyntheticHostLoader(args.batch, args.image_size, NUM_CLASSES, 1 << 30, device, seed=1)
+        sink = {"loss": 0.0}
+
+        def run_e2e(n):
+            for _ in range(n):
+                images, labels = host_loader.batch(counter["i"])   # pinned uint8 -> H2D -> device normalise
+                counter["i"] += 1
+                sink["loss"] = float(step(images, labels).item())  # D2H read of the step's result
+
+        run_e2e(max(3, args.warmup // 2))
+        ms_e, _ = timed_region(run_e2e, args.steps, device, rank)
+        e2e = {"value": args.batch * world * args.steps / (ms_e / 1e3), "unit": "images/sec",
+               "h2d_bytes_per_step": host_loader.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
+               "ms_per_step": ms_e / args.steps}
+
+    if rank == 0:
+        pub = published_baseline()
+        print(json.dumps({
+            "metric": "images/sec at 224^2 bf16 (device-timed, max over ranks)", "value": value, "unit": "images/sec",
+            "impl": "b200", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": (value / pub) if pub else None,
+            "dtype": "bf16", "data": "synthetic (generated + normalised on device; random-init weights)",
+            "config": {"model": f"{args.model}+MLP head ({NUM_CLASSES} classes)", "global_batch": args.batch * world,
+                       "per_gpu_batch": args.batch, "image_size": args.image_size, "seq_len": None,
+                       "optimizer": f"{args.optimizer}-momentum lr={LR} wd={WEIGHT_DECAY}", "sync_bn": args.sync_bn,
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss}))
+    D.barrier()
+    D.shutdown()
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """Runs the UNMODIFIED reference sources installed in baseline/_ref: its Classifier (nn/classifier.py), its
+    train_epoch (train.py:36-73, compiled from the installed file without executing the module-level script), its
+    AverageMeter, wrapped exactly as train.py:124-128 does (SyncBatchNorm optional, .cuda(), DDP).  Deviations, all
+    forced: random-init weights instead of the download, synthetic batches, bf16 autocast and
+    SGD-momentum as named by the BASELINE.json config, LOCAL_RANK handling."""
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.exists(os.path.join(ref_dir, "train.py")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md)"}))
+        return
+    try:
+        from baseline.ref_bench import run
+    except Exception as e:  # noqa: BLE001
+        print(json.dumps({"impl": "reference", "unavailable": f"harness import failed: {e!r}"[:200]}))
+        return
+    run(args, ref_dir, timed_region, published_baseline, dict(num_classes=NUM_CLASSES, class_weights=CLASS_WEIGHTS,
+                                                              lr=LR, momentum=MOMENTUM, weight_decay=WEIGHT_DECAY))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

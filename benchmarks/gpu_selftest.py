@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""GPU self-test + micro-benchmarks for libpicd_b200.so.
+
+Each group runs in its own subprocess under a timeout (a trapped kernel poisons only that process) and appends
+JSON lines to ``gpurun_out/selftest.jsonl``.  Usage on a GPU box:
+
+    python benchmarks/gpu_selftest.py                 # all groups
+    python benchmarks/gpu_selftest.py --group conv    # one group, in-process
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+OUT_DIR = os.path.join(ROOT, "gpurun_out")
+GROUPS = ["basic", "gemm", "conv", "model", "perf"]
+
+
+def emit(rec):
+    os.makedirs(OUT_DIR, exist_ok=True)
+    with open(os.path.join(OUT_DIR, "selftest.jsonl"), "a") as f:
+        f.write(json.dumps(rec) + "\n")
+    print(json.dumps(rec), flush=True)
+
+
+def relerr(a, b):
+    import torch
+    a, b = a.float(), b.float()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-6))
+
+
+def check(name, got, want, tol, group, extra=None):
+    e = relerr(got, want)
+    rec = {"group": group, "test": name, "relerr": e, "tol": tol, "ok": bool(e <= tol) and e == e}
+    if extra:
+        rec.update(extra)
+    emit(rec)
+    return rec["ok"]
+
+
+def time_cuda(fn, iters=10, warmup=3):
+    import torch
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+# ------------------------------------------------------------------------------------------ basic
+def group_basic():
+    import torch
+    import torch.nn.functional as F
+    from picd_b200 import ops
+    from picd_b200.ops import native, reference as ref
+    dev = torch.device("cuda")
+    ok = True
+    g = "basic"
+    # synthetic + normalize
+    img, lab = ops.synthetic_batch(4, 3, 32, 32, 7, 3, 5, dev, torch.float32)
+    rimg, rlab = ref.synthetic_batch(4, 3, 32, 32, 7, 3, 5, "cpu", torch.float32)
+    ok &= check("synthetic_fp32", img.cpu(), rimg, 1e-6, g)
+    emit({"group": g, "test": "synthetic_labels", "ok": bool((lab.cpu() == rlab).all())})
+    u8 = torch.randint(0, 256, (2, 16, 16, 3), dtype=torch.uint8, device=dev)
+    ok &= check("normalize_u8", ops.normalize_u8(u8, torch.bfloat16), ref.normalize_u8(u8), 1e-2, g)
+
+    # BN family
+    for (N, C, H, W, res, act) in [(8, 64, 14, 14, False, "relu"), (4, 256, 7, 7, True, "relu"), (4, 96, 9, 9, False, "none"),
+                                   (2, 2048, 7, 7, True, "relu"), (4, 40, 6, 6, False, "swish")]:
+        x = torch.randn(N, C, H, W, device=dev).mul_(1.5).add_(0.3).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        r = torch.randn(N, C, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) if res else None
+        gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_()
+        beta = (torch.randn(C, device=dev) * 0.1).requires_grad_()
+        rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+        xn = x.clone().requires_grad_()
+        rn = r.clone().requires_grad_() if res else None
+        z = native.bn_act(xn, gamma, beta, rm, rv, training=True, momentum=0.1, eps=1e-5, act=act, residual=rn, sync_group=False)
+        dz = torch.randn_like(z)
+        z.backward(dz)
+        xr = x.float().clone().requires_grad_()
+        rr = r.float().clone().requires_grad_() if res else None
+        g2, b2 = gamma.detach().clone().requires_grad_(), beta.detach().clone().requires_grad_()
+        rm2, rv2 = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+        zr = ref.batch_norm(xr, g2, b2, rm2, rv2, True, 0.1, 1e-5)
+        if res:
+            zr = zr + rr
+        zr = ref.activation(zr, act)
+        zr.backward(dz.float())
+        tag = f"bn[{N}x{C}x{H}x{W},res={res},{act}]"
+        ok &= check(tag + ".fwd", z, zr, 2e-2, g)
+        ok &= check(tag + ".dx", xn.grad, xr.grad, 3e-2, g)
+        ok &= check(tag + ".dgamma", gamma.grad, g2.grad, 3e-2, g)
+        ok &= check(tag + ".dbeta", beta.grad, b2.grad, 3e-2, g)
+        ok &= check(tag + ".running_var", rv, rv2, 1e-2, g)
+        if res:
+            ok &= check(tag + ".dres", rn.grad, rr.grad, 3e-2, g)
+
+    # pooling
+    for (k, s, p, mode) in [(3, 2, 1, "max"), (3, 2, 0, "max"), (3, 1, 1, "avg"), (5, 3, 0, "avg")]:
+        x = torch.randn(2, 64, 17, 17, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        xn = x.clone().requires_grad_()
+        y = native.pool2d(xn, k, s, p, mode)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr = x.float().requires_grad_()
+        yr = (F.max_pool2d if mode == "max" else F.avg_pool2d)(xr, k, s, p)
+        yr.backward(dy.float())
+        ok &= check(f"pool[{mode},{k},{s},{p}].fwd", y, yr, 1e-2, g)
+        ok &= check(f"pool[{mode},{k},{s},{p}].bwd", xn.grad, xr.grad, 2e-2, g)
+    x = torch.randn(4, 128, 7, 7, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xn = x.clone().requires_grad_()
+    y = native.global_avg_pool(xn)
+    y.backward(torch.ones_like(y))
+    ok &= check("gap.fwd", y, x.float().mean((2, 3)), 1e-2, g)
+    ok &= check("gap.bwd", xn.grad, torch.full_like(x, 1 / 49.0), 1e-2, g)
+
+    # cross entropy
+    lg = torch.randn(37, 7, device=dev, requires_grad=True)
+    lb = torch.randint(0, 7, (37,), device=dev)
+    w = torch.tensor([3, 3, 10, 1, 4, 4, 5.0], device=dev)
+    l = native.cross_entropy(lg, lb, w)
+    l.backward()
+    lg2 = lg.detach().clone().requires_grad_()
+    l2 = F.cross_entropy(lg2, lb, w)
+    l2.backward()
+    ok &= check("xent.loss", l.reshape(1), l2.reshape(1), 1e-5, g)
+    ok &= check("xent.grad", lg.grad, lg2.grad, 1e-4, g)
+
+    # layernorm
+    x = torch.randn(50, 768, device=dev).to(torch.bfloat16)
+    gm, bt = (torch.rand(768, device=dev) + 0.5).requires_grad_(), torch.randn(768, device=dev).requires_grad_()
+    xn = x.clone().requires_grad_()
+    y = native.layer_norm(xn, gm, bt, 1e-6)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr, gm2, bt2 = x.float().requires_grad_(), gm.detach().clone().requires_grad_(), bt.detach().clone().requires_grad_()
+    yr = F.layer_norm(xr, (768,), gm2, bt2, 1e-6)
+    yr.backward(dy.float())
+    ok &= check("layernorm.fwd", y, yr, 2e-2, g)
+    ok &= check("layernorm.dx", xn.grad, xr.grad, 3e-2, g)
+    ok &= check("layernorm.dgamma", gm.grad, gm2.grad, 3e-2, g)
+    ok &= check("layernorm.dbeta", bt.grad, bt2.grad, 3e-2, g)
+
+    # small linear
+    for (M, K, N, act) in [(16, 2048, 128, "relu"), (16, 32, 7, None), (5, 64, 32, "relu")]:
+        x = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        wt = (torch.randn(N, K, device=dev) / K ** 0.5).requires_grad_()
+        b = torch.randn(N, device=dev).requires_grad_()
+        xn = x.clone().requires_grad_()
+        y = native.linear(xn, wt, b, act)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr, w2, b2 = x.float().requires_grad_(), wt.detach().clone().requires_grad_(), b.detach().clone().requires_grad_()
+        yr = ref.linear(xr, w2, b2, act)
+        yr.backward(dy.float())
+        ok &= check(f"small_linear[{M},{K},{N},{act}].fwd", y, yr, 2e-2, g)
+        ok &= check(f"small_linear[{M},{K},{N},{act}].dx", xn.grad, xr.grad, 3e-2, g)
+        ok &= check(f"small_linear[{M},{K},{N},{act}].dw", wt.grad, w2.grad, 3e-2, g)
+        ok &= check(f"small_linear[{M},{K},{N},{act}].db", b.grad, b2.grad, 3e-2, g)
+
+    # fused update, single GPU
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    for kind in ["sgd", "adam", "adamw"]:
+        torch.manual_seed(0)
+        lin = torch.nn.Linear(96, 64).to(dev)
+        refm = torch.nn.Linear(96, 64).to(dev)
+        refm.load_state_dict(lin.state_dict())
+        spec = OptimizerSpec(kind=kind, lr=0.1 if kind == "sgd" else 1e-2, momentum=0.9, weight_decay=0.01)
+        dp = FusedDataParallel(lin, spec)
+        opt = {"sgd": lambda p: torch.optim.SGD(p, lr=0.1, momentum=0.9, weight_decay=0.01),
+               "adam": lambda p: torch.optim.Adam(p, lr=1e-2, weight_decay=0.01),
+               "adamw": lambda p: torch.optim.AdamW(p, lr=1e-2, weight_decay=0.01)}[kind](refm.parameters())
+        for it in range(3):
+            x = torch.randn(8, 96, device=dev)
+            loss = dp(x).square().mean()
+            loss.backward()
+            dp.optimizer.step()
+            opt.zero_grad()
+            refm(x).square().mean().backward()
+            opt.step()
+        ok &= check(f"fused_update[{kind}].weight", lin.weight, refm.weight, 1e-4, g)
+        ok &= check(f"fused_update[{kind}].shadow", lin.weight._shadow, refm.weight, 1e-2, g)
+        emit({"group": g, "test": f"fused_update[{kind}].grad_zeroed", "ok": bool(dp.arena.grad.abs().max().item() == 0)})
+    return ok
+
+
+# ------------------------------------------------------------------------------------------ gemm
+def group_gemm():
+    import torch
+    from picd_b200.ops import native
+    dev = torch.device("cuda")
+    ok = True
+    g = "gemm"
+    for (M, N, K) in [(128, 64, 64), (256, 128, 128), (1000, 256, 192), (4096, 768, 768), (50432 // 8, 3072, 768), (300, 2304, 768)]:
+        a = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        b = (torch.randn(N, K, device=dev) / K ** 0.5).to(torch.bfloat16)
+        bias = torch.randn(N, device=dev)
+        d = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        native.call("picd_gemm_nt", a, b, d, bias, 0, M, N, K)
+        torch.cuda.synchronize()
+        want = a.float() @ b.float().t() + bias
+        ok &= check(f"gemm_nt[{M},{N},{K}]", d, want, 1.5e-2, g)
+        d2 = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        native.call("picd_gemm_nt", a, b, d2, None, 1, M, N, K)
+        ok &= check(f"gemm_nt_relu[{M},{N},{K}]", d2, (a.float() @ b.float().t()).relu(), 1.5e-2, g)
+        # dgrad-style: D[M,K] = A[M,N] B[N,K]
+        dy = torch.randn(M, N, device=dev).to(torch.bfloat16)
+        dx = torch.empty(M, K, dtype=torch.bfloat16, device=dev)
+        native.call("picd_gemm_nn", dy, b, dx, M, N, K)
+        ok &= check(f"gemm_nn[{M},{N},{K}]", dx, dy.float() @ b.float(), 1.5e-2, g)
+        dw = torch.zeros(N, K, dtype=torch.float32, device=dev)
+        native.call("picd_gemm_tn_f32", dy, a, dw, M, N, K)
+        ok &= check(f"gemm_tn[{M},{N},{K}]", dw, dy.float().t() @ a.float(), 1.5e-2, g)
+    # throughput of the big ones
+    for (M, N, K) in [(8192, 8192, 8192), (50432, 3072, 768), (50432, 768, 3072)]:
+        a = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        b = torch.randn(N, K, device=dev).to(torch.bfloat16)
+        d = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        ms = time_cuda(lambda: native.call("picd_gemm_nt", a, b, d, None, 0, M, N, K))
+        ms_ref = time_cuda(lambda: torch.matmul(a, b.t()))
+        emit({"group": g, "test": f"gemm_nt_perf[{M},{N},{K}]", "ms": ms, "tflops": 2.0 * M * N * K / ms / 1e9,
+              "cublas_ms": ms_ref, "cublas_tflops": 2.0 * M * N * K / ms_ref / 1e9, "ok": True})
+    return ok
+
+
+# ------------------------------------------------------------------------------------------ conv
+CONV_CASES = [
+    # N, H, W, Cin, Cout, R, S, stride, pad
+    (2, 56, 56, 64, 64, 1, 1, 1, 0), (2, 56, 56, 64, 256, 1, 1, 1, 0), (2, 56, 56, 256, 64, 1, 1, 1, 0),
+    (2, 56, 56, 64, 64, 3, 3, 1, 1), (2, 56, 56, 128, 128, 3, 3, 2, 1), (2, 56, 56, 256, 512, 1, 1, 2, 0),
+    (4, 14, 14, 256, 256, 3, 3, 1, 1), (4, 14, 14, 1024, 2048, 1, 1, 2, 0), (4, 7, 7, 512, 512, 3, 3, 1, 1),
+    (4, 7, 7, 2048, 512, 1, 1, 1, 0), (3, 17, 17, 128, 128, 1, 7, 1, (0, 3)), (3, 17, 17, 160, 192, 7, 1, 1, (3, 0)),
+    (3, 35, 35, 48, 64, 5, 5, 1, 2), (3, 35, 35, 288, 384, 3, 3, 2, 0), (2, 9, 9, 80, 192, 3, 3, 1, 0),
+    (2, 224, 224, 3, 64, 7, 7, 2, 3), (2, 32, 32, 3, 64, 3, 3, 1, 1), (2, 64, 64, 3, 768, 16, 16, 16, 0),
+]
+
+
+def group_conv():
+    import torch
+    import torch.nn.functional as F
+    from picd_b200.ops import native
+    dev = torch.device("cuda")
+    ok = True
+    g = "conv"
+    for case in CONV_CASES:
+        N, H, W, Cin, Cout, R, S, stride, pad = case
+        torch.manual_seed(1)
+        x = torch.randn(N, Cin, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(Cout, Cin, R, S, device=dev) / (Cin * R * S) ** 0.5).contiguous(memory_format=torch.channels_last)
+        w.requires_grad_()
+        first = Cin % 8 != 0
+        xn = x.clone()
+        if not first:
+            xn.requires_grad_()
+        y = native.conv2d(xn, w, None, stride, pad)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr = x.float().requires_grad_()
+        wr = w.detach().to(torch.bfloat16).float().requires_grad_()
+        yr = F.conv2d(xr, wr, None, stride, pad)
+        yr.backward(dy.float())
+        tag = f"conv{list(case)}"
+        ok &= check(tag + ".fprop", y, yr, 1.5e-2, g)
+        ok &= check(tag + ".wgrad", w.grad, wr.grad, 2e-2, g)
+        if not first:
+            ok &= check(tag + ".dgrad", xn.grad, xr.grad, 2e-2, g)
+        # fused statistics epilogue
+        if not first:
+            stats = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
+            y2, _ = native._conv_forward(x, w.detach(), stride, pad, stats, None, None)
+            yf = y2.float()
+            ok &= check(tag + ".stats_sum", stats[:Cout], yf.sum((0, 2, 3)), 1e-2, g)
+            ok &= check(tag + ".stats_sumsq", stats[Cout:], (yf * yf).sum((0, 2, 3)), 1e-2, g)
+    return ok
+
+
+# ------------------------------------------------------------------------------------------ model
+def _model_grads(name, native_path, batch, size, dev):
+    import torch
+    os.environ["PICD_FORCE_TORCH"] = "0" if native_path else "1"
+    from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
+    from picd_b200.models import Classifier
+    from picd_b200.ops import reference as ref
+    torch.manual_seed(0)
+    m = Classifier(name, 7, image_size=size).to(dev)
+    m.train()
+    img, lab = ref.synthetic_batch(batch, 3, size, size, 7, 0, 0, "cpu", torch.float32)
+    img, lab = img.to(dev), lab.to(dev)
+    out = m(img)
+    loss, main = compute_loss(out, lab, WeightedCrossEntropy(None))
+    loss.backward()
+    grads = {k: p.grad.detach().float().clone() for k, p in m.named_parameters() if p.grad is not None}
+    return float(loss.item()), main.detach().float(), grads
+
+
+def group_model():
+    import torch
+    dev = torch.device("cuda")
+    ok = True
+    g = "model"
+    for name, batch, size in [("resnet18", 8, 64), ("resnet50", 8, 96), ("inceptionv3", 4, 299), ("vit_b_16", 4, 224),
+                              ("efficientnet-b0", 4, 64)]:
+        try:
+            l1, o1, g1 = _model_grads(name, True, batch, size, dev)
+            l0, o0, g0 = _model_grads(name, False, batch, size, dev)
+        except Exception as e:  # noqa: BLE001
+            emit({"group": g, "test": name, "ok": False, "error": repr(e)[:400]})
+            ok = False
+            continue
+        emit({"group": g, "test": f"{name}.loss", "native": l1, "torch": l0, "ok": abs(l1 - l0) < 0.05 * max(1.0, abs(l0))})
+        ok &= check(f"{name}.logits", o1, o0, 0.1, g)
+        worst, worst_k, missing = 0.0, None, [k for k in g0 if k not in g1]
+        for k in g0:
+            if k in g1:
+                e = relerr(g1[k], g0[k])
+                if e > worst:
+                    worst, worst_k = e, k
+        emit({"group": g, "test": f"{name}.grads", "worst_relerr": worst, "worst_param": worst_k, "missing": missing[:5],
+              "ok": worst < 0.25 and not missing})
+    os.environ["PICD_FORCE_TORCH"] = "0"
+    return ok
+
+
+# ------------------------------------------------------------------------------------------ perf
+def group_perf():
+    import torch
+    from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
+    from picd_b200.models import Classifier
+    from picd_b200.ops import synthetic_batch
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    dev = torch.device("cuda")
+    g = "perf"
+    for name, batch, size in [("resnet50", 128, 224), ("resnet50", 256, 224)]:
+        torch.manual_seed(0)
+        m = Classifier(name, 1000 if False else 7, image_size=size).to(dev)
+        dp = FusedDataParallel(m, OptimizerSpec(kind="sgd", lr=0.01, momentum=0.9))
+        dp.train()
+        img, lab = synthetic_batch(batch, 3, size, size, 7, 0, 0, dev, torch.bfloat16)
+        loss_fn = WeightedCrossEntropy(None)
+
+        def step():
+            out = dp(img)
+            loss, _ = compute_loss(out, lab, loss_fn)
+            loss.backward()
+            dp.optimizer.step()
+        ms = time_cuda(step, iters=8, warmup=3)
+        emit({"group": g, "test": f"{name}.step[b{batch}]", "ms": ms, "img_per_s": batch / ms * 1e3, "ok": True,
+              "mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30})
+        del dp, m
+        torch.cuda.empty_cache()
+    return True
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--group", default=None, choices=GROUPS)
+    ap.add_argument("--timeout", type=int, default=420)
+    args = ap.parse_args()
+    if args.group:
+        t0 = time.time()
+        try:
+            ok = globals()["group_" + args.group]()
+        except Exception as e:  # noqa: BLE001
+            import traceback
+            traceback.print_exc()
+            emit({"group": args.group, "test": "EXCEPTION", "ok": False, "error": repr(e)[:600]})
+            ok = False
+        emit({"group": args.group, "test": "SUMMARY", "ok": bool(ok), "seconds": time.time() - t0})
+        sys.exit(0 if ok else 1)
+    rc = 0
+    for grp in GROUPS:
+        try:
+            p = subprocess.run([sys.executable, os.path.abspath(__file__), "--group", grp], timeout=args.timeout)
+            if p.returncode != 0:
+                rc = 1
+        except subprocess.TimeoutExpired:
+            emit({"group": grp, "test": "TIMEOUT", "ok": False})
+            rc = 1
+    sys.exit(rc)
+
+
+if __name__ == "__main__":
+    main()

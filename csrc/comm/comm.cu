@@ -1,0 +1,332 @@
+// NVLink peer-memory communication fused with compute (BASELINE.json north-star).
+//
+// Every rank owns one cudaMalloc slab (gradient arena | fp32 masters | bf16 shadows | exchange slots | flags)
+// that is exported with CUDA IPC and mapped by all peers of the node.  Kernels then dereference peer pointers
+// directly; NVSwitch gives every pair full bandwidth, so there is no ring and no NCCL call on the hot path.
+//
+//   fused_allreduce_update_kernel  (one launch per gradient bucket, side stream, overlapped with backward)
+//       barrier-in  : flag words, st.release.sys / ld.acquire.sys, epoch numbered (never reset)
+//       two-shot    : rank r sums slice r of the bucket from all W gradient arenas over NVLink (fixed rank order),
+//                     scales by 1/W, runs SGD-momentum / Adam / AdamW on the fp32 master (optimizer state is
+//                     touched only by the slice owner), and PUSHES the new fp32 master + bf16 shadow to all peers
+//       one-shot    : every rank sums the whole (small, latency-bound) bucket and updates its own replica
+//       barrier-out : once every peer has read my gradients and pushed my weights, re-zero my gradient bucket
+//   bn_finalize_sync_kernel        SyncBatchNorm statistics: publish (sum, sumsq, count), wait, sum all peers'
+//                                   slots in rank order, finalize scale/shift/running stats -- one launch, no NCCL
+//   p2p_allreduce_small_kernel     the same exchange for the two backward BN reductions
+#include "../common/picd_common.cuh"
+
+#include <cstring>
+
+namespace picd {
+
+constexpr int MAX_PEERS = 8;
+
+struct PeerTable {
+    float* grad[MAX_PEERS];
+    float* master[MAX_PEERS];
+    __nv_bfloat16* shadow[MAX_PEERS];
+    float* xchg[MAX_PEERS];          // exchange slots for small collectives
+    unsigned* flags[MAX_PEERS];
+};
+
+struct OptArgs {
+    int kind;            // 0 sgd-momentum, 1 adam, 2 adamw
+    float lr, momentum, beta1, beta2, eps, weight_decay;
+    float bc1, bc2;      // 1 - beta^step (adam bias corrections)
+    int nesterov;
+    float grad_scale;    // 1 / world
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+// Spin until every peer's flag word (in MY flag array) has reached `epoch`; bounded so a lost peer traps
+// instead of hanging the GPU forever.
+__device__ __forceinline__ void wait_flags(const unsigned* my_flags, int slot, int W, unsigned epoch) {
+    if (threadIdx.x < W) {
+        const unsigned* f = my_flags + slot * MAX_PEERS + threadIdx.x;
+        const long long t0 = clock64();
+        while (static_cast<int>(ld_acquire_sys(f) - epoch) < 0) {
+            if (clock64() - t0 > 40000000000LL) __trap();     // ~20 s
+        }
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void signal_peers(const PeerTable& pt, int slot, int rank, int W, unsigned epoch) {
+    __threadfence_system();
+    if (threadIdx.x < W) st_release_sys(pt.flags[threadIdx.x] + slot * MAX_PEERS + rank, epoch);
+}
+
+__device__ __forceinline__ float opt_update(float p, float g, float& s0, float& s1, const OptArgs& o) {
+    g *= o.grad_scale;
+    if (o.kind == 0) {
+        g = fmaf(o.weight_decay, p, g);
+        s0 = fmaf(o.momentum, s0, g);
+        const float upd = o.nesterov ? fmaf(o.momentum, s0, g) : s0;
+        return fmaf(-o.lr, upd, p);
+    }
+    if (o.kind == 2) p *= (1.f - o.lr * o.weight_decay);
+    else g = fmaf(o.weight_decay, p, g);
+    s0 = fmaf(o.beta1, s0, (1.f - o.beta1) * g);
+    s1 = fmaf(o.beta2, s1, (1.f - o.beta2) * g * g);
+    const float denom = sqrtf(s1) / sqrtf(o.bc2) + o.eps;
+    return p - (o.lr / o.bc1) * (s0 / denom);
+}
+
+// mode: 0 = local (W == 1, no flags), 1 = one-shot, 2 = two-shot
+__global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable pt, int rank, int W, int mode,
+                                                                     long long start, long long count,
+                                                                     float* __restrict__ state0,
+                                                                     float* __restrict__ state1, OptArgs opt,
+                                                                     int slot_in, int slot_out, unsigned epoch,
+                                                                     unsigned* block_counter) {
+    const unsigned* my_flags = pt.flags[rank];
+    if (mode != 0) {
+        if (blockIdx.x == 0) signal_peers(pt, slot_in, rank, W, epoch);   // my gradients for this bucket are final
+        wait_flags(my_flags, slot_in, W, epoch);                          // ... and so are everybody else's
+    }
+    long long lo = start, hi = start + count;
+    if (mode == 2) {
+        const long long per = count / W;
+        lo = start + per * rank;
+        hi = lo + per;
+    }
+    const long long nvec = (hi - lo) >> 2;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+        const long long i = lo + (v << 2);
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (mode == 0) {
+            g = *reinterpret_cast<const float4*>(pt.grad[rank] + i);
+        } else {
+            float4 part[MAX_PEERS];
+#pragma unroll
+            for (int p = 0; p < MAX_PEERS; ++p)
+                if (p < W) part[p] = ld_peer_f4(pt.grad[p] + i);          // all W loads in flight together
+#pragma unroll
+            for (int p = 0; p < MAX_PEERS; ++p)
+                if (p < W) { g.x += part[p].x; g.y += part[p].y; g.z += part[p].z; g.w += part[p].w; }
+        }
+        float4 w = *reinterpret_cast<const float4*>(pt.master[rank] + i);
+        float4 s0 = *reinterpret_cast<const float4*>(state0 + i);
+        float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (opt.kind != 0) s1 = *reinterpret_cast<const float4*>(state1 + i);
+        w.x = opt_update(w.x, g.x, s0.x, s1.x, opt);
+        w.y = opt_update(w.y, g.y, s0.y, s1.y, opt);
+        w.z = opt_update(w.z, g.z, s0.z, s1.z, opt);
+        w.w = opt_update(w.w, g.w, s0.w, s1.w, opt);
+        *reinterpret_cast<float4*>(state0 + i) = s0;
+        if (opt.kind != 0) *reinterpret_cast<float4*>(state1 + i) = s1;
+        const uint2 sh = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+        if (mode == 2) {
+#pragma unroll
+            for (int p = 0; p < MAX_PEERS; ++p)
+                if (p < W) {
+                    *reinterpret_cast<float4*>(pt.master[p] + i) = w;     // push over NVLink (all-gather phase)
+                    *reinterpret_cast<uint2*>(pt.shadow[p] + i) = sh;
+                }
+        } else {
+            *reinterpret_cast<float4*>(pt.master[rank] + i) = w;
+            *reinterpret_cast<uint2*>(pt.shadow[rank] + i) = sh;
+        }
+        if (mode == 0) *reinterpret_cast<float4*>(pt.grad[rank] + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (mode == 0) return;
+
+    // barrier-out: the last block of this grid tells the peers that this rank is done reading and pushing
+    __shared__ unsigned s_last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned old = atomicAdd(block_counter, 1u);
+        s_last = ((old + 1u) % gridDim.x == 0u) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) signal_peers(pt, slot_out, rank, W, epoch);
+    wait_flags(my_flags, slot_out, W, epoch);
+    // every peer has consumed my gradients: leave the bucket zeroed for the next accumulation
+    const long long zvec = count >> 2;
+    for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < zvec; v += stride)
+        *reinterpret_cast<float4*>(pt.grad[rank] + start + (v << 2)) = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// ---- small collectives over the exchange slots ----------------------------------------------------------
+// Publish `n` floats, wait for all peers, return the rank-ordered sum.  Single block.
+__device__ __forceinline__ void xchg_publish_and_wait(const PeerTable& pt, int rank, int W, const float* in, int n,
+                                                      long long slot_off, int flag_slot, unsigned epoch) {
+    float* mine = pt.xchg[rank] + slot_off;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mine[i] = in[i];
+    __syncthreads();
+    signal_peers(pt, flag_slot, rank, W, epoch);
+    wait_flags(pt.flags[rank], flag_slot, W, epoch);
+}
+__device__ __forceinline__ float xchg_sum(const PeerTable& pt, int W, long long slot_off, int i) {
+    float acc = 0.f;
+    for (int p = 0; p < W; ++p) {
+        float v;
+        asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(pt.xchg[p] + slot_off + i));
+        acc += v;
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(1024) p2p_allreduce_small_kernel(PeerTable pt, int rank, int W, const float* in,
+                                                                   float* out, int n, long long slot_off,
+                                                                   int flag_slot, unsigned epoch) {
+    xchg_publish_and_wait(pt, rank, W, in, n, slot_off, flag_slot, epoch);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = xchg_sum(pt, W, slot_off, i);
+}
+
+// sums = local [sum(C), sumsq(C)], count = local element count.  Cross-replica merge + finalize in one launch.
+__global__ void __launch_bounds__(1024) bn_finalize_sync_kernel(PeerTable pt, int rank, int W, const float* sums,
+                                                                float count, const float* gamma, const float* beta,
+                                                                float* running_mean, float* running_var,
+                                                                float momentum, float eps, float* scale, float* shift,
+                                                                float* mean_out, float* invstd_out, float* total_count,
+                                                                int C, long long slot_off, int flag_slot,
+                                                                unsigned epoch) {
+    float* mine = pt.xchg[rank] + slot_off;
+    if (threadIdx.x == 0) mine[2 * C] = count;
+    xchg_publish_and_wait(pt, rank, W, sums, 2 * C, slot_off, flag_slot, epoch);
+    const float n = xchg_sum(pt, W, slot_off, 2 * C);
+    if (threadIdx.x == 0) total_count[0] = n;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float mean = xchg_sum(pt, W, slot_off, c) / n;
+        float var = xchg_sum(pt, W, slot_off, C + c) / n - mean * mean;
+        var = fmaxf(var, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        const float sc = gamma[c] * invstd;
+        scale[c] = sc;
+        shift[c] = beta[c] - mean * sc;
+        mean_out[c] = mean;
+        invstd_out[c] = invstd;
+        if (running_mean != nullptr) {
+            const float unbiased = n > 1.f ? var * (n / (n - 1.f)) : var;
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        }
+    }
+}
+
+struct CommCtx {
+    PeerTable pt;
+    int rank, world;
+    unsigned* counters;     // per-bucket block counters (device)
+};
+
+}  // namespace picd
+
+using namespace picd;
+
+// ---- slab + IPC -----------------------------------------------------------------------------------------
+extern "C" int picd_slab_alloc(size_t bytes, void** out) {
+    PICD_CUDA(cudaMalloc(out, bytes));
+    PICD_CUDA(cudaMemset(*out, 0, bytes));
+    return 0;
+}
+extern "C" int picd_slab_free(void* p) {
+    PICD_CUDA(cudaFree(p));
+    return 0;
+}
+extern "C" int picd_ipc_handle_bytes() { return static_cast<int>(sizeof(cudaIpcMemHandle_t)); }
+extern "C" int picd_ipc_get_handle(void* p, void* handle_out) {
+    cudaIpcMemHandle_t h;
+    PICD_CUDA(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle_out, &h, sizeof(h));
+    return 0;
+}
+extern "C" int picd_ipc_open(const void* handle, void** out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    PICD_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int picd_ipc_close(void* p) {
+    PICD_CUDA(cudaIpcCloseMemHandle(p));
+    return 0;
+}
+
+// ---- communicator context -------------------------------------------------------------------------------
+// ptrs: for each of `world` ranks the base pointers (as seen from THIS process) of grad, master, shadow, xchg, flags.
+extern "C" int picd_comm_create(int rank, int world, void* const* grad, void* const* master, void* const* shadow,
+                                void* const* xchg, void* const* flags, int num_buckets, void** ctx_out) {
+    PICD_REQUIRE(world >= 1 && world <= MAX_PEERS, "comm: world=%d unsupported (1..%d ranks of one node)", world, MAX_PEERS);
+    CommCtx* c = new CommCtx();
+    memset(&c->pt, 0, sizeof(c->pt));
+    for (int i = 0; i < world; ++i) {
+        c->pt.grad[i] = static_cast<float*>(grad[i]);
+        c->pt.master[i] = static_cast<float*>(master[i]);
+        c->pt.shadow[i] = static_cast<__nv_bfloat16*>(shadow[i]);
+        c->pt.xchg[i] = static_cast<float*>(xchg ? xchg[i] : nullptr);
+        c->pt.flags[i] = static_cast<unsigned*>(flags ? flags[i] : nullptr);
+    }
+    c->rank = rank;
+    c->world = world;
+    PICD_CUDA(cudaMalloc(&c->counters, sizeof(unsigned) * (num_buckets + 1)));
+    PICD_CUDA(cudaMemset(c->counters, 0, sizeof(unsigned) * (num_buckets + 1)));
+    *ctx_out = c;
+    return 0;
+}
+extern "C" int picd_comm_destroy(void* ctx) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    if (c) {
+        cudaFree(c->counters);
+        delete c;
+    }
+    return 0;
+}
+
+// One gradient bucket: all-reduce over peer memory + 1/W + optimizer + bf16 shadow + gradient re-zero.
+// mode: 0 local, 1 one-shot, 2 two-shot.  `epoch` must increase by one per call per bucket on every rank.
+extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count,
+                                           float* state0, float* state1, int kind, float lr, float momentum,
+                                           float beta1, float beta2, float eps, float weight_decay, float bc1,
+                                           float bc2, int nesterov, unsigned epoch, int blocks, cudaStream_t stream) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(count % (4 * c->world) == 0, "fused_allreduce_update: bucket of %lld elements does not split into "
+                 "16-byte slices over %d ranks", count, c->world);
+    if (c->world == 1) mode = 0;
+    OptArgs o;
+    o.kind = kind; o.lr = lr; o.momentum = momentum; o.beta1 = beta1; o.beta2 = beta2; o.eps = eps;
+    o.weight_decay = weight_decay; o.bc1 = bc1; o.bc2 = bc2; o.nesterov = nesterov;
+    o.grad_scale = 1.f / c->world;
+    const long long work_vecs = (mode == 2 ? count / c->world : count) / 4;
+    long long want = (work_vecs + 511) / 512;
+    if (blocks <= 0) blocks = mode == 0 ? 4 * num_sms() : 32;
+    if (want < blocks) blocks = static_cast<int>(want < 1 ? 1 : want);
+    fused_allreduce_update_kernel<<<blocks, 512, 0, stream>>>(c->pt, c->rank, c->world, mode, start, count, state0, state1, o,
+                                                              2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, float* out, int n, long long slot_off, int flag_slot,
+                                        unsigned epoch, cudaStream_t stream) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, out, n, slot_off, flag_slot, epoch);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, float count, const float* gamma, const float* beta,
+                                     float* running_mean, float* running_var, float momentum, float eps, float* scale,
+                                     float* shift, float* mean, float* invstd, float* total_count, int C,
+                                     long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, count, gamma, beta, running_mean,
+                                                    running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
+                                                    slot_off, flag_slot, epoch);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,398 @@
+// BatchNorm family for NHWC bf16 activations.
+//
+// The reference runs, per BN layer, batch_norm_stats -> (all_gather) -> gather_stats -> batch_norm_elemt -> ReLU
+// forward and backward_reduce -> (all_reduce) -> backward_elemt (+ ReLU backward, + residual add) as separate
+// ATen kernels.  Here:
+//   forward : statistics come for free from the conv epilogue (conv_tc.cu) or from bn_stats;  bn_finalize turns
+//             (sum, sumsq, count) into per-channel scale/shift and updates the running statistics;
+//             bn_apply does y*scale+shift (+residual) (+activation) in ONE pass.
+//   backward: bn_bwd_reduce folds the activation mask into the two reductions; bn_bwd_apply produces the conv
+//             output gradient, the residual-branch gradient and the gamma/beta gradients in ONE pass.
+// All kernels are bandwidth-bound: 16-byte vector accesses, grids sized to a few waves of 148 SMs.
+#include "../common/picd_common.cuh"
+
+namespace picd {
+
+struct Vec8 {
+    uint4 raw;
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { raw = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+    __device__ __forceinline__ void unpack(float (&f)[8]) const {
+        float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y), c = unpack_bf16x2(raw.z), d = unpack_bf16x2(raw.w);
+        f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+    }
+    __device__ __forceinline__ void pack(const float (&f)[8]) {
+        raw.x = pack_bf16x2(f[0], f[1]); raw.y = pack_bf16x2(f[2], f[3]);
+        raw.z = pack_bf16x2(f[4], f[5]); raw.w = pack_bf16x2(f[6], f[7]);
+    }
+};
+
+// 2-D decomposition used by the column reductions: a block of 256 threads covers tx_count channel-vectors
+// (8 channels each) by ty_count rows; consecutive threads read consecutive 16-byte vectors.
+struct ReduceShape {
+    int tx_count, ty_count, grid_x, grid_y, rows_per_block;
+};
+static ReduceShape reduce_shape(long long P, int C) {
+    ReduceShape s;
+    const int vecs = C / 8;
+    s.tx_count = vecs < 256 ? vecs : 256;
+    s.ty_count = 256 / s.tx_count;
+    s.grid_x = (vecs + s.tx_count - 1) / s.tx_count;
+    const int target_blocks = 4 * num_sms();
+    long long gy = target_blocks / s.grid_x;
+    if (gy < 1) gy = 1;
+    long long rpb = (P + gy - 1) / gy;
+    const long long min_rows = 4LL * s.ty_count;
+    if (rpb < min_rows) rpb = min_rows;
+    s.rows_per_block = static_cast<int>(rpb);
+    s.grid_y = static_cast<int>((P + rpb - 1) / rpb);
+    return s;
+}
+
+// Sum the 16 per-thread partials over the ty dimension and add them to two global [C] vectors.
+__device__ __forceinline__ void block_column_reduce(float (&a)[8], float (&b)[8], int tx, int ty, int tx_count,
+                                                    int ty_count, int cv, int vecs, float* out_a, float* out_b) {
+    extern __shared__ float red_smem[];   // [ty_count][tx_count][16]
+    const bool active = ty < ty_count;
+    if (active) {
+        float* slot = red_smem + (static_cast<size_t>(ty) * tx_count + tx) * 16;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { slot[i] = a[i]; slot[8 + i] = b[i]; }
+    }
+    __syncthreads();
+    if (active && ty == 0 && cv < vecs) {
+        float sa[8], sb[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { sa[i] = 0.f; sb[i] = 0.f; }
+        for (int y = 0; y < ty_count; ++y) {
+            const float* slot = red_smem + (static_cast<size_t>(y) * tx_count + tx) * 16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { sa[i] += slot[i]; sb[i] += slot[8 + i]; }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            atomicAdd(out_a + cv * 8 + i, sa[i]);
+            atomicAdd(out_b + cv * 8 + i, sb[i]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- stats
+__global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ stats,
+                                                       long long P, int C, int tx_count, int ty_count,
+                                                       int rows_per_block) {
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    float s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+    if (ty < ty_count && cv < vecs) {
+        const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+        long long r1 = r0 + rows_per_block;
+        if (r1 > P) r1 = P;
+        for (long long r = r0 + ty; r < r1; r += ty_count) {
+            Vec8 v;
+            v.load(x + r * C + cv * 8);
+            float f[8];
+            v.unpack(f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
+        }
+    }
+    block_column_reduce(s, q, tx, ty, tx_count, ty_count, cv, vecs, stats, stats + C);
+}
+
+// ---------------------------------------------------------------------------------------------- finalize
+// sums = [sum(C), sumsq(C)] over `count` elements per channel.  Produces scale = gamma*invstd and
+// shift = beta - mean*scale for the fused apply, saves mean/invstd for backward and updates the running
+// statistics with the unbiased variance (torch semantics, torch/nn/modules/_functions.py:106-115).
+__global__ void bn_finalize_kernel(const float* __restrict__ sums, float count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* running_mean, float* running_var,
+                                   float momentum, float eps, float* scale, float* shift, float* mean_out,
+                                   float* invstd_out, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float mean = sums[c] / count;
+    float var = sums[C + c] / count - mean * mean;
+    var = fmaxf(var, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * invstd;
+    scale[c] = sc;
+    shift[c] = beta[c] - mean * sc;
+    mean_out[c] = mean;
+    invstd_out[c] = invstd;
+    if (running_mean != nullptr) {
+        const float unbiased = count > 1.f ? var * (count / (count - 1.f)) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+}
+
+__global__ void bn_eval_coeffs_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                      const float* __restrict__ running_mean, const float* __restrict__ running_var,
+                                      float eps, float* scale, float* shift, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float sc = gamma[c] * rsqrtf(running_var[c] + eps);
+    scale[c] = sc;
+    shift[c] = beta[c] - running_mean[c] * sc;
+}
+
+// ---------------------------------------------------------------------------------------------- apply
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
+                                                       const float* __restrict__ scale,
+                                                       const float* __restrict__ shift,
+                                                       const __nv_bfloat16* __restrict__ residual, int act,
+                                                       __nv_bfloat16* __restrict__ out, long long total_vecs, int C) {
+    const int vecs = C >> 3;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
+        const int c0 = static_cast<int>(i % vecs) * 8;
+        Vec8 v;
+        v.load(y + i * 8);
+        float f[8];
+        v.unpack(f);
+        const float4 sc0 = *reinterpret_cast<const float4*>(scale + c0), sc1 = *reinterpret_cast<const float4*>(scale + c0 + 4);
+        const float4 sh0 = *reinterpret_cast<const float4*>(shift + c0), sh1 = *reinterpret_cast<const float4*>(shift + c0 + 4);
+        const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+        const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
+        float r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (residual != nullptr) {
+            Vec8 rv;
+            rv.load(residual + i * 8);
+            rv.unpack(r);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = apply_act(fmaf(f[k], sc[k], sh[k]) + r[k], act);
+        v.pack(f);
+        v.store(out + i * 8);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- backward
+// g = dz * act'(pre-activation).  For ReLU the mask is read from the saved output z (z > 0), which is also right
+// when a residual was added before the activation; other activations recompute u = y*scale+shift.
+__device__ __forceinline__ void masked_grad(float (&g)[8], const float (&yv)[8], const float (&zv)[8], bool has_z,
+                                            const float (&sc)[8], const float (&sh)[8], int act) {
+    if (act == ACT_NONE) return;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (act == ACT_RELU) {
+            const float pre = has_z ? zv[k] : fmaf(yv[k], sc[k], sh[k]);
+            g[k] = pre > 0.f ? g[k] : 0.f;
+        } else {
+            g[k] *= act_grad(fmaf(yv[k], sc[k], sh[k]), act);
+        }
+    }
+}
+
+__device__ __forceinline__ void load8f(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz,
+                                                            const __nv_bfloat16* __restrict__ y,
+                                                            const __nv_bfloat16* __restrict__ z,
+                                                            const float* __restrict__ scale,
+                                                            const float* __restrict__ shift,
+                                                            const float* __restrict__ mean,
+                                                            const float* __restrict__ invstd, int act,
+                                                            float* __restrict__ sums, long long P, int C, int tx_count,
+                                                            int ty_count, int rows_per_block) {
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    float sg[8], sgx[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { sg[i] = 0.f; sgx[i] = 0.f; }
+    if (ty < ty_count && cv < vecs) {
+        float sc[8], sh[8], mu[8], is[8];
+        load8f(scale + cv * 8, sc); load8f(shift + cv * 8, sh); load8f(mean + cv * 8, mu); load8f(invstd + cv * 8, is);
+        const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+        long long r1 = r0 + rows_per_block;
+        if (r1 > P) r1 = P;
+        for (long long r = r0 + ty; r < r1; r += ty_count) {
+            const long long off = r * C + cv * 8;
+            Vec8 vd, vy, vz;
+            float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            vd.load(dz + off); vd.unpack(g);
+            vy.load(y + off); vy.unpack(yv);
+            if (z != nullptr && act == ACT_RELU) { vz.load(z + off); vz.unpack(zv); }
+            masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                sg[i] += g[i];
+                sgx[i] += g[i] * (yv[i] - mu[i]) * is[i];
+            }
+        }
+    }
+    block_column_reduce(sg, sgx, tx, ty, tx_count, ty_count, cv, vecs, sums, sums + C);
+}
+
+// dy = gamma*invstd * (g - mean(g) - xhat * mean(g*xhat));  dres = g (gradient of the residual branch).
+// Block 0 also accumulates the parameter gradients dgamma += sum(g*xhat), dbeta += sum(g) from `param_sums`
+// (the LOCAL sums -- with SyncBN `sums` holds the cross-replica totals, `param_sums` this replica's share).
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
+    const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ z,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ invstd, int act, const float* __restrict__ sums, float inv_count,
+    const float* __restrict__ param_sums, float* dgamma, float* dbeta, __nv_bfloat16* __restrict__ dy,
+    __nv_bfloat16* __restrict__ dres, long long total_vecs, int C) {
+    const int vecs = C >> 3;
+    if (blockIdx.x == 0 && dgamma != nullptr) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            dbeta[c] += param_sums[c];
+            dgamma[c] += param_sums[C + c];
+        }
+    }
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
+        const int c0 = static_cast<int>(i % vecs) * 8;
+        float sc[8], sh[8], mu[8], is[8], s1[8], s2[8];
+        load8f(scale + c0, sc); load8f(shift + c0, sh); load8f(mean + c0, mu); load8f(invstd + c0, is);
+        load8f(sums + c0, s1); load8f(sums + C + c0, s2);
+        Vec8 vd, vy, vz;
+        float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        vd.load(dz + i * 8); vd.unpack(g);
+        vy.load(y + i * 8); vy.unpack(yv);
+        if (z != nullptr && act == ACT_RELU) { vz.load(z + i * 8); vz.unpack(zv); }
+        masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
+        if (dres != nullptr) {
+            Vec8 o;
+            o.pack(g);
+            o.store(dres + i * 8);
+        }
+        float d[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xhat = (yv[k] - mu[k]) * is[k];
+            d[k] = sc[k] * (g[k] - s1[k] * inv_count - xhat * s2[k] * inv_count);
+        }
+        Vec8 o;
+        o.pack(d);
+        o.store(dy + i * 8);
+    }
+}
+
+// Backward through a frozen (eval / running-stats) BN: dy = scale * g.
+__global__ void __launch_bounds__(256) bn_bwd_eval_kernel(const __nv_bfloat16* __restrict__ dz,
+                                                          const __nv_bfloat16* __restrict__ y,
+                                                          const __nv_bfloat16* __restrict__ z,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int act,
+                                                          __nv_bfloat16* __restrict__ dy,
+                                                          __nv_bfloat16* __restrict__ dres, long long total_vecs,
+                                                          int C) {
+    const int vecs = C >> 3;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
+        const int c0 = static_cast<int>(i % vecs) * 8;
+        float sc[8], sh[8];
+        load8f(scale + c0, sc); load8f(shift + c0, sh);
+        Vec8 vd, vy, vz;
+        float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        vd.load(dz + i * 8); vd.unpack(g);
+        vy.load(y + i * 8); vy.unpack(yv);
+        if (z != nullptr && act == ACT_RELU) { vz.load(z + i * 8); vz.unpack(zv); }
+        masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
+        if (dres != nullptr) { Vec8 o; o.pack(g); o.store(dres + i * 8); }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= sc[k];
+        Vec8 o;
+        o.pack(g);
+        o.store(dy + i * 8);
+    }
+}
+
+static int elementwise_grid(long long total_vecs) {
+    long long blocks = (total_vecs + 255) / 256;
+    const long long cap = 8LL * num_sms();
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+}  // namespace picd
+
+using namespace picd;
+
+extern "C" int picd_bn_stats(const void* x, float* stats, long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(C % 8 == 0, "bn_stats: C=%d must be a multiple of 8", C);
+    const ReduceShape s = reduce_shape(P, C);
+    const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
+    bn_stats_kernel<<<dim3(s.grid_x, s.grid_y), 256, smem, stream>>>(static_cast<const __nv_bfloat16*>(x), stats, P, C,
+                                                                     s.tx_count, s.ty_count, s.rows_per_block);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_finalize(const float* sums, float count, const float* gamma, const float* beta,
+                                float* running_mean, float* running_var, float momentum, float eps, float* scale,
+                                float* shift, float* mean, float* invstd, int C, cudaStream_t stream) {
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums, count, gamma, beta, running_mean, running_var,
+                                                            momentum, eps, scale, shift, mean, invstd, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
+                                   const float* running_var, float eps, float* scale, float* shift, int C,
+                                   cudaStream_t stream) {
+    bn_eval_coeffs_kernel<<<(C + 127) / 128, 128, 0, stream>>>(gamma, beta, running_mean, running_var, eps, scale,
+                                                               shift, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
+                             void* out, long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(C % 8 == 0, "bn_apply: C=%d must be a multiple of 8", C);
+    const long long total_vecs = P * (C / 8);
+    bn_apply_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,
+        static_cast<__nv_bfloat16*>(out), total_vecs, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale,
+                                  const float* shift, const float* mean, const float* invstd, int act, float* sums,
+                                  long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(C % 8 == 0, "bn_bwd_reduce: C=%d must be a multiple of 8", C);
+    const ReduceShape s = reduce_shape(P, C);
+    const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
+    bn_bwd_reduce_kernel<<<dim3(s.grid_x, s.grid_y), 256, smem, stream>>>(
+        static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
+        static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, P, C, s.tx_count, s.ty_count,
+        s.rows_per_block);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, int act,
+                                 const float* sums, float inv_count, const float* param_sums, float* dgamma,
+                                 float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
+    const long long total_vecs = P * (C / 8);
+    bn_bwd_apply_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
+        static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
+        dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), total_vecs, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+                                int act, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(C % 8 == 0, "bn_bwd_eval: C=%d must be a multiple of 8", C);
+    const long long total_vecs = P * (C / 8);
+    bn_bwd_eval_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
+        static_cast<const __nv_bfloat16*>(z), scale, shift, act, static_cast<__nv_bfloat16*>(dy),
+        static_cast<__nv_bfloat16*>(dres), total_vecs, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}

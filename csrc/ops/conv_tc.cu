@@ -1,0 +1,684 @@
+// Implicit-GEMM convolution / GEMM engine on tcgen05 + TMEM + TMA (sm_100a).
+//
+// Replaces the cuDNN conv fprop/dgrad/wgrad and cuBLAS Linear calls the reference reaches through
+// torchvision.  One design covers every filter shape:
+//
+//   * activations are NHWC bf16; an output tile is a box of 128 pixels [bn images x bh rows x bw cols];
+//   * a convolution is a list of TAPS.  For tap (r,s) the A operand of the GEMM is the SAME box shifted by
+//     (r-pad, s-pad): one 4-D TMA load whose out-of-bounds elements are zero-filled by the hardware, so
+//     padding, 1x7/7x1/5x5 filters and image borders need no special code and no im2col buffer exists;
+//   * stride-2 convolutions address one of four "parity views" of the tensor (x[:, ph::2, pw::2, :], encoded as
+//     plain strided tensor maps), which turns them into stride-1 tap lists; stride-2 dgrad is four such
+//     launches writing through the parity views of dx;
+//   * weights stay in their channels_last layout [Cout, R*S, Cin]: K-major B operand for fprop, MN-major B
+//     operand (same memory, different UMMA descriptor) for dgrad -- no transposed weight copy;
+//   * wgrad is a GEMM over the pixel dimension with BOTH operands MN-major (dy and x tiles exactly as TMA
+//     lands them), split-K over pixel ranges, fp32 accumulation in TMEM, vector red.add into the fp32
+//     gradient arena.
+//
+// conv_gemm_kernel: persistent, warp-specialised (warp0 TMA producer, warp1 MMA issuer, warps2-5 epilogue),
+// 3-4 stage smem ring, double-buffered 128xBN fp32 accumulator in TMEM, epilogue converts to bf16 into a
+// 128B-swizzled staging tile that one thread stores with TMA while all four warps accumulate per-channel
+// sum / sum-of-squares for BatchNorm from the same staging tile (fused BN statistics).
+#include "../common/picd_common.cuh"
+
+#include <algorithm>
+#include <cstring>
+
+namespace picd {
+
+constexpr int MAX_TAPS = 64;
+constexpr int TILE_M = 128;
+constexpr int KCHUNK = 64;                   // bf16 elements per 128B swizzle row
+constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
+constexpr int SMEM_HEADER = 1024;
+constexpr int MAX_DYN_SMEM = 232448;         // 227 KB
+
+struct Tap {
+    int16_t amap;   // which A tensor map (parity view)
+    int16_t dh, dw; // pixel offset added to the tile origin
+    int16_t btap;   // tap index inside the weight tensor
+};
+
+struct ConvGemmParams {
+    CUtensorMap amap[4];
+    CUtensorMap bmap;
+    CUtensorMap dmap;
+    Tap taps[MAX_TAPS];
+    int ntaps, kchunks, b_mn;
+    int BN, numN, num_m_tiles, stages;
+    int tiles_w, tiles_h;
+    int bw_log2, bh_log2;
+    int W, H, N;          // output extents (for masking over-hanging rows)
+    int Cout;
+    float* stats;         // [2][Cout] running (sum, sumsq) accumulators or nullptr
+    const float* bias;    // [Cout] or nullptr
+    int act;
+};
+
+struct WgradParams {
+    CUtensorMap dymap;
+    CUtensorMap xmap[4];
+    Tap taps[MAX_TAPS];
+    int ntaps;
+    float* dw;            // fp32 [Cout][taps_total][Cin], accumulated with red.add
+    int Cout, Cin, taps_total;
+    int BN, numN, numM, ksplit, num_p_tiles, stages;
+    int tiles_w, tiles_h, bw_log2, bh_log2;
+};
+
+struct SmemBars {
+    uint64_t full[8];
+    uint64_t empty[8];
+    uint64_t tfull[2];
+    uint64_t tempty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
+    return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~static_cast<uintptr_t>(1023));
+}
+
+// =====================================================================================================
+//  conv / GEMM forward-style kernel: D[pixels, Cout] = sum_taps A_tap[pixels, Cin] * B_tap[Cout, Cin]^T
+// =====================================================================================================
+__global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align_smem(smem_raw);
+    SmemBars* bars = reinterpret_cast<SmemBars*>(smem);
+    const int BN = p.BN;
+    const int stages = p.stages;
+    const int b_stage = BN * 128;
+    uint8_t* sA = smem + SMEM_HEADER;
+    uint8_t* sB = sA + stages * A_STAGE_BYTES;
+    uint8_t* sOut = sB + stages * b_stage;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(&bars->full[i], 1);
+            mbar_init(&bars->empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&bars->tfull[i], 1);
+            mbar_init(&bars->tempty[i], 4);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&bars->tmem_base, 512);
+        tmem_relinquish();
+    }
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.amap[0]);
+        tma_prefetch_desc(&p.bmap);
+        tma_prefetch_desc(&p.dmap);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    const int numN = p.numN;
+    const int grid_m = gridDim.x / numN;
+    const int n_tile = blockIdx.x % numN;
+    const int m_first = blockIdx.x / numN;
+    const int k_iters = p.ntaps * p.kchunks;
+    const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
+    const int bn = TILE_M >> (p.bw_log2 + p.bh_log2);
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
+            for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+                const int tw = m % p.tiles_w;
+                const int th = (m / p.tiles_w) % p.tiles_h;
+                const int tn = m / (p.tiles_w * p.tiles_h);
+                const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
+                for (int t = 0; t < p.ntaps; ++t) {
+                    const Tap tp = p.taps[t];
+                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                        mbar_wait(&bars->empty[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&bars->full[stage], tx_bytes);
+                        tma_load_4d(sA + stage * A_STAGE_BYTES, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
+                                    w0 + tp.dw, h0 + tp.dh, n0);
+                        uint8_t* dstB = sB + stage * b_stage;
+                        if (!p.b_mn) {
+                            tma_load_3d(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                        } else {
+                            for (int j = 0; j < BN / 64; ++j) {
+                                int c0 = n_tile * BN + j * 64;
+                                if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
+                                tma_load_3d(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
+                            }
+                        }
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t accphase = 0;
+            const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 0, p.b_mn);
+            for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+                mbar_wait(&bars->tempty[acc], accphase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * 256;
+                for (int it = 0; it < k_iters; ++it) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
+                    const uint32_t b_addr = smem_u32(sB + stage * b_stage);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t adesc = make_smem_desc(a_addr + k * 32, 16, 1024);
+                        const uint64_t bdesc = p.b_mn ? make_smem_desc(b_addr + k * 2048, 8192, 1024)
+                                                      : make_smem_desc(b_addr + k * 32, 16, 1024);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, (it | k) != 0);
+                    }
+                    umma_commit(&bars->empty[stage]);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&bars->tfull[acc]);
+                acc ^= 1;
+                if (acc == 0) accphase ^= 1;
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (4 warps)
+        const int q = warp & 3;                  // TMEM lane quarter this warp may read
+        const int row = q * 32 + lane;           // accumulator row == pixel index inside the tile
+        const int tid_e = threadIdx.x - 64;      // 0..127
+        const int colpairs = BN >> 1;
+        const int RG = 128 / colpairs >= 1 ? 128 / colpairs : 1;
+        const int my_cp = tid_e % colpairs;
+        const int my_rg = tid_e / colpairs;
+        const bool stat_thread = (p.stats != nullptr) && (my_rg < RG);
+        const int rows_per_rg = TILE_M / RG;
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        int acc = 0;
+        uint32_t accphase = 0;
+        const int iw = row & (bw - 1);
+        const int ih = (row >> p.bw_log2) & (bh - 1);
+        const int in_ = row >> (p.bw_log2 + p.bh_log2);
+        for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+            const int tw = m % p.tiles_w;
+            const int th = (m / p.tiles_w) % p.tiles_h;
+            const int tn = m / (p.tiles_w * p.tiles_h);
+            const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
+            const bool valid = (w0 + iw < p.W) && (h0 + ih < p.H) && (n0 + in_ < p.N);
+            mbar_wait(&bars->tfull[acc], accphase);
+            tc_fence_after();
+            if (tid_e == 0) tma_store_wait_read();        // previous tile's TMA store has drained the staging tile
+            named_barrier_sync(1, 128);
+            const uint32_t t_row = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
+            for (int g = 0; g < BN / 32; ++g) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + g * 32, v);
+                tmem_ld_wait();
+                const int col0 = n_tile * BN + g * 32;
+                uint32_t packed[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
+                    if (p.bias != nullptr) {
+                        a += (col0 + 2 * i < p.Cout) ? __ldg(p.bias + col0 + 2 * i) : 0.f;
+                        b += (col0 + 2 * i + 1 < p.Cout) ? __ldg(p.bias + col0 + 2 * i + 1) : 0.f;
+                    }
+                    if (p.act != ACT_NONE) { a = apply_act(a, p.act); b = apply_act(b, p.act); }
+                    packed[i] = valid ? pack_bf16x2(a, b) : 0u;
+                }
+                uint8_t* base = sOut + (g >> 1) * 16384 + row * 128;
+                const int chunk0 = (g & 1) * 4;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 val = make_uint4(packed[4 * c], packed[4 * c + 1], packed[4 * c + 2], packed[4 * c + 3]);
+                    *reinterpret_cast<uint4*>(base + (((chunk0 + c) ^ (row & 7)) << 4)) = val;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tempty[acc]);   // accumulator buffer may be overwritten
+            fence_proxy_async_smem();
+            named_barrier_sync(1, 128);
+            if (tid_e == 0) {
+                for (int j = 0; j < BN / 64; ++j) {
+                    const int c0 = n_tile * BN + j * 64;
+                    if (c0 < p.Cout) tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                }
+                tma_store_commit();
+            }
+            if (stat_thread) {
+                // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read)
+                const uint8_t* colbase = sOut + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
+                const int chunk = (my_cp & 31) >> 2;
+                const int r0 = my_rg * rows_per_rg;
+#pragma unroll 4
+                for (int r = r0; r < r0 + rows_per_rg; ++r) {
+                    const uint32_t wv = *reinterpret_cast<const uint32_t*>(colbase + r * 128 + ((chunk ^ (r & 7)) << 4));
+                    const float2 f = unpack_bf16x2(wv);
+                    s0 += f.x; q0 += f.x * f.x;
+                    s1 += f.y; q1 += f.y * f.y;
+                }
+            }
+            acc ^= 1;
+            if (acc == 0) accphase ^= 1;
+        }
+        if (stat_thread) {
+            const int c = n_tile * BN + my_cp * 2;
+            if (c < p.Cout) { atomicAdd(p.stats + c, s0); atomicAdd(p.stats + p.Cout + c, q0); }
+            if (c + 1 < p.Cout) { atomicAdd(p.stats + c + 1, s1); atomicAdd(p.stats + p.Cout + c + 1, q1); }
+        }
+        if (tid_e == 0) tma_store_wait_all();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// =====================================================================================================
+//  wgrad kernel: dW[cout, tap, cin] += sum_pixels dy[pixel, cout] * x[pixel + tap, cin]
+//  One CTA = one (k-split, tap, cout-tile, cin-tile); both operands MN-major as landed by TMA.
+// =====================================================================================================
+__global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constant__ WgradParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align_smem(smem_raw);
+    SmemBars* bars = reinterpret_cast<SmemBars*>(smem);
+    const int BN = p.BN;
+    const int stages = p.stages;
+    const int b_stage = BN * 128;
+    uint8_t* sA = smem + SMEM_HEADER;
+    uint8_t* sB = sA + stages * A_STAGE_BYTES;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(&bars->full[i], 1);
+            mbar_init(&bars->empty[i], 1);
+        }
+        mbar_init(&bars->tfull[0], 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&bars->tmem_base, 256);
+        tmem_relinquish();
+    }
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.dymap);
+        tma_prefetch_desc(&p.xmap[0]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    const int inner = p.ntaps * p.numM * p.numN;
+    const int split = blockIdx.x / inner;
+    int rem = blockIdx.x % inner;
+    const int nt = rem % p.numN; rem /= p.numN;
+    const int mt = rem % p.numM; rem /= p.numM;
+    const Tap tp = p.taps[rem];
+    const int pt_begin = static_cast<int>((static_cast<long long>(p.num_p_tiles) * split) / p.ksplit);
+    const int pt_end = static_cast<int>((static_cast<long long>(p.num_p_tiles) * (split + 1)) / p.ksplit);
+    const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
+    const int bn = 64 >> (p.bw_log2 + p.bh_log2);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
+            int ca1 = mt * TILE_M + 64;
+            if (ca1 >= p.Cout) ca1 = mt * TILE_M;       // duplicate rows instead of a fully out-of-range box
+            for (int pt = pt_begin; pt < pt_end; ++pt) {
+                const int tw = pt % p.tiles_w;
+                const int th = (pt / p.tiles_w) % p.tiles_h;
+                const int tn = pt / (p.tiles_w * p.tiles_h);
+                const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&bars->full[stage], tx_bytes);
+                uint8_t* dA = sA + stage * A_STAGE_BYTES;
+                tma_load_4d(dA, &p.dymap, &bars->full[stage], mt * TILE_M, w0, h0, n0);
+                tma_load_4d(dA + 8192, &p.dymap, &bars->full[stage], ca1, w0, h0, n0);
+                uint8_t* dB = sB + stage * b_stage;
+                for (int j = 0; j < BN / 64; ++j) {
+                    int c0 = nt * BN + j * 64;
+                    if (c0 >= p.Cin) c0 = 0;
+                    tma_load_4d(dB + j * 8192, &p.xmap[tp.amap], &bars->full[stage], c0, w0 + tp.dw, h0 + tp.dh, n0);
+                }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 1, 1);
+            for (int pt = pt_begin; pt < pt_end; ++pt) {
+                mbar_wait(&bars->full[stage], phase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
+                const uint32_t b_addr = smem_u32(sB + stage * b_stage);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint64_t adesc = make_smem_desc(a_addr + k * 2048, 8192, 1024);
+                    const uint64_t bdesc = make_smem_desc(b_addr + k * 2048, 8192, 1024);
+                    umma_bf16(tmem_base, adesc, bdesc, idesc, (pt > pt_begin) || (k != 0));
+                }
+                umma_commit(&bars->empty[stage]);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(&bars->tfull[0]);
+        }
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int cout = mt * TILE_M + row;
+        if (pt_end > pt_begin) {
+            mbar_wait(&bars->tfull[0], 0);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            float* drow = p.dw + (static_cast<size_t>(cout) * p.taps_total + tp.btap) * p.Cin;
+            for (int g = 0; g < BN / 32; ++g) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + g * 32, v);
+                tmem_ld_wait();
+                if (cout < p.Cout) {
+                    const int cin0 = nt * BN + g * 32;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        const int cin = cin0 + i;
+                        if (cin + 3 < p.Cin) {
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(drow + cin),
+                                         "f"(__uint_as_float(v[i])), "f"(__uint_as_float(v[i + 1])),
+                                         "f"(__uint_as_float(v[i + 2])), "f"(__uint_as_float(v[i + 3]))
+                                         : "memory");
+                        } else {
+                            for (int e = 0; e < 4; ++e)
+                                if (cin + e < p.Cin) atomicAdd(drow + cin + e, __uint_as_float(v[i + e]));
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// =====================================================================================================
+//  host side
+// =====================================================================================================
+struct Geometry {
+    int bw_log2, bh_log2, bn;
+    int tiles_w, tiles_h, tiles_n;
+};
+
+// Choose the [bn x bh x bw] pixel box (product = tile_pixels, all powers of two) with the least padding.
+static Geometry choose_geometry(int N, int H, int W, int tile_pixels) {
+    Geometry best{};
+    double best_cost = 1e30;
+    int lg = 0;
+    while ((1 << lg) < tile_pixels) ++lg;
+    for (int lw = 0; lw <= lg; ++lw) {
+        for (int lh = 0; lh + lw <= lg; ++lh) {
+            const int bw = 1 << lw, bh = 1 << lh, bn = tile_pixels >> (lw + lh);
+            if (bw > 256 || bh > 256 || bn > 256) continue;
+            const long long padded = 1LL * ceil_div(W, bw) * bw * ceil_div(H, bh) * bh * ceil_div(N, bn) * bn;
+            // tie-break towards wide boxes (long contiguous runs per TMA row)
+            const double cost = static_cast<double>(padded) * (1.0 + 0.001 * (lg - lw));
+            if (cost < best_cost) {
+                best_cost = cost;
+                best = Geometry{lw, lh, bn, ceil_div(W, bw), ceil_div(H, bh), ceil_div(N, bn)};
+            }
+        }
+    }
+    return best;
+}
+
+static int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static int pos_mod(int a, int b) { return ((a % b) + b) % b; }
+
+// 4-D NHWC activation map (optionally the (ph,pw) parity view for stride 2).  box = (64, bw, bh, bn).
+static int make_act_map(CUtensorMap* m, const void* base, int N, int H, int W, int C, int stride, int ph, int pw,
+                        int bw, int bh, int bn) {
+    const __nv_bfloat16* b = static_cast<const __nv_bfloat16*>(base) + (static_cast<size_t>(ph) * W + pw) * C;
+    const int Hv = (H - ph + stride - 1) / stride, Wv = (W - pw + stride - 1) / stride;
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)std::max(Wv, 1), (uint64_t)std::max(Hv, 1), (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)stride * C * 2, (uint64_t)stride * W * C * 2, (uint64_t)H * W * C * 2};
+    uint32_t box[4] = {64, (uint32_t)bw, (uint32_t)bh, (uint32_t)bn};
+    return make_tensor_map(m, b, 2, 4, dims, strides, box, true);
+}
+
+static int num_n_tiles(int C, int* BN) {
+    const int numN = ceil_div(C, 256);
+    int bn = ceil_div(ceil_div(C, numN), 64) * 64;
+    *BN = bn;
+    return ceil_div(C, bn);
+}
+
+static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t stream) {
+    int BN;
+    p.numN = num_n_tiles(Cout_gemm, &BN);
+    p.BN = BN;
+    p.Cout = Cout_gemm;
+    const int stage_bytes = A_STAGE_BYTES + BN * 128;
+    const int staging = BN * 256;   // 128 rows x BN x 2 B
+    int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging) / stage_bytes;
+    stages = std::min(stages, 6);
+    PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
+    p.stages = stages;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    const int sms = num_sms();
+    const long long total = 1LL * p.num_m_tiles * p.numN;
+    int grid = static_cast<int>(std::min<long long>(total, sms));
+    grid = std::max(p.numN, grid / p.numN * p.numN);
+    // request the whole smem so that exactly one CTA (and one 512-column TMEM allocation) lives on an SM
+    conv_gemm_kernel<<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace picd
+
+using namespace picd;
+
+// y[N,OH,OW,Cout] = conv(x[N,H,W,Cin], w[Cout,R,S,Cin]); optional fused per-channel (sum, sumsq) for BatchNorm,
+// optional bias + activation epilogue.  NHWC bf16, stride 1 or 2.
+extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* stats, const float* bias, int act,
+                               int N, int H, int W, int Cin, int Cout, int R, int S, int stride, int pad_h,
+                               int pad_w, int OH, int OW, cudaStream_t stream) {
+    PICD_REQUIRE(stride == 1 || stride == 2, "conv_fprop: stride %d unsupported", stride);
+    PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_fprop: channels must be multiples of 8 (Cin=%d Cout=%d)", Cin, Cout);
+    PICD_REQUIRE(R * S <= MAX_TAPS, "conv_fprop: %dx%d filter has too many taps", R, S);
+    ConvGemmParams p;
+    std::memset(&p, 0, sizeof(p));
+    const Geometry g = choose_geometry(N, OH, OW, TILE_M);
+    const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
+    for (int ph = 0; ph < stride; ++ph)
+        for (int pw = 0; pw < stride; ++pw)
+            if (make_act_map(&p.amap[ph * stride + pw], x, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+    {
+        uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(R * S), (uint64_t)Cout};
+        uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
+        int BN;
+        num_n_tiles(Cout, &BN);
+        uint32_t box[3] = {64, 1, (uint32_t)BN};
+        if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
+    }
+    if (make_act_map(&p.dmap, y, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
+    int nt = 0;
+    for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s) {
+            const int dr = r - pad_h, ds = s - pad_w;
+            Tap t;
+            t.amap = static_cast<int16_t>(pos_mod(dr, stride) * stride + pos_mod(ds, stride));
+            t.dh = static_cast<int16_t>(floor_div(dr, stride));
+            t.dw = static_cast<int16_t>(floor_div(ds, stride));
+            t.btap = static_cast<int16_t>(r * S + s);
+            p.taps[nt++] = t;
+        }
+    p.ntaps = nt;
+    p.kchunks = ceil_div(Cin, KCHUNK);
+    p.b_mn = 0;
+    p.num_m_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
+    p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
+    p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
+    p.W = OW; p.H = OH; p.N = N;
+    p.stats = stats; p.bias = bias; p.act = act;
+    return launch_conv_gemm(p, Cout, stream);
+}
+
+// dx[N,H,W,Cin] = conv_transpose(dy[N,OH,OW,Cout], w[Cout,R,S,Cin]).  Weights are read through an MN-major
+// descriptor, i.e. the same tensor as fprop.  Stride 2 = one launch per output parity class.
+extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                               cudaStream_t stream) {
+    PICD_REQUIRE(stride == 1 || stride == 2, "conv_dgrad: stride %d unsupported", stride);
+    PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_dgrad: channels must be multiples of 8");
+    bool zeroed = false;
+    for (int ph = 0; ph < stride; ++ph) {
+        for (int pw = 0; pw < stride; ++pw) {
+            const int Hv = (H - ph + stride - 1) / stride, Wv = (W - pw + stride - 1) / stride;
+            if (Hv <= 0 || Wv <= 0) continue;
+            ConvGemmParams p;
+            std::memset(&p, 0, sizeof(p));
+            int nt = 0;
+            for (int r = 0; r < R; ++r)
+                for (int s = 0; s < S; ++s) {
+                    const int eh = ph + pad_h - r, ew = pw + pad_w - s;
+                    if (pos_mod(eh, stride) != 0 || pos_mod(ew, stride) != 0) continue;
+                    Tap t;
+                    t.amap = 0;
+                    t.dh = static_cast<int16_t>(eh / stride);
+                    t.dw = static_cast<int16_t>(ew / stride);
+                    t.btap = static_cast<int16_t>(r * S + s);
+                    p.taps[nt++] = t;
+                }
+            if (nt == 0) {
+                // this parity class receives no gradient (e.g. 1x1 stride-2): make sure dx is zero there
+                if (!zeroed) {
+                    PICD_CUDA(cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * Cin * 2, stream));
+                    zeroed = true;
+                }
+                continue;
+            }
+            const Geometry g = choose_geometry(N, Hv, Wv, TILE_M);
+            const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
+            if (make_act_map(&p.amap[0], dy, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
+            {
+                uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(R * S), (uint64_t)Cout};
+                uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
+                uint32_t box[3] = {64, 1, 64};
+                if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
+            }
+            if (make_act_map(&p.dmap, dx, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+            p.ntaps = nt;
+            p.kchunks = ceil_div(Cout, KCHUNK);
+            p.b_mn = 1;
+            p.num_m_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
+            p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
+            p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
+            p.W = Wv; p.H = Hv; p.N = N;
+            p.stats = nullptr; p.bias = nullptr; p.act = ACT_NONE;
+            if (int rc = launch_conv_gemm(p, Cin, stream)) return rc;
+        }
+    }
+    return 0;
+}
+
+// dw[Cout,R,S,Cin] (fp32) += sum over pixels of dy (x) x.  The caller provides a zeroed (or accumulating) buffer.
+extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
+                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                               cudaStream_t stream) {
+    PICD_REQUIRE(stride == 1 || stride == 2, "conv_wgrad: stride %d unsupported", stride);
+    PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_wgrad: channels must be multiples of 8");
+    PICD_REQUIRE(R * S <= MAX_TAPS, "conv_wgrad: too many taps");
+    WgradParams p;
+    std::memset(&p, 0, sizeof(p));
+    const Geometry g = choose_geometry(N, OH, OW, 64);
+    const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
+    if (make_act_map(&p.dymap, dy, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
+    for (int ph = 0; ph < stride; ++ph)
+        for (int pw = 0; pw < stride; ++pw)
+            if (make_act_map(&p.xmap[ph * stride + pw], x, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+    int nt = 0;
+    for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s) {
+            const int dr = r - pad_h, ds = s - pad_w;
+            Tap t;
+            t.amap = static_cast<int16_t>(pos_mod(dr, stride) * stride + pos_mod(ds, stride));
+            t.dh = static_cast<int16_t>(floor_div(dr, stride));
+            t.dw = static_cast<int16_t>(floor_div(ds, stride));
+            t.btap = static_cast<int16_t>(r * S + s);
+            p.taps[nt++] = t;
+        }
+    p.ntaps = nt;
+    p.dw = dw; p.Cout = Cout; p.Cin = Cin; p.taps_total = R * S;
+    int BN;
+    p.numN = num_n_tiles(Cin, &BN);
+    p.BN = BN;
+    p.numM = ceil_div(Cout, TILE_M);
+    p.num_p_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
+    p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
+    p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
+    const int stage_bytes = A_STAGE_BYTES + BN * 128;
+    // small tiles: shallow ring, two CTAs per SM (2 x 256 TMEM columns) so one CTA's red.add epilogue overlaps
+    // the other's main loop; wide tiles: one CTA per SM with a deep ring.
+    int smem_launch;
+    if (BN <= 128) {
+        p.stages = (BN <= 64) ? 4 : 3;
+        smem_launch = p.stages * stage_bytes + SMEM_HEADER + 1024;
+    } else {
+        p.stages = std::min(6, (MAX_DYN_SMEM - 1024 - SMEM_HEADER) / stage_bytes);
+        smem_launch = MAX_DYN_SMEM;
+    }
+    const int inner = p.ntaps * p.numM * p.numN;
+    const int sms = num_sms();
+    int ksplit = std::max(1, (2 * sms + inner - 1) / inner);
+    ksplit = std::min(ksplit, std::max(1, p.num_p_tiles / 4));   // keep >= 4 k-iterations per CTA
+    ksplit = std::max(1, std::min(ksplit, p.num_p_tiles));
+    p.ksplit = ksplit;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PICD_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    conv_wgrad_kernel<<<inner * ksplit, 192, smem_launch, stream>>>(p);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+// D[M,N] = act(A[M,K] * B[N,K]^T + bias): the Linear forward (and, with swapped roles, every GEMM whose
+// operands are K-major).  All bf16 row-major, fp32 accumulate.
+extern "C" int picd_gemm_nt(const void* a, const void* b, void* d, const float* bias, int act, int M, int N_, int K,
+                            cudaStream_t stream) {
+    return picd_conv_fprop(a, b, d, nullptr, bias, act, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
+}
+// D[M,K] = A[M,N] * B[N,K]  (Linear dgrad: dX = dY * W with W stored [N,K]).
+extern "C" int picd_gemm_nn(const void* a, const void* b, void* d, int M, int N_, int K, cudaStream_t stream) {
+    return picd_conv_dgrad(a, b, d, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
+}
+// D[N,K] (fp32) += A[M,N]^T * B[M,K]  (Linear wgrad: dW = dY^T X).
+extern "C" int picd_gemm_tn_f32(const void* a_dy, const void* b_x, float* d, int M, int N_, int K,
+                                cudaStream_t stream) {
+    return picd_conv_wgrad(b_x, a_dy, d, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
+}

@@ -1,0 +1,633 @@
+// Memory-bound helper kernels: pooling, global average pool, weighted softmax cross-entropy, activations,
+// dropout, LayerNorm, small (SIMT) linear layers, first-layer packing, synthetic data.
+// All activations are NHWC bf16; reductions accumulate in fp32.
+#include "../common/picd_common.cuh"
+
+namespace picd {
+
+static int grid_for(long long work, int block = 256, int waves = 8) {
+    long long b = (work + block - 1) / block;
+    const long long cap = static_cast<long long>(waves) * num_sms();
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return static_cast<int>(b);
+}
+
+__device__ __forceinline__ void unpack8(const uint4& raw, float (&f)[8]) {
+    float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y), c = unpack_bf16x2(raw.z), d = unpack_bf16x2(raw.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
+
+// ------------------------------------------------------------------------------------------------ pooling
+// mode 0 = max (stores the arg-max window offset as one byte per element), 1 = avg (count_include_pad).
+__global__ void __launch_bounds__(256) pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                       uint8_t* __restrict__ argmax, int N, int H, int W, int C, int OH,
+                                                       int OW, int kh, int kw, int stride, int pad, int mode) {
+    const int vecs = C >> 3;
+    const long long total = static_cast<long long>(N) * OH * OW * vecs;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        long long t = i / vecs;
+        const int ow = static_cast<int>(t % OW); t /= OW;
+        const int oh = static_cast<int>(t % OH);
+        const int n = static_cast<int>(t / OH);
+        float acc[8];
+        int arg[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { acc[k] = mode == 0 ? -INFINITY : 0.f; arg[k] = 0; }
+        for (int a = 0; a < kh; ++a) {
+            const int ih = oh * stride - pad + a;
+            if (ih < 0 || ih >= H) continue;
+            for (int b = 0; b < kw; ++b) {
+                const int iw = ow * stride - pad + b;
+                if (iw < 0 || iw >= W) continue;
+                const uint4 raw = *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * H + ih) * W + iw) * C + cv * 8);
+                float f[8];
+                unpack8(raw, f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    if (mode == 0) {
+                        if (f[k] > acc[k]) { acc[k] = f[k]; arg[k] = a * kw + b; }
+                    } else {
+                        acc[k] += f[k];
+                    }
+                }
+            }
+        }
+        if (mode == 1) {
+            const float inv = 1.f / (kh * kw);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] *= inv;
+        }
+        *reinterpret_cast<uint4*>(out + i * 8) = pack8(acc);
+        if (mode == 0 && argmax != nullptr) {
+            uint2 pk;
+            pk.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+            pk.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+            *reinterpret_cast<uint2*>(argmax + i * 8) = pk;
+        }
+    }
+}
+
+// Gather formulation (one thread per INPUT vector, no atomics, deterministic): sum dy over the windows that
+// contain this pixel; for max-pool only where the stored arg-max points back at it.
+__global__ void __launch_bounds__(256) pool_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                       const uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ dx,
+                                                       int N, int H, int W, int C, int OH, int OW, int kh, int kw,
+                                                       int stride, int pad, int mode) {
+    const int vecs = C >> 3;
+    const long long total = static_cast<long long>(N) * H * W * vecs;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    const float inv = 1.f / (kh * kw);
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        long long t = i / vecs;
+        const int iw = static_cast<int>(t % W); t /= W;
+        const int ih = static_cast<int>(t % H);
+        const int n = static_cast<int>(t / H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int a = 0; a < kh; ++a) {
+            const int th = ih + pad - a;
+            if (th < 0 || th % stride != 0) continue;
+            const int oh = th / stride;
+            if (oh >= OH) continue;
+            for (int b = 0; b < kw; ++b) {
+                const int tw = iw + pad - b;
+                if (tw < 0 || tw % stride != 0) continue;
+                const int ow = tw / stride;
+                if (ow >= OW) continue;
+                const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * vecs + cv;
+                float g[8];
+                unpack8(*reinterpret_cast<const uint4*>(dy + o * 8), g);
+                if (mode == 0) {
+                    const uint2 pk = *reinterpret_cast<const uint2*>(argmax + o * 8);
+                    const int want = a * kw + b;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int am = ((k < 4 ? pk.x : pk.y) >> ((k & 3) * 8)) & 0xff;
+                        if (am == want) acc[k] += g[k];
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] += g[k] * inv;
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
+    }
+}
+
+// [N, HW, C] -> [N, C] mean.  One block per (n, 256-channel slab); threads split HW, smem reduce.
+__global__ void __launch_bounds__(256) gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                      int HW, int C) {
+    const int vecs = C >> 3;
+    const int n = blockIdx.y;
+    const int tx_count = vecs < 32 ? vecs : 32;
+    const int ty_count = 256 / tx_count;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    __shared__ float red[256 * 8];
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (ty < ty_count && cv < vecs) {
+        for (int p = ty; p < HW; p += ty_count) {
+            float f[8];
+            unpack8(*reinterpret_cast<const uint4*>(x + (static_cast<long long>(n) * HW + p) * C + cv * 8), f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += f[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) red[threadIdx.x * 8 + k] = acc[k];
+    __syncthreads();
+    if (ty == 0 && cv < vecs) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] += red[(yy * tx_count + tx) * 8 + k];
+        const float inv = 1.f / HW;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s[k] *= inv;
+        *reinterpret_cast<uint4*>(out + static_cast<long long>(n) * C + cv * 8) = pack8(s);
+    }
+}
+
+__global__ void __launch_bounds__(256) gap_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
+                                                      long long total_vecs, int HW, int C) {
+    const int vecs = C >> 3;
+    const float inv = 1.f / HW;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        const long long n = i / (static_cast<long long>(vecs) * HW);
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(dy + n * C + cv * 8), g);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= inv;
+        *reinterpret_cast<uint4*>(dx + i * 8) = pack8(g);
+    }
+}
+
+// ------------------------------------------------------------------------------------ weighted cross-entropy
+// One block.  loss = sum_i w[y_i] * (lse_i - x_i[y_i]) / sum_i w[y_i]; dlogits written in the same launch
+// (d loss / d logits, to be scaled by the incoming scalar gradient).  logits fp32 [B, nc] (tiny: the head output).
+__global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                                                   const float* __restrict__ weight, float* __restrict__ loss,
+                                                   float* __restrict__ dlogits, int B, int nc) {
+    __shared__ float s_num[8], s_den[8];
+    __shared__ float s_total[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float num = 0.f, den = 0.f;
+    for (int r = warp; r < B; r += nwarps) {
+        const float* row = logits + static_cast<long long>(r) * nc;
+        float mx = -INFINITY;
+        for (int j = lane; j < nc; j += 32) mx = fmaxf(mx, row[j]);
+        mx = warp_max(mx);
+        float se = 0.f;
+        for (int j = lane; j < nc; j += 32) se += __expf(row[j] - mx);
+        se = warp_sum(se);
+        const int y = static_cast<int>(labels[r]);
+        const float w = weight != nullptr ? weight[y] : 1.f;
+        if (lane == 0) {
+            num += w * (logf(se) + mx - row[y]);
+            den += w;
+        }
+    }
+    if (lane == 0) { s_num[warp] = num; s_den[warp] = den; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f, b = 0.f;
+        for (int i = 0; i < nwarps; ++i) { a += s_num[i]; b += s_den[i]; }
+        s_total[0] = a; s_total[1] = b;
+        loss[0] = a / b;
+    }
+    __syncthreads();
+    const float inv_den = 1.f / s_total[1];
+    for (int r = warp; r < B; r += nwarps) {
+        const float* row = logits + static_cast<long long>(r) * nc;
+        float mx = -INFINITY;
+        for (int j = lane; j < nc; j += 32) mx = fmaxf(mx, row[j]);
+        mx = warp_max(mx);
+        float se = 0.f;
+        for (int j = lane; j < nc; j += 32) se += __expf(row[j] - mx);
+        se = warp_sum(se);
+        const int y = static_cast<int>(labels[r]);
+        const float w = (weight != nullptr ? weight[y] : 1.f) * inv_den;
+        for (int j = lane; j < nc; j += 32) {
+            const float pr = __expf(row[j] - mx) / se;
+            dlogits[static_cast<long long>(r) * nc + j] = w * (pr - (j == y ? 1.f : 0.f));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ element-wise activation
+__global__ void __launch_bounds__(256) act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bias,
+                                                      __nv_bfloat16* __restrict__ out, long long total_vecs, int C,
+                                                      int act) {
+    const int vecs = C >> 3;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+        const int c0 = static_cast<int>(i % vecs) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k] + (bias != nullptr ? bias[c0 + k] : 0.f), act);
+        *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
+    }
+}
+// dx = dy * act'(x + bias)
+__global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                      const float* __restrict__ bias, __nv_bfloat16* __restrict__ dx,
+                                                      long long total_vecs, int C, int act) {
+    const int vecs = C >> 3;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
+        float g[8], f[8];
+        unpack8(*reinterpret_cast<const uint4*>(dy + i * 8), g);
+        unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+        const int c0 = static_cast<int>(i % vecs) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= act_grad(f[k] + (bias != nullptr ? bias[c0 + k] : 0.f), act);
+        *reinterpret_cast<uint4*>(dx + i * 8) = pack8(g);
+    }
+}
+
+// out[c] += sum over rows of x[r, c] (bias gradients).  2-D blocks, fp32 atomics.
+__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
+                                                     long long P, int C, int rows_per_block) {
+    const int c = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int ty = threadIdx.x >> 6;
+    __shared__ float red[256];
+    float acc = 0.f;
+    if (c < C) {
+        const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+        long long r1 = r0 + rows_per_block;
+        if (r1 > P) r1 = P;
+        for (long long r = r0 + ty; r < r1; r += 4) acc += __bfloat162float(x[r * C + c]);
+    }
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (ty == 0 && c < C) atomicAdd(out + c, red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
+}
+
+// ------------------------------------------------------------------------------------ dropout (counter hash)
+__device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+    return x;
+}
+__global__ void __launch_bounds__(256) dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                      long long n, float p, uint32_t seed) {
+    const float scale = 1.f / (1.f - p);
+    const uint32_t thr = static_cast<uint32_t>(p * 4294967296.0);
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += step) {
+        const uint32_t h = hash_u32(static_cast<uint32_t>(i) * 0x9E3779B1u + seed);
+        const float v = __bfloat162float(x[i]);
+        out[i] = __float2bfloat16(h >= thr ? v * scale : 0.f);
+    }
+}
+
+// ------------------------------------------------------------------------------------ LayerNorm (row = one warp)
+__global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                            long long M, int D, float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    if (row >= M) return;
+    const __nv_bfloat16* xr = x + row * D;
+    float s = 0.f, q = 0.f;
+    for (int j = lane * 8; j < D; j += 256) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(xr + j), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { s += f[k]; q += f[k] * f[k]; }
+    }
+    s = warp_sum(s); q = warp_sum(q);
+    const float mean = s / D;
+    const float rstd = rsqrtf(fmaxf(q / D - mean * mean, 0.f) + eps);
+    if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+    for (int j = lane * 8; j < D; j += 256) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(xr + j), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = (f[k] - mean) * rstd * gamma[j + k] + beta[j + k];
+        *reinterpret_cast<uint4*>(y + row * D + j) = pack8(f);
+    }
+}
+// dx and (atomically accumulated) dgamma/dbeta.  Each block keeps per-column partials in shared memory.
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                            const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                            const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
+                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                            long long M, int D, int rows_per_block) {
+    extern __shared__ float sm[];   // [2][D]
+    float* sg = sm;
+    float* sb = sm + D;
+    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) sm[j] = 0.f;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
+    long long r1 = r0 + rows_per_block;
+    if (r1 > M) r1 = M;
+    for (long long row = r0 + warp; row < r1; row += nw) {
+        const float mu = mean[row], rs = rstd[row];
+        float a = 0.f, b = 0.f;
+        for (int j = lane * 8; j < D; j += 256) {
+            float g[8], f[8];
+            unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
+            unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float xh = (f[k] - mu) * rs, gg = g[k] * gamma[j + k];
+                a += gg; b += gg * xh;
+                atomicAdd(sg + j + k, g[k] * xh);
+                atomicAdd(sb + j + k, g[k]);
+            }
+        }
+        a = warp_sum(a) / D; b = warp_sum(b) / D;
+        for (int j = lane * 8; j < D; j += 256) {
+            float g[8], f[8], o[8];
+            unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
+            unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float xh = (f[k] - mu) * rs;
+                o[k] = rs * (g[k] * gamma[j + k] - a - xh * b);
+            }
+            *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < D; j += blockDim.x) {
+        atomicAdd(dgamma + j, sg[j]);
+        atomicAdd(dbeta + j, sb[j]);
+    }
+}
+
+// ------------------------------------------------------------------------------------ small linear layers (SIMT)
+// The classifier head (2048->128->64->32->nc, batch rows) is far below one tensor-core tile; a warp per output
+// element keeps it simple and exact.  x bf16 [M,K], w fp32 [N,K] (the master weights), y bf16 or fp32 [M,N].
+__global__ void __launch_bounds__(256) small_linear_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                                               const float* __restrict__ bias, void* __restrict__ y,
+                                                               int M, int N, int K, int act, int out_fp32) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= M * N) return;
+    const int m = warp / N, n = warp % N;
+    float acc = 0.f;
+    for (int k = lane; k < K; k += 32) acc += __bfloat162float(x[static_cast<long long>(m) * K + k]) * w[static_cast<long long>(n) * K + k];
+    acc = warp_sum(acc);
+    if (lane == 0) {
+        acc = apply_act(acc + (bias != nullptr ? bias[n] : 0.f), act);
+        if (out_fp32) static_cast<float*>(y)[static_cast<long long>(m) * N + n] = acc;
+        else static_cast<__nv_bfloat16*>(y)[static_cast<long long>(m) * N + n] = __float2bfloat16(acc);
+    }
+}
+// dpre[m,n] = dy[m,n] * act'(y[m,n]) for relu (y>0) / none; then dx = dpre W, dW += dpre^T x, db += sum dpre.
+__global__ void __launch_bounds__(256) small_linear_dpre_kernel(const void* __restrict__ dy, const void* __restrict__ y,
+                                                                float* __restrict__ dpre, int total, int act, int dy_fp32,
+                                                                int y_fp32) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    float g = dy_fp32 ? static_cast<const float*>(dy)[i] : __bfloat162float(static_cast<const __nv_bfloat16*>(dy)[i]);
+    if (act == ACT_RELU) {
+        const float v = y_fp32 ? static_cast<const float*>(y)[i] : __bfloat162float(static_cast<const __nv_bfloat16*>(y)[i]);
+        g = v > 0.f ? g : 0.f;
+    }
+    dpre[i] = g;
+}
+__global__ void __launch_bounds__(256) small_linear_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ w,
+                                                              __nv_bfloat16* __restrict__ dx, int M, int N, int K) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M * K) return;
+    const int m = i / K, k = i % K;
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc += dpre[m * N + n] * w[static_cast<long long>(n) * K + k];
+    dx[i] = __float2bfloat16(acc);
+}
+__global__ void __launch_bounds__(256) small_linear_dw_kernel(const float* __restrict__ dpre, const __nv_bfloat16* __restrict__ x,
+                                                              float* __restrict__ dw, float* __restrict__ db, int M, int N,
+                                                              int K) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N * K) {
+        const int n = i / K, k = i % K;
+        float acc = 0.f;
+        for (int m = 0; m < M; ++m) acc += dpre[m * N + n] * __bfloat162float(x[static_cast<long long>(m) * K + k]);
+        dw[i] += acc;
+    }
+    if (db != nullptr && i < N) {
+        float acc = 0.f;
+        for (int m = 0; m < M; ++m) acc += dpre[m * N + i];
+        db[i] += acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------ first-layer packing
+// out[n, i, j, (a*s + b)*C + c] = x[n, i*s + a - pad_h, j*s + b - pad_w, c]  (zero outside the image / padding
+// channels).  Turns a stride-s RxS convolution over 3 channels into a stride-1 ceil(R/s) x ceil(S/s) convolution
+// over s*s*3 (padded to Cp) channels, i.e. into tensor-core friendly K (ResNet 7x7/s2 stem, ViT 16x16/s16 patches).
+// Input may be bf16 NHWC or uint8 NHWC (then ImageNet normalisation is fused: dp/loader.py:86-91).
+template <typename T>
+__global__ void __launch_bounds__(256) pack_s2d_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int H,
+                                                       int W, int C, int Hp, int Wp, int Cp, int s, int pad_h, int pad_w,
+                                                       int normalize) {
+    const long long total = static_cast<long long>(N) * Hp * Wp * Cp;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const int cp = static_cast<int>(i % Cp);
+        long long t = i / Cp;
+        const int j = static_cast<int>(t % Wp); t /= Wp;
+        const int ii = static_cast<int>(t % Hp);
+        const int n = static_cast<int>(t / Hp);
+        float v = 0.f;
+        if (cp < s * s * C) {
+            const int c = cp % C, ab = cp / C, a = ab / s, b = ab % s;
+            const int ih = ii * s + a - pad_h, iw = j * s + b - pad_w;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+                const T raw = x[((static_cast<long long>(n) * H + ih) * W + iw) * C + c];
+                v = static_cast<float>(raw);
+                if (normalize) v = (v / 255.f - mean[c % 3]) / stdv[c % 3];
+            }
+        }
+        out[i] = __float2bfloat16(v);
+    }
+}
+
+// ------------------------------------------------------------------------------------ synthetic / normalise
+__global__ void __launch_bounds__(256) synth_kernel(void* __restrict__ img, long long* __restrict__ labels, long long n_el,
+                                                    int batch, int C, int num_classes, uint32_t base, int out_fp32) {
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_el; i += step) {
+        const uint32_t h = hash_u32(static_cast<uint32_t>(i) + base);
+        const int c = static_cast<int>(i % C);
+        const float px = static_cast<float>(h & 255u) / 255.0f;
+        const float v = (px - mean[c % 3]) / stdv[c % 3];
+        if (out_fp32) static_cast<float*>(img)[i] = v;
+        else static_cast<__nv_bfloat16*>(img)[i] = __float2bfloat16(v);
+        if (i < batch) labels[i] = static_cast<long long>(hash_u32(static_cast<uint32_t>(i) + (base ^ 0xA5A5A5A5u)) % static_cast<uint32_t>(num_classes));
+    }
+}
+__global__ void __launch_bounds__(256) normalize_u8_kernel(const uint8_t* __restrict__ in, void* __restrict__ out, long long n_el,
+                                                           int C, int out_fp32) {
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_el; i += step) {
+        const int c = static_cast<int>(i % C);
+        const float v = (static_cast<float>(in[i]) / 255.0f - mean[c % 3]) / stdv[c % 3];
+        if (out_fp32) static_cast<float*>(out)[i] = v;
+        else static_cast<__nv_bfloat16*>(out)[i] = __float2bfloat16(v);
+    }
+}
+
+// fp32 -> bf16 cast of a flat buffer (shadow-weight refresh)
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += step) out[i] = __float2bfloat16(in[i]);
+}
+
+}  // namespace picd
+
+using namespace picd;
+typedef __nv_bfloat16 bf16;
+
+extern "C" int picd_pool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C, int OH, int OW, int kh,
+                             int kw, int stride, int pad, int mode, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "pool: C=%d must be a multiple of 8", C);
+    PICD_REQUIRE(kh * kw <= 255, "pool: window too large");
+    const long long total = 1LL * N * OH * OW * (C / 8);
+    pool_fwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out),
+                                                     static_cast<uint8_t*>(argmax), N, H, W, C, OH, OW, kh, kw, stride, pad, mode);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_pool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W, int C, int OH, int OW,
+                             int kh, int kw, int stride, int pad, int mode, cudaStream_t st) {
+    const long long total = 1LL * N * H * W * (C / 8);
+    pool_bwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(dy), static_cast<const uint8_t*>(argmax),
+                                                     static_cast<bf16*>(dx), N, H, W, C, OH, OW, kh, kw, stride, pad, mode);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_gap_fwd(const void* x, void* out, int N, int HW, int C, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "gap: C=%d must be a multiple of 8", C);
+    const int vecs = C / 8, tx = vecs < 32 ? vecs : 32;
+    gap_fwd_kernel<<<dim3((vecs + tx - 1) / tx, N), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), HW, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_gap_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t st) {
+    const long long total = 1LL * N * HW * (C / 8);
+    gap_bwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(dy), static_cast<bf16*>(dx), total, HW, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_cross_entropy(const float* logits, const long long* labels, const float* weight, float* loss,
+                                  float* dlogits, int B, int nc, cudaStream_t st) {
+    xent_kernel<<<1, 256, 0, st>>>(logits, labels, weight, loss, dlogits, B, nc);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, int C, int act, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "act: C=%d must be a multiple of 8", C);
+    const long long total = rows * (C / 8);
+    act_fwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(x), bias, static_cast<bf16*>(out), total, C, act);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, long long rows, int C, int act,
+                            cudaStream_t st) {
+    const long long total = rows * (C / 8);
+    act_bwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(dy), static_cast<const bf16*>(x), bias,
+                                                    static_cast<bf16*>(dx), total, C, act);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t st) {
+    const int gx = (C + 63) / 64;
+    long long gy = (4LL * num_sms()) / gx;
+    if (gy < 1) gy = 1;
+    long long rpb = (P + gy - 1) / gy;
+    if (rpb < 16) rpb = 16;
+    gy = (P + rpb - 1) / rpb;
+    colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, st>>>(static_cast<const bf16*>(x), out, P, C, static_cast<int>(rpb));
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, cudaStream_t st) {
+    dropout_kernel<<<grid_for(n), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), n, p, seed);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                                  long long M, int D, float eps, cudaStream_t st) {
+    PICD_REQUIRE(D % 8 == 0, "layernorm: D=%d must be a multiple of 8", D);
+    layernorm_fwd_kernel<<<static_cast<unsigned>((M + 7) / 8), 256, 0, st>>>(static_cast<const bf16*>(x), gamma, beta,
+                                                                            static_cast<bf16*>(y), mean, rstd, M, D, eps);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                                  void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
+    long long blocks = 2LL * num_sms();
+    long long rpb = (M + blocks - 1) / blocks;
+    if (rpb < 8) rpb = 8;
+    blocks = (M + rpb - 1) / rpb;
+    layernorm_bwd_kernel<<<static_cast<unsigned>(blocks), 256, 2 * D * sizeof(float), st>>>(
+        static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta,
+        M, D, static_cast<int>(rpb));
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_small_linear_fwd(const void* x, const float* w, const float* bias, void* y, int M, int N, int K, int act,
+                                     int out_fp32, cudaStream_t st) {
+    const long long threads = 32LL * M * N;
+    small_linear_fwd_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(static_cast<const bf16*>(x), w, bias, y,
+                                                                                         M, N, K, act, out_fp32);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_small_linear_bwd(const void* dy, const void* y, const void* x, const float* w, float* dpre_scratch,
+                                     void* dx, float* dw, float* db, int M, int N, int K, int act, int dy_fp32, int y_fp32,
+                                     cudaStream_t st) {
+    small_linear_dpre_kernel<<<(M * N + 255) / 256, 256, 0, st>>>(dy, y, dpre_scratch, M * N, act, dy_fp32, y_fp32);
+    if (dx != nullptr)
+        small_linear_dx_kernel<<<(M * K + 255) / 256, 256, 0, st>>>(dpre_scratch, w, static_cast<bf16*>(dx), M, N, K);
+    const int work = N * K > N ? N * K : N;
+    small_linear_dw_kernel<<<(work + 255) / 256, 256, 0, st>>>(dpre_scratch, static_cast<const bf16*>(x), dw, db, M, N, K);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_pack_s2d(const void* x, void* out, int N, int H, int W, int C, int Hp, int Wp, int Cp, int s, int pad_h,
+                             int pad_w, int src_u8, cudaStream_t st) {
+    const long long total = 1LL * N * Hp * Wp * Cp;
+    if (src_u8)
+        pack_s2d_kernel<uint8_t><<<grid_for(total), 256, 0, st>>>(static_cast<const uint8_t*>(x), static_cast<bf16*>(out), N, H, W, C,
+                                                                  Hp, Wp, Cp, s, pad_h, pad_w, 1);
+    else
+        pack_s2d_kernel<bf16><<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), N, H, W, C, Hp,
+                                                               Wp, Cp, s, pad_h, pad_w, 0);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_synthetic_batch(void* img, long long* labels, int batch, int H, int W, int C, int num_classes,
+                                    unsigned base, int out_fp32, cudaStream_t st) {
+    const long long n_el = 1LL * batch * H * W * C;
+    synth_kernel<<<grid_for(n_el), 256, 0, st>>>(img, labels, n_el, batch, C, num_classes, base, out_fp32);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_normalize_u8(const void* in, void* out, long long n_el, int C, int out_fp32, cudaStream_t st) {
+    normalize_u8_kernel<<<grid_for(n_el), 256, 0, st>>>(static_cast<const uint8_t*>(in), out, n_el, C, out_fp32);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t st) {
+    cast_f32_bf16_kernel<<<grid_for(n), 256, 0, st>>>(in, static_cast<bf16*>(out), n);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,130 @@
+/* picd_b200 -- C ABI of libpicd_b200.so (sm_100a kernels for the B200-native image-classification trainer).
+ *
+ * Conventions: every function returns 0 on success; on failure picd_last_error() (thread local) describes it.
+ * Pointers are device pointers unless stated.  Activations are NHWC bf16 ("void*"), statistics / master weights /
+ * gradients are fp32.  All launches are asynchronous on `stream`.  Citations name the reference behaviour each
+ * entry point replaces (file:line in /root/reference or SURVEY.md row).
+ */
+#ifndef PICD_B200_H
+#define PICD_B200_H
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* activation codes */
+enum { PICD_ACT_NONE = 0, PICD_ACT_RELU = 1, PICD_ACT_GELU = 2, PICD_ACT_SWISH = 3, PICD_ACT_SIGMOID = 4 };
+/* optimizer kinds */
+enum { PICD_OPT_SGD = 0, PICD_OPT_ADAM = 1, PICD_OPT_ADAMW = 2 };
+/* all-reduce variants */
+enum { PICD_AR_LOCAL = 0, PICD_AR_ONE_SHOT = 1, PICD_AR_TWO_SHOT = 2 };
+
+const char* picd_last_error(void);
+int picd_version(void);
+int picd_num_sms(void);
+unsigned long long picd_launch_count(void);   /* kernel launches issued by the library so far */
+
+/* ---- tcgen05 implicit-GEMM convolution / GEMM (replaces cuDNN conv + cuBLAS Linear: SURVEY.md K1-K4,
+ *      nn/classifier.py:26-37 via torchvision) ------------------------------------------------------------- */
+/* y = conv(x, w) [+ bias][act]; stats (nullable) accumulates per-channel [sum(Cout), sumsq(Cout)] of y for BatchNorm */
+int picd_conv_fprop(const void* x, const void* w, void* y, float* stats, const float* bias, int act, int N, int H,
+                    int W, int Cin, int Cout, int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                    cudaStream_t stream);
+int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
+                    int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
+/* dw (fp32, [Cout,R,S,Cin]) += ...; accumulates with red.add, so it can target the gradient arena directly */
+int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
+                    int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
+int picd_gemm_nt(const void* a, const void* b, void* d, const float* bias, int act, int M, int N, int K,
+                 cudaStream_t stream);                       /* D[M,N] = act(A[M,K] B[N,K]^T + bias) */
+int picd_gemm_nn(const void* a, const void* b, void* d, int M, int N, int K, cudaStream_t stream);
+                                                             /* D[M,K] = A[M,N] B[N,K] */
+int picd_gemm_tn_f32(const void* a, const void* b, float* d, int M, int N, int K, cudaStream_t stream);
+                                                             /* D[N,K] += A[M,N]^T B[M,K] (fp32) */
+
+/* ---- BatchNorm family (torch/nn/modules/_functions.py:39-179 = SURVEY.md K5-K10,K12) ------------------- */
+int picd_bn_stats(const void* x, float* stats, long long P, int C, cudaStream_t stream);
+int picd_bn_finalize(const float* sums, float count, const float* gamma, const float* beta, float* running_mean,
+                     float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                     float* invstd, int C, cudaStream_t stream);
+int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                        float eps, float* scale, float* shift, int C, cudaStream_t stream);
+int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
+                  long long P, int C, cudaStream_t stream);
+int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+                       const float* mean, const float* invstd, int act, float* sums, long long P, int C,
+                       cudaStream_t stream);
+int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+                      const float* mean, const float* invstd, int act, const float* sums, float inv_count,
+                      const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
+                      cudaStream_t stream);
+int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift, int act,
+                     void* dy, void* dres, long long P, int C, cudaStream_t stream);
+
+/* ---- pooling, loss, activations, LayerNorm, small linear, packing, data (SURVEY.md K10-K15,K18-K21) ---- */
+int picd_pool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C, int OH, int OW, int kh, int kw,
+                  int stride, int pad, int mode /*0 max, 1 avg*/, cudaStream_t stream);
+int picd_pool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W, int C, int OH, int OW, int kh,
+                  int kw, int stride, int pad, int mode, cudaStream_t stream);
+int picd_gap_fwd(const void* x, void* out, int N, int HW, int C, cudaStream_t stream);
+int picd_gap_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);
+/* class-weighted softmax cross-entropy (train.py:157-158): loss[0] and d loss/d logits in one launch */
+int picd_cross_entropy(const float* logits, const long long* labels, const float* weight, float* loss,
+                       float* dlogits, int B, int nc, cudaStream_t stream);
+int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, int C, int act, cudaStream_t stream);
+int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, long long rows, int C, int act,
+                 cudaStream_t stream);
+int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t stream);
+int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, cudaStream_t stream);
+int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                       long long M, int D, float eps, cudaStream_t stream);
+int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                       void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t stream);
+int picd_small_linear_fwd(const void* x, const float* w, const float* bias, void* y, int M, int N, int K, int act,
+                          int out_fp32, cudaStream_t stream);
+int picd_small_linear_bwd(const void* dy, const void* y, const void* x, const float* w, float* dpre_scratch, void* dx,
+                          float* dw, float* db, int M, int N, int K, int act, int dy_fp32, int y_fp32,
+                          cudaStream_t stream);
+int picd_pack_s2d(const void* x, void* out, int N, int H, int W, int C, int Hp, int Wp, int Cp, int s, int pad_h,
+                  int pad_w, int src_u8, cudaStream_t stream);
+/* on-device synthetic batches + ImageNet normalisation (replaces dp/loader.py:39-91 and the H2D copy) */
+int picd_synthetic_batch(void* img, long long* labels, int batch, int H, int W, int C, int num_classes, unsigned base,
+                         int out_fp32, cudaStream_t stream);
+int picd_normalize_u8(const void* in, void* out, long long n_el, int C, int out_fp32, cudaStream_t stream);
+int picd_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t stream);
+
+/* ---- NVLink peer-memory communicator (replaces DDP's NCCL all-reduce + optimizer.step + SyncBN collectives:
+ *      train.py:72-73,124,128 = SURVEY.md N5-N7, K16) ------------------------------------------------------ */
+int picd_slab_alloc(size_t bytes, void** out);
+int picd_slab_free(void* p);
+int picd_ipc_handle_bytes(void);
+int picd_ipc_get_handle(void* p, void* handle_out);
+int picd_ipc_open(const void* handle, void** out);
+int picd_ipc_close(void* p);
+int picd_comm_create(int rank, int world, void* const* grad, void* const* master, void* const* shadow,
+                     void* const* xchg, void* const* flags, int num_buckets, void** ctx_out);
+int picd_comm_destroy(void* ctx);
+int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count, float* state0,
+                                float* state1, int kind, float lr, float momentum, float beta1, float beta2, float eps,
+                                float weight_decay, float bc1, float bc2, int nesterov, unsigned epoch, int blocks,
+                                cudaStream_t stream);
+int picd_p2p_allreduce_small(void* ctx, const float* in, float* out, int n, long long slot_off, int flag_slot,
+                             unsigned epoch, cudaStream_t stream);
+int picd_bn_finalize_sync(void* ctx, const float* sums, float count, const float* gamma, const float* beta,
+                          float* running_mean, float* running_var, float momentum, float eps, float* scale,
+                          float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
+                          int flag_slot, unsigned epoch, cudaStream_t stream);
+
+/* ---- runtime ---------------------------------------------------------------------------------------------- */
+/* reverse-order bucket plan (torch DDP Reducer semantics); host function */
+int picd_plan_buckets(const int64_t* padded_sizes, int n_params, int64_t first_bytes, int64_t cap_bytes,
+                      int elem_bytes, int64_t* starts, int64_t* ends, int* param_bucket, int max_buckets);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PICD_B200_H */

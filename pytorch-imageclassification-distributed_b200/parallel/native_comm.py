@@ -1,0 +1,245 @@
+"""NVLink peer-memory backend of the data-parallel engine (CUDA only).
+
+``SymmetricSlab``  one ``cudaMalloc`` allocation per rank holding
+                   [gradient arena fp32 | master weights fp32 | bf16 shadow | exchange slots | flag words],
+                   exported with CUDA IPC and mapped by every peer of the node (handles travel over the
+                   existing torch.distributed group once, at construction).
+``NativeReducer``  launches ``picd_fused_allreduce_update`` per bucket on a side stream as soon as the bucket's
+                   last gradient kernel has been queued (reference: DDP Reducer + NCCL + optimizer.step,
+                   train.py:72-73).
+``Comm``           small latency-bound collectives for SyncBatchNorm over the same slab
+                   (reference: torch/nn/modules/_functions.py:74-76,158-164).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops._lib import check, require_lib
+
+SLOT_FLOATS = 2 * 2048 + 8          # (sum, sumsq) for up to 2048 channels + count
+N_SLOTS = 512                       # small-collective slots (each double-buffered)
+MAX_PEERS = 8
+TWO_SHOT_MIN_BYTES = 256 << 10      # below this a bucket is latency-bound: one-shot
+
+_current: Optional["Comm"] = None
+
+
+def current_comm() -> Optional["Comm"]:
+    return _current
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class _DevMem:
+    """Expose a raw device range through __cuda_array_interface__ so torch can view it without copying."""
+
+    def __init__(self, ptr: int, shape, typestr: str, owner):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+        self._owner = owner
+
+
+def _view(ptr: int, n: int, typestr: str, device, owner) -> torch.Tensor:
+    return torch.as_tensor(_DevMem(ptr, (n,), typestr, owner), device=device)
+
+
+class SymmetricSlab:
+    def __init__(self, total: int, n_state: int, device: torch.device, world: int, rank: int,
+                 num_buckets_hint: int = 256):
+        self.lib = require_lib()
+        self.total, self.device, self.world, self.rank = total, device, world, rank
+        if world > MAX_PEERS:
+            raise RuntimeError(f"picd_b200: the peer-memory engine supports up to {MAX_PEERS} ranks of one node "
+                               f"(got world_size={world})")
+        self.off_grad = 0
+        self.off_master = _align(self.off_grad + total * 4)
+        self.off_shadow = _align(self.off_master + total * 4)
+        self.off_xchg = _align(self.off_shadow + total * 2)
+        self.off_flags = _align(self.off_xchg + N_SLOTS * 2 * SLOT_FLOATS * 4)
+        self.flag_words = (2 * num_buckets_hint + N_SLOTS) * MAX_PEERS
+        self.nbytes = _align(self.off_flags + self.flag_words * 4)
+        self.max_buckets = num_buckets_hint
+        base = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            self.lib.picd_slab_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
+            check(self.lib.picd_slab_alloc(self.nbytes, ctypes.byref(base)), "picd_slab_alloc")
+        self.base = base.value
+        self.grad = _view(self.base + self.off_grad, total, "<f4", device, self)
+        self.master = _view(self.base + self.off_master, total, "<f4", device, self)
+        self.shadow = _view(self.base + self.off_shadow, total, "<i2", device, self).view(torch.bfloat16)
+        self.state = [torch.zeros(total, dtype=torch.float32, device=device) for _ in range(n_state)]
+        self.peer_bases: List[int] = [self.base] * max(world, 1)
+        if world > 1:
+            self._exchange_handles()
+
+    def _exchange_handles(self):
+        nb = self.lib.picd_ipc_handle_bytes()
+        buf = ctypes.create_string_buffer(nb)
+        self.lib.picd_ipc_get_handle.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        check(self.lib.picd_ipc_get_handle(self.base, buf), "picd_ipc_get_handle")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (self.rank, bytes(buf.raw)))
+        self.lib.picd_ipc_open.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        bases = [0] * self.world
+        with torch.cuda.device(self.device):
+            for r, raw in handles:
+                if r == self.rank:
+                    bases[r] = self.base
+                    continue
+                p = ctypes.c_void_p()
+                check(self.lib.picd_ipc_open(ctypes.create_string_buffer(raw, nb), ctypes.byref(p)),
+                      f"picd_ipc_open(rank {r})")
+                bases[r] = p.value
+        self.peer_bases = bases
+        dist.barrier(device_ids=[self.device.index]) if dist.get_backend() == "nccl" else dist.barrier()
+
+    def region_ptrs(self, off: int):
+        arr = (ctypes.c_void_p * MAX_PEERS)()
+        for i, b in enumerate(self.peer_bases):
+            arr[i] = b + off
+        return arr
+
+
+class Comm:
+    """Owns the native communicator context for one slab."""
+
+    def __init__(self, slab: SymmetricSlab, num_buckets: int):
+        global _current
+        self.slab, self.lib = slab, slab.lib
+        if num_buckets > slab.max_buckets:
+            raise RuntimeError(f"picd_b200: {num_buckets} buckets exceed the slab's flag space")
+        self.num_buckets = num_buckets
+        ctx = ctypes.c_void_p()
+        f = self.lib.picd_comm_create
+        f.argtypes = [ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+        with torch.cuda.device(slab.device):
+            check(f(slab.rank, max(slab.world, 1), slab.region_ptrs(slab.off_grad), slab.region_ptrs(slab.off_master),
+                    slab.region_ptrs(slab.off_shadow), slab.region_ptrs(slab.off_xchg),
+                    slab.region_ptrs(slab.off_flags), slab.max_buckets, ctypes.byref(ctx)), "picd_comm_create")
+        self.ctx = ctx
+        self._slot_epoch = {}
+        self._next_slot = 0
+        self._f_upd = self.lib.picd_fused_allreduce_update
+        self._f_upd.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
+                                 ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 8 +
+                                [ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p])
+        self._f_small = self.lib.picd_p2p_allreduce_small
+        self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong,
+                                  ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
+        self._f_bn = self.lib.picd_bn_finalize_sync
+        self._f_bn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_float] + [ctypes.c_void_p] * 4 +
+                               [ctypes.c_float, ctypes.c_float] + [ctypes.c_void_p] * 5 +
+                               [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p])
+        _current = self
+
+    # -- gradient buckets ---------------------------------------------------------------------------
+    def fused_update(self, bucket_index: int, mode: int, start: int, count: int, state, spec, step: int,
+                     epoch: int, blocks: int = 0):
+        s0 = state[0].data_ptr()
+        s1 = state[1].data_ptr() if len(state) > 1 else None
+        b1, b2 = spec.betas
+        bc1, bc2 = 1.0 - b1 ** step, 1.0 - b2 ** step
+        check(self._f_upd(self.ctx, bucket_index, mode, start, count, s0, s1, spec.KINDS[spec.kind], spec.lr,
+                          spec.momentum, b1, b2, spec.eps, spec.weight_decay, bc1, bc2, int(spec.nesterov),
+                          epoch & 0xFFFFFFFF, blocks, torch.cuda.current_stream().cuda_stream),
+              "picd_fused_allreduce_update")
+
+    # -- small collectives (SyncBN) ------------------------------------------------------------------
+    def _slot(self, key) -> int:
+        s = getattr(key, "_picd_slot", None)
+        if s is None:
+            s = self._next_slot
+            self._next_slot += 1
+            if s >= N_SLOTS:
+                raise RuntimeError("picd_b200: out of small-collective slots")
+            key._picd_slot = s
+        return s
+
+    def _next(self, slot: int):
+        e = self._slot_epoch.get(slot, 0) + 1
+        self._slot_epoch[slot] = e
+        off = (slot * 2 + (e & 1)) * SLOT_FLOATS
+        return e, off, 2 * self.slab.max_buckets + slot
+
+    def bn_finalize_sync(self, sums, count, gamma, beta, rm, rv, momentum, eps, coef) -> float:
+        C = gamma.numel()
+        if 2 * C + 1 > SLOT_FLOATS:
+            raise RuntimeError(f"picd_b200: SyncBN with {C} channels exceeds the exchange slot")
+        e, off, fslot = self._next(self._slot(gamma))
+        total = torch.empty(1, dtype=torch.float32, device=sums.device)
+        check(self._f_bn(self.ctx, sums.data_ptr(), float(count), gamma.data_ptr(), beta.data_ptr(),
+                         None if rm is None else rm.data_ptr(), None if rv is None else rv.data_ptr(),
+                         float(momentum), float(eps), coef[0].data_ptr(), coef[1].data_ptr(), coef[2].data_ptr(),
+                         coef[3].data_ptr(), total.data_ptr(), C, off, fslot, e & 0xFFFFFFFF,
+                         torch.cuda.current_stream().cuda_stream), "picd_bn_finalize_sync")
+        # every rank holds an equally sized shard (ShardedSampler pads), so the global count is known on the host
+        return float(count) * self.slab.world
+
+    def allreduce_small(self, vec: torch.Tensor, key=None) -> torch.Tensor:
+        n = vec.numel()
+        if n > SLOT_FLOATS:
+            raise RuntimeError("picd_b200: small all-reduce payload exceeds the exchange slot")
+        holder = key if key is not None else self
+        e, off, fslot = self._next(self._slot(_BwdKey.of(holder, n)))
+        out = torch.empty_like(vec)
+        check(self._f_small(self.ctx, vec.data_ptr(), out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
+                            torch.cuda.current_stream().cuda_stream), "picd_p2p_allreduce_small")
+        return out
+
+
+class _BwdKey:
+    """Slot identity for backward reductions: one per (call order position) -- every rank runs the same
+    sequence of BN backward calls per step, so a round-robin over positions is consistent across ranks."""
+    _ring: List["_BwdKey"] = []
+    _cursor = 0
+    RING = 192
+
+    @classmethod
+    def of(cls, holder, n):
+        if not cls._ring:
+            cls._ring = [cls() for _ in range(cls.RING)]
+        k = cls._ring[cls._cursor % cls.RING]
+        cls._cursor += 1
+        return k
+
+
+class NativeReducer:
+    def __init__(self, engine):
+        self.e = engine
+        a = engine.arena
+        self.comm = Comm(a.native, len(a.buckets))
+        self.side = torch.cuda.Stream(device=engine.device)
+        self._epoch = 0
+        self._dirty = False
+
+    def _mode(self, b) -> int:
+        if self.e.world == 1:
+            return 0
+        forced = self.e.comm
+        if forced == "one_shot":
+            return 1
+        if forced == "two_shot":
+            return 2
+        return 2 if b.numel * 4 >= TWO_SHOT_MIN_BYTES else 1
+
+    def launch_bucket(self, b):
+        e = self.e
+        cur = torch.cuda.current_stream(e.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.side.wait_event(ev)
+        with torch.cuda.stream(self.side):
+            self.comm.fused_update(b.index, self._mode(b), b.start, b.numel, e.arena.state, e.spec,
+                                   e.step_index + 1, e.step_index + 1)
+        self._dirty = True
+
+    def finish(self):
+        if self._dirty:
+            torch.cuda.current_stream(self.e.device).wait_stream(self.side)
+            self._dirty = False
