@@ -286,49 +286,76 @@ def group_conv():
 
 
 # ------------------------------------------------------------------------------------------ model
-def _model_grads(name, native_path, batch, size, dev):
+def _model_grads(name, mode, batch, size, dev):
+    """mode: 'native' (sm_100a kernels, bf16), 'torch_bf16' (library ops, bf16), 'torch_fp32' (the oracle)."""
     import torch
-    os.environ["PICD_FORCE_TORCH"] = "0" if native_path else "1"
+    os.environ["PICD_FORCE_TORCH"] = "0" if mode == "native" else "1"
+    os.environ["PICD_REF_FP32"] = "1" if mode == "torch_fp32" else "0"
     from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
     from picd_b200.models import Classifier
     from picd_b200.ops import reference as ref
     torch.manual_seed(0)
     m = Classifier(name, 7, image_size=size).to(dev)
     m.train()
+    for mod in m.modules():           # stochastic layers draw different random numbers on the two paths
+        if hasattr(mod, "p") and mod.__class__.__name__ == "Dropout":
+            mod.p = 0.0
+        if hasattr(mod, "drop_connect"):
+            mod.drop_connect = 0.0
     img, lab = ref.synthetic_batch(batch, 3, size, size, 7, 0, 0, "cpu", torch.float32)
     img, lab = img.to(dev), lab.to(dev)
     out = m(img)
     loss, main = compute_loss(out, lab, WeightedCrossEntropy(None))
     loss.backward()
     grads = {k: p.grad.detach().float().clone() for k, p in m.named_parameters() if p.grad is not None}
+    os.environ["PICD_FORCE_TORCH"] = "0"
+    os.environ["PICD_REF_FP32"] = "0"
     return float(loss.item()), main.detach().float(), grads
 
 
+def _min_cos(ga, gb):
+    import torch
+    worst, key = 1.0, None
+    for k in gb:
+        if k in ga:
+            c = float(torch.nn.functional.cosine_similarity(ga[k].flatten(), gb[k].flatten(), dim=0))
+            if c < worst:
+                worst, key = c, k
+    return worst, key
+
+
 def group_model():
+    """Gradients of whole models: the native bf16 path must be as close to the fp32 oracle as the library bf16
+    path is (bf16 noise makes early-layer gradients of a random-init deep net only loosely reproducible)."""
     import torch
     dev = torch.device("cuda")
     ok = True
     g = "model"
-    for name, batch, size in [("resnet18", 8, 64), ("resnet50", 8, 96), ("inceptionv3", 4, 299), ("vit_b_16", 4, 224),
-                              ("efficientnet-b0", 4, 64)]:
+    for name, batch, size in [("resnet18", 16, 64), ("resnet50", 16, 128), ("inceptionv3", 4, 299), ("vit_b_16", 4, 224),
+                              ("efficientnet-b0", 8, 64)]:
         try:
-            l1, o1, g1 = _model_grads(name, True, batch, size, dev)
-            l0, o0, g0 = _model_grads(name, False, batch, size, dev)
+            l1, o1, g1 = _model_grads(name, "native", batch, size, dev)
+            l0, o0, g0 = _model_grads(name, "torch_bf16", batch, size, dev)
+            l2, o2, g2 = _model_grads(name, "torch_fp32", batch, size, dev)
         except Exception as e:  # noqa: BLE001
+            import traceback
+            traceback.print_exc()
             emit({"group": g, "test": name, "ok": False, "error": repr(e)[:400]})
             ok = False
             continue
-        emit({"group": g, "test": f"{name}.loss", "native": l1, "torch": l0, "ok": abs(l1 - l0) < 0.05 * max(1.0, abs(l0))})
-        ok &= check(f"{name}.logits", o1, o0, 0.1, g)
-        worst, worst_k, missing = 0.0, None, [k for k in g0 if k not in g1]
-        for k in g0:
-            if k in g1:
-                e = relerr(g1[k], g0[k])
-                if e > worst:
-                    worst, worst_k = e, k
-        emit({"group": g, "test": f"{name}.grads", "worst_relerr": worst, "worst_param": worst_k, "missing": missing[:5],
-              "ok": worst < 0.25 and not missing})
-    os.environ["PICD_FORCE_TORCH"] = "0"
+        emit({"group": g, "test": f"{name}.loss", "native": l1, "torch_bf16": l0, "fp32": l2,
+              "ok": abs(l1 - l2) < 0.05 * max(1.0, abs(l2))})
+        ok &= check(f"{name}.logits_vs_fp32", o1, o2, 0.1, g, {"torch_bf16_relerr": relerr(o0, o2)})
+        missing = [k for k in g2 if k not in g1]
+        cn, kn = _min_cos(g1, g2)
+        ct, kt = _min_cos(g0, g2)
+        mean_cn = sum(float(torch.nn.functional.cosine_similarity(g1[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g1) / max(1, len(g2))
+        mean_ct = sum(float(torch.nn.functional.cosine_similarity(g0[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g0) / max(1, len(g2))
+        good = (not missing) and mean_cn >= mean_ct - 0.02 and cn >= min(0.9, ct - 0.1)
+        emit({"group": g, "test": f"{name}.grads_vs_fp32", "native_min_cos": cn, "native_min_param": kn,
+              "torch_bf16_min_cos": ct, "torch_bf16_min_param": kt, "native_mean_cos": mean_cn,
+              "torch_bf16_mean_cos": mean_ct, "missing": missing[:5], "ok": good})
+        ok &= good
     return ok
 
 

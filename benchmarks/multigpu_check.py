@@ -1,0 +1,242 @@
+#!/usr/bin/env python
+"""Multi-GPU correctness + bandwidth checks for the NVLink peer-memory engine.  Launch with torchrun:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29501 \
+        benchmarks/multigpu_check.py [--sweep]
+
+Checks (every rank; rank 0 prints JSON lines and appends them to gpurun_out/multigpu.jsonl):
+  1. fused all-reduce + update (one-shot and two-shot) == dist.all_reduce + /W + torch optimizer, replicas identical
+  2. SyncBatchNorm over peer memory == torch.nn.SyncBatchNorm (forward, running stats, dx, dgamma, dbeta)
+  3. a few ResNet-18 training steps: replicas stay bit-identical, loss finite
+  4. (--sweep) config 5 of BASELINE.json: all-reduce + update time and bus bandwidth, 1 KB .. 1 GB, vs NCCL + foreach SGD
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def emit(rec):
+    if dist.get_rank() == 0:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "multigpu.jsonl"), "a") as f:
+            f.write(json.dumps(rec) + "\n")
+        print(json.dumps(rec), flush=True)
+
+
+def relerr(a, b):
+    return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6))
+
+
+def all_ok(flag: bool, device) -> bool:
+    t = torch.tensor([1 if flag else 0], device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item())
+
+
+def check_fused_update(device, mode):
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ok = True
+    for kind in ("sgd", "adamw"):
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.ReLU(), torch.nn.Linear(512, 1024),
+                                  torch.nn.ReLU(), torch.nn.Linear(1024, 8)).to(device)
+        ref = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.ReLU(), torch.nn.Linear(512, 1024),
+                                  torch.nn.ReLU(), torch.nn.Linear(1024, 8)).to(device)
+        ref.load_state_dict(net.state_dict())
+        lr = 0.05 if kind == "sgd" else 1e-3
+        dp = FusedDataParallel(net, OptimizerSpec(kind=kind, lr=lr, momentum=0.9, weight_decay=0.01),
+                               first_bucket_bytes=64 << 10, bucket_cap_bytes=1 << 20, comm=mode)
+        opt = (torch.optim.SGD(ref.parameters(), lr=lr, momentum=0.9, weight_decay=0.01) if kind == "sgd"
+               else torch.optim.AdamW(ref.parameters(), lr=lr, weight_decay=0.01))
+        for it in range(4):
+            g = torch.Generator(device="cpu").manual_seed(100 * it + rank)
+            x = torch.randn(32, 256, generator=g).to(device)
+            dp(x).square().mean().backward()
+            dp.optimizer.step()
+            opt.zero_grad()
+            ref(x).square().mean().backward()
+            for p in ref.parameters():
+                dist.all_reduce(p.grad)
+                p.grad /= world
+            opt.step()
+        torch.cuda.synchronize()
+        errs = [relerr(a, b) for a, b in zip(net.parameters(), ref.parameters())]
+        flat = dp.arena.master.clone()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        identical = all(torch.equal(gathered[0], t) for t in gathered)
+        sh_ok = relerr(dp.arena.shadow.float(), dp.arena.master) < 1e-2
+        zero = dp.arena.grad.abs().max().item() == 0
+        good = max(errs) < 2e-4 and identical and sh_ok and zero
+        emit({"test": f"fused_update[{mode},{kind}]", "max_relerr": max(errs), "replicas_identical": identical,
+              "shadow_ok": sh_ok, "grad_zeroed": zero, "buckets": len(dp.arena.buckets), "ok": good})
+        ok &= good
+        del dp
+    return ok
+
+
+def check_sync_bn(device):
+    from picd_b200.ops import native
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank = dist.get_rank()
+    # a slab (and therefore a communicator) exists once any model is wrapped
+    holder = FusedDataParallel(torch.nn.Linear(8, 8).to(device), OptimizerSpec("sgd", lr=0.0))
+    ok = True
+    for (N, C, H) in [(4, 64, 8), (2, 256, 7), (3, 2048, 3)]:
+        g = torch.Generator().manual_seed(7 + rank)
+        x = (torch.randn(N, C, H, H, generator=g) * (1 + rank) + 0.2 * rank).to(device)
+        xb = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        gamma = (torch.rand(C, generator=torch.Generator().manual_seed(1)) + 0.5).to(device).requires_grad_()
+        beta = torch.zeros(C, device=device).requires_grad_()
+        rm, rv = torch.zeros(C, device=device), torch.ones(C, device=device)
+        xn = xb.clone().requires_grad_()
+        z = native.bn_act(xn, gamma, beta, rm, rv, training=True, momentum=0.1, eps=1e-5, act="relu", residual=None,
+                          sync_group=True)
+        dz = torch.randn(N, C, H, H, generator=g).to(device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        z.backward(dz)
+        bn = torch.nn.SyncBatchNorm(C).to(device)
+        with torch.no_grad():
+            bn.weight.copy_(gamma)
+        xr = xb.float().requires_grad_()
+        zr = torch.relu(bn(xr))
+        zr.backward(dz.float())
+        torch.cuda.synchronize()
+        res = {"fwd": relerr(z, zr), "dx": relerr(xn.grad, xr.grad), "dgamma": relerr(gamma.grad, bn.weight.grad),
+               "dbeta": relerr(beta.grad, bn.bias.grad), "running_mean": relerr(rm, bn.running_mean),
+               "running_var": relerr(rv, bn.running_var)}
+        good = all_ok(max(res.values()) < 3e-2, device)
+        emit({"test": f"sync_bn[{N}x{C}x{H}x{H}]", **res, "ok": good})
+        ok &= good
+    del holder
+    return ok
+
+
+def check_training(device):
+    from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
+    from picd_b200.models import Classifier, convert_sync_batchnorm
+    from picd_b200.ops import synthetic_batch
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ok = True
+    for sync in (False, True):
+        torch.manual_seed(0)
+        m = Classifier("resnet18", 7, image_size=64)
+        if sync:
+            convert_sync_batchnorm(m)
+        dp = FusedDataParallel(m.to(device), OptimizerSpec("sgd", lr=0.05, momentum=0.9))
+        dp.train()
+        losses = []
+        for it in range(5):
+            img, lab = synthetic_batch(16, 3, 64, 64, 7, 0, it * world + rank, device, torch.bfloat16)
+            loss, _ = compute_loss(dp(img), lab, WeightedCrossEntropy(None))
+            loss.backward()
+            dp.optimizer.step()
+            losses.append(float(loss.item()))
+        flat = dp.arena.master.clone()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        identical = all(torch.equal(gathered[0], t) for t in gathered)
+        good = identical and all(l == l and l < 50 for l in losses)
+        emit({"test": f"resnet18_train[sync_bn={sync}]", "losses": losses, "replicas_identical": identical, "ok": good})
+        ok &= good
+        del dp
+    return ok
+
+
+def sweep(device):
+    """all-reduce + SGD-momentum update, fused over peer memory vs NCCL all_reduce + torch._foreach update."""
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    world = dist.get_world_size()
+    sizes = [1 << k for k in range(8, 29, 2)]          # elements: 1 KB .. 1 GB of fp32
+    for n in sizes:
+        p = torch.nn.Parameter(torch.zeros(n, device=device))
+        holder = torch.nn.Module()
+        holder.w = p
+        for mode in ("one_shot", "two_shot"):
+            if mode == "one_shot" and n * 4 > (64 << 20):
+                continue
+            dp = FusedDataParallel(holder, OptimizerSpec("sgd", lr=0.01, momentum=0.9), first_bucket_bytes=1 << 40,
+                                   bucket_cap_bytes=1 << 40, comm=mode, overlap=False)
+            b = dp.arena.buckets[0]
+
+            def once():
+                dp._impl.launch_bucket(b)
+                dp._impl.finish()
+                dp.step_index += 1
+            for _ in range(3):
+                once()
+            torch.cuda.synchronize(); dist.barrier(device_ids=[device.index])
+            a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            iters = 20 if n < (1 << 24) else 5
+            a.record()
+            for _ in range(iters):
+                once()
+            e.record(); torch.cuda.synchronize()
+            ms = torch.tensor([a.elapsed_time(e) / iters], device=device)
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            bytes_ = dp.arena.total * 4
+            emit({"test": "sweep", "impl": f"p2p_{mode}", "bytes": bytes_, "ms": float(ms), "world": world,
+                  "busbw_GBs": 2 * (world - 1) / world * bytes_ / (float(ms) * 1e-3) / 1e9, "ok": True})
+            del dp
+        # NCCL baseline: all_reduce + /W + momentum SGD (foreach) + bf16 cast, what DDP + optimizer.step amount to
+        g = torch.zeros(n, device=device); w = torch.zeros(n, device=device); mom = torch.zeros(n, device=device)
+        sh = torch.zeros(n, device=device, dtype=torch.bfloat16)
+
+        def nccl_once():
+            dist.all_reduce(g)
+            g.div_(world)
+            mom.mul_(0.9).add_(g)
+            w.add_(mom, alpha=-0.01)
+            sh.copy_(w)
+            g.zero_()
+        for _ in range(3):
+            nccl_once()
+        torch.cuda.synchronize(); dist.barrier(device_ids=[device.index])
+        a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 20 if n < (1 << 24) else 5
+        a.record()
+        for _ in range(iters):
+            nccl_once()
+        e.record(); torch.cuda.synchronize()
+        ms = torch.tensor([a.elapsed_time(e) / iters], device=device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        emit({"test": "sweep", "impl": "nccl+foreach", "bytes": n * 4, "ms": float(ms), "world": world,
+              "busbw_GBs": 2 * (world - 1) / world * n * 4 / (float(ms) * 1e-3) / 1e9, "ok": True})
+        del g, w, mom, sh
+        torch.cuda.empty_cache()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--skip-checks", action="store_true")
+    args = ap.parse_args()
+    from picd_b200.parallel import dist as D
+    D.init_distributed("b200")
+    device = torch.device("cuda", torch.cuda.current_device())
+    ok = True
+    if not args.skip_checks:
+        for mode in ("one_shot", "two_shot", "auto"):
+            ok &= check_fused_update(device, mode)
+        ok &= check_sync_bn(device)
+        ok &= check_training(device)
+    if args.sweep:
+        sweep(device)
+    emit({"test": "SUMMARY", "world": dist.get_world_size(), "ok": bool(ok)})
+    D.barrier()
+    D.shutdown()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

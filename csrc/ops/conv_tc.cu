@@ -554,7 +554,19 @@ extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, i
                                cudaStream_t stream) {
     PICD_REQUIRE(stride == 1 || stride == 2, "conv_dgrad: stride %d unsupported", stride);
     PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_dgrad: channels must be multiples of 8");
-    bool zeroed = false;
+    // If some output parity class receives no tap (e.g. 1x1 stride-2), zero dx once BEFORE any class is written.
+    if (stride > 1) {
+        bool any_empty = false;
+        for (int ph = 0; ph < stride && !any_empty; ++ph)
+            for (int pw = 0; pw < stride && !any_empty; ++pw) {
+                int cnt = 0;
+                for (int r = 0; r < R; ++r)
+                    for (int s = 0; s < S; ++s)
+                        if (pos_mod(ph + pad_h - r, stride) == 0 && pos_mod(pw + pad_w - s, stride) == 0) ++cnt;
+                if (cnt == 0) any_empty = true;
+            }
+        if (any_empty) PICD_CUDA(cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * Cin * 2, stream));
+    }
     for (int ph = 0; ph < stride; ++ph) {
         for (int pw = 0; pw < stride; ++pw) {
             const int Hv = (H - ph + stride - 1) / stride, Wv = (W - pw + stride - 1) / stride;
@@ -573,14 +585,7 @@ extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, i
                     t.btap = static_cast<int16_t>(r * S + s);
                     p.taps[nt++] = t;
                 }
-            if (nt == 0) {
-                // this parity class receives no gradient (e.g. 1x1 stride-2): make sure dx is zero there
-                if (!zeroed) {
-                    PICD_CUDA(cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * Cin * 2, stream));
-                    zeroed = true;
-                }
-                continue;
-            }
+            if (nt == 0) continue;   // zeroed above
             const Geometry g = choose_geometry(N, Hv, Wv, TILE_M);
             const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
             if (make_act_map(&p.amap[0], dy, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;

@@ -7,6 +7,7 @@ lives in :mod:`picd_b200.ops`, which fuses conv + BN + activation + residual.
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -164,8 +165,8 @@ class MLPHead(nn.Sequential):
 def prepare_input(x: torch.Tensor) -> torch.Tensor:
     """Bring a batch into the layout/dtype the backbone computes in: channels_last always,
     bf16 on CUDA (fp32 on CPU, where the torch oracle runs)."""
-    if x.is_cuda and x.dtype != torch.bfloat16:
-        x = x.to(torch.bfloat16)
+    if x.is_cuda and x.dtype != torch.bfloat16 and os.environ.get("PICD_REF_FP32", "0") != "1":
+        x = x.to(torch.bfloat16)      # PICD_REF_FP32=1 (with PICD_FORCE_TORCH=1) keeps an fp32 oracle run in fp32
     if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
         x = x.contiguous(memory_format=torch.channels_last)
     return x

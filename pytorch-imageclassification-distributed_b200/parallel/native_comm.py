@@ -124,6 +124,8 @@ class Comm:
                     slab.region_ptrs(slab.off_flags), slab.max_buckets, ctypes.byref(ctx)), "picd_comm_create")
         self.ctx = ctx
         self._slot_epoch = {}
+        self._slots = {}
+        self._slot_keys = []
         self._next_slot = 0
         self._f_upd = self.lib.picd_fused_allreduce_update
         self._f_upd.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
@@ -152,13 +154,14 @@ class Comm:
 
     # -- small collectives (SyncBN) ------------------------------------------------------------------
     def _slot(self, key) -> int:
-        s = getattr(key, "_picd_slot", None)
+        s = self._slots.get(id(key))
         if s is None:
             s = self._next_slot
             self._next_slot += 1
             if s >= N_SLOTS:
                 raise RuntimeError("picd_b200: out of small-collective slots")
-            key._picd_slot = s
+            self._slots[id(key)] = s
+            self._slot_keys.append(key)          # keep the key alive so its id() stays unique
         return s
 
     def _next(self, slot: int):

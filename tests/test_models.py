@@ -1,0 +1,88 @@
+"""Model zoo: state-dict parity with torchvision, forward parity on CPU, Classifier behaviour (nn/classifier.py:7-37)."""
+import pytest
+import torch
+import torchvision
+
+from picd_b200.models import (BACKBONES, Classifier, MLPHead, SyncBatchNorm, convert_sync_batchnorm, inception_v3,
+                              resnet18, resnet50, vit_b_16)
+
+
+def _same_keys(a, b):
+    sa, sb = a.state_dict(), b.state_dict()
+    assert set(sa) == set(sb)
+    for k in sa:
+        assert sa[k].shape == sb[k].shape, k
+
+
+def test_state_dict_keys_match_torchvision():
+    _same_keys(resnet18(), torchvision.models.resnet18())
+    _same_keys(resnet50(), torchvision.models.resnet50())
+    _same_keys(vit_b_16(), torchvision.models.vit_b_16())
+    _same_keys(inception_v3(), torchvision.models.inception_v3(weights=None, aux_logits=True, init_weights=False))
+
+
+@pytest.mark.parametrize("builder,tv,size", [(resnet18, torchvision.models.resnet18, 64),
+                                             (resnet50, torchvision.models.resnet50, 64)])
+def test_resnet_forward_matches_torchvision(builder, tv, size):
+    torch.manual_seed(0)
+    ref = tv()
+    ours = builder()
+    ours.load_state_dict(ref.state_dict())
+    x = torch.randn(2, 3, size, size)
+    for mode in ("train", "eval"):
+        getattr(ref, mode)(); getattr(ours, mode)()
+        assert torch.allclose(ours(x), ref(x), atol=2e-4, rtol=1e-4)
+    # running statistics advanced identically in train mode
+    assert torch.allclose(ours.bn1.running_var, ref.bn1.running_var, atol=1e-5)
+
+
+def test_inception_forward_matches_torchvision_and_returns_aux():
+    torch.manual_seed(0)
+    ref = torchvision.models.inception_v3(weights=None, aux_logits=True, init_weights=False, transform_input=False)
+    ours = inception_v3()
+    ours.load_state_dict(ref.state_dict())
+    x = torch.randn(2, 3, 299, 299)
+    ref.eval(); ours.eval()
+    assert torch.allclose(ours(x), ref(x), atol=1e-3, rtol=1e-3)
+    ours.train()
+    out = ours(x)
+    assert isinstance(out, tuple) and out.logits.shape == (2, 1000) and out.aux_logits.shape == (2, 1000)
+
+
+def test_vit_forward_matches_torchvision():
+    torch.manual_seed(0)
+    ref = torchvision.models.vit_b_16().eval()
+    ours = vit_b_16().eval()
+    ours.load_state_dict(ref.state_dict())
+    x = torch.randn(1, 3, 224, 224)
+    assert torch.allclose(ours(x), ref(x), atol=2e-3, rtol=1e-3)
+
+
+def test_classifier_head_and_names():
+    for name in ("resnet18", "resnet50", "inceptionv3", "efficientnet-b0", "vit_tiny_test"):
+        m = Classifier(name, 7)
+        head = m.encoder.heads.head if name.startswith("vit") else (m.encoder._fc if "efficientnet" in name else m.encoder.fc)
+        assert isinstance(head, MLPHead)
+        dims = [(l.in_features, l.out_features) for l in head if hasattr(l, "in_features")]
+        assert [d[1] for d in dims] == [128, 64, 32, 7]
+        assert [i for i, l in enumerate(head) if hasattr(l, "in_features")] == [0, 2, 4, 6]
+    m = Classifier("inceptionv3", 7)
+    assert m.encoder.AuxLogits.fc.out_features == 7 and m.returns_aux
+    assert "encoder.fc.0.weight" in m.state_dict()
+
+
+def test_classifier_rejects_unknown_and_empty():
+    with pytest.raises(ValueError):
+        Classifier("alexnet", 7)
+    with pytest.raises(ValueError):
+        Classifier("resnet18", 0)
+    assert "resnet101" in BACKBONES and "efficientnet-b3" in BACKBONES
+
+
+def test_convert_sync_batchnorm_marks_every_bn():
+    m = convert_sync_batchnorm(Classifier("resnet18", 3, small_input=True))
+    bns = [x for x in m.modules() if hasattr(x, "running_mean")]
+    assert bns and all(isinstance(b, SyncBatchNorm) and b.sync_group is True for b in bns)
+    # single process: falls back to local statistics and still trains
+    out = m(torch.randn(2, 3, 32, 32))
+    out.sum().backward()
