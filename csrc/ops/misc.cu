@@ -631,3 +631,70 @@ extern "C" int picd_cast_f32_bf16(const float* in, void* out, long long n, cudaS
     PICD_LAUNCH_CHECK();
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of picd_small_linear_bwd.
+//
+// Who needs it: a host that is not allowed to create device memory at the point where it runs the classifier-head
+// backward -- for example a serving or training process that handed its whole memory budget to its own pool at
+// start-up and forbids cudaMalloc afterwards, a plug-in living under another framework's allocator, or a
+// latency-critical loop that cannot afford cudaMalloc's device-wide synchronisation.  Such a caller still owns the
+// inputs and outputs, but it has nowhere to get the `dpre` scratch (M*N floats) the ordinary entry point asks for.
+//
+// Here that scratch is a fixed array compiled into the library image.  Consequences a user must know:
+//   * capacity: M*N <= PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS (262144 floats = 1 MiB); larger problems are rejected
+//     with an error, nothing is launched.  Every GPU that loads the library carries this 1 MiB until exit.
+//   * the array is shared by ALL calls on a device and keeps whatever the previous call left in it.  Nothing in it
+//     has to start at zero: the first kernel of each call overwrites the M*N floats it uses before anything reads
+//     them.  Two calls whose kernels overlap on the GPU (different streams without an ordering between them) race
+//     on the array; issue them on one stream or order them with events.
+//   * the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+//     current).  That first call should therefore happen before any stream capture begins.
+//   * no cudaMalloc / cudaFree / allocating library routine is called here, on any call.
+// Results are bit-identical to picd_small_linear_bwd given the same inputs (same kernels, same launch shapes).
+#include <mutex>
+
+#define PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS (1 << 18)
+
+static __device__ __align__(256) float g_small_linear_noalloc_scratch[PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS];
+
+// In host code the array's name is only a handle for the runtime, not a device address; the address a kernel can use
+// has to be asked for, once per device, while that device is current.
+static float* g_noalloc_scratch_addr[64] = {nullptr};
+static std::mutex g_noalloc_mutex;
+
+static int small_linear_noalloc_scratch(float** out) {
+    int dev = -1;
+    PICD_CUDA(cudaGetDevice(&dev));
+    PICD_REQUIRE(dev >= 0 && dev < 64, "small_linear_bwd_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_scratch_addr[dev] == nullptr) {
+        void* p = nullptr;
+        PICD_CUDA(cudaGetSymbolAddress(&p, g_small_linear_noalloc_scratch));
+        PICD_REQUIRE(p != nullptr, "small_linear_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_scratch_addr[dev] = static_cast<float*>(p);
+    }
+    *out = g_noalloc_scratch_addr[dev];
+    return 0;
+}
+
+extern "C" int picd_small_linear_noalloc_max_floats() { return PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS; }
+
+extern "C" int picd_small_linear_bwd_noalloc(const void* dy, const void* y, const void* x, const float* w, void* dx,
+                                             float* dw, float* db, int M, int N, int K, int act, int dy_fp32,
+                                             int y_fp32, cudaStream_t st) {
+    PICD_REQUIRE(M > 0 && N > 0 && K > 0, "small_linear_bwd_noalloc: M, N, K must be positive (got %d, %d, %d)", M, N, K);
+    const long long need = static_cast<long long>(M) * N;
+    PICD_REQUIRE(need <= PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS,
+                 "small_linear_bwd_noalloc: M*N = %lld floats of scratch exceed the built-in %d; use "
+                 "picd_small_linear_bwd with caller-provided scratch", need, PICD_SMALL_LINEAR_NOALLOC_MAX_FLOATS);
+    float* scratch = nullptr;
+    if (int rc = small_linear_noalloc_scratch(&scratch)) return rc;
+    small_linear_dpre_kernel<<<(M * N + 255) / 256, 256, 0, st>>>(dy, y, scratch, M * N, act, dy_fp32, y_fp32);
+    if (dx != nullptr)
+        small_linear_dx_kernel<<<(M * K + 255) / 256, 256, 0, st>>>(scratch, w, static_cast<bf16*>(dx), M, N, K);
+    const int work = N * K > N ? N * K : N;
+    small_linear_dw_kernel<<<(work + 255) / 256, 256, 0, st>>>(scratch, static_cast<const bf16*>(x), dw, db, M, N, K);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}

@@ -89,6 +89,19 @@ int picd_small_linear_fwd(const void* x, const float* w, const float* bias, void
 int picd_small_linear_bwd(const void* dy, const void* y, const void* x, const float* w, float* dpre_scratch, void* dx,
                           float* dw, float* db, int M, int N, int K, int act, int dy_fp32, int y_fp32,
                           cudaStream_t stream);
+/* No counterpart in the reference (it has no native code and lets PyTorch allocate everything).  Same computation
+ * and results as picd_small_linear_bwd, for hosts that may not allocate device memory when they call it (a fixed
+ * memory budget handed out at start-up, a plug-in under a foreign allocator, a loop that cannot take cudaMalloc's
+ * device-wide synchronisation): the M*N-float `dpre` scratch lives in a 1 MiB array built into the library, so
+ * M*N must be <= picd_small_linear_noalloc_max_floats() (262144) or the call fails without launching.  The array
+ * is shared by all calls on a device and keeps the previous call's contents (none of it needs to be zero: each
+ * call overwrites what it uses first); calls whose kernels overlap on the GPU race on it -- keep them on one stream
+ * or order them.  The first call on each device resolves the array's device address and should come before any
+ * stream capture.  The call itself never allocates or frees. */
+int picd_small_linear_bwd_noalloc(const void* dy, const void* y, const void* x, const float* w, void* dx, float* dw,
+                                  float* db, int M, int N, int K, int act, int dy_fp32, int y_fp32,
+                                  cudaStream_t stream);
+int picd_small_linear_noalloc_max_floats(void);
 int picd_pack_s2d(const void* x, void* out, int N, int H, int W, int C, int Hp, int Wp, int Cp, int s, int pad_h,
                   int pad_w, int src_u8, cudaStream_t stream);
 /* on-device synthetic batches + ImageNet normalisation (replaces dp/loader.py:39-91 and the H2D copy) */
