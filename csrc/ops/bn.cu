@@ -78,6 +78,8 @@ __device__ __forceinline__ void block_column_reduce(float (&a)[8], float (&b)[8]
 }
 
 // ---------------------------------------------------------------------------------------------- stats
+constexpr int ROW_UNROLL = 4;   // rows in flight per thread (memory-level parallelism of the streaming kernels)
+
 __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ stats,
                                                        long long P, int C, int tx_count, int ty_count,
                                                        int rows_per_block) {
@@ -91,13 +93,20 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
         const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
         long long r1 = r0 + rows_per_block;
         if (r1 > P) r1 = P;
-        for (long long r = r0 + ty; r < r1; r += ty_count) {
-            Vec8 v;
-            v.load(x + r * C + cv * 8);
-            float f[8];
-            v.unpack(f);
+        for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * ROW_UNROLL) {
+            Vec8 v[ROW_UNROLL];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
+            for (int u = 0; u < ROW_UNROLL; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                if (rr < r1) v[u].load(x + rr * C + cv * 8); else v[u].raw = make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < ROW_UNROLL; ++u) {
+                float f[8];
+                v[u].unpack(f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
+            }
         }
     }
     block_column_reduce(s, q, tx, ty, tx_count, ty_count, cv, vecs, stats, stats + C);
@@ -140,39 +149,60 @@ __global__ void bn_eval_coeffs_kernel(const float* __restrict__ gamma, const flo
 }
 
 // ---------------------------------------------------------------------------------------------- apply
-__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
+// All streaming kernels below share one thread mapping: a thread owns ONE vector of 8 channels (its per-channel
+// coefficients live in registers for the whole kernel) and walks over rows, ROW_UNROLL rows in flight.  Consecutive
+// threads read consecutive 16-byte vectors, so a warp touches whole 128-byte lines.
+__device__ __forceinline__ void load8f(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+
+__global__ void __launch_bounds__(256, 2) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
                                                        const float* __restrict__ scale,
                                                        const float* __restrict__ shift,
                                                        const __nv_bfloat16* __restrict__ residual, int act,
-                                                       __nv_bfloat16* __restrict__ out, long long total_vecs, int C) {
+                                                       __nv_bfloat16* __restrict__ out, long long P, int C,
+                                                       int tx_count, int ty_count, int rows_per_block) {
     const int vecs = C >> 3;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
-        const int c0 = static_cast<int>(i % vecs) * 8;
-        Vec8 v;
-        v.load(y + i * 8);
-        float f[8];
-        v.unpack(f);
-        const float4 sc0 = *reinterpret_cast<const float4*>(scale + c0), sc1 = *reinterpret_cast<const float4*>(scale + c0 + 4);
-        const float4 sh0 = *reinterpret_cast<const float4*>(shift + c0), sh1 = *reinterpret_cast<const float4*>(shift + c0 + 4);
-        const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
-        const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
-        float r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (residual != nullptr) {
-            Vec8 rv;
-            rv.load(residual + i * 8);
-            rv.unpack(r);
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    if (ty >= ty_count || cv >= vecs) return;
+    float sc[8], sh[8];
+    load8f(scale + cv * 8, sc);
+    load8f(shift + cv * 8, sh);
+    const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+    long long r1 = r0 + rows_per_block;
+    if (r1 > P) r1 = P;
+    for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * ROW_UNROLL) {
+        Vec8 v[ROW_UNROLL], rv[ROW_UNROLL];
+#pragma unroll
+        for (int u = 0; u < ROW_UNROLL; ++u) {
+            const long long rr = r + static_cast<long long>(u) * ty_count;
+            if (rr < r1) {
+                v[u].load(y + rr * C + cv * 8);
+                if (residual != nullptr) rv[u].load(residual + rr * C + cv * 8);
+            }
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = apply_act(fmaf(f[k], sc[k], sh[k]) + r[k], act);
-        v.pack(f);
-        v.store(out + i * 8);
+        for (int u = 0; u < ROW_UNROLL; ++u) {
+            const long long rr = r + static_cast<long long>(u) * ty_count;
+            if (rr < r1) {
+                float f[8], rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                v[u].unpack(f);
+                if (residual != nullptr) rv[u].unpack(rs);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[k] = apply_act(fmaf(f[k], sc[k], sh[k]) + rs[k], act);
+                Vec8 o;
+                o.pack(f);
+                o.store(out + rr * C + cv * 8);
+            }
+        }
     }
 }
 
 // ---------------------------------------------------------------------------------------------- backward
-// g = dz * act'(pre-activation).  For ReLU the mask is read from the saved output z (z > 0), which is also right
-// when a residual was added before the activation; other activations recompute u = y*scale+shift.
+// g = dz * act'(pre-activation).  For ReLU the mask is read from the saved output z (z > 0) when a residual was
+// added before the activation, otherwise it is recomputed from y*scale+shift (one tensor less to read).
 __device__ __forceinline__ void masked_grad(float (&g)[8], const float (&yv)[8], const float (&zv)[8], bool has_z,
                                             const float (&sc)[8], const float (&sh)[8], int act) {
     if (act == ACT_NONE) return;
@@ -187,12 +217,7 @@ __device__ __forceinline__ void masked_grad(float (&g)[8], const float (&yv)[8],
     }
 }
 
-__device__ __forceinline__ void load8f(const float* p, float (&o)[8]) {
-    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
-}
-
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz,
+__global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz,
                                                             const __nv_bfloat16* __restrict__ y,
                                                             const __nv_bfloat16* __restrict__ z,
                                                             const float* __restrict__ scale,
@@ -210,108 +235,134 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
     if (ty < ty_count && cv < vecs) {
         float sc[8], sh[8], mu[8], is[8];
         load8f(scale + cv * 8, sc); load8f(shift + cv * 8, sh); load8f(mean + cv * 8, mu); load8f(invstd + cv * 8, is);
+        const bool use_z = (z != nullptr) && (act == ACT_RELU);
         const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
         long long r1 = r0 + rows_per_block;
         if (r1 > P) r1 = P;
-        for (long long r = r0 + ty; r < r1; r += ty_count) {
-            const long long off = r * C + cv * 8;
-            Vec8 vd, vy, vz;
-            float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            vd.load(dz + off); vd.unpack(g);
-            vy.load(y + off); vy.unpack(yv);
-            if (z != nullptr && act == ACT_RELU) { vz.load(z + off); vz.unpack(zv); }
-            masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
+        for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * ROW_UNROLL) {
+            Vec8 vd[ROW_UNROLL], vy[ROW_UNROLL], vz[ROW_UNROLL];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                sg[i] += g[i];
-                sgx[i] += g[i] * (yv[i] - mu[i]) * is[i];
+            for (int u = 0; u < ROW_UNROLL; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                if (rr < r1) {
+                    const long long off = rr * C + cv * 8;
+                    vd[u].load(dz + off);
+                    vy[u].load(y + off);
+                    if (use_z) vz[u].load(z + off);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < ROW_UNROLL; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                if (rr < r1) {
+                    float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                    vd[u].unpack(g);
+                    vy[u].unpack(yv);
+                    if (use_z) vz[u].unpack(zv);
+                    masked_grad(g, yv, zv, use_z, sc, sh, act);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        sg[i] += g[i];
+                        sgx[i] += g[i] * (yv[i] - mu[i]) * is[i];
+                    }
+                }
             }
         }
     }
     block_column_reduce(sg, sgx, tx, ty, tx_count, ty_count, cv, vecs, sums, sums + C);
 }
 
-// dy = gamma*invstd * (g - mean(g) - xhat * mean(g*xhat));  dres = g (gradient of the residual branch).
-// Block 0 also accumulates the parameter gradients dgamma += sum(g*xhat), dbeta += sum(g) from `param_sums`
-// (the LOCAL sums -- with SyncBN `sums` holds the cross-replica totals, `param_sums` this replica's share).
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
+// dy = gamma*invstd * (g - mean(g) - xhat * mean(g*xhat)) = A*g + B*y + Cc per channel;  dres = g (gradient of the
+// residual branch).  Block (0,0) also accumulates the parameter gradients dgamma += sum(g*xhat), dbeta += sum(g) from
+// `param_sums` (the LOCAL sums -- with SyncBN `sums` holds the cross-replica totals, `param_sums` this replica's).
+// `eval_mode`: the statistics were frozen (running stats), so dy = scale * g.
+__global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ z,
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ invstd, int act, const float* __restrict__ sums, float inv_count,
     const float* __restrict__ param_sums, float* dgamma, float* dbeta, __nv_bfloat16* __restrict__ dy,
-    __nv_bfloat16* __restrict__ dres, long long total_vecs, int C) {
+    __nv_bfloat16* __restrict__ dres, long long P, int C, int tx_count, int ty_count, int rows_per_block,
+    int eval_mode) {
     const int vecs = C >> 3;
-    if (blockIdx.x == 0 && dgamma != nullptr) {
+    if (blockIdx.x == 0 && blockIdx.y == 0 && dgamma != nullptr) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             dbeta[c] += param_sums[c];
             dgamma[c] += param_sums[C + c];
         }
     }
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
-        const int c0 = static_cast<int>(i % vecs) * 8;
-        float sc[8], sh[8], mu[8], is[8], s1[8], s2[8];
-        load8f(scale + c0, sc); load8f(shift + c0, sh); load8f(mean + c0, mu); load8f(invstd + c0, is);
-        load8f(sums + c0, s1); load8f(sums + C + c0, s2);
-        Vec8 vd, vy, vz;
-        float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        vd.load(dz + i * 8); vd.unpack(g);
-        vy.load(y + i * 8); vy.unpack(yv);
-        if (z != nullptr && act == ACT_RELU) { vz.load(z + i * 8); vz.unpack(zv); }
-        masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
-        if (dres != nullptr) {
-            Vec8 o;
-            o.pack(g);
-            o.store(dres + i * 8);
-        }
-        float d[8];
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    if (ty >= ty_count || cv >= vecs) return;
+    float sc[8], sh[8], cb[8], cc[8];
+    load8f(scale + cv * 8, sc);
+    load8f(shift + cv * 8, sh);
+    if (!eval_mode) {
+        float mu[8], is[8], s1[8], s2[8];
+        load8f(mean + cv * 8, mu); load8f(invstd + cv * 8, is);
+        load8f(sums + cv * 8, s1); load8f(sums + C + cv * 8, s2);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float xhat = (yv[k] - mu[k]) * is[k];
-            d[k] = sc[k] * (g[k] - s1[k] * inv_count - xhat * s2[k] * inv_count);
+            cb[k] = -sc[k] * is[k] * s2[k] * inv_count;
+            cc[k] = -sc[k] * s1[k] * inv_count - cb[k] * mu[k];
         }
-        Vec8 o;
-        o.pack(d);
-        o.store(dy + i * 8);
-    }
-}
-
-// Backward through a frozen (eval / running-stats) BN: dy = scale * g.
-__global__ void __launch_bounds__(256) bn_bwd_eval_kernel(const __nv_bfloat16* __restrict__ dz,
-                                                          const __nv_bfloat16* __restrict__ y,
-                                                          const __nv_bfloat16* __restrict__ z,
-                                                          const float* __restrict__ scale,
-                                                          const float* __restrict__ shift, int act,
-                                                          __nv_bfloat16* __restrict__ dy,
-                                                          __nv_bfloat16* __restrict__ dres, long long total_vecs,
-                                                          int C) {
-    const int vecs = C >> 3;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
-        const int c0 = static_cast<int>(i % vecs) * 8;
-        float sc[8], sh[8];
-        load8f(scale + c0, sc); load8f(shift + c0, sh);
-        Vec8 vd, vy, vz;
-        float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        vd.load(dz + i * 8); vd.unpack(g);
-        vy.load(y + i * 8); vy.unpack(yv);
-        if (z != nullptr && act == ACT_RELU) { vz.load(z + i * 8); vz.unpack(zv); }
-        masked_grad(g, yv, zv, z != nullptr, sc, sh, act);
-        if (dres != nullptr) { Vec8 o; o.pack(g); o.store(dres + i * 8); }
+    } else {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] *= sc[k];
-        Vec8 o;
-        o.pack(g);
-        o.store(dy + i * 8);
+        for (int k = 0; k < 8; ++k) { cb[k] = 0.f; cc[k] = 0.f; }
+    }
+    const bool use_z = (z != nullptr) && (act == ACT_RELU);
+    const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+    long long r1 = r0 + rows_per_block;
+    if (r1 > P) r1 = P;
+    for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * ROW_UNROLL) {
+        Vec8 vd[ROW_UNROLL], vy[ROW_UNROLL], vz[ROW_UNROLL];
+#pragma unroll
+        for (int u = 0; u < ROW_UNROLL; ++u) {
+            const long long rr = r + static_cast<long long>(u) * ty_count;
+            if (rr < r1) {
+                const long long off = rr * C + cv * 8;
+                vd[u].load(dz + off);
+                vy[u].load(y + off);
+                if (use_z) vz[u].load(z + off);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < ROW_UNROLL; ++u) {
+            const long long rr = r + static_cast<long long>(u) * ty_count;
+            if (rr < r1) {
+                const long long off = rr * C + cv * 8;
+                float g[8], yv[8], zv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                vd[u].unpack(g);
+                vy[u].unpack(yv);
+                if (use_z) vz[u].unpack(zv);
+                masked_grad(g, yv, zv, use_z, sc, sh, act);
+                if (dres != nullptr) {
+                    Vec8 o;
+                    o.pack(g);
+                    o.store(dres + off);
+                }
+                float d[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] = fmaf(sc[k], g[k], fmaf(cb[k], yv[k], cc[k]));
+                Vec8 o;
+                o.pack(d);
+                o.store(dy + off);
+            }
+        }
     }
 }
 
-static int elementwise_grid(long long total_vecs) {
-    long long blocks = (total_vecs + 255) / 256;
-    const long long cap = 8LL * num_sms();
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return static_cast<int>(blocks);
+// grid/block shape for the streaming (non-reducing) kernels: more blocks than the reductions, no smem needed
+static ReduceShape stream_shape(long long P, int C) {
+    ReduceShape s = reduce_shape(P, C);
+    const int target_blocks = 8 * num_sms();
+    long long gy = target_blocks / s.grid_x;
+    if (gy < 1) gy = 1;
+    long long rpb = (P + gy - 1) / gy;
+    const long long min_rows = static_cast<long long>(ROW_UNROLL) * s.ty_count;
+    if (rpb < min_rows) rpb = min_rows;
+    s.rows_per_block = static_cast<int>(rpb);
+    s.grid_y = static_cast<int>((P + rpb - 1) / rpb);
+    return s;
 }
 
 }  // namespace picd
@@ -349,10 +400,10 @@ extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const 
 extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
                              void* out, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_apply: C=%d must be a multiple of 8", C);
-    const long long total_vecs = P * (C / 8);
-    bn_apply_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+    const ReduceShape s = stream_shape(P, C);
+    bn_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,
-        static_cast<__nv_bfloat16*>(out), total_vecs, C);
+        static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -376,11 +427,12 @@ extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, c
                                  const float* sums, float inv_count, const float* param_sums, float* dgamma,
                                  float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
-    const long long total_vecs = P * (C / 8);
-    bn_bwd_apply_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+    const ReduceShape s = stream_shape(P, C);
+    bn_bwd_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
-        dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), total_vecs, C);
+        dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
+        s.rows_per_block, 0);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -388,11 +440,12 @@ extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, c
 extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
                                 int act, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_eval: C=%d must be a multiple of 8", C);
-    const long long total_vecs = P * (C / 8);
-    bn_bwd_eval_kernel<<<elementwise_grid(total_vecs), 256, 0, stream>>>(
+    const ReduceShape s = stream_shape(P, C);
+    bn_bwd_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
-        static_cast<const __nv_bfloat16*>(z), scale, shift, act, static_cast<__nv_bfloat16*>(dy),
-        static_cast<__nv_bfloat16*>(dres), total_vecs, C);
+        static_cast<const __nv_bfloat16*>(z), scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
+        nullptr, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
+        s.rows_per_block, 1);
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -82,6 +82,7 @@ __device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
 // =====================================================================================================
 //  conv / GEMM forward-style kernel: D[pixels, Cout] = sum_taps A_tap[pixels, Cin] * B_tap[Cout, Cin]^T
 // =====================================================================================================
+template <bool kBiasAct>
 __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align_smem(smem_raw);
@@ -196,6 +197,8 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         }
     } else {
         // ------------------------------------------------------------------ epilogue (4 warps)
+        // Kept deliberately compact (explicit shared-space accesses, no per-element branches): an earlier version
+        // unrolled into ~4800 SASS instructions and stalled on instruction fetch (profiles/ncu_fprop_64_256_v1.md).
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
         const int row = q * 32 + lane;           // accumulator row == pixel index inside the tile
         const int tid_e = threadIdx.x - 64;      // 0..127
@@ -211,39 +214,49 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         const int iw = row & (bw - 1);
         const int ih = (row >> p.bw_log2) & (bh - 1);
         const int in_ = row >> (p.bw_log2 + p.bh_log2);
+        const uint32_t sOut_u32 = smem_u32(sOut);
+        const uint32_t row_base = sOut_u32 + row * 128;
+        const uint32_t row_xor = static_cast<uint32_t>(row & 7) << 4;
+        // statistics read-back: this thread's column pair, swizzled exactly like the writes above
+        const uint32_t stat_base = sOut_u32 + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
+        const uint32_t stat_chunk = static_cast<uint32_t>((my_cp & 31) >> 2);
         for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
             const int tw = m % p.tiles_w;
             const int th = (m / p.tiles_w) % p.tiles_h;
             const int tn = m / (p.tiles_w * p.tiles_h);
             const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
             const bool valid = (w0 + iw < p.W) && (h0 + ih < p.H) && (n0 + in_ < p.N);
+            const uint32_t vmask = valid ? 0xffffffffu : 0u;     // rows hanging over the tensor edge are stored as 0
             mbar_wait(&bars->tfull[acc], accphase);
             tc_fence_after();
             if (tid_e == 0) tma_store_wait_read();        // previous tile's TMA store has drained the staging tile
             named_barrier_sync(1, 128);
             const uint32_t t_row = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
             for (int g = 0; g < BN / 32; ++g) {
                 uint32_t v[32];
                 tmem_ld_32x32(t_row + g * 32, v);
                 tmem_ld_wait();
-                const int col0 = n_tile * BN + g * 32;
-                uint32_t packed[16];
+                if (kBiasAct) {
+                    const int col0 = n_tile * BN + g * 32;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
-                    if (p.bias != nullptr) {
-                        a += (col0 + 2 * i < p.Cout) ? __ldg(p.bias + col0 + 2 * i) : 0.f;
-                        b += (col0 + 2 * i + 1 < p.Cout) ? __ldg(p.bias + col0 + 2 * i + 1) : 0.f;
+                    for (int i = 0; i < 32; ++i) {
+                        float a = __uint_as_float(v[i]);
+                        if (p.bias != nullptr && col0 + i < p.Cout) a += __ldg(p.bias + col0 + i);
+                        v[i] = __float_as_uint(apply_act(a, p.act));
                     }
-                    if (p.act != ACT_NONE) { a = apply_act(a, p.act); b = apply_act(b, p.act); }
-                    packed[i] = valid ? pack_bf16x2(a, b) : 0u;
                 }
-                uint8_t* base = sOut + (g >> 1) * 16384 + row * 128;
-                const int chunk0 = (g & 1) * 4;
+                const uint32_t dst = row_base + (g >> 1) * 16384;
+                const uint32_t chunk0 = static_cast<uint32_t>(g & 1) * 64;
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    uint4 val = make_uint4(packed[4 * c], packed[4 * c + 1], packed[4 * c + 2], packed[4 * c + 3]);
-                    *reinterpret_cast<uint4*>(base + (((chunk0 + c) ^ (row & 7)) << 4)) = val;
+                    const uint32_t a0 = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1])) & vmask;
+                    const uint32_t a1 = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])) & vmask;
+                    const uint32_t a2 = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])) & vmask;
+                    const uint32_t a3 = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])) & vmask;
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((chunk0 + c * 16) ^ row_xor)),
+                                 "r"(a0), "r"(a1), "r"(a2), "r"(a3)
+                                 : "memory");
                 }
             }
             tc_fence_before();
@@ -260,16 +273,18 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             }
             if (stat_thread) {
                 // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read)
-                const uint8_t* colbase = sOut + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
-                const int chunk = (my_cp & 31) >> 2;
                 const int r0 = my_rg * rows_per_rg;
+                float t0 = 0.f, t1 = 0.f, u0 = 0.f, u1 = 0.f;     // second accumulator chain for ILP
 #pragma unroll 4
-                for (int r = r0; r < r0 + rows_per_rg; ++r) {
-                    const uint32_t wv = *reinterpret_cast<const uint32_t*>(colbase + r * 128 + ((chunk ^ (r & 7)) << 4));
-                    const float2 f = unpack_bf16x2(wv);
-                    s0 += f.x; q0 += f.x * f.x;
-                    s1 += f.y; q1 += f.y * f.y;
+                for (int r = r0; r < r0 + rows_per_rg; r += 2) {
+                    uint32_t wa, wb;
+                    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wa) : "r"(stat_base + r * 128 + ((stat_chunk ^ (r & 7)) << 4)));
+                    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wb) : "r"(stat_base + (r + 1) * 128 + ((stat_chunk ^ ((r + 1) & 7)) << 4)));
+                    const float2 fa = unpack_bf16x2(wa), fb = unpack_bf16x2(wb);
+                    s0 += fa.x; q0 = fmaf(fa.x, fa.x, q0); s1 += fa.y; q1 = fmaf(fa.y, fa.y, q1);
+                    t0 += fb.x; u0 = fmaf(fb.x, fb.x, u0); t1 += fb.y; u1 = fmaf(fb.y, fb.y, u1);
                 }
+                s0 += t0; s1 += t1; q0 += u0; q1 += u1;
             }
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
@@ -484,7 +499,8 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     p.stages = stages;
     static bool attr_set = false;
     if (!attr_set) {
-        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
         attr_set = true;
     }
     const int sms = num_sms();
@@ -492,7 +508,10 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     int grid = static_cast<int>(std::min<long long>(total, sms));
     grid = std::max(p.numN, grid / p.numN * p.numN);
     // request the whole smem so that exactly one CTA (and one 512-column TMEM allocation) lives on an SM
-    conv_gemm_kernel<<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+    if (p.bias != nullptr || p.act != ACT_NONE)
+        conv_gemm_kernel<true><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+    else
+        conv_gemm_kernel<false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
     PICD_LAUNCH_CHECK();
     return 0;
 }
