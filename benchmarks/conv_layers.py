@@ -71,7 +71,7 @@ for (H, W, Cin, Cout, R, S, stride, pad), count in sorted(shapes.items(), key=la
     dy = torch.randn_like(y)
     dx = torch.empty_like(x)
     dw = torch.zeros(Cout, Cin, R, S, device=dev).contiguous(memory_format=torch.channels_last)
-    stats = torch.zeros(2 * Cout, device=dev)
+    stats = native.stat_buffer(Cout, dev)
     geo = (N, H, W, Cin, Cout, R, S, stride, pad[0], pad[1], OH, OW)
     tf = timeit(lambda: native.call("picd_conv_fprop", x, w, y, stats, None, 0, *geo))
     td = timeit(lambda: native.call("picd_conv_dgrad", dy, w, dx, *geo))

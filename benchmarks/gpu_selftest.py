@@ -77,7 +77,10 @@ def group_basic():
 
     # BN family
     for (N, C, H, W, res, act) in [(8, 64, 14, 14, False, "relu"), (4, 256, 7, 7, True, "relu"), (4, 96, 9, 9, False, "none"),
-                                   (2, 2048, 7, 7, True, "relu"), (4, 40, 6, 6, False, "swish")]:
+                                   (2, 2048, 7, 7, True, "relu"), (4, 40, 6, 6, False, "swish"),
+                                   # >= 4 MB: these take the TMA-streamed kernels (bn_stream.cu)
+                                   (32, 64, 56, 56, False, "relu"), (16, 256, 28, 28, True, "relu"),
+                                   (64, 128, 16, 17, False, "none"), (24, 512, 14, 14, True, "relu")]:
         x = torch.randn(N, C, H, W, device=dev).mul_(1.5).add_(0.3).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         r = torch.randn(N, C, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) if res else None
         gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_()
@@ -279,8 +282,9 @@ def group_conv():
             ok &= check(tag + ".dgrad", xn.grad, xr.grad, 2e-2, g)
         # fused statistics epilogue
         if not first:
-            stats = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
-            y2, _ = native._conv_forward(x, w.detach(), stride, pad, stats, None, None)
+            stats_r = native.stat_buffer(Cout, dev)
+            y2, _ = native._conv_forward(x, w.detach(), stride, pad, stats_r, None, None)
+            stats = stats_r.view(-1, 2 * Cout).sum(0)
             yf = y2.float()
             ok &= check(tag + ".stats_sum", stats[:Cout], yf.sum((0, 2, 3)), 1e-2, g)
             ok &= check(tag + ".stats_sumsq", stats[Cout:], (yf * yf).sum((0, 2, 3)), 1e-2, g)

@@ -26,7 +26,7 @@ y = torch.empty(N, Cout, OH, OW, device=dev, dtype=torch.bfloat16).contiguous(me
 dy = torch.randn_like(y)
 dx = torch.empty_like(x)
 dw = torch.zeros(Cout, Cin, R, S, device=dev).contiguous(memory_format=torch.channels_last)
-stats = None if a.no_stats else torch.zeros(2 * Cout, device=dev)
+stats = None if a.no_stats else native.stat_buffer(Cout, dev)
 geo = (N, H, W, Cin, Cout, R, S, stride, pad, pad, OH, OW)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.iters + 1)]
 ev[0].record()

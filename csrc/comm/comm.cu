@@ -164,9 +164,14 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
 // ---- small collectives over the exchange slots ----------------------------------------------------------
 // Publish `n` floats, wait for all peers, return the rank-ordered sum.  Single block.
 __device__ __forceinline__ void xchg_publish_and_wait(const PeerTable& pt, int rank, int W, const float* in, int n,
-                                                      long long slot_off, int flag_slot, unsigned epoch) {
+                                                      int in_replicas, long long slot_off, int flag_slot,
+                                                      unsigned epoch) {
     float* mine = pt.xchg[rank] + slot_off;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) mine[i] = in[i];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        float acc = 0.f;                                   // fold the per-CTA-group replicas while publishing
+        for (int r = 0; r < in_replicas; ++r) acc += in[static_cast<size_t>(r) * n + i];
+        mine[i] = acc;
+    }
     __syncthreads();
     signal_peers(pt, flag_slot, rank, W, epoch);
     wait_flags(pt.flags[rank], flag_slot, W, epoch);
@@ -182,15 +187,15 @@ __device__ __forceinline__ float xchg_sum(const PeerTable& pt, int W, long long 
 }
 
 __global__ void __launch_bounds__(1024) p2p_allreduce_small_kernel(PeerTable pt, int rank, int W, const float* in,
-                                                                   float* out, int n, long long slot_off,
-                                                                   int flag_slot, unsigned epoch) {
-    xchg_publish_and_wait(pt, rank, W, in, n, slot_off, flag_slot, epoch);
+                                                                   int in_replicas, float* out, int n,
+                                                                   long long slot_off, int flag_slot, unsigned epoch) {
+    xchg_publish_and_wait(pt, rank, W, in, n, in_replicas, slot_off, flag_slot, epoch);
     for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = xchg_sum(pt, W, slot_off, i);
 }
 
 // sums = local [sum(C), sumsq(C)], count = local element count.  Cross-replica merge + finalize in one launch.
 __global__ void __launch_bounds__(1024) bn_finalize_sync_kernel(PeerTable pt, int rank, int W, const float* sums,
-                                                                float count, const float* gamma, const float* beta,
+                                                                int replicas, float count, const float* gamma, const float* beta,
                                                                 float* running_mean, float* running_var,
                                                                 float momentum, float eps, float* scale, float* shift,
                                                                 float* mean_out, float* invstd_out, float* total_count,
@@ -198,7 +203,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_sync_kernel(PeerTable pt, in
                                                                 unsigned epoch) {
     float* mine = pt.xchg[rank] + slot_off;
     if (threadIdx.x == 0) mine[2 * C] = count;
-    xchg_publish_and_wait(pt, rank, W, sums, 2 * C, slot_off, flag_slot, epoch);
+    xchg_publish_and_wait(pt, rank, W, sums, 2 * C, replicas, slot_off, flag_slot, epoch);
     const float n = xchg_sum(pt, W, slot_off, 2 * C);
     if (threadIdx.x == 0) total_count[0] = n;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -311,20 +316,21 @@ extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long
     return 0;
 }
 
-extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, float* out, int n, long long slot_off, int flag_slot,
-                                        unsigned epoch, cudaStream_t stream) {
+extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n,
+                                        long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
-    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, out, n, slot_off, flag_slot, epoch);
+    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, in_replicas, out, n, slot_off, flag_slot,
+                                                       epoch);
     PICD_LAUNCH_CHECK();
     return 0;
 }
 
-extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, float count, const float* gamma, const float* beta,
+extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
                                      float* running_mean, float* running_var, float momentum, float eps, float* scale,
                                      float* shift, float* mean, float* invstd, float* total_count, int C,
                                      long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
-    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, count, gamma, beta, running_mean,
+    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, replicas, count, gamma, beta, running_mean,
                                                     running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
                                                     slot_off, flag_slot, epoch);
     PICD_LAUNCH_CHECK();

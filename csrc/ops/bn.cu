@@ -11,6 +11,8 @@
 // All kernels are bandwidth-bound: 16-byte vector accesses, grids sized to a few waves of 148 SMs.
 #include "../common/picd_common.cuh"
 
+#include <cstdlib>
+
 namespace picd {
 
 struct Vec8 {
@@ -109,21 +111,28 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
             }
         }
     }
-    block_column_reduce(s, q, tx, ty, tx_count, ty_count, cv, vecs, stats, stats + C);
+    float* rep = stats + static_cast<size_t>(blockIdx.y % STAT_REPLICAS) * 2 * C;
+    block_column_reduce(s, q, tx, ty, tx_count, ty_count, cv, vecs, rep, rep + C);
 }
 
 // ---------------------------------------------------------------------------------------------- finalize
 // sums = [sum(C), sumsq(C)] over `count` elements per channel.  Produces scale = gamma*invstd and
 // shift = beta - mean*scale for the fused apply, saves mean/invstd for backward and updates the running
 // statistics with the unbiased variance (torch semantics, torch/nn/modules/_functions.py:106-115).
-__global__ void bn_finalize_kernel(const float* __restrict__ sums, float count, const float* __restrict__ gamma,
+__device__ __forceinline__ float fold_replicas(const float* base, int idx, int stride, int replicas) {
+    float acc = 0.f;
+    for (int r = 0; r < replicas; ++r) acc += base[static_cast<size_t>(r) * stride + idx];
+    return acc;
+}
+
+__global__ void bn_finalize_kernel(const float* __restrict__ sums, int replicas, float count, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, float* running_mean, float* running_var,
                                    float momentum, float eps, float* scale, float* shift, float* mean_out,
                                    float* invstd_out, int C) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
-    const float mean = sums[c] / count;
-    float var = sums[C + c] / count - mean * mean;
+    const float mean = fold_replicas(sums, c, 2 * C, replicas) / count;
+    float var = fold_replicas(sums, C + c, 2 * C, replicas) / count - mean * mean;
     var = fmaxf(var, 0.f);
     const float invstd = rsqrtf(var + eps);
     const float sc = gamma[c] * invstd;
@@ -269,7 +278,8 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const __nv_bfloat
             }
         }
     }
-    block_column_reduce(sg, sgx, tx, ty, tx_count, ty_count, cv, vecs, sums, sums + C);
+    float* rep = sums + static_cast<size_t>(blockIdx.y % STAT_REPLICAS) * 2 * C;
+    block_column_reduce(sg, sgx, tx, ty, tx_count, ty_count, cv, vecs, rep, rep + C);
 }
 
 // dy = gamma*invstd * (g - mean(g) - xhat * mean(g*xhat)) = A*g + B*y + Cc per channel;  dres = g (gradient of the
@@ -282,12 +292,12 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(
     const float* __restrict__ invstd, int act, const float* __restrict__ sums, float inv_count,
     const float* __restrict__ param_sums, float* dgamma, float* dbeta, __nv_bfloat16* __restrict__ dy,
     __nv_bfloat16* __restrict__ dres, long long P, int C, int tx_count, int ty_count, int rows_per_block,
-    int eval_mode) {
+    int eval_mode, int sums_replicas, int param_replicas) {
     const int vecs = C >> 3;
     if (blockIdx.x == 0 && blockIdx.y == 0 && dgamma != nullptr) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
-            dbeta[c] += param_sums[c];
-            dgamma[c] += param_sums[C + c];
+            dbeta[c] += fold_replicas(param_sums, c, 2 * C, param_replicas);
+            dgamma[c] += fold_replicas(param_sums, C + c, 2 * C, param_replicas);
         }
     }
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
@@ -299,7 +309,11 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(
     if (!eval_mode) {
         float mu[8], is[8], s1[8], s2[8];
         load8f(mean + cv * 8, mu); load8f(invstd + cv * 8, is);
-        load8f(sums + cv * 8, s1); load8f(sums + C + cv * 8, s2);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] = fold_replicas(sums, cv * 8 + k, 2 * C, sums_replicas);
+            s2[k] = fold_replicas(sums, C + cv * 8 + k, 2 * C, sums_replicas);
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             cb[k] = -sc[k] * is[k] * s2[k] * inv_count;
@@ -365,6 +379,21 @@ static ReduceShape stream_shape(long long P, int C) {
     return s;
 }
 
+// TMA-streamed variants (bn_stream.cu); each returns -1 when the shape is not eligible.
+int bn_stream_apply(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
+                    long long P, int C, cudaStream_t stream);
+int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+                         const float* mean, const float* invstd, int act, float* sums, long long P, int C,
+                         cudaStream_t stream);
+int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+                        const float* mean, const float* invstd, int act, const float* sums, float inv_count,
+                        const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
+                        int eval_mode, cudaStream_t stream);
+static bool use_stream_kernels() {
+    static const bool on = [] { const char* e = getenv("PICD_BN_STREAM"); return e == nullptr || e[0] != '0'; }();
+    return on;
+}
+
 }  // namespace picd
 
 using namespace picd;
@@ -379,10 +408,13 @@ extern "C" int picd_bn_stats(const void* x, float* stats, long long P, int C, cu
     return 0;
 }
 
-extern "C" int picd_bn_finalize(const float* sums, float count, const float* gamma, const float* beta,
+extern "C" int picd_stat_replicas() { return STAT_REPLICAS; }
+
+// sums: `replicas` copies of [sum(C), sumsq(C)] (1 for an already folded buffer, STAT_REPLICAS straight from a kernel)
+extern "C" int picd_bn_finalize(const float* sums, int replicas, float count, const float* gamma, const float* beta,
                                 float* running_mean, float* running_var, float momentum, float eps, float* scale,
                                 float* shift, float* mean, float* invstd, int C, cudaStream_t stream) {
-    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums, count, gamma, beta, running_mean, running_var,
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums, replicas, count, gamma, beta, running_mean, running_var,
                                                             momentum, eps, scale, shift, mean, invstd, C);
     PICD_LAUNCH_CHECK();
     return 0;
@@ -400,6 +432,13 @@ extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const 
 extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
                              void* out, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_apply: C=%d must be a multiple of 8", C);
+    // The TMA-streamed forward apply measured SLOWER (2.5 TB/s) than this register-streaming kernel (4.8 TB/s) --
+    // one input tensor gives the ring too little work per handshake -- so it is opt-in (PICD_BN_STREAM_APPLY=1).
+    static const bool stream_apply = [] { const char* e = getenv("PICD_BN_STREAM_APPLY"); return e != nullptr && e[0] == '1'; }();
+    if (stream_apply && use_stream_kernels()) {
+        const int rc = bn_stream_apply(y, scale, shift, residual, act, out, P, C, stream);
+        if (rc >= 0) return rc;
+    }
     const ReduceShape s = stream_shape(P, C);
     bn_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,
@@ -412,6 +451,10 @@ extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, 
                                   const float* shift, const float* mean, const float* invstd, int act, float* sums,
                                   long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_reduce: C=%d must be a multiple of 8", C);
+    if (use_stream_kernels()) {
+        const int rc = bn_stream_bwd_reduce(dz, y, z, scale, shift, mean, invstd, act, sums, P, C, stream);
+        if (rc >= 0) return rc;
+    }
     const ReduceShape s = reduce_shape(P, C);
     const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
     bn_bwd_reduce_kernel<<<dim3(s.grid_x, s.grid_y), 256, smem, stream>>>(
@@ -422,17 +465,42 @@ extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, 
     return 0;
 }
 
+// In-place fold of `replicas` copies of n floats into copy 0.
+__global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float acc = buf[i];
+    for (int r = 1; r < replicas; ++r) acc += buf[static_cast<size_t>(r) * n + i];
+    buf[i] = acc;
+}
+
+// NOTE: folds `sums` / `param_sums` in place (copy 0 receives the totals) before the streaming kernel runs.
 extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale,
                                  const float* shift, const float* mean, const float* invstd, int act,
-                                 const float* sums, float inv_count, const float* param_sums, float* dgamma,
-                                 float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
+                                 const float* sums, int sums_replicas, float inv_count, const float* param_sums,
+                                 int param_replicas, float* dgamma, float* dbeta, void* dy, void* dres, long long P,
+                                 int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
+    if (param_sums != nullptr && param_sums != sums && param_replicas > 1) {
+        fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(param_sums), 2 * C, param_replicas);
+        param_replicas = 1;
+    }
+    if (sums_replicas > 1) {
+        fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(sums), 2 * C, sums_replicas);
+        if (param_sums == sums) param_replicas = 1;
+        sums_replicas = 1;
+    }
+    if (use_stream_kernels()) {
+        const int rc = bn_stream_bwd_apply(dz, y, z, scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
+                                           dbeta, dy, dres, P, C, 0, stream);
+        if (rc >= 0) return rc;
+    }
     const ReduceShape s = stream_shape(P, C);
     bn_bwd_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
         dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
-        s.rows_per_block, 0);
+        s.rows_per_block, 0, sums_replicas, param_replicas);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -440,12 +508,17 @@ extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, c
 extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
                                 int act, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_eval: C=%d must be a multiple of 8", C);
+    if (use_stream_kernels()) {
+        const int rc = bn_stream_bwd_apply(dz, y, z, scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
+                                           nullptr, dy, dres, P, C, 1, stream);
+        if (rc >= 0) return rc;
+    }
     const ReduceShape s = stream_shape(P, C);
     bn_bwd_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
         nullptr, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
-        s.rows_per_block, 1);
+        s.rows_per_block, 1, 1, 1);
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -23,6 +23,7 @@
 #include "../common/picd_common.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace picd {
@@ -51,7 +52,7 @@ struct ConvGemmParams {
     int bw_log2, bh_log2;
     int W, H, N;          // output extents (for masking over-hanging rows)
     int Cout;
-    float* stats;         // [2][Cout] running (sum, sumsq) accumulators or nullptr
+    float* stats;         // [STAT_REPLICAS][2][Cout] (sum, sumsq) accumulators or nullptr
     const float* bias;    // [Cout] or nullptr
     int act;
 };
@@ -65,6 +66,7 @@ struct WgradParams {
     int Cout, Cin, taps_total;
     int BN, numN, numM, ksplit, num_p_tiles, stages;
     int tiles_w, tiles_h, bw_log2, bh_log2;
+    int G, cin_blocks, ngroups;   // taps per CTA (their B tiles sit side by side along N), 64-channel blocks per tap
 };
 
 struct SmemBars {
@@ -291,8 +293,9 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         }
         if (stat_thread) {
             const int c = n_tile * BN + my_cp * 2;
-            if (c < p.Cout) { atomicAdd(p.stats + c, s0); atomicAdd(p.stats + p.Cout + c, q0); }
-            if (c + 1 < p.Cout) { atomicAdd(p.stats + c + 1, s1); atomicAdd(p.stats + p.Cout + c + 1, q1); }
+            float* st = p.stats + static_cast<size_t>((blockIdx.x / numN) % STAT_REPLICAS) * 2 * p.Cout;
+            if (c < p.Cout) { atomicAdd(st + c, s0); atomicAdd(st + p.Cout + c, q0); }
+            if (c + 1 < p.Cout) { atomicAdd(st + c + 1, s1); atomicAdd(st + p.Cout + c + 1, q1); }
         }
         if (tid_e == 0) tma_store_wait_all();
     }
@@ -340,12 +343,12 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
-    const int inner = p.ntaps * p.numM * p.numN;
+    const int inner = p.ngroups * p.numM * p.numN;
     const int split = blockIdx.x / inner;
     int rem = blockIdx.x % inner;
     const int nt = rem % p.numN; rem /= p.numN;
     const int mt = rem % p.numM; rem /= p.numM;
-    const Tap tp = p.taps[rem];
+    const int group = rem;                      // taps [group*G, group*G + G) share this CTA's dy tiles
     const int pt_begin = static_cast<int>((static_cast<long long>(p.num_p_tiles) * split) / p.ksplit);
     const int pt_end = static_cast<int>((static_cast<long long>(p.num_p_tiles) * (split + 1)) / p.ksplit);
     const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
@@ -358,6 +361,19 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
             const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
             int ca1 = mt * TILE_M + 64;
             if (ca1 >= p.Cout) ca1 = mt * TILE_M;       // duplicate rows instead of a fully out-of-range box
+            // per 64-column block of B: which tap (shift + parity map) and which channel offset -- fixed for the CTA
+            int b_dw[4], b_dh[4], b_c0[4];
+            const CUtensorMap* b_map[4];
+            const int nblk = BN / 64;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                int tj = p.G == 1 ? group : group * p.G + j / p.cin_blocks;
+                if (tj >= p.ntaps) tj = p.ntaps - 1;                // padding block of the last group (ignored later)
+                const Tap tp = p.taps[tj];
+                int c0 = p.G == 1 ? nt * BN + j * 64 : (j % p.cin_blocks) * 64;
+                if (c0 >= p.Cin) c0 = 0;
+                b_dw[j] = tp.dw; b_dh[j] = tp.dh; b_c0[j] = c0; b_map[j] = &p.xmap[tp.amap];
+            }
             for (int pt = pt_begin; pt < pt_end; ++pt) {
                 const int tw = pt % p.tiles_w;
                 const int th = (pt / p.tiles_w) % p.tiles_h;
@@ -369,11 +385,10 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
                 tma_load_4d(dA, &p.dymap, &bars->full[stage], mt * TILE_M, w0, h0, n0);
                 tma_load_4d(dA + 8192, &p.dymap, &bars->full[stage], ca1, w0, h0, n0);
                 uint8_t* dB = sB + stage * b_stage;
-                for (int j = 0; j < BN / 64; ++j) {
-                    int c0 = nt * BN + j * 64;
-                    if (c0 >= p.Cin) c0 = 0;
-                    tma_load_4d(dB + j * 8192, &p.xmap[tp.amap], &bars->full[stage], c0, w0 + tp.dw, h0 + tp.dh, n0);
-                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (j < nblk)
+                        tma_load_4d(dB + j * 8192, b_map[j], &bars->full[stage], b_c0[j], w0 + b_dw[j], h0 + b_dh[j], n0);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
@@ -406,13 +421,15 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
             mbar_wait(&bars->tfull[0], 0);
             tc_fence_after();
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-            float* drow = p.dw + (static_cast<size_t>(cout) * p.taps_total + tp.btap) * p.Cin;
             for (int g = 0; g < BN / 32; ++g) {
                 uint32_t v[32];
                 tmem_ld_32x32(t_row + g * 32, v);
                 tmem_ld_wait();
-                if (cout < p.Cout) {
-                    const int cin0 = nt * BN + g * 32;
+                const int j = g >> 1;
+                const int tj = p.G == 1 ? group : group * p.G + j / p.cin_blocks;
+                if (cout < p.Cout && tj < p.ntaps) {
+                    float* drow = p.dw + (static_cast<size_t>(cout) * p.taps_total + p.taps[tj].btap) * p.Cin;
+                    const int cin0 = (p.G == 1 ? nt * BN + j * 64 : (j % p.cin_blocks) * 64) + (g & 1) * 32;
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
                         const int cin = cin0 + i;
@@ -659,6 +676,25 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
     p.dw = dw; p.Cout = Cout; p.Cin = Cin; p.taps_total = R * S;
     int BN;
     p.numN = num_n_tiles(Cin, &BN);
+    p.cin_blocks = ceil_div(Cin, 64);
+    p.G = 1;
+    p.ngroups = p.ntaps;
+    static const bool group_taps = []{ const char* e = getenv("PICD_WGRAD_GROUP"); return e == nullptr || e[0] != '0'; }();
+    if (group_taps && p.ntaps > 1 && p.cin_blocks <= 2) {
+        // several taps per CTA: one dy tile (A) feeds G shifted x tiles (B) laid side by side along N
+        const int maxG = std::min(p.ntaps, 4 / p.cin_blocks);
+        int bestG = 1, best_cost = 1 << 30;
+        for (int G = 1; G <= maxG; ++G) {
+            const int cost = ceil_div(p.ntaps, G) * (2 + G * p.cin_blocks);     // TMA boxes per pixel tile
+            if (cost <= best_cost) { best_cost = cost; bestG = G; }
+        }
+        p.G = bestG;
+        if (p.G > 1) {
+            p.ngroups = ceil_div(p.ntaps, p.G);
+            p.numN = 1;
+            BN = p.G * p.cin_blocks * 64;
+        }
+    }
     p.BN = BN;
     p.numM = ceil_div(Cout, TILE_M);
     p.num_p_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
@@ -675,7 +711,7 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
         p.stages = std::min(6, (MAX_DYN_SMEM - 1024 - SMEM_HEADER) / stage_bytes);
         smem_launch = MAX_DYN_SMEM;
     }
-    const int inner = p.ntaps * p.numM * p.numN;
+    const int inner = p.ngroups * p.numM * p.numN;
     const int sms = num_sms();
     int ksplit = std::max(1, (2 * sms + inner - 1) / inner);
     ksplit = std::min(ksplit, std::max(1, p.num_p_tiles / 4));   // keep >= 4 k-iterations per CTA

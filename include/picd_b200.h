@@ -47,8 +47,11 @@ int picd_gemm_tn_f32(const void* a, const void* b, float* d, int M, int N, int K
                                                              /* D[N,K] += A[M,N]^T B[M,K] (fp32) */
 
 /* ---- BatchNorm family (torch/nn/modules/_functions.py:39-179 = SURVEY.md K5-K10,K12) ------------------- */
+/* Statistics buffers produced by kernels (conv_fprop `stats`, bn_stats, bn_bwd_reduce `sums`) hold
+ * picd_stat_replicas() (= 16) copies of [2C] floats, zeroed by the caller; consumers take the number of copies. */
+int picd_stat_replicas(void);
 int picd_bn_stats(const void* x, float* stats, long long P, int C, cudaStream_t stream);
-int picd_bn_finalize(const float* sums, float count, const float* gamma, const float* beta, float* running_mean,
+int picd_bn_finalize(const float* sums, int replicas, float count, const float* gamma, const float* beta, float* running_mean,
                      float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
                      float* invstd, int C, cudaStream_t stream);
 int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
@@ -59,9 +62,9 @@ int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float
                        const float* mean, const float* invstd, int act, float* sums, long long P, int C,
                        cudaStream_t stream);
 int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
-                      const float* mean, const float* invstd, int act, const float* sums, float inv_count,
-                      const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
-                      cudaStream_t stream);
+                      const float* mean, const float* invstd, int act, const float* sums, int sums_replicas,
+                      float inv_count, const float* param_sums, int param_replicas, float* dgamma, float* dbeta, void* dy,
+                      void* dres, long long P, int C, cudaStream_t stream);
 int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift, int act,
                      void* dy, void* dres, long long P, int C, cudaStream_t stream);
 
@@ -125,9 +128,9 @@ int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start
                                 float* state1, int kind, float lr, float momentum, float beta1, float beta2, float eps,
                                 float weight_decay, float bc1, float bc2, int nesterov, unsigned epoch, int blocks,
                                 cudaStream_t stream);
-int picd_p2p_allreduce_small(void* ctx, const float* in, float* out, int n, long long slot_off, int flag_slot,
-                             unsigned epoch, cudaStream_t stream);
-int picd_bn_finalize_sync(void* ctx, const float* sums, float count, const float* gamma, const float* beta,
+int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
+                             int flag_slot, unsigned epoch, cudaStream_t stream);
+int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
                           float* running_mean, float* running_var, float momentum, float eps, float* scale,
                           float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
                           int flag_slot, unsigned epoch, cudaStream_t stream);

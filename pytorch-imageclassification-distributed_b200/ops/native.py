@@ -23,6 +23,7 @@ import torch.nn.functional as F
 from . import reference as ref
 from ._lib import check, require_lib
 
+STAT_REPLICAS = 16        # must equal picd_stat_replicas(); checked at first use
 ACT = {None: 0, "none": 0, "relu": 1, "gelu": 2, "swish": 3, "silu": 3, "sigmoid": 4}
 
 _SIG = {
@@ -33,11 +34,11 @@ _SIG = {
     "picd_gemm_nn": "pppiiip",
     "picd_gemm_tn_f32": "pppiiip",
     "picd_bn_stats": "pplip",
-    "picd_bn_finalize": "pfppppffppppip",
+    "picd_bn_finalize": "pifppppffppppip",
     "picd_bn_eval_coeffs": "ppppfppip",
     "picd_bn_apply": "ppppiplip",
     "picd_bn_bwd_reduce": "pppppppiplip",
-    "picd_bn_bwd_apply": "pppppppipfpppppplip"[:0] + "pppppppi" + "pf" + "ppp" + "pp" + "lip",
+    "picd_bn_bwd_apply": "pppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_eval": "pppppipplip",
     "picd_pool_fwd": "ppp" + "i" * 11 + "p",
     "picd_pool_bwd": "ppp" + "i" * 11 + "p",
@@ -143,6 +144,19 @@ def _out_size(h, k, s, p):
 
 def _round_up(a, b):
     return (a + b - 1) // b * b
+
+
+_replicas_checked = False
+
+
+def stat_buffer(C: int, device) -> torch.Tensor:
+    """Zeroed [STAT_REPLICAS, 2C] accumulator for the statistics kernels."""
+    global _replicas_checked
+    if not _replicas_checked:
+        lib = require_lib()
+        assert lib.picd_stat_replicas() == STAT_REPLICAS, "library / Python STAT_REPLICAS mismatch"
+        _replicas_checked = True
+    return torch.zeros(STAT_REPLICAS * 2 * C, dtype=torch.float32, device=device)
 
 
 # --------------------------------------------------------------------------- conv core
@@ -259,25 +273,26 @@ def _bn_forward_coeffs(sums, count, gamma, beta, rm, rv, momentum, eps, sync_gro
             return coef, tot
         # no peer-mapped slab (e.g. model not wrapped yet): NCCL fallback for the statistics only
         import torch.distributed as dist
-        packed = torch.cat([sums, sums.new_tensor([float(count)])])
+        packed = torch.cat([sums.view(-1, 2 * C).sum(0), sums.new_tensor([float(count)])])
         dist.all_reduce(packed, group=None if sync_group is True else sync_group)
         sums = packed[:-1].contiguous()
         total_t = packed[-1:]
         total = float(total_t.item())
-    call("picd_bn_finalize", sums, total, gamma, beta, rm, rv, float(momentum), float(eps),
+    call("picd_bn_finalize", sums, sums.numel() // (2 * C), total, gamma, beta, rm, rv, float(momentum), float(eps),
          coef[0], coef[1], coef[2], coef[3], C)
     return coef, total
 
 
-def _bn_allreduce_bwd(sums2, sync_group):
+def _bn_allreduce_bwd(sums2, sync_group, C):
+    """[STAT_REPLICAS, 2C] local sums -> the sums bn_bwd_apply should use (folded + all-reduced under SyncBN)."""
     if _sync_world(sync_group) <= 1:
         return sums2
     from ..parallel import native_comm
     comm = native_comm.current_comm()
     if comm is not None:
-        return comm.allreduce_small(sums2)
+        return comm.allreduce_small(sums2, 2 * C)
     import torch.distributed as dist
-    out = sums2.clone()
+    out = sums2.view(-1, 2 * C).sum(0)
     dist.all_reduce(out, group=None if sync_group is True else sync_group)
     return out
 
@@ -316,13 +331,13 @@ def _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, need_dres):
     if not ctx.bn_training:
         call("picd_bn_bwd_eval", dz, y, zmask, coef[0], coef[1], act, dy, dres, P, C)
         return dy, dres, None, None
-    sums2 = torch.zeros(2 * C, dtype=torch.float32, device=y.device)
+    sums2 = stat_buffer(C, y.device)
     call("picd_bn_bwd_reduce", dz, y, zmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
-    gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync)
+    gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C)
     gt, g_routed = _grad_target(gamma)
     bt, b_routed = _grad_target(beta)
-    call("picd_bn_bwd_apply", dz, y, zmask, coef[0], coef[1], coef[2], coef[3], act, gsums,
-         1.0 / ctx.bn_total, sums2, gt, bt, dy, dres, P, C)
+    call("picd_bn_bwd_apply", dz, y, zmask, coef[0], coef[1], coef[2], coef[3], act, gsums, gsums.numel() // (2 * C),
+         1.0 / ctx.bn_total, sums2, STAT_REPLICAS, gt, bt, dy, dres, P, C)
     if g_routed:
         _mark_ready(gamma)
     if b_routed:
@@ -335,7 +350,7 @@ class _ConvBnAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, gamma, beta, residual, cfg: _BNCfg):
         C = w.shape[0]
-        stats = torch.zeros(2 * C, dtype=torch.float32, device=x.device) if cfg.training else None
+        stats = stat_buffer(C, x.device) if cfg.training else None
         y, info = _conv_forward(x, w, cfg.stride, cfg.padding, stats, None, None)
         count = y.numel() // C
         z, coef = _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg, stats, count)
@@ -369,7 +384,7 @@ class _BnAct(torch.autograd.Function):
         P = y.numel() // C
         sums = None
         if cfg.training:
-            sums = torch.zeros(2 * C, dtype=torch.float32, device=y.device)
+            sums = stat_buffer(C, y.device)
             call("picd_bn_stats", y, sums, P, C)
         z, coef = _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg, sums, P)
         ctx.save_for_backward(gamma, beta, y, z, coef)

@@ -132,10 +132,10 @@ class Comm:
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 8 +
                                 [ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p])
         self._f_small = self.lib.picd_p2p_allreduce_small
-        self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong,
-                                  ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
+        self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                  ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
         self._f_bn = self.lib.picd_bn_finalize_sync
-        self._f_bn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_float] + [ctypes.c_void_p] * 4 +
+        self._f_bn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float] + [ctypes.c_void_p] * 4 +
                                [ctypes.c_float, ctypes.c_float] + [ctypes.c_void_p] * 5 +
                                [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p])
         _current = self
@@ -176,7 +176,7 @@ class Comm:
             raise RuntimeError(f"picd_b200: SyncBN with {C} channels exceeds the exchange slot")
         e, off, fslot = self._next(self._slot(gamma))
         total = torch.empty(1, dtype=torch.float32, device=sums.device)
-        check(self._f_bn(self.ctx, sums.data_ptr(), float(count), gamma.data_ptr(), beta.data_ptr(),
+        check(self._f_bn(self.ctx, sums.data_ptr(), sums.numel() // (2 * C), float(count), gamma.data_ptr(), beta.data_ptr(),
                          None if rm is None else rm.data_ptr(), None if rv is None else rv.data_ptr(),
                          float(momentum), float(eps), coef[0].data_ptr(), coef[1].data_ptr(), coef[2].data_ptr(),
                          coef[3].data_ptr(), total.data_ptr(), C, off, fslot, e & 0xFFFFFFFF,
@@ -184,14 +184,17 @@ class Comm:
         # every rank holds an equally sized shard (ShardedSampler pads), so the global count is known on the host
         return float(count) * self.slab.world
 
-    def allreduce_small(self, vec: torch.Tensor, key=None) -> torch.Tensor:
-        n = vec.numel()
+    def allreduce_small(self, vec: torch.Tensor, n: Optional[int] = None, key=None) -> torch.Tensor:
+        """Sum ``n`` floats over all ranks.  ``vec`` may hold several replicas of the payload ([R, n]); they are
+        folded while publishing.  Returns a single [n] tensor."""
+        n = vec.numel() if n is None else n
+        replicas = vec.numel() // n
         if n > SLOT_FLOATS:
             raise RuntimeError("picd_b200: small all-reduce payload exceeds the exchange slot")
         holder = key if key is not None else self
         e, off, fslot = self._next(self._slot(_BwdKey.of(holder, n)))
-        out = torch.empty_like(vec)
-        check(self._f_small(self.ctx, vec.data_ptr(), out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
+        out = torch.empty(n, dtype=vec.dtype, device=vec.device)
+        check(self._f_small(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
                             torch.cuda.current_stream().cuda_stream), "picd_p2p_allreduce_small")
         return out
 
