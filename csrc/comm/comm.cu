@@ -104,43 +104,57 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
     }
     const long long nvec = (hi - lo) >> 2;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
-        const long long i = lo + (v << 2);
-        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (mode == 0) {
-            g = *reinterpret_cast<const float4*>(pt.grad[rank] + i);
-        } else {
-            float4 part[MAX_PEERS];
+    constexpr int UNR = 2;     // independent 16-byte vectors per thread per iteration (2 x W peer loads in flight)
+    for (long long v0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < nvec; v0 += stride * UNR) {
+        float4 g[UNR], w[UNR], s0[UNR], s1[UNR];
+        bool live[UNR];
 #pragma unroll
-            for (int p = 0; p < MAX_PEERS; ++p)
-                if (p < W) part[p] = ld_peer_f4(pt.grad[p] + i);          // all W loads in flight together
+        for (int u = 0; u < UNR; ++u) {
+            const long long v = v0 + u * stride;
+            live[u] = v < nvec;
+            g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            s1[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!live[u]) continue;
+            const long long i = lo + (v << 2);
+            if (mode == 0) {
+                g[u] = *reinterpret_cast<const float4*>(pt.grad[rank] + i);
+            } else {
+                float4 part[MAX_PEERS];
 #pragma unroll
-            for (int p = 0; p < MAX_PEERS; ++p)
-                if (p < W) { g.x += part[p].x; g.y += part[p].y; g.z += part[p].z; g.w += part[p].w; }
+                for (int p = 0; p < MAX_PEERS; ++p)
+                    if (p < W) part[p] = ld_peer_f4(pt.grad[p] + i);          // all W loads in flight together
+#pragma unroll
+                for (int p = 0; p < MAX_PEERS; ++p)                           // fixed rank order: bitwise reproducible
+                    if (p < W) { g[u].x += part[p].x; g[u].y += part[p].y; g[u].z += part[p].z; g[u].w += part[p].w; }
+            }
+            w[u] = *reinterpret_cast<const float4*>(pt.master[rank] + i);
+            s0[u] = *reinterpret_cast<const float4*>(state0 + i);
+            if (opt.kind != 0) s1[u] = *reinterpret_cast<const float4*>(state1 + i);
         }
-        float4 w = *reinterpret_cast<const float4*>(pt.master[rank] + i);
-        float4 s0 = *reinterpret_cast<const float4*>(state0 + i);
-        float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (opt.kind != 0) s1 = *reinterpret_cast<const float4*>(state1 + i);
-        w.x = opt_update(w.x, g.x, s0.x, s1.x, opt);
-        w.y = opt_update(w.y, g.y, s0.y, s1.y, opt);
-        w.z = opt_update(w.z, g.z, s0.z, s1.z, opt);
-        w.w = opt_update(w.w, g.w, s0.w, s1.w, opt);
-        *reinterpret_cast<float4*>(state0 + i) = s0;
-        if (opt.kind != 0) *reinterpret_cast<float4*>(state1 + i) = s1;
-        const uint2 sh = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
-        if (mode == 2) {
 #pragma unroll
-            for (int p = 0; p < MAX_PEERS; ++p)
-                if (p < W) {
-                    *reinterpret_cast<float4*>(pt.master[p] + i) = w;     // push over NVLink (all-gather phase)
-                    *reinterpret_cast<uint2*>(pt.shadow[p] + i) = sh;
-                }
-        } else {
-            *reinterpret_cast<float4*>(pt.master[rank] + i) = w;
-            *reinterpret_cast<uint2*>(pt.shadow[rank] + i) = sh;
+        for (int u = 0; u < UNR; ++u) {
+            if (!live[u]) continue;
+            const long long i = lo + ((v0 + u * stride) << 2);
+            w[u].x = opt_update(w[u].x, g[u].x, s0[u].x, s1[u].x, opt);
+            w[u].y = opt_update(w[u].y, g[u].y, s0[u].y, s1[u].y, opt);
+            w[u].z = opt_update(w[u].z, g[u].z, s0[u].z, s1[u].z, opt);
+            w[u].w = opt_update(w[u].w, g[u].w, s0[u].w, s1[u].w, opt);
+            *reinterpret_cast<float4*>(state0 + i) = s0[u];
+            if (opt.kind != 0) *reinterpret_cast<float4*>(state1 + i) = s1[u];
+            const uint2 sh = make_uint2(pack_bf16x2(w[u].x, w[u].y), pack_bf16x2(w[u].z, w[u].w));
+            if (mode == 2) {
+#pragma unroll
+                for (int p = 0; p < MAX_PEERS; ++p)
+                    if (p < W) {
+                        *reinterpret_cast<float4*>(pt.master[p] + i) = w[u];     // push over NVLink (all-gather phase)
+                        *reinterpret_cast<uint2*>(pt.shadow[p] + i) = sh;
+                    }
+            } else {
+                *reinterpret_cast<float4*>(pt.master[rank] + i) = w[u];
+                *reinterpret_cast<uint2*>(pt.shadow[rank] + i) = sh;
+            }
+            if (mode == 0) *reinterpret_cast<float4*>(pt.grad[rank] + i) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (mode == 0) *reinterpret_cast<float4*>(pt.grad[rank] + i) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (mode == 0) return;
 
@@ -308,8 +322,20 @@ extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long
     o.grad_scale = 1.f / c->world;
     const long long work_vecs = (mode == 2 ? count / c->world : count) / 4;
     long long want = (work_vecs + 511) / 512;
-    if (blocks <= 0) blocks = mode == 0 ? 4 * num_sms() : 32;
+    // Peer kernels spin on flags, so the grid must be able to become co-resident: at most 2 CTAs of 512 threads per SM.
+    // Small buckets (the usual <= 25 MiB, overlapped with backward) use few CTAs to leave the SMs to the wgrads.
+    if (blocks <= 0) blocks = mode == 0 ? 4 * num_sms() : (count * 4 >= (32LL << 20) ? 2 * num_sms() : (count * 4 >= (4LL << 20) ? 64 : 32));
     if (want < blocks) blocks = static_cast<int>(want < 1 ? 1 : want);
+    if (mode != 0) {
+        // CTAs of this grid wait (through the peers) on each other, so the whole grid must fit on the GPU at once
+        static int max_resident = 0;
+        if (max_resident == 0) {
+            int per_sm = 0;
+            PICD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_allreduce_update_kernel, 512, 0));
+            max_resident = (per_sm > 0 ? per_sm : 1) * num_sms();
+        }
+        if (blocks > max_resident) blocks = max_resident;
+    }
     fused_allreduce_update_kernel<<<blocks, 512, 0, stream>>>(c->pt, c->rank, c->world, mode, start, count, state0, state1, o,
                                                               2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket);
     PICD_LAUNCH_CHECK();
