@@ -324,7 +324,9 @@ extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long
     long long want = (work_vecs + 511) / 512;
     // Peer kernels spin on flags, so the grid must be able to become co-resident: at most 2 CTAs of 512 threads per SM.
     // Small buckets (the usual <= 25 MiB, overlapped with backward) use few CTAs to leave the SMs to the wgrads.
-    if (blocks <= 0) blocks = mode == 0 ? 4 * num_sms() : (count * 4 >= (32LL << 20) ? 2 * num_sms() : (count * 4 >= (4LL << 20) ? 64 : 32));
+    // (a CTA of this kernel holds 59K registers, so it evicts a persistent conv CTA from its SM: measured +2 ms/step
+    //  on one GPU when the local update used 4 CTAs per SM.)
+    if (blocks <= 0) blocks = count * 4 >= (32LL << 20) ? 2 * num_sms() : (count * 4 >= (4LL << 20) ? 64 : 32);
     if (want < blocks) blocks = static_cast<int>(want < 1 ? 1 : want);
     if (mode != 0) {
         // CTAs of this grid wait (through the peers) on each other, so the whole grid must fit on the GPU at once
