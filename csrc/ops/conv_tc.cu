@@ -32,7 +32,8 @@ constexpr int MAX_TAPS = 64;
 constexpr int TILE_M = 128;
 constexpr int KCHUNK = 64;                   // bf16 elements per 128B swizzle row
 constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
-constexpr int SMEM_HEADER = 1024;
+constexpr int SMEM_HEADER = 2048;           // mbarriers + TMEM base (first 512 B), bias tile of the CTA (1 KB at +512)
+constexpr int SMEM_BIAS_OFF = 512;
 constexpr int MAX_DYN_SMEM = 232448;         // 227 KB
 
 struct Tap {
@@ -129,6 +130,15 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
     const int n_tile = blockIdx.x % numN;
     const int m_first = blockIdx.x / numN;
     const int k_iters = p.ntaps * p.kchunks;
+    float* sBias = reinterpret_cast<float*>(smem + SMEM_BIAS_OFF);
+    if (kBiasAct) {
+        // a CTA keeps one column tile for its whole life, so its slice of the bias vector is staged once
+        for (int i = threadIdx.x; i < BN; i += blockDim.x) {
+            const int c = n_tile * BN + i;
+            sBias[i] = (p.bias != nullptr && c < p.Cout) ? p.bias[c] : 0.f;
+        }
+        __syncthreads();
+    }
     const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
     const int bn = TILE_M >> (p.bw_log2 + p.bh_log2);
 
@@ -240,12 +250,22 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                 tmem_ld_32x32(t_row + g * 32, v);
                 tmem_ld_wait();
                 if (kBiasAct) {
-                    const int col0 = n_tile * BN + g * 32;
+                    const uint32_t bsrc = smem_u32(sBias) + g * 128;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        float a = __uint_as_float(v[i]);
-                        if (p.bias != nullptr && col0 + i < p.Cout) a += __ldg(p.bias + col0 + i);
-                        v[i] = __float_as_uint(apply_act(a, p.act));
+                    for (int i = 0; i < 32; i += 4) {
+                        float b0, b1, b2, b3;     // same address in every lane: a shared-memory broadcast
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(bsrc + i * 4));
+                        v[i + 0] = __float_as_uint(__uint_as_float(v[i + 0]) + b0);
+                        v[i + 1] = __float_as_uint(__uint_as_float(v[i + 1]) + b1);
+                        v[i + 2] = __float_as_uint(__uint_as_float(v[i + 2]) + b2);
+                        v[i + 3] = __float_as_uint(__uint_as_float(v[i + 3]) + b3);
+                    }
+                    if (p.act == ACT_RELU) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+                    } else if (p.act != ACT_NONE) {
+#pragma unroll 4
+                        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(apply_act(__uint_as_float(v[i]), p.act));
                     }
                 }
                 const uint32_t dst = row_base + (g >> 1) * 16384;

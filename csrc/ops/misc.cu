@@ -255,9 +255,53 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __res
     }
 }
 
-// out[c] += sum over rows of x[r, c] (bias gradients).  2-D blocks, fp32 atomics.
+// out[c] += sum over rows of x[r, c] (bias gradients).  Thread = one vector of 8 channels, rows strided over the
+// block, 4 rows in flight; shared-memory fold over the row dimension, one fp32 atomic per channel per block.
 __global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
-                                                     long long P, int C, int rows_per_block) {
+                                                     long long P, int C, int tx_count, int ty_count, int rows_per_block) {
+    extern __shared__ float cs_red[];     // [ty_count][tx_count][8]
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const bool active = ty < ty_count && cv < vecs;
+    if (active) {
+        const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+        long long r1 = r0 + rows_per_block;
+        if (r1 > P) r1 = P;
+        for (long long r = r0 + ty; r < r1; r += 4LL * ty_count) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                v[u] = rr < r1 ? *reinterpret_cast<const uint4*>(x + rr * C + cv * 8) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                float f[8];
+                unpack8(v[u], f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] += f[k];
+            }
+        }
+    }
+    if (ty < ty_count) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) cs_red[(ty * tx_count + tx) * 8 + k] = acc[k];
+    }
+    __syncthreads();
+    if (active && ty == 0) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] += cs_red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(out + cv * 8 + k, s[k]);
+    }
+}
+// scalar fallback for C not a multiple of 8
+__global__ void __launch_bounds__(256) colsum_scalar_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
+                                                            long long P, int C, int rows_per_block) {
     const int c = blockIdx.x * 64 + (threadIdx.x & 63);
     const int ty = threadIdx.x >> 6;
     __shared__ float red[256];
@@ -318,7 +362,10 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
         *reinterpret_cast<uint4*>(y + row * D + j) = pack8(f);
     }
 }
-// dx and (atomically accumulated) dgamma/dbeta.  Each block keeps per-column partials in shared memory.
+// dx and (atomically accumulated) dgamma/dbeta.  A lane owns the same columns (lane*8 + 256*i) for every row its warp
+// handles, so the parameter-gradient partials live in registers; they are folded across the block's warps through shared
+// memory once at the end (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).
+constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
 __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                                             const float* __restrict__ gamma, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
@@ -330,35 +377,55 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
     for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) sm[j] = 0.f;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    float pg[LN_MAX_VECS][8], pb[LN_MAX_VECS][8], gm[LN_MAX_VECS][8];
+#pragma unroll
+    for (int i = 0; i < LN_MAX_VECS; ++i) {
+        const int j = lane * 8 + i * 256;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; }
+    }
     const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
     long long r1 = r0 + rows_per_block;
     if (r1 > M) r1 = M;
     for (long long row = r0 + warp; row < r1; row += nw) {
         const float mu = mean[row], rs = rstd[row];
+        float g[LN_MAX_VECS][8], xh[LN_MAX_VECS][8];
         float a = 0.f, b = 0.f;
-        for (int j = lane * 8; j < D; j += 256) {
-            float g[8], f[8];
-            unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
-            unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float xh = (f[k] - mu) * rs, gg = g[k] * gamma[j + k];
-                a += gg; b += gg * xh;
-                atomicAdd(sg + j + k, g[k] * xh);
-                atomicAdd(sb + j + k, g[k]);
+        for (int i = 0; i < LN_MAX_VECS; ++i) {
+            const int j = lane * 8 + i * 256;
+            if (j < D) {
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g[i]);
+                unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    xh[i][k] = (f[k] - mu) * rs;
+                    const float gg = g[i][k] * gm[i][k];
+                    a += gg; b += gg * xh[i][k];
+                    pg[i][k] += g[i][k] * xh[i][k];
+                    pb[i][k] += g[i][k];
+                }
             }
         }
         a = warp_sum(a) / D; b = warp_sum(b) / D;
-        for (int j = lane * 8; j < D; j += 256) {
-            float g[8], f[8], o[8];
-            unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
-            unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float xh = (f[k] - mu) * rs;
-                o[k] = rs * (g[k] * gamma[j + k] - a - xh * b);
+        for (int i = 0; i < LN_MAX_VECS; ++i) {
+            const int j = lane * 8 + i * 256;
+            if (j < D) {
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = rs * (g[i][k] * gm[i][k] - a - xh[i][k] * b);
+                *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
             }
-            *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < LN_MAX_VECS; ++i) {
+        const int j = lane * 8 + i * 256;
+        if (j < D) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { atomicAdd(sg + j + k, pg[i][k]); atomicAdd(sb + j + k, pb[i][k]); }
         }
     }
     __syncthreads();
@@ -548,13 +615,27 @@ extern "C" int picd_act_bwd(const void* dy, const void* x, const float* bias, vo
     return 0;
 }
 extern "C" int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t st) {
-    const int gx = (C + 63) / 64;
-    long long gy = (4LL * num_sms()) / gx;
-    if (gy < 1) gy = 1;
-    long long rpb = (P + gy - 1) / gy;
-    if (rpb < 16) rpb = 16;
-    gy = (P + rpb - 1) / rpb;
-    colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, st>>>(static_cast<const bf16*>(x), out, P, C, static_cast<int>(rpb));
+    if (C % 8 == 0) {
+        const int vecs = C / 8;
+        const int tx = vecs < 32 ? vecs : 32, ty = 256 / tx;     // a warp covers 512 contiguous bytes of a row
+        const int gx = (vecs + tx - 1) / tx;
+        long long gy = (4LL * num_sms()) / gx;
+        if (gy < 1) gy = 1;
+        long long rpb = (P + gy - 1) / gy;
+        if (rpb < 4LL * ty) rpb = 4LL * ty;
+        gy = (P + rpb - 1) / rpb;
+        colsum_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, tx * ty * 8 * sizeof(float), st>>>(
+            static_cast<const bf16*>(x), out, P, C, tx, ty, static_cast<int>(rpb));
+    } else {
+        const int gx = (C + 63) / 64;
+        long long gy = (4LL * num_sms()) / gx;
+        if (gy < 1) gy = 1;
+        long long rpb = (P + gy - 1) / gy;
+        if (rpb < 16) rpb = 16;
+        gy = (P + rpb - 1) / rpb;
+        colsum_scalar_kernel<<<dim3(gx, static_cast<unsigned>(gy)), 256, 0, st>>>(static_cast<const bf16*>(x), out, P, C,
+                                                                                  static_cast<int>(rpb));
+    }
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -565,7 +646,7 @@ extern "C" int picd_dropout(const void* x, void* out, long long n, float p, unsi
 }
 extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                                   long long M, int D, float eps, cudaStream_t st) {
-    PICD_REQUIRE(D % 8 == 0, "layernorm: D=%d must be a multiple of 8", D);
+    PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
     layernorm_fwd_kernel<<<static_cast<unsigned>((M + 7) / 8), 256, 0, st>>>(static_cast<const bf16*>(x), gamma, beta,
                                                                             static_cast<bf16*>(y), mean, rstd, M, D, eps);
     PICD_LAUNCH_CHECK();

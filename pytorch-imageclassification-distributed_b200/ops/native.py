@@ -719,7 +719,7 @@ class _LayerNorm(torch.autograd.Function):
 
 
 def layer_norm(x, gamma, beta, eps):
-    if x.shape[-1] % 8 != 0:
+    if x.shape[-1] % 8 != 0 or x.shape[-1] > 1024:
         return ref.layer_norm(x, gamma, beta, eps)
     return _LayerNorm.apply(x, gamma, beta, eps)
 
