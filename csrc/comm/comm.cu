@@ -364,3 +364,16 @@ extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas,
     PICD_LAUNCH_CHECK();
     return 0;
 }
+
+// NVLS probe: does the device expose NVSwitch multicast objects (cuMulticastCreate & friends)?  picd_b200 does not use
+// them yet (one-/two-shot peer loads/stores only); the probe lets hosts report it.  Returns 1 / 0, or -1 if unknown.
+extern "C" int picd_nvls_supported() {
+    typedef CUresult (*GetAttrFn)(int*, CUdevice_attribute, CUdevice);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &fn, cudaEnableDefault, &q) != cudaSuccess || fn == nullptr) return -1;
+    int dev = 0, val = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (reinterpret_cast<GetAttrFn>(fn)(&val, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS) return -1;
+    return val ? 1 : 0;
+}

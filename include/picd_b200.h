@@ -135,6 +135,8 @@ int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float coun
                           float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
                           int flag_slot, unsigned epoch, cudaStream_t stream);
 
+int picd_nvls_supported(void);   /* 1/0/-1: NVSwitch multicast available (probe only; the kernels use P2P loads/stores) */
+
 /* ---- runtime ---------------------------------------------------------------------------------------------- */
 /* reverse-order bucket plan (torch DDP Reducer semantics); host function */
 int picd_plan_buckets(const int64_t* padded_sizes, int n_params, int64_t first_bytes, int64_t cap_bytes,

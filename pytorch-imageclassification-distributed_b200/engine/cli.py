@@ -57,6 +57,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--pretrained", default=None, help="local torchvision state-dict file")
     p.add_argument("--trace", default=None, help="write phase timings / metrics JSONL here")
     p.add_argument("--seed", default=0, type=int)
+    p.add_argument("--calibrate-comm", action="store_true",
+                   help="measure one-shot vs two-shot all-reduce at start-up and pick the switch-over bucket size")
     return p
 
 
@@ -105,6 +107,11 @@ def main(argv: Optional[List[str]] = None) -> int:
     model = model.to(device)
     spec = OptimizerSpec(kind=args.optimizer, lr=args.lr, momentum=args.momentum,
                          weight_decay=args.weight_decay)
+    if args.calibrate_comm and device.type == "cuda" and D.get_world_size() > 1:
+        from ..parallel import native_comm
+        thr = native_comm.calibrate_two_shot_threshold(device)
+        if D.is_main():
+            print(f"comm: two-shot all-reduce from {thr} bytes (NVLS supported: {native_comm.nvls_supported()})")
     model = FusedDataParallel(model, spec)                                       # train.py:126-128
     optimizer = model.optimizer
 

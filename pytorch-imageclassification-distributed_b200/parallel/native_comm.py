@@ -249,3 +249,50 @@ class NativeReducer:
         if self._dirty:
             torch.cuda.current_stream(self.e.device).wait_stream(self.side)
             self._dirty = False
+
+
+def nvls_supported() -> int:
+    """1 / 0 / -1: whether the device exposes NVSwitch multicast (NVLS).  Informational: the engine uses one-/two-shot
+    peer loads and stores; an NVLS variant (multimem.ld_reduce / multimem.st) is future work."""
+    lib = require_lib()
+    lib.picd_nvls_supported.restype = ctypes.c_int
+    return int(lib.picd_nvls_supported())
+
+
+def calibrate_two_shot_threshold(device: torch.device, sizes_bytes=(64 << 10, 256 << 10, 1 << 20, 4 << 20),
+                                 iters: int = 10) -> int:
+    """Measure one-shot vs two-shot on this machine and set ``TWO_SHOT_MIN_BYTES`` to the smallest bucket size at which
+    two-shot wins (BASELINE.json: "the variant picked per bucket size from measured bus bandwidth").  Collective: every
+    rank must call it; timings are max-reduced so all ranks agree.  Returns the chosen threshold in bytes."""
+    global TWO_SHOT_MIN_BYTES
+    from .engine import FusedDataParallel, OptimizerSpec
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if world == 1:
+        return TWO_SHOT_MIN_BYTES
+    n = max(sizes_bytes) // 4
+    holder = torch.nn.Module()
+    holder.w = torch.nn.Parameter(torch.zeros(n, device=device))
+    eng = FusedDataParallel(holder, OptimizerSpec("sgd", lr=0.0, momentum=0.0), overlap=False)
+    comm, state, spec = eng._impl.comm, eng.arena.state, eng.spec
+    epoch = 0
+    chosen = None
+    for size in sorted(sizes_bytes):
+        count = size // 4 // (64 * world) * (64 * world)
+        t = {}
+        for mode in (1, 2):
+            for it in range(3 + iters):
+                if it == 3:
+                    torch.cuda.synchronize(device)
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                epoch += 1
+                comm.fused_update(0, mode, 0, count, state, spec, 1, epoch, 0)
+            b.record()
+            torch.cuda.synchronize(device)
+            ms = torch.tensor([a.elapsed_time(b) / iters], device=device)
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            t[mode] = float(ms)
+        if chosen is None and t[2] < t[1] * 0.98:
+            chosen = size
+    TWO_SHOT_MIN_BYTES = chosen if chosen is not None else max(sizes_bytes) * 4
+    return TWO_SHOT_MIN_BYTES
