@@ -19,7 +19,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 OUT_DIR = os.path.join(ROOT, "gpurun_out")
-GROUPS = ["basic", "gemm", "conv", "model", "perf"]
+GROUPS = ["basic", "gemm", "attn", "conv", "model", "perf"]
 
 
 def emit(rec):
@@ -236,6 +236,46 @@ def group_gemm():
         ms_ref = time_cuda(lambda: torch.matmul(a, b.t()))
         emit({"group": g, "test": f"gemm_nt_perf[{M},{N},{K}]", "ms": ms, "tflops": 2.0 * M * N * K / ms / 1e9,
               "cublas_ms": ms_ref, "cublas_tflops": 2.0 * M * N * K / ms_ref / 1e9, "ok": True})
+    return ok
+
+
+# ------------------------------------------------------------------------------------------ attention
+def group_attn():
+    import torch
+    from picd_b200.ops import native, reference as ref
+    dev = torch.device("cuda")
+    ok = True
+    g = "attn"
+    for (B, S, H) in [(2, 197, 3), (3, 64, 2), (2, 128, 4), (1, 256, 2), (5, 130, 1)]:
+        torch.manual_seed(S)
+        qkv = (torch.randn(B * S, 3 * H * 64, device=dev) * 0.8).to(torch.bfloat16).requires_grad_()
+        o = native.attention_packed(qkv, B, S, H)
+        do = torch.randn_like(o)
+        o.backward(do)
+        q32 = qkv.detach().float().requires_grad_()
+        t = q32.view(B, S, 3, H, 64).permute(2, 0, 3, 1, 4)
+        orf = ref.attention(t[0], t[1], t[2]).permute(0, 2, 1, 3).reshape(B * S, H * 64)
+        orf.backward(do.float())
+        tag = f"attention[B{B},S{S},H{H}]"
+        ok &= check(tag + ".fwd", o, orf, 2e-2, g)
+        dq = qkv.grad.float().view(B, S, 3, H * 64)
+        dr = q32.grad.view(B, S, 3, H * 64)
+        for i, nm in enumerate(("dq", "dk", "dv")):
+            ok &= check(f"{tag}.{nm}", dq[:, :, i], dr[:, :, i], 3e-2, g)
+    # throughput at ViT-B/16 size
+    B, S, H = 256, 197, 12
+    qkv = torch.randn(B * S, 3 * H * 64, device=dev).to(torch.bfloat16).requires_grad_()
+    o = native.attention_packed(qkv, B, S, H)
+    do = torch.randn_like(o)
+    ms_f = time_cuda(lambda: native.attention_packed(qkv.detach(), B, S, H))
+    def fb():
+        qkv.grad = None
+        native.attention_packed(qkv, B, S, H).backward(do)
+    ms_fb = time_cuda(fb)
+    t = qkv.detach().view(B, S, 3, H, 64).permute(2, 0, 3, 1, 4)
+    ms_lib = time_cuda(lambda: torch.nn.functional.scaled_dot_product_attention(t[0], t[1], t[2]))
+    emit({"group": g, "test": "attention_perf[B256,S197,H12]", "fwd_ms": ms_f, "fwd_bwd_ms": ms_fb, "library_fwd_ms": ms_lib,
+          "fwd_tflops": 4.0 * B * H * S * S * 64 / ms_f / 1e9, "ok": True})
     return ok
 
 

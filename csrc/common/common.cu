@@ -49,6 +49,14 @@ static EncodeTiledFn encode_fn() {
 
 int make_tensor_map(CUtensorMap* out, const void* base, int elem_bytes, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
+    // cuTensorMapEncodeTiled is a DRIVER call and needs a current context on the calling thread.  A thread that has only
+    // ever been handed cached allocations (e.g. a fresh autograd worker thread) has none bound yet: CUDA_ERROR_INVALID_CONTEXT.
+    // One runtime call binds the primary context.
+    static thread_local bool context_bound = false;
+    if (!context_bound) {
+        cudaFree(nullptr);
+        context_bound = true;
+    }
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) {
         set_error("cuTensorMapEncodeTiled is not available from the driver");

@@ -46,6 +46,12 @@ int picd_gemm_nn(const void* a, const void* b, void* d, int M, int N, int K, cud
 int picd_gemm_tn_f32(const void* a, const void* b, float* d, int M, int N, int K, cudaStream_t stream);
                                                              /* D[N,K] += A[M,N]^T B[M,K] (fp32) */
 
+/* ---- multi-head self-attention, head dim 64, S <= 256 (ViT; the reference has no attention -- BASELINE.json config 4).
+ *      qkv is the packed projection output [B*S, 3*H*64]; o is [B*S, H*64]; lse/delta are fp32 [B,H,S]. */
+int picd_attention_fwd(const void* qkv, void* o, float* lse, int B, int S, int H, cudaStream_t stream);
+int picd_attention_bwd(const void* qkv, const void* o, const void* dout, const float* lse, float* delta, void* dqkv, int B,
+                       int S, int H, cudaStream_t stream);
+
 /* ---- BatchNorm family (torch/nn/modules/_functions.py:39-179 = SURVEY.md K5-K10,K12) ------------------- */
 /* Statistics buffers produced by kernels (conv_fprop `stats`, bn_stats, bn_bwd_reduce `sums`) hold
  * picd_stat_replicas() (= 16) copies of [2C] floats, zeroed by the caller; consumers take the number of copies. */

@@ -30,10 +30,8 @@ class SelfAttention(nn.Module):
 
     def forward(self, x):
         b, s, d = x.shape
-        qkv = ops.linear(x.reshape(b * s, d), self.in_proj_weight, self.in_proj_bias)
-        qkv = qkv.view(b, s, 3, self.heads, d // self.heads).permute(2, 0, 3, 1, 4)
-        o = ops.attention(qkv[0], qkv[1], qkv[2])            # [b, heads, s, dh]
-        o = o.permute(0, 2, 1, 3).reshape(b * s, d)
+        qkv = ops.linear(x.reshape(b * s, d), self.in_proj_weight, self.in_proj_bias)    # [b*s, 3d], packed q|k|v
+        o = ops.attention_packed(qkv, b, s, self.heads)                                    # [b*s, d]
         return self.out_proj(o).view(b, s, d)
 
 

@@ -127,6 +127,20 @@ def attention(q, k, v, scale=None):
     return ref.attention(q, k, v, scale)
 
 
+def attention_packed(qkv, batch: int, seq: int, heads: int):
+    """Self-attention on the packed QKV projection ``[batch*seq, 3*heads*dh]`` -> ``[batch*seq, heads*dh]``.
+    CUDA + head dim 64 + seq <= 256 runs the tcgen05 kernels; everything else the generic path."""
+    d3 = qkv.shape[-1]
+    dh = d3 // (3 * heads)
+    if use_native(qkv) and dh == 64:
+        from . import native
+        if native.attention_packed_supported(qkv, seq, heads):
+            return native.attention_packed(qkv, batch, seq, heads)
+    q = qkv.view(batch, seq, 3, heads, dh).permute(2, 0, 3, 1, 4)
+    o = attention(q[0], q[1], q[2])
+    return o.permute(0, 2, 1, 3).reshape(batch * seq, heads * dh)
+
+
 def dropout(x, p, training):
     if not training or p == 0.0:
         return x

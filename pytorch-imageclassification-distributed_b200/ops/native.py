@@ -30,6 +30,8 @@ _SIG = {
     "picd_conv_fprop": "pppppi" + "i" * 12 + "p",
     "picd_conv_dgrad": "ppp" + "i" * 12 + "p",
     "picd_conv_wgrad": "ppp" + "i" * 12 + "p",
+    "picd_attention_fwd": "pppiiip",
+    "picd_attention_bwd": "ppppppiiip",
     "picd_gemm_nt": "ppppiiiip",
     "picd_gemm_nn": "pppiiip",
     "picd_gemm_tn_f32": "pppiiip",
@@ -724,9 +726,41 @@ def layer_norm(x, gamma, beta, eps):
     return _LayerNorm.apply(x, gamma, beta, eps)
 
 
+class _AttentionPacked(torch.autograd.Function):
+    """softmax(q k^T / sqrt(64)) v on the tcgen05 kernels, reading q/k/v out of the packed projection [B*S, 3*H*64]."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, S, H):
+        qkv = qkv.contiguous()
+        o = torch.empty((B * S, H * 64), dtype=torch.bfloat16, device=qkv.device)
+        lse = torch.empty((B, H, S), dtype=torch.float32, device=qkv.device)
+        call("picd_attention_fwd", qkv, o, lse, B, S, H)
+        ctx.dims = (B, S, H)
+        ctx.save_for_backward(qkv, o, lse)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse = ctx.saved_tensors
+        B, S, H = ctx.dims
+        do = do.to(torch.bfloat16).contiguous()
+        dqkv = torch.empty_like(qkv)
+        delta = torch.empty_like(lse)
+        call("picd_attention_bwd", qkv, o, do, lse, delta, dqkv, B, S, H)
+        return dqkv, None, None, None
+
+
+def attention_packed_supported(qkv, S: int, H: int) -> bool:
+    return qkv.dtype == torch.bfloat16 and qkv.shape[-1] == 3 * H * 64 and 1 <= S <= 256
+
+
+def attention_packed(qkv, B: int, S: int, H: int):
+    return _AttentionPacked.apply(qkv, B, S, H)
+
+
 def attention(q, k, v, scale):
-    # TODO(round 2): tcgen05 batched QK^T / PV with fused softmax.  The 197-token ViT-B/16 problem is a single
-    # CTA tile per head; until the batched-B extension of conv_tc.cu lands this uses the library kernel.
+    # generic [B, heads, S, D] entry (head dim != 64 or S > 256): library kernel.  ViT-B/16 goes through
+    # attention_packed (csrc/ops/attention.cu) instead.
     return F.scaled_dot_product_attention(q, k, v, scale=scale)
 
 

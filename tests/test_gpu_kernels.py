@@ -25,6 +25,11 @@ def test_tcgen05_gemm():
     assert gpu_selftest.group_gemm()
 
 
+def test_tcgen05_attention():
+    import gpu_selftest
+    assert gpu_selftest.group_attn()
+
+
 def test_tcgen05_conv_fprop_dgrad_wgrad():
     import gpu_selftest
     assert gpu_selftest.group_conv()
