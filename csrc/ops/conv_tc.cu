@@ -56,6 +56,7 @@ struct ConvGemmParams {
     float* stats;         // [STAT_REPLICAS][2][Cout] (sum, sumsq) accumulators or nullptr
     const float* bias;    // [Cout] or nullptr
     int act;
+    int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
 };
 
 struct WgradParams {
@@ -289,7 +290,10 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             if (tid_e == 0) {
                 for (int j = 0; j < BN / 64; ++j) {
                     const int c0 = n_tile * BN + j * 64;
-                    if (c0 < p.Cout) tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                    if (c0 < p.Cout) {
+                        if (p.reduce_add) tma_reduce_add_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                        else tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                    }
                 }
                 tma_store_commit();
             }
@@ -605,9 +609,9 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
 
 // dx[N,H,W,Cin] = conv_transpose(dy[N,OH,OW,Cout], w[Cout,R,S,Cin]).  Weights are read through an MN-major
 // descriptor, i.e. the same tensor as fprop.  Stride 2 = one launch per output parity class.
-extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
-                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
-                               cudaStream_t stream) {
+static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                           int R, int S, int stride, int pad_h, int pad_w, int OH, int OW, int accumulate,
+                           cudaStream_t stream) {
     PICD_REQUIRE(stride == 1 || stride == 2, "conv_dgrad: stride %d unsupported", stride);
     PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_dgrad: channels must be multiples of 8");
     // If some output parity class receives no tap (e.g. 1x1 stride-2), zero dx once BEFORE any class is written.
@@ -621,7 +625,7 @@ extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, i
                         if (pos_mod(ph + pad_h - r, stride) == 0 && pos_mod(pw + pad_w - s, stride) == 0) ++cnt;
                 if (cnt == 0) any_empty = true;
             }
-        if (any_empty) PICD_CUDA(cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * Cin * 2, stream));
+        if (any_empty && !accumulate) PICD_CUDA(cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * Cin * 2, stream));
     }
     for (int ph = 0; ph < stride; ++ph) {
         for (int pw = 0; pw < stride; ++pw) {
@@ -660,10 +664,24 @@ extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, i
             p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
             p.W = Wv; p.H = Hv; p.N = N;
             p.stats = nullptr; p.bias = nullptr; p.act = ACT_NONE;
+            p.reduce_add = accumulate;
             if (int rc = launch_conv_gemm(p, Cin, stream)) return rc;
         }
     }
     return 0;
+}
+
+extern "C" int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                               cudaStream_t stream) {
+    return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, 0, stream);
+}
+// dx += conv_transpose(dy, w): the input gradient is accumulated into an existing bf16 tensor with TMA reduce-add
+// (fuses the residual-branch gradient sum of a ResNet block into the dgrad store).
+extern "C" int picd_conv_dgrad_accumulate(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                          int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                                          cudaStream_t stream) {
+    return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, 1, stream);
 }
 
 // dw[Cout,R,S,Cin] (fp32) += sum over pixels of dy (x) x.  The caller provides a zeroed (or accumulating) buffer.
@@ -755,7 +773,7 @@ extern "C" int picd_gemm_nt(const void* a, const void* b, void* d, const float* 
 }
 // D[M,K] = A[M,N] * B[N,K]  (Linear dgrad: dX = dY * W with W stored [N,K]).
 extern "C" int picd_gemm_nn(const void* a, const void* b, void* d, int M, int N_, int K, cudaStream_t stream) {
-    return picd_conv_dgrad(a, b, d, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
+    return conv_dgrad_impl(a, b, d, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, 0, stream);
 }
 // D[N,K] (fp32) += A[M,N]^T * B[M,K]  (Linear wgrad: dW = dY^T X).
 extern "C" int picd_gemm_tn_f32(const void* a_dy, const void* b_x, float* d, int M, int N_, int K,

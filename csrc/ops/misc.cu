@@ -90,14 +90,15 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(const __nv_bfloat16* __re
         const int ih = static_cast<int>(t % H);
         const int n = static_cast<int>(t / H);
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int a = 0; a < kh; ++a) {
+        // only window offsets congruent to (i + pad) mod stride can contain this pixel: step by `stride`
+        for (int a = (ih + pad) % stride; a < kh; a += stride) {
             const int th = ih + pad - a;
-            if (th < 0 || th % stride != 0) continue;
+            if (th < 0) break;
             const int oh = th / stride;
             if (oh >= OH) continue;
-            for (int b = 0; b < kw; ++b) {
+            for (int b = (iw + pad) % stride; b < kw; b += stride) {
                 const int tw = iw + pad - b;
-                if (tw < 0 || tw % stride != 0) continue;
+                if (tw < 0) break;
                 const int ow = tw / stride;
                 if (ow >= OW) continue;
                 const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * vecs + cv;
@@ -501,26 +502,33 @@ template <typename T>
 __global__ void __launch_bounds__(256) pack_s2d_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int H,
                                                        int W, int C, int Hp, int Wp, int Cp, int s, int pad_h, int pad_w,
                                                        int normalize) {
-    const long long total = static_cast<long long>(N) * Hp * Wp * Cp;
+    // one thread = 8 consecutive packed channels of one cell (a 16-byte store); Cp is a multiple of 16
+    const int vecs = Cp >> 3;
+    const long long total = static_cast<long long>(N) * Hp * Wp * vecs;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
     const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
-        const int cp = static_cast<int>(i % Cp);
-        long long t = i / Cp;
+        const int cv = static_cast<int>(i % vecs);
+        long long t = i / vecs;
         const int j = static_cast<int>(t % Wp); t /= Wp;
         const int ii = static_cast<int>(t % Hp);
         const int n = static_cast<int>(t / Hp);
-        float v = 0.f;
-        if (cp < s * s * C) {
-            const int c = cp % C, ab = cp / C, a = ab / s, b = ab % s;
-            const int ih = ii * s + a - pad_h, iw = j * s + b - pad_w;
-            if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
-                const T raw = x[((static_cast<long long>(n) * H + ih) * W + iw) * C + c];
-                v = static_cast<float>(raw);
-                if (normalize) v = (v / 255.f - mean[c % 3]) / stdv[c % 3];
+        float f[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int cp = cv * 8 + k;
+            float v = 0.f;
+            if (cp < s * s * C) {
+                const int c = cp % C, ab = cp / C, a = ab / s, b = ab % s;
+                const int ih = ii * s + a - pad_h, iw = j * s + b - pad_w;
+                if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+                    v = static_cast<float>(x[((static_cast<long long>(n) * H + ih) * W + iw) * C + c]);
+                    if (normalize) v = (v / 255.f - mean[c % 3]) / stdv[c % 3];
+                }
             }
+            f[k] = v;
         }
-        out[i] = __float2bfloat16(v);
+        *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
     }
 }
 
@@ -685,7 +693,8 @@ extern "C" int picd_small_linear_bwd(const void* dy, const void* y, const void* 
 }
 extern "C" int picd_pack_s2d(const void* x, void* out, int N, int H, int W, int C, int Hp, int Wp, int Cp, int s, int pad_h,
                              int pad_w, int src_u8, cudaStream_t st) {
-    const long long total = 1LL * N * Hp * Wp * Cp;
+    PICD_REQUIRE(Cp % 8 == 0, "pack_s2d: packed channel count %d must be a multiple of 8", Cp);
+    const long long total = 1LL * N * Hp * Wp * (Cp / 8);
     if (src_u8)
         pack_s2d_kernel<uint8_t><<<grid_for(total), 256, 0, st>>>(static_cast<const uint8_t*>(x), static_cast<bf16*>(out), N, H, W, C,
                                                                   Hp, Wp, Cp, s, pad_h, pad_w, 1);

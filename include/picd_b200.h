@@ -36,6 +36,9 @@ int picd_conv_fprop(const void* x, const void* w, void* y, float* stats, const f
                     cudaStream_t stream);
 int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
                     int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
+/* dx += ...: same as picd_conv_dgrad but ADDS into the existing bf16 dx with TMA reduce-add (residual-gradient fusion) */
+int picd_conv_dgrad_accumulate(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R,
+                               int S, int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
 /* dw (fp32, [Cout,R,S,Cin]) += ...; accumulates with red.add, so it can target the gradient arena directly */
 int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
                     int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);

@@ -88,7 +88,7 @@ def convert_sync_batchnorm(module: nn.Module, process_group=None) -> nn.Module:
     return module
 
 
-def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", residual=None):
+def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", residual=None, grad_fork=None):
     """Fused act(BN(conv(x)) + residual) using the parameters of a Conv2d/BatchNorm2d pair."""
     if bn.training:
         bn.num_batches_tracked += 1
@@ -96,7 +96,7 @@ def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", r
         x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
         stride=conv.stride, padding=conv.padding, groups=conv.groups, training=bn.training,
         momentum=bn.momentum, eps=bn.eps, act=act or "none", residual=residual,
-        sync_group=bn.sync_group)
+        sync_group=bn.sync_group, grad_fork=grad_fork)
 
 
 class Linear(nn.Module):

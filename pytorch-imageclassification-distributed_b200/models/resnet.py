@@ -28,11 +28,13 @@ class BasicBlock(nn.Module):
         self.downsample = downsample
 
     def forward(self, x):
-        identity = x
-        if self.downsample is not None:
-            identity = conv_bn_act(x, self.downsample[0], self.downsample[1], act=None)
-        out = conv_bn_act(x, self.conv1, self.bn1, "relu")
-        return conv_bn_act(out, self.conv2, self.bn2, "relu", residual=identity)
+        # the block input feeds two branches; ops.fork lets the first conv's dgrad add straight into the skip gradient
+        x1, x2, fk = ops.fork(x)
+        out = conv_bn_act(x1, self.conv1, self.bn1, "relu", grad_fork=(fk, "accumulate"))
+        if self.downsample is not None:      # created after conv1 so that its backward (the deposit) runs first
+            identity = conv_bn_act(x2, self.downsample[0], self.downsample[1], act=None, grad_fork=(fk, "deposit_dx"))
+            return conv_bn_act(out, self.conv2, self.bn2, "relu", residual=identity)
+        return conv_bn_act(out, self.conv2, self.bn2, "relu", residual=x2, grad_fork=(fk, "deposit_res"))
 
 
 class Bottleneck(nn.Module):
@@ -49,12 +51,13 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
     def forward(self, x):
-        identity = x
-        if self.downsample is not None:
-            identity = conv_bn_act(x, self.downsample[0], self.downsample[1], act=None)
-        out = conv_bn_act(x, self.conv1, self.bn1, "relu")
+        x1, x2, fk = ops.fork(x)
+        out = conv_bn_act(x1, self.conv1, self.bn1, "relu", grad_fork=(fk, "accumulate"))
         out = conv_bn_act(out, self.conv2, self.bn2, "relu")
-        return conv_bn_act(out, self.conv3, self.bn3, "relu", residual=identity)
+        if self.downsample is not None:      # created after conv1/conv2 so that its backward (the deposit) runs first
+            identity = conv_bn_act(x2, self.downsample[0], self.downsample[1], act=None, grad_fork=(fk, "deposit_dx"))
+            return conv_bn_act(out, self.conv3, self.bn3, "relu", residual=identity)
+        return conv_bn_act(out, self.conv3, self.bn3, "relu", residual=x2, grad_fork=(fk, "deposit_res"))
 
 
 class ResNet(nn.Module):

@@ -30,13 +30,28 @@ def use_native(x: torch.Tensor) -> bool:
 
 
 # ---------------------------------------------------------------------- CNN ops
+def fork(x):
+    """Split an activation that feeds two branches (a residual block's input) into two autograd aliases plus a side
+    channel, so that on the native path the two branch gradients are summed by the dgrad store instead of a separate
+    kernel.  Returns ``(x1, x2, fork)``; off the native path it is the identity and ``fork`` is None."""
+    if x.is_cuda and not _force_torch() and torch.is_grad_enabled() and x.requires_grad:
+        from . import native
+        return native.fork(x)
+    return x, x, None
+
+
 def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, padding=0, groups=1,
-                training=True, momentum=0.1, eps=1e-5, act="relu", residual=None, sync_group=False):
+                training=True, momentum=0.1, eps=1e-5, act="relu", residual=None, sync_group=False,
+                grad_fork=None):
+    """``grad_fork=(fork, role)`` with role 'accumulate' (this conv's input gradient is added into the gradient the
+    other branch deposited), 'deposit_dx' or 'deposit_res' (this op's input / residual gradient is the deposit)."""
+    if grad_fork is not None and grad_fork[0] is None:
+        grad_fork = None
     if use_native(x) and groups == 1:
         from . import native
         return native.conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride,
                                   padding=padding, training=training, momentum=momentum, eps=eps,
-                                  act=act, residual=residual, sync_group=sync_group)
+                                  act=act, residual=residual, sync_group=sync_group, grad_fork=grad_fork)
     if x.is_cuda and not _force_torch() and groups != 1:
         # depthwise convs (EfficientNet) keep the library conv but use the native BN/act kernels
         from . import native

@@ -29,6 +29,7 @@ ACT = {None: 0, "none": 0, "relu": 1, "gelu": 2, "swish": 3, "silu": 3, "sigmoid
 _SIG = {
     "picd_conv_fprop": "pppppi" + "i" * 12 + "p",
     "picd_conv_dgrad": "ppp" + "i" * 12 + "p",
+    "picd_conv_dgrad_accumulate": "ppp" + "i" * 12 + "p",
     "picd_conv_wgrad": "ppp" + "i" * 12 + "p",
     "picd_attention_fwd": "pppiiip",
     "picd_attention_bwd": "ppppppiiip",
@@ -219,16 +220,53 @@ def _conv_forward(x, w, stride, padding, stats, bias, act) -> Tuple[torch.Tensor
     return y, info
 
 
-def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool):
-    """Returns (dx or None, dw tensor or None).  dw is None when it was routed into the arena."""
+class GradFork:
+    """Side channel between the two consumers of one activation (ResNet block input: first conv + skip path).
+    The skip path's backward *deposits* its gradient tensor here; the first conv's dgrad then ADDS its result into
+    that tensor with a TMA reduce-add store, so autograd's separate gradient-sum kernel disappears."""
+    __slots__ = ("partner",)
+
+    def __init__(self):
+        self.partner = None
+
+
+class _ForkFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x), x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g1, g2):
+        if g1 is None or g2 is None:
+            return g1 if g2 is None else g2
+        if g1.data_ptr() == g2.data_ptr():
+            return g1                       # the dgrad already accumulated into the deposited tensor
+        return g1 + g2
+
+
+def fork(x):
+    """(x1, x2, fork): two autograd-distinct aliases of x plus the side channel that lets their gradients be fused."""
+    x1, x2 = _ForkFn.apply(x)
+    return x1, x2, GradFork()
+
+
+def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool, accumulate_into=None):
+    """Returns (dx or None, dw tensor or None).  dw is None when it was routed into the arena.  ``accumulate_into``:
+    an existing bf16 NHWC tensor of dx's shape that dx is added to (and which is returned as dx)."""
     i = info
     dx = None
     if need_dx:
         if i.packed:
             raise NotImplementedError("picd conv: input gradient of a packed first-layer conv")
-        dx = empty_nhwc(i.N, i.Cin, i.H, i.W, dy.device)
-        call("picd_conv_dgrad", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
-             i.OH, i.OW)
+        if accumulate_into is not None and tuple(accumulate_into.shape) == (i.N, i.Cin, i.H, i.W) and \
+                accumulate_into.dtype == torch.bfloat16 and accumulate_into.is_contiguous(memory_format=torch.channels_last):
+            dx = accumulate_into
+            call("picd_conv_dgrad_accumulate", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph,
+                 i.pw, i.OH, i.OW)
+        else:
+            dx = empty_nhwc(i.N, i.Cin, i.H, i.W, dy.device)
+            call("picd_conv_dgrad", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                 i.OH, i.OW)
     dw_ret = None
     if need_dw:
         if i.packed:
@@ -300,7 +338,7 @@ def _bn_allreduce_bwd(sums2, sync_group, C):
 
 
 class _BNCfg:
-    __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group")
+    __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group", "fork", "fork_role")
 
 
 def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
@@ -359,22 +397,33 @@ class _ConvBnAct(torch.autograd.Function):
         ctx.info = info
         ctx.save_for_backward(w, gamma, beta, y, z, coef)
         ctx.x_needs_grad = x.requires_grad
+        ctx.fork, ctx.fork_role = getattr(cfg, "fork", None), getattr(cfg, "fork_role", None)
         return z
 
     @staticmethod
     def backward(ctx, dz):
         w, gamma, beta, y, z, coef = ctx.saved_tensors
         need = ctx.needs_input_grad
+        fork_, role = ctx.fork, ctx.fork_role
         dy, dres, dgamma, dbeta = _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, ctx.has_res and need[4])
-        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1])
+        if fork_ is not None and role == "deposit_res" and dres is not None:
+            fork_.partner = dres
+        acc = fork_.partner if (fork_ is not None and role == "accumulate") else None
+        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1], accumulate_into=acc)
+        if fork_ is not None:
+            if role == "deposit_dx" and dx is not None:
+                fork_.partner = dx
+            elif role == "accumulate":
+                fork_.partner = None
         return dx, dw, dgamma, dbeta, dres, None
 
 
 def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride, padding, training, momentum, eps,
-                act, residual, sync_group):
+                act, residual, sync_group, grad_fork=None):
     cfg = _BNCfg()
     cfg.stride, cfg.padding, cfg.training, cfg.momentum, cfg.eps = stride, padding, training, momentum, eps
     cfg.act, cfg.rm, cfg.rv, cfg.sync_group = act or "none", running_mean, running_var, sync_group
+    cfg.fork, cfg.fork_role = grad_fork if grad_fork is not None else (None, None)
     return _ConvBnAct.apply(x, w, gamma, beta, residual, cfg)
 
 
@@ -403,6 +452,7 @@ class _BnAct(torch.autograd.Function):
 def bn_act(y, gamma, beta, running_mean, running_var, *, training, momentum, eps, act, residual, sync_group):
     cfg = _BNCfg()
     cfg.stride = cfg.padding = None
+    cfg.fork = cfg.fork_role = None
     cfg.training, cfg.momentum, cfg.eps = training, momentum, eps
     cfg.act, cfg.rm, cfg.rv, cfg.sync_group = act or "none", running_mean, running_var, sync_group
     return _BnAct.apply(y, gamma, beta, residual, cfg)
