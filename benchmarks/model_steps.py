@@ -1,0 +1,52 @@
+#!/usr/bin/env python
+"""Training-step time of every backbone on the native path (1 GPU, bf16, SGD-momentum, synthetic data)."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss  # noqa: E402
+from picd_b200.models import Classifier  # noqa: E402
+from picd_b200.ops import synthetic_batch  # noqa: E402
+from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec  # noqa: E402
+
+dev = torch.device("cuda")
+out = []
+for name, batch, size, opt in [("resnet18", 256, 224, "sgd"), ("resnet50", 256, 224, "sgd"), ("resnet101", 128, 224, "sgd"),
+                               ("inceptionv3", 128, 299, "adam"), ("efficientnet-b3", 64, 300, "sgd"), ("vit_b_16", 128, 224, "adamw")]:
+    try:
+        torch.manual_seed(0)
+        m = Classifier(name, 7, image_size=size).to(dev)
+        dp = FusedDataParallel(m, OptimizerSpec(opt, lr=1e-3, momentum=0.9))
+        dp.train()
+        img, lab = synthetic_batch(batch, 3, size, size, 7, 0, 0, dev, torch.bfloat16)
+        loss_fn = WeightedCrossEntropy(None)
+
+        def step():
+            loss, _ = compute_loss(dp(img), lab, loss_fn)
+            loss.backward()
+            dp.optimizer.step()
+            return loss
+        for _ in range(3):
+            l = step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(8):
+            l = step()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 8
+        rec = {"model": name, "batch": batch, "size": size, "optimizer": opt, "ms_per_step": ms, "img_per_s": batch / ms * 1e3,
+               "loss": float(l.item()), "mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30}
+    except Exception as e:  # noqa: BLE001
+        rec = {"model": name, "error": repr(e)[:300]}
+    out.append(rec)
+    print(json.dumps(rec), flush=True)
+    del m, dp
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+open(os.path.join(ROOT, "gpurun_out", "model_steps.jsonl"), "w").write("\n".join(json.dumps(r) for r in out) + "\n")

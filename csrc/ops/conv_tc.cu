@@ -56,6 +56,7 @@ struct ConvGemmParams {
     float* stats;         // [STAT_REPLICAS][2][Cout] (sum, sumsq) accumulators or nullptr
     const float* bias;    // [Cout] or nullptr
     int act;
+    int cluster;          // 1: launched as clusters of 2 with multicast B tiles (set by the host launcher)
     int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
 };
 
@@ -86,7 +87,10 @@ __device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
 // =====================================================================================================
 //  conv / GEMM forward-style kernel: D[pixels, Cout] = sum_taps A_tap[pixels, Cin] * B_tap[Cout, Cin]^T
 // =====================================================================================================
-template <bool kBiasAct>
+// kCluster: CTAs run in clusters of two that work on adjacent pixel tiles of the SAME column tile; each loads half of
+// every B (weight) tile and multicasts it to both, halving the L2->SM operand traffic of the pair (the single-CTA kernel
+// is L2-bandwidth bound on large-K tiles: ncu shows 48% tensor-pipe activity at 94 B/clk/SM of operand traffic).
+template <bool kBiasAct, bool kCluster>
 __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align_smem(smem_raw);
@@ -104,7 +108,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
     if (threadIdx.x == 0) {
         for (int i = 0; i < stages; ++i) {
             mbar_init(&bars->full[i], 1);
-            mbar_init(&bars->empty[i], 1);
+            mbar_init(&bars->empty[i], kCluster ? 2 : 1);     // cluster: both CTAs' MMA warps release a stage
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bars->tfull[i], 1);
@@ -123,13 +127,20 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
     }
     tc_fence_before();
     __syncthreads();
+    if (kCluster) cluster_sync();          // the peer's barriers exist before anything is multicast at them
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
     const int numN = p.numN;
-    const int grid_m = gridDim.x / numN;
-    const int n_tile = blockIdx.x % numN;
-    const int m_first = blockIdx.x / numN;
+    const int crank = kCluster ? static_cast<int>(cluster_ctarank()) : 0;
+    // tile walk: (non-cluster) CTA b owns column tile b % numN and pixel tiles b/numN, +grid_m, ...
+    //            (cluster)     cluster c owns column tile c % numN; its two CTAs take pixel tiles 2j and 2j+1 in lockstep
+    const int unit = kCluster ? (blockIdx.x >> 1) : blockIdx.x;
+    const int units = kCluster ? (gridDim.x >> 1) : gridDim.x;
+    const int n_tile = unit % numN;
+    const int grid_m = kCluster ? 2 * (units / numN) : units / numN;
+    const int m_first = kCluster ? 2 * (unit / numN) + crank : unit / numN;
+    const int m_limit = kCluster ? p.num_m_tiles + crank : p.num_m_tiles;   // the pair iterates while its EVEN tile exists
     const int k_iters = p.ntaps * p.kchunks;
     float* sBias = reinterpret_cast<float*>(smem + SMEM_BIAS_OFF);
     if (kBiasAct) {
@@ -149,7 +160,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
-            for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+            for (int m = m_first; m < m_limit; m += grid_m) {
                 const int tw = m % p.tiles_w;
                 const int th = (m / p.tiles_w) % p.tiles_h;
                 const int tn = m / (p.tiles_w * p.tiles_h);
@@ -163,12 +174,22 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                                     w0 + tp.dw, h0 + tp.dh, n0);
                         uint8_t* dstB = sB + stage * b_stage;
                         if (!p.b_mn) {
-                            tma_load_3d(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                            if (kCluster) {     // this CTA fetches rows [crank*BN/2, +BN/2) of the tile for both CTAs
+                                tma_load_3d_mc(dstB + crank * (b_stage >> 1), &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
+                                               n_tile * BN + crank * (BN >> 1), 3);
+                            } else {
+                                tma_load_3d(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                            }
                         } else {
                             for (int j = 0; j < BN / 64; ++j) {
                                 int c0 = n_tile * BN + j * 64;
                                 if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
-                                tma_load_3d(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
+                                if (kCluster) {
+                                    if ((j & 1) == crank)
+                                        tma_load_3d_mc(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK, 3);
+                                } else {
+                                    tma_load_3d(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
+                                }
                             }
                         }
                         if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -184,7 +205,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             int acc = 0;
             uint32_t accphase = 0;
             const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 0, p.b_mn);
-            for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+            for (int m = m_first; m < m_limit; m += grid_m) {
                 mbar_wait(&bars->tempty[acc], accphase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * 256;
@@ -200,7 +221,8 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                                                       : make_smem_desc(b_addr + k * 32, 16, 1024);
                         umma_bf16(tmem_d, adesc, bdesc, idesc, (it | k) != 0);
                     }
-                    umma_commit(&bars->empty[stage]);
+                    if (kCluster) umma_commit_mc(&bars->empty[stage], 3);   // frees the stage in both CTAs
+                    else umma_commit(&bars->empty[stage]);
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(&bars->tfull[acc]);
@@ -215,13 +237,11 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
         const int row = q * 32 + lane;           // accumulator row == pixel index inside the tile
         const int tid_e = threadIdx.x - 64;      // 0..127
-        const int colpairs = BN >> 1;
-        const int RG = 128 / colpairs >= 1 ? 128 / colpairs : 1;
-        const int my_cp = tid_e % colpairs;
-        const int my_rg = tid_e / colpairs;
-        const bool stat_thread = (p.stats != nullptr) && (my_rg < RG);
-        const int rows_per_rg = TILE_M / RG;
-        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        // The tile is drained in column halves of <= 128 channels through ONE 32 KB staging buffer (the smem this saves buys a
+        // 4th operand stage for 256-wide tiles: with 3 stages the TMA round trip was longer than the MMA time it had to hide).
+        // statistics: per half, thread -> (column pair, row group); partial sums live in registers across all tiles
+        float stA[4] = {0.f, 0.f, 0.f, 0.f}, stB[4] = {0.f, 0.f, 0.f, 0.f};   // (s0, s1, q0, q1) of half 0 / half 1
+        const int n_halves = (BN + 127) >> 7;
         int acc = 0;
         uint32_t accphase = 0;
         const int iw = row & (bw - 1);
@@ -230,102 +250,118 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         const uint32_t sOut_u32 = smem_u32(sOut);
         const uint32_t row_base = sOut_u32 + row * 128;
         const uint32_t row_xor = static_cast<uint32_t>(row & 7) << 4;
-        // statistics read-back: this thread's column pair, swizzled exactly like the writes above
-        const uint32_t stat_base = sOut_u32 + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
-        const uint32_t stat_chunk = static_cast<uint32_t>((my_cp & 31) >> 2);
-        for (int m = m_first; m < p.num_m_tiles; m += grid_m) {
+        for (int m = m_first; m < m_limit; m += grid_m) {
             const int tw = m % p.tiles_w;
             const int th = (m / p.tiles_w) % p.tiles_h;
             const int tn = m / (p.tiles_w * p.tiles_h);
             const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
-            const bool valid = (w0 + iw < p.W) && (h0 + ih < p.H) && (n0 + in_ < p.N);
+            const bool tile_ok = m < p.num_m_tiles;          // the odd CTA of the last pair may have no tile of its own
+            const bool valid = tile_ok && (w0 + iw < p.W) && (h0 + ih < p.H) && (n0 + in_ < p.N);
             const uint32_t vmask = valid ? 0xffffffffu : 0u;     // rows hanging over the tensor edge are stored as 0
             mbar_wait(&bars->tfull[acc], accphase);
             tc_fence_after();
-            if (tid_e == 0) tma_store_wait_read();        // previous tile's TMA store has drained the staging tile
-            named_barrier_sync(1, 128);
             const uint32_t t_row = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
-            for (int g = 0; g < BN / 32; ++g) {
-                uint32_t v[32];
-                tmem_ld_32x32(t_row + g * 32, v);
-                tmem_ld_wait();
-                if (kBiasAct) {
-                    const uint32_t bsrc = smem_u32(sBias) + g * 128;
+            for (int hf = 0; hf < n_halves; ++hf) {
+                const int hcols = (BN - hf * 128) < 128 ? (BN - hf * 128) : 128;     // 64 or 128 columns in this half
+                if (tid_e == 0) tma_store_wait_read();        // the previous TMA store has drained the staging buffer
+                named_barrier_sync(1, 128);
+#pragma unroll 1
+                for (int gg = 0; gg < (hcols >> 5); ++gg) {
+                    const int g = hf * 4 + gg;
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + g * 32, v);
+                    tmem_ld_wait();
+                    if (kBiasAct) {
+                        const uint32_t bsrc = smem_u32(sBias) + g * 128;
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        float b0, b1, b2, b3;     // same address in every lane: a shared-memory broadcast
-                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(bsrc + i * 4));
-                        v[i + 0] = __float_as_uint(__uint_as_float(v[i + 0]) + b0);
-                        v[i + 1] = __float_as_uint(__uint_as_float(v[i + 1]) + b1);
-                        v[i + 2] = __float_as_uint(__uint_as_float(v[i + 2]) + b2);
-                        v[i + 3] = __float_as_uint(__uint_as_float(v[i + 3]) + b3);
+                        for (int i = 0; i < 32; i += 4) {
+                            float b0, b1, b2, b3;     // same address in every lane: a shared-memory broadcast
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(bsrc + i * 4));
+                            v[i + 0] = __float_as_uint(__uint_as_float(v[i + 0]) + b0);
+                            v[i + 1] = __float_as_uint(__uint_as_float(v[i + 1]) + b1);
+                            v[i + 2] = __float_as_uint(__uint_as_float(v[i + 2]) + b2);
+                            v[i + 3] = __float_as_uint(__uint_as_float(v[i + 3]) + b3);
+                        }
+                        if (p.act == ACT_RELU) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+                        }   // other activations are separate kernels: a generic switch here forced v[] into local memory
                     }
-                    if (p.act == ACT_RELU) {
+                    const uint32_t dst = row_base + (gg >> 1) * 16384;
+                    const uint32_t chunk0 = static_cast<uint32_t>(gg & 1) * 64;
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
-                    } else if (p.act != ACT_NONE) {
+                    for (int c = 0; c < 4; ++c) {
+                        const uint32_t a0 = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1])) & vmask;
+                        const uint32_t a1 = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])) & vmask;
+                        const uint32_t a2 = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])) & vmask;
+                        const uint32_t a3 = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])) & vmask;
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((chunk0 + c * 16) ^ row_xor)),
+                                     "r"(a0), "r"(a1), "r"(a2), "r"(a3)
+                                     : "memory");
+                    }
+                }
+                if (hf == n_halves - 1) {                     // every accumulator column has been read
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bars->tempty[acc]);
+                }
+                fence_proxy_async_smem();
+                named_barrier_sync(1, 128);
+                if (tid_e == 0) {
+                    for (int j = 0; j < (hcols >> 6) && tile_ok; ++j) {
+                        const int c0 = n_tile * BN + hf * 128 + j * 64;
+                        if (c0 < p.Cout) {
+                            if (p.reduce_add) tma_reduce_add_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                            else tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
+                        }
+                    }
+                    tma_store_commit();
+                }
+                if (p.stats != nullptr) {
+                    // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read)
+                    const int colpairs = hcols >> 1;                       // 64 or 32
+                    const int my_cp = tid_e & (colpairs - 1);
+                    const int my_rg = tid_e / colpairs;                    // 2 or 4 row groups
+                    const int rows_per_rg = (TILE_M * colpairs) >> 7;      // 64 or 32
+                    const uint32_t stat_base = sOut_u32 + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
+                    const uint32_t stat_chunk = static_cast<uint32_t>((my_cp & 31) >> 2);
+                    const int r0 = my_rg * rows_per_rg;
+                    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f, t0 = 0.f, t1 = 0.f, u0 = 0.f, u1 = 0.f;
 #pragma unroll 4
-                        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(apply_act(__uint_as_float(v[i]), p.act));
+                    for (int r = r0; r < r0 + rows_per_rg; r += 2) {
+                        uint32_t wa, wb;
+                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wa) : "r"(stat_base + r * 128 + ((stat_chunk ^ (r & 7)) << 4)));
+                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wb) : "r"(stat_base + (r + 1) * 128 + ((stat_chunk ^ ((r + 1) & 7)) << 4)));
+                        const float2 fa = unpack_bf16x2(wa), fb = unpack_bf16x2(wb);
+                        s0 += fa.x; q0 = fmaf(fa.x, fa.x, q0); s1 += fa.y; q1 = fmaf(fa.y, fa.y, q1);
+                        t0 += fb.x; u0 = fmaf(fb.x, fb.x, u0); t1 += fb.y; u1 = fmaf(fb.y, fb.y, u1);
                     }
+                    if (hf == 0) { stA[0] += s0 + t0; stA[1] += s1 + t1; stA[2] += q0 + u0; stA[3] += q1 + u1; }
+                    else         { stB[0] += s0 + t0; stB[1] += s1 + t1; stB[2] += q0 + u0; stB[3] += q1 + u1; }
                 }
-                const uint32_t dst = row_base + (g >> 1) * 16384;
-                const uint32_t chunk0 = static_cast<uint32_t>(g & 1) * 64;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const uint32_t a0 = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1])) & vmask;
-                    const uint32_t a1 = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])) & vmask;
-                    const uint32_t a2 = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])) & vmask;
-                    const uint32_t a3 = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])) & vmask;
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((chunk0 + c * 16) ^ row_xor)),
-                                 "r"(a0), "r"(a1), "r"(a2), "r"(a3)
-                                 : "memory");
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bars->tempty[acc]);   // accumulator buffer may be overwritten
-            fence_proxy_async_smem();
-            named_barrier_sync(1, 128);
-            if (tid_e == 0) {
-                for (int j = 0; j < BN / 64; ++j) {
-                    const int c0 = n_tile * BN + j * 64;
-                    if (c0 < p.Cout) {
-                        if (p.reduce_add) tma_reduce_add_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
-                        else tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
-                    }
-                }
-                tma_store_commit();
-            }
-            if (stat_thread) {
-                // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read)
-                const int r0 = my_rg * rows_per_rg;
-                float t0 = 0.f, t1 = 0.f, u0 = 0.f, u1 = 0.f;     // second accumulator chain for ILP
-#pragma unroll 4
-                for (int r = r0; r < r0 + rows_per_rg; r += 2) {
-                    uint32_t wa, wb;
-                    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wa) : "r"(stat_base + r * 128 + ((stat_chunk ^ (r & 7)) << 4)));
-                    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wb) : "r"(stat_base + (r + 1) * 128 + ((stat_chunk ^ ((r + 1) & 7)) << 4)));
-                    const float2 fa = unpack_bf16x2(wa), fb = unpack_bf16x2(wb);
-                    s0 += fa.x; q0 = fmaf(fa.x, fa.x, q0); s1 += fa.y; q1 = fmaf(fa.y, fa.y, q1);
-                    t0 += fb.x; u0 = fmaf(fb.x, fb.x, u0); t1 += fb.y; u1 = fmaf(fb.y, fb.y, u1);
-                }
-                s0 += t0; s1 += t1; q0 += u0; q1 += u1;
             }
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
         }
-        if (stat_thread) {
-            const int c = n_tile * BN + my_cp * 2;
+        if (p.stats != nullptr) {
             float* st = p.stats + static_cast<size_t>((blockIdx.x / numN) % STAT_REPLICAS) * 2 * p.Cout;
-            if (c < p.Cout) { atomicAdd(st + c, s0); atomicAdd(st + p.Cout + c, q0); }
-            if (c + 1 < p.Cout) { atomicAdd(st + c + 1, s1); atomicAdd(st + p.Cout + c + 1, q1); }
+            for (int hf = 0; hf < n_halves; ++hf) {
+                const int hcols = (BN - hf * 128) < 128 ? (BN - hf * 128) : 128;
+                const int my_cp = tid_e & ((hcols >> 1) - 1);
+                const int c = n_tile * BN + hf * 128 + my_cp * 2;
+                const float v0 = hf == 0 ? stA[0] : stB[0], v1 = hf == 0 ? stA[1] : stB[1];
+                const float w0 = hf == 0 ? stA[2] : stB[2], w1 = hf == 0 ? stA[3] : stB[3];
+                if (c < p.Cout) { atomicAdd(st + c, v0); atomicAdd(st + p.Cout + c, w0); }
+                if (c + 1 < p.Cout) { atomicAdd(st + c + 1, v1); atomicAdd(st + p.Cout + c + 1, w1); }
+            }
         }
         if (tid_e == 0) tma_store_wait_all();
     }
 
     tc_fence_before();
     __syncthreads();
+    if (kCluster) cluster_sync();          // nobody leaves while the peer can still multicast into / arrive on this CTA
     if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
@@ -527,32 +563,64 @@ static int num_n_tiles(int C, int* BN) {
     return ceil_div(C, bn);
 }
 
+// Cluster-of-2 multicast pays when operand traffic (not the output) limits the kernel: enough K work per tile.
+// PICD_CLUSTER=0 disables it, =1 forces it wherever it is legal, unset = heuristic.
+static bool want_cluster(int k_iters, int num_m_tiles, int BN, bool b_mn) {
+    static const int mode = [] { const char* e = getenv("PICD_CLUSTER"); return e == nullptr ? -1 : atoi(e); }();
+    if (mode == 0 || num_m_tiles < 2) return false;
+    if (b_mn && ((BN / 64) & 1)) return false;          // MN-major B is split box-wise between the two CTAs
+    if (mode == 1) return true;
+    return k_iters >= 4;
+}
+
 static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t stream) {
     int BN;
     p.numN = num_n_tiles(Cout_gemm, &BN);
     p.BN = BN;
     p.Cout = Cout_gemm;
     const int stage_bytes = A_STAGE_BYTES + BN * 128;
-    const int staging = BN * 256;   // 128 rows x BN x 2 B
+    const int staging = std::min(BN, 128) * 256;   // 128 rows x (<= 128 columns) x 2 B: the tile is drained in halves
     int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging) / stage_bytes;
     stages = std::min(stages, 6);
     PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
     p.stages = stages;
     static bool attr_set = false;
     if (!attr_set) {
-        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
-        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        PICD_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
         attr_set = true;
     }
     const int sms = num_sms();
+    const bool bias_act = p.bias != nullptr || p.act != ACT_NONE;
+    if (p.cluster) {
+        int nclusters = std::max(p.numN, (sms / 2) / p.numN * p.numN);
+        const long long pairs = 1LL * ((p.num_m_tiles + 1) / 2) * p.numN;
+        if (nclusters > pairs) nclusters = static_cast<int>(std::max<long long>(p.numN, pairs / p.numN * p.numN));
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(2 * nclusters);
+        cfg.blockDim = dim3(192);
+        cfg.dynamicSmemBytes = MAX_DYN_SMEM;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (bias_act) PICD_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<true, true>, p));
+        else PICD_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<false, true>, p));
+        count_launch();
+        return 0;
+    }
     const long long total = 1LL * p.num_m_tiles * p.numN;
     int grid = static_cast<int>(std::min<long long>(total, sms));
     grid = std::max(p.numN, grid / p.numN * p.numN);
     // request the whole smem so that exactly one CTA (and one 512-column TMEM allocation) lives on an SM
-    if (p.bias != nullptr || p.act != ACT_NONE)
-        conv_gemm_kernel<true><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+    if (bias_act)
+        conv_gemm_kernel<true, false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
     else
-        conv_gemm_kernel<false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+        conv_gemm_kernel<false, false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -566,6 +634,7 @@ using namespace picd;
 extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* stats, const float* bias, int act,
                                int N, int H, int W, int Cin, int Cout, int R, int S, int stride, int pad_h,
                                int pad_w, int OH, int OW, cudaStream_t stream) {
+    PICD_REQUIRE(act == ACT_NONE || act == ACT_RELU, "conv_fprop: only none/relu are fused into the epilogue (act=%d)", act);
     PICD_REQUIRE(stride == 1 || stride == 2, "conv_fprop: stride %d unsupported", stride);
     PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_fprop: channels must be multiples of 8 (Cin=%d Cout=%d)", Cin, Cout);
     PICD_REQUIRE(R * S <= MAX_TAPS, "conv_fprop: %dx%d filter has too many taps", R, S);
@@ -581,7 +650,8 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
         uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
         int BN;
         num_n_tiles(Cout, &BN);
-        uint32_t box[3] = {64, 1, (uint32_t)BN};
+        p.cluster = want_cluster(R * S * ceil_div(Cin, KCHUNK), g.tiles_w * g.tiles_h * g.tiles_n, BN, false) ? 1 : 0;
+        uint32_t box[3] = {64, 1, (uint32_t)(p.cluster ? BN / 2 : BN)};     // cluster: each CTA fetches half the rows
         if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
     }
     if (make_act_map(&p.dmap, y, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
@@ -665,6 +735,11 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
             p.W = Wv; p.H = Hv; p.N = N;
             p.stats = nullptr; p.bias = nullptr; p.act = ACT_NONE;
             p.reduce_add = accumulate;
+            {
+                int BNd;
+                num_n_tiles(Cin, &BNd);
+                p.cluster = want_cluster(nt * p.kchunks, p.num_m_tiles, BNd, true) ? 1 : 0;
+            }
             if (int rc = launch_conv_gemm(p, Cin, stream)) return rc;
         }
     }
