@@ -826,9 +826,16 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
     }
     const int inner = p.ngroups * p.numM * p.numN;
     const int sms = num_sms();
-    int ksplit = std::max(1, (2 * sms + inner - 1) / inner);
-    ksplit = std::min(ksplit, std::max(1, p.num_p_tiles / 4));   // keep >= 4 k-iterations per CTA
-    ksplit = std::max(1, std::min(ksplit, p.num_p_tiles));
+    // split-K factor: minimise (waves) x (k-iterations per CTA + epilogue), i.e. avoid a nearly empty last wave
+    const int capacity = sms * (BN <= 128 ? 2 : 1);
+    const int max_split = std::max(1, std::min(p.num_p_tiles / 4, (4 * capacity) / inner));
+    int ksplit = 1;
+    long long best_cost = -1;
+    for (int ks = 1; ks <= max_split; ++ks) {
+        const long long waves = (1LL * inner * ks + capacity - 1) / capacity;
+        const long long cost = waves * ((p.num_p_tiles + ks - 1) / ks + 8);      // 8 ~ epilogue + prologue in k-iterations
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; ksplit = ks; }
+    }
     p.ksplit = ksplit;
     static bool attr_set = false;
     if (!attr_set) {
