@@ -56,6 +56,7 @@ struct ConvGemmParams {
     float* stats;         // [STAT_REPLICAS][2][Cout] (sum, sumsq) accumulators or nullptr
     const float* bias;    // [Cout] or nullptr
     int act;
+    int half_w;           // columns drained per staging pass: 128 (deep operand ring) or 256 (short-K tiles, one pass)
     int cluster;          // 1: launched as clusters of 2 with multicast B tiles (set by the host launcher)
     int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
 };
@@ -241,7 +242,8 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         // 4th operand stage for 256-wide tiles: with 3 stages the TMA round trip was longer than the MMA time it had to hide).
         // statistics: per half, thread -> (column pair, row group); partial sums live in registers across all tiles
         float stA[4] = {0.f, 0.f, 0.f, 0.f}, stB[4] = {0.f, 0.f, 0.f, 0.f};   // (s0, s1, q0, q1) of half 0 / half 1
-        const int n_halves = (BN + 127) >> 7;
+        const int hw = p.half_w, hw_log2 = hw == 256 ? 8 : 7;
+        const int n_halves = (BN + hw - 1) >> hw_log2;
         int acc = 0;
         uint32_t accphase = 0;
         const int iw = row & (bw - 1);
@@ -263,12 +265,12 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             const uint32_t t_row = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
             for (int hf = 0; hf < n_halves; ++hf) {
-                const int hcols = (BN - hf * 128) < 128 ? (BN - hf * 128) : 128;     // 64 or 128 columns in this half
+                const int hcols = (BN - hf * hw) < hw ? (BN - hf * hw) : hw;     // 64, 128 or 256 columns in this pass
                 if (tid_e == 0) tma_store_wait_read();        // the previous TMA store has drained the staging buffer
                 named_barrier_sync(1, 128);
 #pragma unroll 1
                 for (int gg = 0; gg < (hcols >> 5); ++gg) {
-                    const int g = hf * 4 + gg;
+                    const int g = hf * (hw >> 5) + gg;
                     uint32_t v[32];
                     tmem_ld_32x32(t_row + g * 32, v);
                     tmem_ld_wait();
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                 named_barrier_sync(1, 128);
                 if (tid_e == 0) {
                     for (int j = 0; j < (hcols >> 6) && tile_ok; ++j) {
-                        const int c0 = n_tile * BN + hf * 128 + j * 64;
+                        const int c0 = n_tile * BN + hf * hw + j * 64;
                         if (c0 < p.Cout) {
                             if (p.reduce_add) tma_reduce_add_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
                             else tma_store_4d(&p.dmap, sOut + j * 16384, c0, w0, h0, n0);
@@ -347,9 +349,9 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         if (p.stats != nullptr) {
             float* st = p.stats + static_cast<size_t>((blockIdx.x / numN) % STAT_REPLICAS) * 2 * p.Cout;
             for (int hf = 0; hf < n_halves; ++hf) {
-                const int hcols = (BN - hf * 128) < 128 ? (BN - hf * 128) : 128;
+                const int hcols = (BN - hf * hw) < hw ? (BN - hf * hw) : hw;
                 const int my_cp = tid_e & ((hcols >> 1) - 1);
-                const int c = n_tile * BN + hf * 128 + my_cp * 2;
+                const int c = n_tile * BN + hf * hw + my_cp * 2;
                 const float v0 = hf == 0 ? stA[0] : stB[0], v1 = hf == 0 ? stA[1] : stB[1];
                 const float w0 = hf == 0 ? stA[2] : stB[2], w1 = hf == 0 ? stA[3] : stB[3];
                 if (c < p.Cout) { atomicAdd(st + c, v0); atomicAdd(st + p.Cout + c, w0); }
@@ -579,7 +581,9 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     p.BN = BN;
     p.Cout = Cout_gemm;
     const int stage_bytes = A_STAGE_BYTES + BN * 128;
-    const int staging = std::min(BN, 128) * 256;   // 128 rows x (<= 128 columns) x 2 B: the tile is drained in halves
+    // short-K tiles are epilogue-bound: drain 256 columns in one pass; otherwise drain halves and spend the smem on stages
+    p.half_w = (BN == 256 && p.ntaps * p.kchunks <= 2) ? 256 : 128;
+    const int staging = std::min(BN, p.half_w) * 256;   // 128 rows x half_w columns x 2 B
     int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging) / stage_bytes;
     stages = std::min(stages, 6);
     PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
