@@ -121,6 +121,25 @@ def group_basic():
         if res:
             ok &= check_sparse(tag + ".dres", rn.grad, rr.grad, 3e-2, g)
 
+    # depthwise convolution (EfficientNet), symmetric and TF-"same" asymmetric padding
+    for (N, C, H, K, stride, pad) in [(2, 32, 17, 3, 1, (1, 1, 1, 1)), (2, 96, 16, 3, 2, (0, 0, 1, 1)), (2, 144, 15, 5, 2, (2, 2, 2, 2)),
+                                      (3, 40, 9, 5, 1, (2, 2, 2, 2))]:
+        x = torch.randn(N, C, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(C, 1, K, K, device=dev) / K).requires_grad_()
+        xn = x.clone().requires_grad_()
+        y = native.depthwise_conv2d(xn, w, stride, pad)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr = x.float().contiguous().requires_grad_()
+        wr = w.detach().clone().requires_grad_()
+        pt, pl, pb, pr = pad
+        yr = F.conv2d(F.pad(xr, [pl, pr, pt, pb]), wr, None, stride, 0, 1, C)
+        yr.backward(dy.float().contiguous())
+        tag = f"depthwise[{N}x{C}x{H},k{K},s{stride},pad{pad}]"
+        ok &= check(tag + ".fwd", y, yr, 2e-2, g)
+        ok &= check(tag + ".dx", xn.grad, xr.grad, 2e-2, g)
+        ok &= check(tag + ".dw", w.grad, wr.grad, 2e-2, g)
+
     # pooling
     for (k, s, p, mode) in [(3, 2, 1, "max"), (3, 2, 0, "max"), (3, 1, 1, "avg"), (5, 3, 0, "avg")]:
         x = torch.randn(2, 64, 17, 17, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)

@@ -1,0 +1,203 @@
+// Depthwise convolution (EfficientNet MBConv) for NHWC bf16: one input channel per output channel, so there is no GEMM
+// and no tensor-core shape -- it is a bandwidth-bound stencil.  Thread = 8 channels (one 16-byte vector) of one pixel;
+// weights are passed tap-major, fp32: wt[tap][C].  fprop and dgrad are gathers (no atomics); wgrad keeps the per-tap
+// partial sums of a thread's 8 channels in registers over a strip of pixels and folds them with fp32 atomics.
+#include "../common/picd_common.cuh"
+
+namespace picd {
+
+__device__ __forceinline__ void dw_unpack8(const uint4& raw, float (&f)[8]) {
+    float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y), c = unpack_bf16x2(raw.z), d = unpack_bf16x2(raw.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 dw_pack8(const float (&f)[8]) {
+    return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
+
+__global__ void __launch_bounds__(256) dw_fprop_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wt,
+                                                       __nv_bfloat16* __restrict__ y, int N, int H, int W, int C, int OH,
+                                                       int OW, int K, int stride, int pad_t, int pad_l) {
+    const int vecs = C >> 3;
+    const long long total = static_cast<long long>(N) * OH * OW * vecs;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        long long t = i / vecs;
+        const int ow = static_cast<int>(t % OW); t /= OW;
+        const int oh = static_cast<int>(t % OH);
+        const int n = static_cast<int>(t / OH);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int r = 0; r < K; ++r) {
+            const int ih = oh * stride - pad_t + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int q = 0; q < K; ++q) {
+                const int iw = ow * stride - pad_l + q;
+                if (iw < 0 || iw >= W) continue;
+                float f[8];
+                dw_unpack8(*reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * H + ih) * W + iw) * C + cv * 8), f);
+                const float* wp = wt + static_cast<long long>(r * K + q) * C + cv * 8;
+                const float4 w0 = *reinterpret_cast<const float4*>(wp), w1 = *reinterpret_cast<const float4*>(wp + 4);
+                acc[0] = fmaf(f[0], w0.x, acc[0]); acc[1] = fmaf(f[1], w0.y, acc[1]);
+                acc[2] = fmaf(f[2], w0.z, acc[2]); acc[3] = fmaf(f[3], w0.w, acc[3]);
+                acc[4] = fmaf(f[4], w1.x, acc[4]); acc[5] = fmaf(f[5], w1.y, acc[5]);
+                acc[6] = fmaf(f[6], w1.z, acc[6]); acc[7] = fmaf(f[7], w1.w, acc[7]);
+            }
+        }
+        *reinterpret_cast<uint4*>(y + i * 8) = dw_pack8(acc);
+    }
+}
+
+__global__ void __launch_bounds__(256) dw_dgrad_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ wt,
+                                                       __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int OH,
+                                                       int OW, int K, int stride, int pad_t, int pad_l) {
+    const int vecs = C >> 3;
+    const long long total = static_cast<long long>(N) * H * W * vecs;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        long long t = i / vecs;
+        const int iw = static_cast<int>(t % W); t /= W;
+        const int ih = static_cast<int>(t % H);
+        const int n = static_cast<int>(t / H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int r = (ih + pad_t) % stride; r < K; r += stride) {
+            const int th = ih + pad_t - r;
+            if (th < 0) break;
+            const int oh = th / stride;
+            if (oh >= OH) continue;
+            for (int q = (iw + pad_l) % stride; q < K; q += stride) {
+                const int tw = iw + pad_l - q;
+                if (tw < 0) break;
+                const int ow = tw / stride;
+                if (ow >= OW) continue;
+                float g[8];
+                dw_unpack8(*reinterpret_cast<const uint4*>(dy + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + cv * 8), g);
+                const float* wp = wt + static_cast<long long>(r * K + q) * C + cv * 8;
+                const float4 w0 = *reinterpret_cast<const float4*>(wp), w1 = *reinterpret_cast<const float4*>(wp + 4);
+                acc[0] = fmaf(g[0], w0.x, acc[0]); acc[1] = fmaf(g[1], w0.y, acc[1]);
+                acc[2] = fmaf(g[2], w0.z, acc[2]); acc[3] = fmaf(g[3], w0.w, acc[3]);
+                acc[4] = fmaf(g[4], w1.x, acc[4]); acc[5] = fmaf(g[5], w1.y, acc[5]);
+                acc[6] = fmaf(g[6], w1.z, acc[6]); acc[7] = fmaf(g[7], w1.w, acc[7]);
+            }
+        }
+        *reinterpret_cast<uint4*>(dx + i * 8) = dw_pack8(acc);
+    }
+}
+
+constexpr int DW_TAPS_PER_PASS = 9;
+// dwt[tap][C] += sum over output pixels of dy * x(shifted).  blockIdx = (channel-vector block, pixel strip, tap group).
+__global__ void __launch_bounds__(256) dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                                       float* __restrict__ dwt, int N, int H, int W, int C, int OH, int OW,
+                                                       int K, int stride, int pad_t, int pad_l, int tx_count, int ty_count,
+                                                       long long pix_per_block) {
+    extern __shared__ float dw_red[];          // [ty_count][tx_count][8]
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    const int tap0 = blockIdx.z * DW_TAPS_PER_PASS;
+    const int ntap = min(DW_TAPS_PER_PASS, K * K - tap0);
+    float acc[DW_TAPS_PER_PASS][8];
+#pragma unroll
+    for (int t = 0; t < DW_TAPS_PER_PASS; ++t)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[t][k] = 0.f;
+    const bool active = ty < ty_count && cv < vecs;
+    if (active) {
+        const long long P = static_cast<long long>(N) * OH * OW;
+        const long long p0 = blockIdx.y * pix_per_block;
+        long long p1 = p0 + pix_per_block;
+        if (p1 > P) p1 = P;
+        for (long long pix = p0 + ty; pix < p1; pix += ty_count) {
+            long long t = pix;
+            const int ow = static_cast<int>(t % OW); t /= OW;
+            const int oh = static_cast<int>(t % OH);
+            const int n = static_cast<int>(t / OH);
+            float g[8];
+            dw_unpack8(*reinterpret_cast<const uint4*>(dy + pix * C + cv * 8), g);
+#pragma unroll
+            for (int tt = 0; tt < DW_TAPS_PER_PASS; ++tt) {
+                if (tt < ntap) {
+                    const int tap = tap0 + tt;
+                    const int ih = oh * stride - pad_t + tap / K, iw = ow * stride - pad_l + tap % K;
+                    if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+                        float f[8];
+                        dw_unpack8(*reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * H + ih) * W + iw) * C + cv * 8), f);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) acc[tt][k] = fmaf(g[k], f[k], acc[tt][k]);
+                    }
+                }
+            }
+        }
+    }
+    // fold the row dimension of the block through shared memory, one tap at a time
+#pragma unroll
+    for (int tt = 0; tt < DW_TAPS_PER_PASS; ++tt) {
+        if (tt >= ntap) break;                 // uniform over the block
+        __syncthreads();
+        if (ty < ty_count) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dw_red[(ty * tx_count + tx) * 8 + k] = acc[tt][k];
+        }
+        __syncthreads();
+        if (active && ty == 0) {
+            float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += dw_red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(dwt + static_cast<long long>(tap0 + tt) * C + cv * 8 + k, s[k]);
+        }
+    }
+}
+
+static int dw_grid(long long work) {
+    long long b = (work + 255) / 256;
+    const long long cap = 16LL * num_sms();
+    if (b > cap) b = cap;
+    return static_cast<int>(b < 1 ? 1 : b);
+}
+
+}  // namespace picd
+
+using namespace picd;
+
+// y[N,OH,OW,C] = depthwise KxK conv of x[N,H,W,C]; wt = weights as fp32 [K*K][C]; padding may be asymmetric
+// (pad_t/pad_l given, bottom/right implied by OH/OW), which is how TF-"same" stride-2 layers are expressed.
+extern "C" int picd_depthwise_fprop(const void* x, const float* wt, void* y, int N, int H, int W, int C, int OH, int OW, int K,
+                                    int stride, int pad_t, int pad_l, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    const long long total = 1LL * N * OH * OW * (C / 8);
+    dw_fprop_kernel<<<dw_grid(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), wt, static_cast<__nv_bfloat16*>(y), N, H, W,
+                                                   C, OH, OW, K, stride, pad_t, pad_l);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, int N, int H, int W, int C, int OH, int OW, int K,
+                                    int stride, int pad_t, int pad_l, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    const long long total = 1LL * N * H * W * (C / 8);
+    dw_dgrad_kernel<<<dw_grid(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), wt, static_cast<__nv_bfloat16*>(dx), N, H, W,
+                                                   C, OH, OW, K, stride, pad_t, pad_l);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// dwt (fp32 [K*K][C]) += ...
+extern "C" int picd_depthwise_wgrad(const void* x, const void* dy, float* dwt, int N, int H, int W, int C, int OH, int OW, int K,
+                                    int stride, int pad_t, int pad_l, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    const int vecs = C / 8;
+    const int tx = vecs < 32 ? vecs : 32, ty = 256 / tx;
+    const int gx = (vecs + tx - 1) / tx;
+    const long long P = 1LL * N * OH * OW;
+    long long gy = (4LL * num_sms()) / gx;
+    if (gy < 1) gy = 1;
+    long long ppb = (P + gy - 1) / gy;
+    if (ppb < ty) ppb = ty;
+    gy = (P + ppb - 1) / ppb;
+    const int gz = (K * K + DW_TAPS_PER_PASS - 1) / DW_TAPS_PER_PASS;
+    dw_wgrad_kernel<<<dim3(gx, static_cast<unsigned>(gy), gz), 256, tx * ty * 8 * sizeof(float), st>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dwt, N, H, W, C, OH, OW, K, stride, pad_t, pad_l,
+        tx, ty, ppb);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}

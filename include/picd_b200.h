@@ -55,6 +55,15 @@ int picd_attention_fwd(const void* qkv, void* o, float* lse, int B, int S, int H
 int picd_attention_bwd(const void* qkv, const void* o, const void* dout, const float* lse, float* delta, void* dqkv, int B,
                        int S, int H, cudaStream_t stream);
 
+/* ---- depthwise convolution (EfficientNet MBConv; reference backbone 'efficientnet-b3', nn/classifier.py:17-18).
+ *      wt / dwt are fp32 tap-major [K*K][C]; asymmetric (TF-"same") padding via pad_t/pad_l + explicit OH/OW. */
+int picd_depthwise_fprop(const void* x, const float* wt, void* y, int N, int H, int W, int C, int OH, int OW, int K, int stride,
+                         int pad_t, int pad_l, cudaStream_t stream);
+int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, int N, int H, int W, int C, int OH, int OW, int K, int stride,
+                         int pad_t, int pad_l, cudaStream_t stream);
+int picd_depthwise_wgrad(const void* x, const void* dy, float* dwt, int N, int H, int W, int C, int OH, int OW, int K, int stride,
+                         int pad_t, int pad_l, cudaStream_t stream);
+
 /* ---- BatchNorm family (torch/nn/modules/_functions.py:39-179 = SURVEY.md K5-K10,K12) ------------------- */
 /* Statistics buffers produced by kernels (conv_fprop `stats`, bn_stats, bn_bwd_reduce `sums`) hold
  * picd_stat_replicas() (= 16) copies of [2C] floats, zeroed by the caller; consumers take the number of copies. */

@@ -7,9 +7,10 @@ TF-style "same" padding, swish) with the same state-dict keys (``_conv_stem``,
 ``_blocks.N._expand_conv`` ...) so such checkpoints load, and exposes the head as
 ``_fc`` for :class:`picd_b200.models.Classifier` to swap.
 
-Depthwise convolutions have no GEMM shape (one input channel per output channel),
-so they run on the library path; the pointwise convs, BN, swish, SE and head go
-through the same fused ops as the other backbones.
+Depthwise convolutions have no GEMM shape (one input channel per output channel):
+they run on a native bandwidth-bound stencil kernel (csrc/ops/depthwise.cu) that also
+takes the asymmetric TF-"same" padding directly; the pointwise convs, BN, swish, SE and
+head go through the same fused ops as the other backbones.
 """
 from __future__ import annotations
 
@@ -41,6 +42,14 @@ def _round_filters(f, width, divisor=8):
     if new_f < 0.9 * f:
         new_f += divisor
     return int(new_f)
+
+
+def _same_pad_amounts(x, k, s):
+    """(top, left, bottom, right) of TF 'SAME' padding for the current spatial size."""
+    ih, iw = x.shape[-2:]
+    ph = max((math.ceil(ih / s) - 1) * s + k - ih, 0)
+    pw = max((math.ceil(iw / s) - 1) * s + k - iw, 0)
+    return (ph // 2, pw // 2, ph - ph // 2, pw - pw // 2)
 
 
 def _same_pad(x, k, s):
@@ -76,7 +85,7 @@ class MBConv(nn.Module):
         inp = x
         if self.expand != 1:
             x = conv_bn_act(x, self._expand_conv, self._bn0, "swish")
-        x = conv_bn_act(_same_pad(x, self.k, self.s), self._depthwise_conv, self._bn1, "swish")
+        x = conv_bn_act(x, self._depthwise_conv, self._bn1, "swish", padding=_same_pad_amounts(x, self.k, self.s))
         # squeeze-excite on the pooled [N, C] vector: two tiny GEMMs
         s = ops.global_avg_pool(x)
         s = ops.linear(s, self._se_reduce.weight.flatten(1), self._se_reduce.bias, "swish")

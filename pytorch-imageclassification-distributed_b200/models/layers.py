@@ -88,13 +88,16 @@ def convert_sync_batchnorm(module: nn.Module, process_group=None) -> nn.Module:
     return module
 
 
-def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", residual=None, grad_fork=None):
-    """Fused act(BN(conv(x)) + residual) using the parameters of a Conv2d/BatchNorm2d pair."""
+def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", residual=None, grad_fork=None,
+                padding=None):
+    """Fused act(BN(conv(x)) + residual) using the parameters of a Conv2d/BatchNorm2d pair.  ``padding`` overrides the
+    conv's own (used for TF-"same" layers: a (top, left, bottom, right) tuple)."""
     if bn.training:
         bn.num_batches_tracked += 1
     return ops.conv_bn_act(
         x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
-        stride=conv.stride, padding=conv.padding, groups=conv.groups, training=bn.training,
+        stride=conv.stride, padding=conv.padding if padding is None else padding, groups=conv.groups,
+        training=bn.training,
         momentum=bn.momentum, eps=bn.eps, act=act or "none", residual=residual,
         sync_group=bn.sync_group, grad_fork=grad_fork)
 

@@ -47,15 +47,27 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, paddi
     other branch deposited), 'deposit_dx' or 'deposit_res' (this op's input / residual gradient is the deposit)."""
     if grad_fork is not None and grad_fork[0] is None:
         grad_fork = None
+    if isinstance(padding, (tuple, list)) and len(padding) == 4:
+        # (top, left, bottom, right): TF-"same" layers.  The native depthwise kernel takes it as is; everything else pads.
+        pt, pl, pb, pr = padding
+        dw = groups != 1 and groups == x.shape[1] == w.shape[0] and groups % 8 == 0 and x.is_cuda and not _force_torch()
+        if not dw:
+            if pt or pl or pb or pr:
+                x = torch.nn.functional.pad(x, [pl, pr, pt, pb])
+                if x.dim() == 4:
+                    x = x.contiguous(memory_format=torch.channels_last)
+            padding = 0
     if use_native(x) and groups == 1:
         from . import native
         return native.conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride,
                                   padding=padding, training=training, momentum=momentum, eps=eps,
                                   act=act, residual=residual, sync_group=sync_group, grad_fork=grad_fork)
     if x.is_cuda and not _force_torch() and groups != 1:
-        # depthwise convs (EfficientNet) keep the library conv but use the native BN/act kernels
         from . import native
-        y = ref.conv2d(x, w, None, stride, padding, groups)
+        if groups == x.shape[1] == w.shape[0] and w.shape[1] == 1 and w.shape[2] == w.shape[3] and groups % 8 == 0:
+            y = native.depthwise_conv2d(x, w, stride, padding)       # native stencil kernel (csrc/ops/depthwise.cu)
+        else:
+            y = ref.conv2d(x, w, None, stride, padding, groups)      # generic grouped conv: library
         return native.bn_act(y, gamma, beta, running_mean, running_var, training=training,
                              momentum=momentum, eps=eps, act=act, residual=residual,
                              sync_group=sync_group)

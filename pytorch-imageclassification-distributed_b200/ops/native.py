@@ -33,6 +33,9 @@ _SIG = {
     "picd_conv_wgrad": "ppp" + "i" * 12 + "p",
     "picd_attention_fwd": "pppiiip",
     "picd_attention_bwd": "ppppppiiip",
+    "picd_depthwise_fprop": "ppp" + "i" * 10 + "p",
+    "picd_depthwise_dgrad": "ppp" + "i" * 10 + "p",
+    "picd_depthwise_wgrad": "ppp" + "i" * 10 + "p",
     "picd_gemm_nt": "ppppiiiip",
     "picd_gemm_nn": "pppiiip",
     "picd_gemm_tn_f32": "pppiiip",
@@ -489,6 +492,58 @@ def conv2d(x, w, bias, stride, padding):
     return _Conv2d.apply(x, w, bias, stride, padding)
 
 
+# --------------------------------------------------------------------------- depthwise conv
+class _Depthwise(torch.autograd.Function):
+    """Depthwise KxK convolution (groups == channels).  ``pad`` = (top, left, bottom, right) so TF-"same" layers need no
+    explicit padding copy."""
+
+    @staticmethod
+    def forward(ctx, x, w, stride, pad):
+        x = nhwc(x)
+        N, C, H, W = x.shape
+        K = w.shape[2]
+        pt, pl, pb, pr = pad
+        OH, OW = (H + pt + pb - K) // stride + 1, (W + pl + pr - K) // stride + 1
+        wt = w.detach().reshape(C, K * K).t().contiguous().float()             # tap-major fp32 [K*K, C]
+        y = empty_nhwc(N, C, OH, OW, x.device)
+        call("picd_depthwise_fprop", x, wt, y, N, H, W, C, OH, OW, K, stride, pt, pl)
+        ctx.geom = (N, H, W, C, OH, OW, K, stride, pt, pl)
+        ctx.save_for_backward(x, w, wt)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, wt = ctx.saved_tensors
+        N, H, W, C, OH, OW, K, stride, pt, pl = ctx.geom
+        dy = nhwc(dy)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = empty_nhwc(N, C, H, W, dy.device)
+            call("picd_depthwise_dgrad", dy, wt, dx, N, H, W, C, OH, OW, K, stride, pt, pl)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dwt = torch.zeros(K * K, C, dtype=torch.float32, device=dy.device)
+            call("picd_depthwise_wgrad", x, dy, dwt, N, H, W, C, OH, OW, K, stride, pt, pl)
+            g = dwt.t().reshape(C, 1, K, K)
+            tgt, routed = _grad_target(w, True)
+            if routed:
+                tgt.add_(g)
+                _mark_ready(w)
+            else:
+                dw = g.contiguous(memory_format=torch.channels_last)
+        return dx, dw, None, None
+
+
+def depthwise_conv2d(x, w, stride, pad):
+    """pad: int, (ph, pw) or (top, left, bottom, right)."""
+    if isinstance(pad, int):
+        pad = (pad, pad, pad, pad)
+    elif len(pad) == 2:
+        pad = (pad[0], pad[1], pad[0], pad[1])
+    s = stride if isinstance(stride, int) else stride[0]
+    return _Depthwise.apply(x, w, s, tuple(pad))
+
+
 # --------------------------------------------------------------------------- linear
 _TC_MIN_WORK = 1 << 24
 
@@ -602,7 +657,8 @@ def linear(x, w, b, act):
         return _LinearTC.apply(x, w, b, act)
     if act in (None, "none", "relu"):
         return _LinearSmall.apply(x, w, b, act)
-    return ref.linear(x, w, b, act)          # swish/sigmoid squeeze-excite vectors: library path
+    # swish / sigmoid / gelu on tiny tensors (squeeze-excite vectors): native linear, element-wise torch activation
+    return ref.activation(_LinearSmall.apply(x, w, b, None), act).to(torch.bfloat16)
 
 
 # --------------------------------------------------------------------------- pooling
