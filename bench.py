@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--sync-bn", action="store_true")
     ap.add_argument("--optimizer", default="sgd")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying the "
+                    "captured CUDA graph of the step")
     ap.add_argument("--local_rank", "--local-rank", type=int, default=0)
     return ap.parse_args()
 
@@ -87,7 +89,8 @@ def timed_region(run_steps, steps, device, rank):
 def run_b200(args):
     import torch
     from picd_b200.data import SyntheticDeviceLoader, SyntheticHostLoader
-    from picd_b200.engine.trainer import WeightedCrossEntropy, compute_loss
+    from picd_b200.engine.graphed import GraphedTrainStep
+    from picd_b200.engine.trainer import WeightedCrossEntropy
     from picd_b200.models import Classifier, convert_sync_batchnorm
     from picd_b200.ops import require_lib
     from picd_b200.parallel import dist as D
@@ -112,13 +115,8 @@ def run_b200(args):
     counter = {"i": 0}
     last = {}
 
-    def step(images, labels):
-        out = dp(images)
-        loss, _ = compute_loss(out, labels, loss_fn)
-        dp.optimizer.zero_grad()
-        loss.backward()
-        dp.optimizer.step()
-        return loss
+    # the public training-step API: eager for the first calls, then one CUDA-graph replay per step (engine/graphed.py)
+    step = GraphedTrainStep(dp, loss_fn, dp.optimizer, warmup=max(1, min(2, args.warmup - 1)), enabled=not args.no_graph)
 
     def run_device(n):
         for _ in range(n):
@@ -127,9 +125,10 @@ def run_b200(args):
             last["loss"] = step(images, labels)
 
     run_device(args.warmup)
-    l0 = lib.picd_launch_count()
+    l0, r0 = lib.picd_launch_count(), step.replays
     ms, clocks = timed_region(run_device, args.steps, device, rank)
-    launches = int(lib.picd_launch_count() - l0)
+    # kernels of this library launched in the timed region: direct launches + those inside the replayed graphs
+    launches = int(lib.picd_launch_count() - l0) + (step.replays - r0) * step.launches_per_replay
     final_loss = float(last["loss"].item())
     value = args.batch * world * args.steps / (ms / 1e3)
 
@@ -160,7 +159,8 @@ def run_b200(args):
             "config": {"model": f"{args.model}+MLP head ({NUM_CLASSES} classes)", "global_batch": args.batch * world,
                        "per_gpu_batch": args.batch, "image_size": args.image_size, "seq_len": None,
                        "optimizer": f"{args.optimizer}-momentum lr={LR} wd={WEIGHT_DECAY}", "sync_bn": args.sync_bn,
-                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)",
+                       "cuda_graph": bool(step.graph is not None)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss}))
     D.barrier()
     D.shutdown()

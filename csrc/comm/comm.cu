@@ -90,7 +90,14 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
                                                                      float* __restrict__ state0,
                                                                      float* __restrict__ state1, OptArgs opt,
                                                                      int slot_in, int slot_out, unsigned epoch,
-                                                                     unsigned* block_counter) {
+                                                                     unsigned* block_counter,
+                                                                     const float* __restrict__ dyn) {
+    if (dyn != nullptr) {
+        // step-varying scalars come from device memory so that a captured CUDA graph can be replayed step after step:
+        // (lr, 1 - beta1^t, 1 - beta2^t, flag epoch as raw bits), rewritten by the host before each replay
+        opt.lr = dyn[0]; opt.bc1 = dyn[1]; opt.bc2 = dyn[2];
+        epoch = __float_as_uint(dyn[3]);
+    }
     const unsigned* my_flags = pt.flags[rank];
     if (mode != 0) {
         if (blockIdx.x == 0) signal_peers(pt, slot_in, rank, W, epoch);   // my gradients for this bucket are final
@@ -308,10 +315,10 @@ extern "C" int picd_comm_destroy(void* ctx) {
 
 // One gradient bucket: all-reduce over peer memory + 1/W + optimizer + bf16 shadow + gradient re-zero.
 // mode: 0 local, 1 one-shot, 2 two-shot.  `epoch` must increase by one per call per bucket on every rank.
-extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count,
-                                           float* state0, float* state1, int kind, float lr, float momentum,
-                                           float beta1, float beta2, float eps, float weight_decay, float bc1,
-                                           float bc2, int nesterov, unsigned epoch, int blocks, cudaStream_t stream) {
+static int fused_update_impl(void* ctx, int bucket, int mode, long long start, long long count,
+                             float* state0, float* state1, int kind, float lr, float momentum,
+                             float beta1, float beta2, float eps, float weight_decay, float bc1,
+                             float bc2, int nesterov, unsigned epoch, int blocks, const float* dyn, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
     PICD_REQUIRE(count % (4 * c->world) == 0, "fused_allreduce_update: bucket of %lld elements does not split into "
                  "16-byte slices over %d ranks", count, c->world);
@@ -339,9 +346,28 @@ extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long
         if (blocks > max_resident) blocks = max_resident;
     }
     fused_allreduce_update_kernel<<<blocks, 512, 0, stream>>>(c->pt, c->rank, c->world, mode, start, count, state0, state1, o,
-                                                              2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket);
+                                                              2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket, dyn);
     PICD_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count,
+                                           float* state0, float* state1, int kind, float lr, float momentum,
+                                           float beta1, float beta2, float eps, float weight_decay, float bc1,
+                                           float bc2, int nesterov, unsigned epoch, int blocks, cudaStream_t stream) {
+    return fused_update_impl(ctx, bucket, mode, start, count, state0, state1, kind, lr, momentum, beta1, beta2, eps,
+                             weight_decay, bc1, bc2, nesterov, epoch, blocks, nullptr, stream);
+}
+
+// Graph-replay variant: lr, the two Adam bias corrections and the flag epoch are read from the device array
+// dyn[4] = {lr, bc1, bc2, epoch bits} at run time instead of being frozen into the launch.
+extern "C" int picd_fused_allreduce_update_dyn(void* ctx, int bucket, int mode, long long start, long long count,
+                                               float* state0, float* state1, int kind, float momentum, float beta1,
+                                               float beta2, float eps, float weight_decay, int nesterov, int blocks,
+                                               const float* dyn, cudaStream_t stream) {
+    PICD_REQUIRE(dyn != nullptr, "fused_allreduce_update_dyn: dyn must point at 4 device floats");
+    return fused_update_impl(ctx, bucket, mode, start, count, state0, state1, kind, 0.f, momentum, beta1, beta2, eps,
+                             weight_decay, 1.f, 1.f, nesterov, 0u, blocks, dyn, stream);
 }
 
 extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n,

@@ -92,7 +92,7 @@ __device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
 // every B (weight) tile and multicasts it to both, halving the L2->SM operand traffic of the pair (the single-CTA kernel
 // is L2-bandwidth bound on large-K tiles: ncu shows 48% tensor-pipe activity at 94 B/clk/SM of operand traffic).
 template <bool kBiasAct, bool kCluster>
-__global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+__global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align_smem(smem_raw);
     SmemBars* bars = reinterpret_cast<SmemBars*>(smem);
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bars->tfull[i], 1);
-            mbar_init(&bars->tempty[i], 4);
+            mbar_init(&bars->tempty[i], 8);
         }
         fence_mbar_init();
     }
@@ -232,16 +232,21 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
             }
         }
     } else {
-        // ------------------------------------------------------------------ epilogue (4 warps)
+        // ------------------------------------------------------------------ epilogue (8 warps)
         // Kept deliberately compact (explicit shared-space accesses, no per-element branches): an earlier version
         // unrolled into ~4800 SASS instructions and stalled on instruction fetch (profiles/ncu_fprop_64_256_v1.md).
+        // Two warps share each TMEM lane quarter and split the columns of a pass between them: with one warp per SM
+        // sub-partition nothing hid the tcgen05.ld / ld.shared latencies and short-K layers ran at the epilogue's pace.
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
+        const int colhalf = (warp - 2) >> 2;     // which 32-column groups of a pass this warp drains (even / odd)
         const int row = q * 32 + lane;           // accumulator row == pixel index inside the tile
-        const int tid_e = threadIdx.x - 64;      // 0..127
-        // The tile is drained in column halves of <= 128 channels through ONE 32 KB staging buffer (the smem this saves buys a
+        const int tid_e = threadIdx.x - 64;      // 0..255
+        // The tile is drained in column passes of <= half_w channels through ONE staging buffer (the smem this saves buys a
         // 4th operand stage for 256-wide tiles: with 3 stages the TMA round trip was longer than the MMA time it had to hide).
-        // statistics: per half, thread -> (column pair, row group); partial sums live in registers across all tiles
-        float stA[4] = {0.f, 0.f, 0.f, 0.f}, stB[4] = {0.f, 0.f, 0.f, 0.f};   // (s0, s1, q0, q1) of half 0 / half 1
+        // statistics: per pass, thread -> (8-channel chunk, row group); partial sums live in registers across all tiles
+        float stS[2][8], stQ[2][8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { stS[0][i] = stS[1][i] = 0.f; stQ[0][i] = stQ[1][i] = 0.f; }
         const int hw = p.half_w, hw_log2 = hw == 256 ? 8 : 7;
         const int n_halves = (BN + hw - 1) >> hw_log2;
         int acc = 0;
@@ -252,6 +257,40 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
         const uint32_t sOut_u32 = smem_u32(sOut);
         const uint32_t row_base = sOut_u32 + row * 128;
         const uint32_t row_xor = static_cast<uint32_t>(row & 7) << 4;
+        const uint32_t bias_u32 = smem_u32(sBias);
+
+        // converts one 32-column group to bf16 and writes it into the 128B-swizzled staging tile
+        auto stage_group = [&](uint32_t (&v)[32], int g, int gg, uint32_t vmask) {
+            if (kBiasAct) {
+                const uint32_t bsrc = bias_u32 + g * 128;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    float b0, b1, b2, b3;     // same address in every lane: a shared-memory broadcast
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(bsrc + i * 4));
+                    v[i + 0] = __float_as_uint(__uint_as_float(v[i + 0]) + b0);
+                    v[i + 1] = __float_as_uint(__uint_as_float(v[i + 1]) + b1);
+                    v[i + 2] = __float_as_uint(__uint_as_float(v[i + 2]) + b2);
+                    v[i + 3] = __float_as_uint(__uint_as_float(v[i + 3]) + b3);
+                }
+                if (p.act == ACT_RELU) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+                }   // other activations are separate kernels: a generic switch here forced v[] into local memory
+            }
+            const uint32_t dst = row_base + (gg >> 1) * 16384;
+            const uint32_t chunk0 = static_cast<uint32_t>(gg & 1) * 64;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint32_t a0 = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1])) & vmask;
+                const uint32_t a1 = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])) & vmask;
+                const uint32_t a2 = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])) & vmask;
+                const uint32_t a3 = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])) & vmask;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((chunk0 + c * 16) ^ row_xor)),
+                             "r"(a0), "r"(a1), "r"(a2), "r"(a3)
+                             : "memory");
+            }
+        };
+
         for (int m = m_first; m < m_limit; m += grid_m) {
             const int tw = m % p.tiles_w;
             const int th = (m / p.tiles_w) % p.tiles_h;
@@ -266,41 +305,22 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
 #pragma unroll 1
             for (int hf = 0; hf < n_halves; ++hf) {
                 const int hcols = (BN - hf * hw) < hw ? (BN - hf * hw) : hw;     // 64, 128 or 256 columns in this pass
+                const int g0 = hf * (hw >> 5);
+                const int ngt = hcols >> 6;                   // 32-column groups per thread: 1, 2 or 4
+                uint32_t va[32], vb[32];
+                tmem_ld_32x32(t_row + (g0 + colhalf) * 32, va);       // in flight while the staging buffer drains
                 if (tid_e == 0) tma_store_wait_read();        // the previous TMA store has drained the staging buffer
-                named_barrier_sync(1, 128);
+                named_barrier_sync(1, 256);
 #pragma unroll 1
-                for (int gg = 0; gg < (hcols >> 5); ++gg) {
-                    const int g = hf * (hw >> 5) + gg;
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_row + g * 32, v);
+                for (int j = 0; j < ngt; j += 2) {            // software pipeline: the next group loads while this one converts
+                    const int gg = 2 * j + colhalf;
                     tmem_ld_wait();
-                    if (kBiasAct) {
-                        const uint32_t bsrc = smem_u32(sBias) + g * 128;
-#pragma unroll
-                        for (int i = 0; i < 32; i += 4) {
-                            float b0, b1, b2, b3;     // same address in every lane: a shared-memory broadcast
-                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(bsrc + i * 4));
-                            v[i + 0] = __float_as_uint(__uint_as_float(v[i + 0]) + b0);
-                            v[i + 1] = __float_as_uint(__uint_as_float(v[i + 1]) + b1);
-                            v[i + 2] = __float_as_uint(__uint_as_float(v[i + 2]) + b2);
-                            v[i + 3] = __float_as_uint(__uint_as_float(v[i + 3]) + b3);
-                        }
-                        if (p.act == ACT_RELU) {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
-                        }   // other activations are separate kernels: a generic switch here forced v[] into local memory
-                    }
-                    const uint32_t dst = row_base + (gg >> 1) * 16384;
-                    const uint32_t chunk0 = static_cast<uint32_t>(gg & 1) * 64;
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const uint32_t a0 = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1])) & vmask;
-                        const uint32_t a1 = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])) & vmask;
-                        const uint32_t a2 = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])) & vmask;
-                        const uint32_t a3 = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])) & vmask;
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((chunk0 + c * 16) ^ row_xor)),
-                                     "r"(a0), "r"(a1), "r"(a2), "r"(a3)
-                                     : "memory");
+                    if (j + 1 < ngt) tmem_ld_32x32(t_row + (g0 + gg + 2) * 32, vb);
+                    stage_group(va, g0 + gg, gg, vmask);
+                    if (j + 1 < ngt) {
+                        tmem_ld_wait();
+                        if (j + 2 < ngt) tmem_ld_32x32(t_row + (g0 + gg + 4) * 32, va);
+                        stage_group(vb, g0 + gg + 2, gg + 2, vmask);
                     }
                 }
                 if (hf == n_halves - 1) {                     // every accumulator column has been read
@@ -309,7 +329,7 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                     if (lane == 0) mbar_arrive(&bars->tempty[acc]);
                 }
                 fence_proxy_async_smem();
-                named_barrier_sync(1, 128);
+                named_barrier_sync(1, 256);
                 if (tid_e == 0) {
                     for (int j = 0; j < (hcols >> 6) && tile_ok; ++j) {
                         const int c0 = n_tile * BN + hf * hw + j * 64;
@@ -321,44 +341,71 @@ __global__ void __launch_bounds__(192, 1) conv_gemm_kernel(const __grid_constant
                     tma_store_commit();
                 }
                 if (p.stats != nullptr) {
-                    // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read)
-                    const int colpairs = hcols >> 1;                       // 64 or 32
-                    const int my_cp = tid_e & (colpairs - 1);
-                    const int my_rg = tid_e / colpairs;                    // 2 or 4 row groups
-                    const int rows_per_rg = (TILE_M * colpairs) >> 7;      // 64 or 32
-                    const uint32_t stat_base = sOut_u32 + (my_cp >> 5) * 16384 + (my_cp & 3) * 4;
-                    const uint32_t stat_chunk = static_cast<uint32_t>((my_cp & 31) >> 2);
-                    const int r0 = my_rg * rows_per_rg;
-                    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f, t0 = 0.f, t1 = 0.f, u0 = 0.f, u1 = 0.f;
-#pragma unroll 4
-                    for (int r = r0; r < r0 + rows_per_rg; r += 2) {
-                        uint32_t wa, wb;
-                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wa) : "r"(stat_base + r * 128 + ((stat_chunk ^ (r & 7)) << 4)));
-                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wb) : "r"(stat_base + (r + 1) * 128 + ((stat_chunk ^ ((r + 1) & 7)) << 4)));
-                        const float2 fa = unpack_bf16x2(wa), fb = unpack_bf16x2(wb);
-                        s0 += fa.x; q0 = fmaf(fa.x, fa.x, q0); s1 += fa.y; q1 = fmaf(fa.y, fa.y, q1);
-                        t0 += fb.x; u0 = fmaf(fb.x, fb.x, u0); t1 += fb.y; u1 = fmaf(fb.y, fb.y, u1);
+                    // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read): every thread
+                    // owns one 16-byte chunk (8 channels) over a group of rows, read back from the staging tile with v4 loads
+                    const int nch = hcols >> 3;                            // 8, 16 or 32 chunks per row
+                    const int my_ch = tid_e & (nch - 1);
+                    const int rows_per_rg = nch >> 1;                      // 4, 8 or 16 rows per thread
+                    const int r0 = (tid_e / nch) * rows_per_rg;
+                    const uint32_t stat_base = sOut_u32 + (my_ch >> 3) * 16384;
+                    const uint32_t stat_chunk = static_cast<uint32_t>(my_ch & 7);
+                    float s[8], qq[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] = 0.f; qq[i] = 0.f; }
+#pragma unroll 2
+                    for (int r = r0; r < r0 + rows_per_rg; ++r) {
+                        uint32_t w4[4];
+                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(w4[0]), "=r"(w4[1]), "=r"(w4[2]), "=r"(w4[3])
+                                     : "r"(stat_base + r * 128 + ((stat_chunk ^ (r & 7)) << 4)));
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 f = unpack_bf16x2(w4[i]);
+                            s[2 * i] += f.x; qq[2 * i] = fmaf(f.x, f.x, qq[2 * i]);
+                            s[2 * i + 1] += f.y; qq[2 * i + 1] = fmaf(f.y, f.y, qq[2 * i + 1]);
+                        }
                     }
-                    if (hf == 0) { stA[0] += s0 + t0; stA[1] += s1 + t1; stA[2] += q0 + u0; stA[3] += q1 + u1; }
-                    else         { stB[0] += s0 + t0; stB[1] += s1 + t1; stB[2] += q0 + u0; stB[3] += q1 + u1; }
+                    if (hf == 0) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { stS[0][i] += s[i]; stQ[0][i] += qq[i]; }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { stS[1][i] += s[i]; stQ[1][i] += qq[i]; }
+                    }
                 }
             }
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
         }
+        if (tid_e == 0) tma_store_wait_all();
         if (p.stats != nullptr) {
+            // fold the row groups through the (now idle) staging buffer, then one atomic per channel and statistic
             float* st = p.stats + static_cast<size_t>((blockIdx.x / numN) % STAT_REPLICAS) * 2 * p.Cout;
+            float* red = reinterpret_cast<float*>(sOut);       // [row group][2][hcols] floats: 16 KB for every pass width
             for (int hf = 0; hf < n_halves; ++hf) {
                 const int hcols = (BN - hf * hw) < hw ? (BN - hf * hw) : hw;
-                const int my_cp = tid_e & ((hcols >> 1) - 1);
-                const int c = n_tile * BN + hf * hw + my_cp * 2;
-                const float v0 = hf == 0 ? stA[0] : stB[0], v1 = hf == 0 ? stA[1] : stB[1];
-                const float w0 = hf == 0 ? stA[2] : stB[2], w1 = hf == 0 ? stA[3] : stB[3];
-                if (c < p.Cout) { atomicAdd(st + c, v0); atomicAdd(st + p.Cout + c, w0); }
-                if (c + 1 < p.Cout) { atomicAdd(st + c + 1, v1); atomicAdd(st + p.Cout + c + 1, w1); }
+                const int nch = hcols >> 3;
+                const int my_ch = tid_e & (nch - 1);
+                const int my_rg = tid_e / nch;
+                const int nrg = 256 / nch;
+                named_barrier_sync(1, 256);                    // staging buffer free (TMA drained / previous pass consumed)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    red[(my_rg * 2 + 0) * hcols + my_ch * 8 + i] = hf == 0 ? stS[0][i] : stS[1][i];
+                    red[(my_rg * 2 + 1) * hcols + my_ch * 8 + i] = hf == 0 ? stQ[0][i] : stQ[1][i];
+                }
+                named_barrier_sync(1, 256);
+                if (tid_e < hcols) {
+                    float a = 0.f, b = 0.f;
+                    for (int g = 0; g < nrg; ++g) {
+                        a += red[(g * 2 + 0) * hcols + tid_e];
+                        b += red[(g * 2 + 1) * hcols + tid_e];
+                    }
+                    const int c = n_tile * BN + hf * hw + tid_e;
+                    if (c < p.Cout) { atomicAdd(st + c, a); atomicAdd(st + p.Cout + c, b); }
+                }
             }
         }
-        if (tid_e == 0) tma_store_wait_all();
     }
 
     tc_fence_before();
@@ -604,7 +651,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
         if (nclusters > pairs) nclusters = static_cast<int>(std::max<long long>(p.numN, pairs / p.numN * p.numN));
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(2 * nclusters);
-        cfg.blockDim = dim3(192);
+        cfg.blockDim = dim3(320);
         cfg.dynamicSmemBytes = MAX_DYN_SMEM;
         cfg.stream = stream;
         cudaLaunchAttribute attr[1];
@@ -622,9 +669,9 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     grid = std::max(p.numN, grid / p.numN * p.numN);
     // request the whole smem so that exactly one CTA (and one 512-column TMEM allocation) lives on an SM
     if (bias_act)
-        conv_gemm_kernel<true, false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+        conv_gemm_kernel<true, false><<<grid, 320, MAX_DYN_SMEM, stream>>>(p);
     else
-        conv_gemm_kernel<false, false><<<grid, 192, MAX_DYN_SMEM, stream>>>(p);
+        conv_gemm_kernel<false, false><<<grid, 320, MAX_DYN_SMEM, stream>>>(p);
     PICD_LAUNCH_CHECK();
     return 0;
 }

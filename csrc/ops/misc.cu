@@ -324,7 +324,9 @@ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
     return x;
 }
 __global__ void __launch_bounds__(256) dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
-                                                      long long n, float p, uint32_t seed) {
+                                                      long long n, float p, uint32_t seed,
+                                                      const uint32_t* __restrict__ step_word) {
+    if (step_word != nullptr) seed += step_word[0] * 0x632BE5ABu;   // graph replay: a fresh mask per step from a device counter
     const float scale = 1.f / (1.f - p);
     const uint32_t thr = static_cast<uint32_t>(p * 4294967296.0);
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -648,7 +650,16 @@ extern "C" int picd_colsum(const void* x, float* out, long long P, int C, cudaSt
     return 0;
 }
 extern "C" int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, cudaStream_t st) {
-    dropout_kernel<<<grid_for(n), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), n, p, seed);
+    dropout_kernel<<<grid_for(n), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), n, p, seed, nullptr);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// Same mask generator, but the seed is mixed with a 32-bit step word read from device memory when the kernel runs, so a
+// launch recorded in a CUDA graph draws a different mask at every replay (forward and backward read the same word).
+extern "C" int picd_dropout_dyn(const void* x, void* out, long long n, float p, unsigned seed, const void* step_word,
+                                cudaStream_t st) {
+    dropout_kernel<<<grid_for(n), 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), n, p, seed,
+                                                static_cast<const uint32_t*>(step_word));
     PICD_LAUNCH_CHECK();
     return 0;
 }

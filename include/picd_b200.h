@@ -101,6 +101,9 @@ int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, lon
                  cudaStream_t stream);
 int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t stream);
 int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, cudaStream_t stream);
+/* graph-replay variant: the seed is mixed with the 32-bit word at step_word (device memory) when the kernel runs */
+int picd_dropout_dyn(const void* x, void* out, long long n, float p, unsigned seed, const void* step_word,
+                     cudaStream_t stream);
 int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                        long long M, int D, float eps, cudaStream_t stream);
 int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
@@ -146,6 +149,11 @@ int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start
                                 float* state1, int kind, float lr, float momentum, float beta1, float beta2, float eps,
                                 float weight_decay, float bc1, float bc2, int nesterov, unsigned epoch, int blocks,
                                 cudaStream_t stream);
+/* Same bucket update for CUDA-graph replay: the step-varying scalars (lr, 1-beta1^t, 1-beta2^t, flag epoch as raw bits)
+ * are read from the device array dyn[4] when the kernel runs, so one captured launch serves every later step. */
+int picd_fused_allreduce_update_dyn(void* ctx, int bucket, int mode, long long start, long long count, float* state0,
+                                    float* state1, int kind, float momentum, float beta1, float beta2, float eps,
+                                    float weight_decay, int nesterov, int blocks, const float* dyn, cudaStream_t stream);
 int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
                              int flag_slot, unsigned epoch, cudaStream_t stream);
 int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,

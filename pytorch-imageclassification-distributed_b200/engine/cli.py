@@ -59,6 +59,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--seed", default=0, type=int)
     p.add_argument("--calibrate-comm", action="store_true",
                    help="measure one-shot vs two-shot all-reduce at start-up and pick the switch-over bucket size")
+    p.add_argument("--cuda-graph", action="store_true",
+                   help="record the training step once and replay it as a CUDA graph (b200 backend, no SyncBN)")
     return p
 
 
@@ -129,7 +131,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     history, best = fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device,
                         name=args.model, epochs=args.epochs, start_epoch=start_epoch, best_score=best_score,
                         ckpt_dir=args.ckpt_dir, log_interval=args.log_interval, tracer=tracer,
-                        max_steps=args.max_steps)
+                        max_steps=args.max_steps, cuda_graph=args.cuda_graph)
     if args.trace:
         tracer.log(event="summary", phases=tracer.summary(), history=history, best=best)
         tracer.close()

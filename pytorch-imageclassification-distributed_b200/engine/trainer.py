@@ -60,7 +60,9 @@ def _to_device(batch, device):
 
 def train_epoch(epoch: int, model, loss_fn, optimizer, loader, device, log_interval: int = 50,
                 tracer: Optional[Tracer] = None, max_steps: Optional[int] = None,
-                printer: Callable[[str], None] = print) -> float:
+                printer: Callable[[str], None] = print, step_fn=None) -> float:
+    """``step_fn`` (an :class:`picd_b200.engine.graphed.GraphedTrainStep`) replaces the forward/backward/step sequence
+    with one CUDA-graph replay per batch; the loop around it is unchanged."""
     model.train()
     losses = AverageMeter()
     tracer = tracer or Tracer(enabled=False)
@@ -70,15 +72,20 @@ def train_epoch(epoch: int, model, loss_fn, optimizer, loader, device, log_inter
             break
         with tracer.range("h2d"):
             images, labels = _to_device(batch, device)
-        with tracer.range("forward"):
-            outputs = model(images)
-            loss, _ = compute_loss(outputs, labels, loss_fn)
-        losses.update(loss.detach().float(), images.size(0))       # stays on device
-        optimizer.zero_grad()
-        with tracer.range("backward"):
-            loss.backward()
-        with tracer.range("step"):
-            optimizer.step()
+        if step_fn is not None:
+            with tracer.range("graph_step"):
+                loss = step_fn(images, labels)
+            losses.update(loss.detach().float(), images.size(0))
+        else:
+            with tracer.range("forward"):
+                outputs = model(images)
+                loss, _ = compute_loss(outputs, labels, loss_fn)
+            losses.update(loss.detach().float(), images.size(0))       # stays on device
+            optimizer.zero_grad()
+            with tracer.range("backward"):
+                loss.backward()
+            with tracer.range("step"):
+                optimizer.step()
         seen += images.size(0)
         if log_interval and (index + 1) % log_interval == 0:
             # running sums are linear, so one all-reduce of (val, sum) gives the global averages
@@ -120,16 +127,23 @@ def val_epoch(epoch: int, model, loader, device, printer: Callable[[str], None] 
 def fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device, *, name: str,
         epochs: int = 100, start_epoch: int = 0, best_score: float = 0.0, ckpt_dir: str = "dtmodel/cp",
         save_every: int = 5, log_interval: int = 50, tracer: Optional[Tracer] = None,
-        max_steps: Optional[int] = None, printer: Callable[[str], None] = print):
-    """The reference's epoch driver (train.py:161-188) with start_epoch honoured (fix D10)."""
+        max_steps: Optional[int] = None, printer: Callable[[str], None] = print, cuda_graph: bool = False):
+    """The reference's epoch driver (train.py:161-188) with start_epoch honoured (fix D10).  ``cuda_graph`` replays the
+    training step from a captured CUDA graph where the model allows it (see engine/graphed.py)."""
     history = []
+    step_fn = None
+    if cuda_graph and device.type == "cuda":
+        from .graphed import GraphedTrainStep
+        step_fn = GraphedTrainStep(model, loss_fn, optimizer)
+        if not step_fn.enabled:
+            step_fn = None
     for epoch in range(start_epoch, epochs):
         if hasattr(train_loader, "sampler") and hasattr(train_loader.sampler, "set_epoch"):
             train_loader.sampler.set_epoch(epoch)                 # train.py:164
         elif hasattr(train_loader, "set_epoch"):
             train_loader.set_epoch(epoch)
         loss = train_epoch(epoch, model, loss_fn, optimizer, train_loader, device, log_interval,
-                           tracer, max_steps, printer)
+                           tracer, max_steps, printer, step_fn)
         scheduler.step()                                          # train.py:166
         acc = val_epoch(epoch, model, val_loader, device, printer, max_steps)
         if D.is_main():

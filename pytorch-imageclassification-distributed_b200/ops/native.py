@@ -55,6 +55,7 @@ _SIG = {
     "picd_act_bwd": "ppppliip",
     "picd_colsum": "pplip",
     "picd_dropout": "pplfup",
+    "picd_dropout_dyn": "pplfupp",
     "picd_layernorm_fwd": "pppppplifp",
     "picd_layernorm_bwd": "pppppppplip",
     "picd_small_linear_fwd": "ppppiiiiip",
@@ -767,6 +768,22 @@ def activation(x, act):
     return _Activation.apply(x, act)
 
 
+_step_word = None     # device uint32 view of the step counter while a CUDA graph of the step is recorded (engine/graphed.py)
+
+
+def set_step_word(t):
+    """Route dropout through the graph-replayable kernel variant that reads the step counter from device memory."""
+    global _step_word
+    _step_word = t
+
+
+def _dropout_call(src, dst, p, seed, word):
+    if word is not None:
+        call("picd_dropout_dyn", src, dst, src.numel(), float(p), seed, word)
+    else:
+        call("picd_dropout", src, dst, src.numel(), float(p), seed)
+
+
 class _Dropout(torch.autograd.Function):
     _counter = 0
 
@@ -777,14 +794,15 @@ class _Dropout(torch.autograd.Function):
         ctx.p = p
         xc = x.contiguous()
         out = torch.empty_like(xc)
-        call("picd_dropout", xc, out, xc.numel(), float(p), ctx.seed)
+        ctx.word = _step_word
+        _dropout_call(xc, out, p, ctx.seed, ctx.word)
         return out
 
     @staticmethod
     def backward(ctx, dy):
         dyc = dy.contiguous()
         dx = torch.empty_like(dyc)
-        call("picd_dropout", dyc, dx, dyc.numel(), float(ctx.p), ctx.seed)
+        _dropout_call(dyc, dx, ctx.p, ctx.seed, ctx.word)
         return dx, None
 
 

@@ -257,6 +257,7 @@ class FusedDataParallel(nn.Module):
         self.rank = dist.get_rank(process_group) if is_dist() else 0
         self.overlap, self.comm = overlap, comm
         self.step_index = 0
+        self.capturing = False          # True while a CUDA graph of the step is being recorded (engine/graphed.py)
         try:
             device = next(module.parameters()).device
         except StopIteration:
@@ -348,8 +349,8 @@ class FusedDataParallel(nn.Module):
 
     # -- nn.Module plumbing -------------------------------------------------------------------
     def forward(self, *args, **kw):
-        if self.broadcast_buffers and self.module.training and torch.is_grad_enabled():
-            self._sync_buffers()
+        if self.broadcast_buffers and self.module.training and torch.is_grad_enabled() and not self.capturing:
+            self._sync_buffers()        # (a captured step broadcasts eagerly before each replay instead)
         return self.module(*args, **kw)
 
     def load_state_dict(self, state_dict, strict: bool = True, **kw):

@@ -15,6 +15,7 @@ from __future__ import annotations
 import ctypes
 from typing import List, Optional
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -131,6 +132,10 @@ class Comm:
         self._f_upd.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 8 +
                                 [ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p])
+        self._f_upd_dyn = self.lib.picd_fused_allreduce_update_dyn
+        self._f_upd_dyn.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
+                                     ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 5 +
+                                    [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p])
         self._f_small = self.lib.picd_p2p_allreduce_small
         self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                   ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
@@ -142,10 +147,16 @@ class Comm:
 
     # -- gradient buckets ---------------------------------------------------------------------------
     def fused_update(self, bucket_index: int, mode: int, start: int, count: int, state, spec, step: int,
-                     epoch: int, blocks: int = 0):
+                     epoch: int, blocks: int = 0, dyn: Optional[torch.Tensor] = None):
         s0 = state[0].data_ptr()
         s1 = state[1].data_ptr() if len(state) > 1 else None
         b1, b2 = spec.betas
+        if dyn is not None:      # CUDA-graph capture: lr / bias corrections / epoch are read from `dyn` at run time
+            check(self._f_upd_dyn(self.ctx, bucket_index, mode, start, count, s0, s1, spec.KINDS[spec.kind],
+                                  spec.momentum, b1, b2, spec.eps, spec.weight_decay, int(spec.nesterov), blocks,
+                                  dyn.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                  "picd_fused_allreduce_update_dyn")
+            return
         bc1, bc2 = 1.0 - b1 ** step, 1.0 - b2 ** step
         check(self._f_upd(self.ctx, bucket_index, mode, start, count, s0, s1, spec.KINDS[spec.kind], spec.lr,
                           spec.momentum, b1, b2, spec.eps, spec.weight_decay, bc1, bc2, int(spec.nesterov),
@@ -223,6 +234,21 @@ class NativeReducer:
         self.side = torch.cuda.Stream(device=engine.device)
         self._epoch = 0
         self._dirty = False
+        self.dyn = None            # device float[4] (lr, bc1, bc2, epoch bits) while a step is captured / replayed
+
+    def enable_dyn(self):
+        if self.dyn is None:
+            self.dyn = torch.zeros(4, dtype=torch.float32, device=self.e.device)
+        return self.dyn
+
+    def write_dyn(self, step: int):
+        """Refresh the step-varying scalars the captured update kernels read (host values -> device, in stream order)."""
+        s = self.e.spec
+        b1, b2 = s.betas
+        bits = np.array([step & 0xFFFFFFFF], dtype=np.uint32).view(np.float32)[0]
+        host = torch.tensor([s.lr, 1.0 - b1 ** step, 1.0 - b2 ** step, 0.0], dtype=torch.float32)
+        host.numpy()[3] = bits                      # raw epoch bits (may not be a valid float: never touched as one)
+        self.dyn.copy_(host)                        # pageable H2D: staged before the call returns, so `host` may die
 
     def _mode(self, b) -> int:
         if self.e.world == 1:
@@ -242,7 +268,7 @@ class NativeReducer:
         self.side.wait_event(ev)
         with torch.cuda.stream(self.side):
             self.comm.fused_update(b.index, self._mode(b), b.start, b.numel, e.arena.state, e.spec,
-                                   e.step_index + 1, e.step_index + 1)
+                                   e.step_index + 1, e.step_index + 1, dyn=self.dyn if e.capturing else None)
         self._dirty = True
 
     def finish(self):
