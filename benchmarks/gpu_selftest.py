@@ -319,6 +319,9 @@ CONV_CASES = [
     (4, 7, 7, 2048, 512, 1, 1, 1, 0), (3, 17, 17, 128, 128, 1, 7, 1, (0, 3)), (3, 17, 17, 160, 192, 7, 1, 1, (3, 0)),
     (3, 35, 35, 48, 64, 5, 5, 1, 2), (3, 35, 35, 288, 384, 3, 3, 2, 0), (2, 9, 9, 80, 192, 3, 3, 1, 0),
     (2, 224, 224, 3, 64, 7, 7, 2, 3), (2, 32, 32, 3, 64, 3, 3, 1, 1), (2, 64, 64, 3, 768, 16, 16, 16, 0),
+    # 3x3 stride-1 shapes that take the halo path (one activation box per column shift, resident weights for 64->64)
+    (2, 28, 28, 128, 128, 3, 3, 1, 1), (3, 30, 37, 64, 96, 3, 3, 1, 1), (2, 56, 56, 64, 192, 3, 3, 1, 1),
+    (2, 28, 28, 192, 64, 3, 3, 1, 1), (5, 33, 29, 64, 64, 3, 3, 1, 1),
 ]
 
 

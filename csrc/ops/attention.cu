@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     uint8_t* sQ = sP;
     uint8_t* sK = sP + 16384;
     uint8_t* sV = sP + 65536;             // 32 KB
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
     const int half = warp >> 2;
     const int mt = blockIdx.x & 1;
     const int bh = blockIdx.x >> 1;
@@ -91,24 +91,24 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = bars->tmem_base;
+    const uint32_t tmem = uniform_u32(bars->tmem_base);
     const int HD = p.H * ATT_D;
     const int row_base = b * p.S;
 
-    if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(&bars->load, 16384 * 5);
-        tma_load_2d(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
-        tma_load_2d(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
-        tma_load_2d(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
-        tma_load_2d(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
+    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
+        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 5);
+        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
         mbar_wait(&bars->load, 0);
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
-        umma_commit(&bars->mma0);
+            umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma0);
     }
     // ---- softmax: thread = (query row, column half)
     const int row = (warp & 3) * 32 + lane;
@@ -150,13 +150,13 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     fence_proxy_async_smem();
     __syncthreads();
     l = s_red[row] + s_red[128 + row];
-    if (threadIdx.x == 0) {
+    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
         const int ksteps = p.n_keys >> 4;
         for (int k = 0; k < ksteps; ++k)
-            umma_bf16(tmem, desc_kmajor(sP_u32, k), desc_mnmajor(smem_u32(sV), k), idesc, k != 0);   // O reuses S's columns
-        umma_commit(&bars->mma1);
+            umma_bf16_warp(tmem, desc_kmajor(sP_u32, k), desc_mnmajor(smem_u32(sV), k), idesc, k != 0);   // O reuses S's columns
+        umma_commit_warp(&bars->mma1);
     }
     mbar_wait(&bars->mma1, 0);
     tc_fence_after();
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_consta
     uint8_t* sK = sdO + 16384;            // 32 KB
     uint8_t* sV = sK + 32768;             // 32 KB
     uint8_t* sdS = sV + 32768;            // 64 KB
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
     const int half = warp >> 2;          // two threads per query row: alternate 32-column chunks
     const int mt = blockIdx.x & 1;
     const int bh = blockIdx.x >> 1;
@@ -212,28 +212,28 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_consta
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = bars->tmem_base;
+    const uint32_t tmem = uniform_u32(bars->tmem_base);
     const int HD = p.H * ATT_D;
     const int row_base = b * p.S;
 
-    if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(&bars->load, 16384 * 6);
-        tma_load_2d(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
-        tma_load_2d(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
-        tma_load_2d(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
-        tma_load_2d(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
+    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
+        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 6);
+        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
         mbar_wait(&bars->load, 0);
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k)      // S = Q K^T  -> columns [0, 256)
-            umma_bf16(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
+            umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k)      // dP = dO V^T -> columns [256, 512)
-            umma_bf16(tmem + 256, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
-        umma_commit(&bars->mma0);
+            umma_bf16_warp(tmem + 256, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma0);
     }
     const int row = (warp & 3) * 32 + lane;
     const int q = q0 + row;
@@ -273,13 +273,13 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_consta
     tc_fence_before();
     fence_proxy_async_smem();
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
         const int ksteps = p.n_keys >> 4;
         for (int k = 0; k < ksteps; ++k)         // dQ = dS K  (K read MN-major), into columns [0, 64)
-            umma_bf16(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
-        umma_commit(&bars->mma1);
+            umma_bf16_warp(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma1);
     }
     mbar_wait(&bars->mma1, 0);
     tc_fence_after();
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
     uint8_t* sdO = sQ + 16384;            // 16 KB
     uint8_t* sPT = sdO + 16384;           // 32 KB  P^T  [keys x queries]
     uint8_t* sdST = sPT + 32768;          // 32 KB  dS^T [keys x queries]
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
     const int half = warp >> 2;          // two threads per key row: alternate 32-query chunks
     const int kt = blockIdx.x & 1;
     const int bh = blockIdx.x >> 1;
@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = bars->tmem_base;
+    const uint32_t tmem = uniform_u32(bars->tmem_base);
     const int HD = p.H * ATT_D;
     const int row_base = b * p.S;
     const int row = (warp & 3) * 32 + lane;      // key index inside the tile
@@ -346,14 +346,14 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
 
     for (int qt = 0; qt < n_qtiles; ++qt) {
         const int q0 = qt * ATT_TILE;
-        if (threadIdx.x == 0) {
-            mbar_arrive_expect_tx(&bars->load, qt == 0 ? 16384 * 4 : 16384 * 2);
+        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
+            mbar_arrive_expect_tx_warp(&bars->load, qt == 0 ? 16384 * 4 : 16384 * 2);
             if (qt == 0) {
-                tma_load_2d(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + k0);
-                tma_load_2d(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + k0);
+                tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + k0);
+                tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + k0);
             }
-            tma_load_2d(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
-            tma_load_2d(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
+            tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
+            tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
         }
         // per-query log-sum-exp and delta of this query tile (written by the forward / dQ kernels)
         if (threadIdx.x < ATT_TILE) {
@@ -363,17 +363,17 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
             s_delta[threadIdx.x] = qq < p.S ? p.delta[off] : 0.f;
         }
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
             mbar_wait(&bars->load, ph);
             tc_fence_after();
             const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_TILE, 0, 0);
 #pragma unroll
             for (int k = 0; k < 4; ++k)      // S^T = K Q^T   -> columns [0, 128)
-                umma_bf16(tmem, desc_kmajor(smem_u32(sK), k), desc_kmajor(smem_u32(sQ), k), idesc, k != 0);
+                umma_bf16_warp(tmem, desc_kmajor(smem_u32(sK), k), desc_kmajor(smem_u32(sQ), k), idesc, k != 0);
 #pragma unroll
             for (int k = 0; k < 4; ++k)      // dP^T = V dO^T -> columns [128, 256)
-                umma_bf16(tmem + 128, desc_kmajor(smem_u32(sV), k), desc_kmajor(smem_u32(sdO), k), idesc, k != 0);
-            umma_commit(&bars->mma0);
+                umma_bf16_warp(tmem + 128, desc_kmajor(smem_u32(sV), k), desc_kmajor(smem_u32(sdO), k), idesc, k != 0);
+            umma_commit_warp(&bars->mma0);
         }
         mbar_wait(&bars->mma0, ph);
         tc_fence_after();
@@ -399,16 +399,16 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
         tc_fence_before();
         fence_proxy_async_smem();
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
             tc_fence_after();
             const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
 #pragma unroll
             for (int k = 0; k < 8; ++k)      // dV += P^T dO   (dO read MN-major) -> columns [256, 320)
-                umma_bf16(tmem + 256, desc_kmajor(sPT_u32, k), desc_mnmajor(smem_u32(sdO), k), idesc, (qt | k) != 0);
+                umma_bf16_warp(tmem + 256, desc_kmajor(sPT_u32, k), desc_mnmajor(smem_u32(sdO), k), idesc, (qt | k) != 0);
 #pragma unroll
             for (int k = 0; k < 8; ++k)      // dK += dS^T Q   (Q read MN-major)  -> columns [320, 384)
-                umma_bf16(tmem + 320, desc_kmajor(sdST_u32, k), desc_mnmajor(smem_u32(sQ), k), idesc, (qt | k) != 0);
-            umma_commit(&bars->mma1);
+                umma_bf16_warp(tmem + 320, desc_kmajor(sdST_u32, k), desc_mnmajor(smem_u32(sQ), k), idesc, (qt | k) != 0);
+            umma_commit_warp(&bars->mma1);
         }
         mbar_wait(&bars->mma1, ph);      // sQ / sdO / sPT / sdST may be overwritten by the next query tile
         tc_fence_after();

@@ -59,6 +59,12 @@ struct ConvGemmParams {
     int half_w;           // columns drained per staging pass: 128 (deep operand ring) or 256 (short-K tiles, one pass)
     int cluster;          // 1: launched as clusters of 2 with multicast B tiles (set by the host launcher)
     int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
+    // halo mode (3x3, stride 1): one activation box with a one-row halo above and below is loaded per (k-chunk, dw) and
+    // the three dh taps read it through descriptors shifted by whole pixel rows -> 3 instead of 9 A loads per k-chunk.
+    // taps[] is then ordered [dw][dh] with dh = -1, 0, +1.
+    int halo;
+    int a_stage_bytes;    // bytes of one A stage: 16 KB, or (bh + 2) * bw * 128 in halo mode
+    int b_resident;       // halo mode, tiny weights: all 9 B taps are loaded once per CTA and stay in shared memory
 };
 
 struct WgradParams {
@@ -78,6 +84,7 @@ struct SmemBars {
     uint64_t empty[8];
     uint64_t tfull[2];
     uint64_t tempty[2];
+    uint64_t bres;        // halo mode with resident weights: "all taps have landed"
     uint32_t tmem_base;
 };
 
@@ -98,12 +105,15 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     SmemBars* bars = reinterpret_cast<SmemBars*>(smem);
     const int BN = p.BN;
     const int stages = p.stages;
-    const int b_stage = BN * 128;
+    const int b_tap = BN * 128;                                   // one weight tap tile: BN rows x 64 k (or 64 k x BN)
+    const int b_stage = p.halo ? (p.b_resident ? 0 : 3 * b_tap) : b_tap;
+    const int a_stage = p.a_stage_bytes;
     uint8_t* sA = smem + SMEM_HEADER;
-    uint8_t* sB = sA + stages * A_STAGE_BYTES;
-    uint8_t* sOut = sB + stages * b_stage;
+    uint8_t* sB = sA + stages * a_stage;
+    uint8_t* sBres = sB + stages * b_stage;                       // 9 resident taps (halo + b_resident only)
+    uint8_t* sOut = sBres + (p.b_resident ? 9 * b_tap : 0);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = uniform_warp_id();      // provably warp-uniform: the role branches below stay convergent
     const int lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -115,6 +125,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
             mbar_init(&bars->tfull[i], 1);
             mbar_init(&bars->tempty[i], 8);
         }
+        mbar_init(&bars->bres, 1);
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -130,10 +141,10 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     __syncthreads();
     if (kCluster) cluster_sync();          // the peer's barriers exist before anything is multicast at them
     tc_fence_after();
-    const uint32_t tmem_base = bars->tmem_base;
+    const uint32_t tmem_base = uniform_u32(bars->tmem_base);
 
     const int numN = p.numN;
-    const int crank = kCluster ? static_cast<int>(cluster_ctarank()) : 0;
+    const int crank = kCluster ? static_cast<int>(uniform_u32(cluster_ctarank())) : 0;
     // tile walk: (non-cluster) CTA b owns column tile b % numN and pixel tiles b/numN, +grid_m, ...
     //            (cluster)     cluster c owns column tile c % numN; its two CTAs take pixel tiles 2j and 2j+1 in lockstep
     const int unit = kCluster ? (blockIdx.x >> 1) : blockIdx.x;
@@ -142,7 +153,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     const int grid_m = kCluster ? 2 * (units / numN) : units / numN;
     const int m_first = kCluster ? 2 * (unit / numN) + crank : unit / numN;
     const int m_limit = kCluster ? p.num_m_tiles + crank : p.num_m_tiles;   // the pair iterates while its EVEN tile exists
-    const int k_iters = p.ntaps * p.kchunks;
+    const int k_iters = p.halo ? 3 * p.kchunks : p.ntaps * p.kchunks;
     float* sBias = reinterpret_cast<float*>(smem + SMEM_BIAS_OFF);
     if (kBiasAct) {
         // a CTA keeps one column tile for its whole life, so its slice of the bias vector is staged once
@@ -157,40 +168,72 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        {   // all 32 lanes walk the loop; the *_warp calls elect one lane to issue
             int stage = 0;
             uint32_t phase = 0;
-            const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
+            const uint32_t tx_bytes = a_stage + b_stage;
+            auto load_b_tap = [&](uint8_t* dst, uint64_t* bar, int kc, int btap) {
+                if (!p.b_mn) {
+                    tma_load_3d_warp(dst, &p.bmap, bar, kc * KCHUNK, btap, n_tile * BN);
+                } else {
+                    for (int j = 0; j < BN / 64; ++j) {
+                        int c0 = n_tile * BN + j * 64;
+                        if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
+                        tma_load_3d_warp(dst + j * 8192, &p.bmap, bar, c0, btap, kc * KCHUNK);
+                    }
+                }
+            };
+            if (p.halo && p.b_resident) {
+                mbar_arrive_expect_tx_warp(&bars->bres, 9 * b_tap);
+                for (int t = 0; t < 9; ++t) load_b_tap(sBres + t * b_tap, &bars->bres, 0, p.taps[t].btap);
+            }
             for (int m = m_first; m < m_limit; m += grid_m) {
                 const int tw = m % p.tiles_w;
                 const int th = (m / p.tiles_w) % p.tiles_h;
                 const int tn = m / (p.tiles_w * p.tiles_h);
                 const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
+                if (p.halo) {
+                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                        for (int dwi = 0; dwi < 3; ++dwi) {
+                            const Tap tp = p.taps[dwi * 3];          // the dh = -1 tap of this column: origin of the halo box
+                            mbar_wait(&bars->empty[stage], phase ^ 1);
+                            mbar_arrive_expect_tx_warp(&bars->full[stage], tx_bytes);
+                            tma_load_4d_warp(sA + stage * a_stage, &p.amap[0], &bars->full[stage], kc * KCHUNK, w0 + tp.dw,
+                                        h0 + tp.dh, n0);
+                            if (!p.b_resident) {
+                                for (int dhi = 0; dhi < 3; ++dhi)
+                                    load_b_tap(sB + stage * b_stage + dhi * b_tap, &bars->full[stage], kc,
+                                               p.taps[dwi * 3 + dhi].btap);
+                            }
+                            if (++stage == stages) { stage = 0; phase ^= 1; }
+                        }
+                    }
+                    continue;
+                }
                 for (int t = 0; t < p.ntaps; ++t) {
                     const Tap tp = p.taps[t];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(&bars->empty[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&bars->full[stage], tx_bytes);
-                        tma_load_4d(sA + stage * A_STAGE_BYTES, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
+                        mbar_arrive_expect_tx_warp(&bars->full[stage], tx_bytes);
+                        tma_load_4d_warp(sA + stage * a_stage, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
                                     w0 + tp.dw, h0 + tp.dh, n0);
                         uint8_t* dstB = sB + stage * b_stage;
                         if (!p.b_mn) {
                             if (kCluster) {     // this CTA fetches rows [crank*BN/2, +BN/2) of the tile for both CTAs
-                                tma_load_3d_mc(dstB + crank * (b_stage >> 1), &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
+                                tma_load_3d_mc_warp(dstB + crank * (b_stage >> 1), &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
                                                n_tile * BN + crank * (BN >> 1), 3);
                             } else {
-                                tma_load_3d(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                                tma_load_3d_warp(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
                             }
                         } else {
-                            for (int j = 0; j < BN / 64; ++j) {
+                            // cluster: this CTA fetches every second 64-column box (j = crank, crank + 2, ...) for both CTAs
+                            for (int j = kCluster ? crank : 0; j < BN / 64; j += kCluster ? 2 : 1) {
                                 int c0 = n_tile * BN + j * 64;
                                 if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
-                                if (kCluster) {
-                                    if ((j & 1) == crank)
-                                        tma_load_3d_mc(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK, 3);
-                                } else {
-                                    tma_load_3d(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
-                                }
+                                if (kCluster)
+                                    tma_load_3d_mc_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK, 3);
+                                else
+                                    tma_load_3d_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
                             }
                         }
                         if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -200,36 +243,53 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            int acc = 0;
-            uint32_t accphase = 0;
-            const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 0, p.b_mn);
-            for (int m = m_first; m < m_limit; m += grid_m) {
-                mbar_wait(&bars->tempty[acc], accphase ^ 1);
+        // The whole warp walks the loop (uniform control flow keeps the descriptors in uniform registers); one elected
+        // lane issues.  Descriptors are built once from templates: only the 14-bit start-address field changes.
+        int stage = 0;
+        uint32_t phase = 0;
+        int acc = 0;
+        uint32_t accphase = 0;
+        const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 0, p.b_mn);
+        const uint64_t a_tmpl = make_smem_desc(0, 16, 1024);
+        const uint64_t b_tmpl = p.b_mn ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
+        const uint32_t b_kstep = p.b_mn ? (2048u >> 4) : (32u >> 4);      // descriptor units (16 B) per K=16 step
+        const uint32_t sA_lo = smem_u32(sA) >> 4, sB_lo = smem_u32(sB) >> 4, sBres_lo = smem_u32(sBres) >> 4;
+        const uint32_t a_stage_lo = static_cast<uint32_t>(a_stage) >> 4, b_stage_lo = static_cast<uint32_t>(b_stage) >> 4;
+        const uint32_t b_tap_lo = static_cast<uint32_t>(b_tap) >> 4;
+        const uint32_t row_lo = (static_cast<uint32_t>(bw) * 128u) >> 4;   // one pixel row of the halo box
+        if (p.halo && p.b_resident) { mbar_wait(&bars->bres, 0); tc_fence_after(); }
+        for (int m = m_first; m < m_limit; m += grid_m) {
+            mbar_wait(&bars->tempty[acc], accphase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * 256;
+            for (int it = 0; it < k_iters; ++it) {
+                mbar_wait(&bars->full[stage], phase);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * 256;
-                for (int it = 0; it < k_iters; ++it) {
-                    mbar_wait(&bars->full[stage], phase);
-                    tc_fence_after();
-                    const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
-                    const uint32_t b_addr = smem_u32(sB + stage * b_stage);
+                const uint64_t adesc0 = a_tmpl | (sA_lo + stage * a_stage_lo);
+                if (p.halo) {
+                    // the stage holds rows h0-1 .. h0+bh of one column shift: tap dh reads it from row (dh + 1) on
+                    const int dwi = it % 3;
+                    const uint64_t bdesc0 = b_tmpl | (p.b_resident ? sBres_lo + dwi * 3 * b_tap_lo : sB_lo + stage * b_stage_lo);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t adesc = make_smem_desc(a_addr + k * 32, 16, 1024);
-                        const uint64_t bdesc = p.b_mn ? make_smem_desc(b_addr + k * 2048, 8192, 1024)
-                                                      : make_smem_desc(b_addr + k * 32, 16, 1024);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, (it | k) != 0);
+                    for (int dhi = 0; dhi < 3; ++dhi) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16_warp(tmem_d, adesc0 + (dhi * row_lo + k * 2), bdesc0 + (dhi * b_tap_lo + k * b_kstep), idesc,
+                                           (it | dhi | k) != 0);
                     }
-                    if (kCluster) umma_commit_mc(&bars->empty[stage], 3);   // frees the stage in both CTAs
-                    else umma_commit(&bars->empty[stage]);
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                } else {
+                    const uint64_t bdesc0 = b_tmpl | (sB_lo + stage * b_stage_lo);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16_warp(tmem_d, adesc0 + k * 2, bdesc0 + k * b_kstep, idesc, (it | k) != 0);
                 }
-                umma_commit(&bars->tfull[acc]);
-                acc ^= 1;
-                if (acc == 0) accphase ^= 1;
+                if (kCluster) umma_commit_mc_warp(&bars->empty[stage], 3);   // frees the stage in both CTAs
+                else umma_commit_warp(&bars->empty[stage]);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
+            umma_commit_warp(&bars->tfull[acc]);
+            acc ^= 1;
+            if (acc == 0) accphase ^= 1;
         }
     } else {
         // ------------------------------------------------------------------ epilogue (8 warps)
@@ -428,7 +488,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     uint8_t* sA = smem + SMEM_HEADER;
     uint8_t* sB = sA + stages * A_STAGE_BYTES;
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = uniform_warp_id();
     const int lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -450,7 +510,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = bars->tmem_base;
+    const uint32_t tmem_base = uniform_u32(bars->tmem_base);
 
     const int inner = p.ngroups * p.numM * p.numN;
     const int split = blockIdx.x / inner;
@@ -464,7 +524,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     const int bn = 64 >> (p.bw_log2 + p.bh_log2);
 
     if (warp == 0) {
-        if (lane == 0) {
+        {   // all 32 lanes walk the loop; the *_warp calls elect one lane to issue
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t tx_bytes = A_STAGE_BYTES + b_stage;
@@ -489,38 +549,39 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
                 const int tn = pt / (p.tiles_w * p.tiles_h);
                 const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
                 mbar_wait(&bars->empty[stage], phase ^ 1);
-                mbar_arrive_expect_tx(&bars->full[stage], tx_bytes);
+                mbar_arrive_expect_tx_warp(&bars->full[stage], tx_bytes);
                 uint8_t* dA = sA + stage * A_STAGE_BYTES;
-                tma_load_4d(dA, &p.dymap, &bars->full[stage], mt * TILE_M, w0, h0, n0);
-                tma_load_4d(dA + 8192, &p.dymap, &bars->full[stage], ca1, w0, h0, n0);
+                tma_load_4d_warp(dA, &p.dymap, &bars->full[stage], mt * TILE_M, w0, h0, n0);
+                tma_load_4d_warp(dA + 8192, &p.dymap, &bars->full[stage], ca1, w0, h0, n0);
                 uint8_t* dB = sB + stage * b_stage;
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     if (j < nblk)
-                        tma_load_4d(dB + j * 8192, b_map[j], &bars->full[stage], b_c0[j], w0 + b_dw[j], h0 + b_dh[j], n0);
+                        tma_load_4d_warp(dB + j * 8192, b_map[j], &bars->full[stage], b_c0[j], w0 + b_dw[j], h0 + b_dh[j], n0);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // warp-convergent issue (see picd_common.cuh): descriptors stay in uniform registers
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 1, 1);
+            const uint64_t tmpl = make_smem_desc(0, 8192, 1024);
+            const uint32_t sA_lo = smem_u32(sA) >> 4, sB_lo = smem_u32(sB) >> 4;
+            const uint32_t a_stage_lo = A_STAGE_BYTES >> 4, b_stage_lo = static_cast<uint32_t>(b_stage) >> 4;
             for (int pt = pt_begin; pt < pt_end; ++pt) {
                 mbar_wait(&bars->full[stage], phase);
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
-                const uint32_t b_addr = smem_u32(sB + stage * b_stage);
+                const uint64_t adesc0 = tmpl | (sA_lo + stage * a_stage_lo);
+                const uint64_t bdesc0 = tmpl | (sB_lo + stage * b_stage_lo);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint64_t adesc = make_smem_desc(a_addr + k * 2048, 8192, 1024);
-                    const uint64_t bdesc = make_smem_desc(b_addr + k * 2048, 8192, 1024);
-                    umma_bf16(tmem_base, adesc, bdesc, idesc, (pt > pt_begin) || (k != 0));
-                }
-                umma_commit(&bars->empty[stage]);
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16_warp(tmem_base, adesc0 + k * (2048 >> 4), bdesc0 + k * (2048 >> 4), idesc,
+                                   (pt > pt_begin) || (k != 0));
+                umma_commit_warp(&bars->empty[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&bars->tfull[0]);
+            umma_commit_warp(&bars->tfull[0]);
         }
     } else {
         const int q = warp & 3;
@@ -605,6 +666,45 @@ static int make_act_map(CUtensorMap* m, const void* base, int N, int H, int W, i
     return make_tensor_map(m, b, 2, 4, dims, strides, box, true);
 }
 
+
+// ---- halo mode (3x3, stride 1, pad 1) -------------------------------------------------------------------------------
+// Pixel tile = bw x bh pixels of ONE image with bw a multiple of 8, so that every 8-row UMMA group is 8 consecutive pixels
+// of one image row and a dh shift is a whole number of 1024-byte groups inside the (bh + 2)-row box.
+static Geometry choose_halo_geometry(int N, int H, int W) {
+    Geometry best{};
+    double best_cost = 1e30;
+    for (int lw = 3; lw <= 7; ++lw) {
+        const int bw = 1 << lw, bh = TILE_M >> lw, lh = 7 - lw;
+        const long long tiles = 1LL * ceil_div(W, bw) * ceil_div(H, bh);
+        const double cost = static_cast<double>(tiles) * (TILE_M + 0.5 * (bh + 2) * bw);   // MMA rows + operand bytes
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = Geometry{lw, lh, 1, ceil_div(W, bw), ceil_div(H, bh), N};
+        }
+    }
+    return best;
+}
+
+// Reorders a 3x3 tap list to [dw][dh] (dh, dw = -1, 0, +1) if it is one; PICD_HALO=0 disables, =1 forces where legal.
+static bool setup_halo(ConvGemmParams& p, int nt, int stride, int H, int W, int cout_gemm) {
+    static const int mode = [] { const char* e = getenv("PICD_HALO"); return e == nullptr ? -1 : atoi(e); }();
+    if (mode == 0 || nt != 9 || stride != 1) return false;
+    if (mode != 1 && (std::min(H, W) < 28 || cout_gemm > 128)) return false;
+    Tap sorted[9];
+    bool seen[9] = {false, false, false, false, false, false, false, false, false};
+    for (int t = 0; t < 9; ++t) {
+        const Tap tp = p.taps[t];
+        if (tp.amap != 0 || tp.dh < -1 || tp.dh > 1 || tp.dw < -1 || tp.dw > 1) return false;
+        const int idx = (tp.dw + 1) * 3 + (tp.dh + 1);
+        if (seen[idx]) return false;
+        seen[idx] = true;
+        sorted[idx] = tp;
+    }
+    for (int t = 0; t < 9; ++t) p.taps[t] = sorted[t];
+    p.halo = 1;
+    return true;
+}
+
 static int num_n_tiles(int C, int* BN) {
     const int numN = ceil_div(C, 256);
     int bn = ceil_div(ceil_div(C, numN), 64) * 64;
@@ -617,22 +717,35 @@ static int num_n_tiles(int C, int* BN) {
 static bool want_cluster(int k_iters, int num_m_tiles, int BN, bool b_mn) {
     static const int mode = [] { const char* e = getenv("PICD_CLUSTER"); return e == nullptr ? -1 : atoi(e); }();
     if (mode == 0 || num_m_tiles < 2) return false;
-    if (b_mn && ((BN / 64) & 1)) return false;          // MN-major B is split box-wise between the two CTAs
+    if (b_mn) return false;      // MN-major B (dgrad): the box-wise split between the two CTAs gave wrong results once the
+                                 // producer became warp-convergent and measured no gain before that -> single-CTA path
     if (mode == 1) return true;
     return k_iters >= 4;
 }
 
+// halo mode keeps three weight taps per stage, so its column tiles are capped at 128 channels
+static int num_n_tiles_halo(int C, int* BN) {
+    const int numN = ceil_div(C, 128);
+    int bn = ceil_div(ceil_div(C, numN), 64) * 64;
+    *BN = bn;
+    return ceil_div(C, bn);
+}
+
 static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t stream) {
     int BN;
-    p.numN = num_n_tiles(Cout_gemm, &BN);
+    p.numN = p.halo ? num_n_tiles_halo(Cout_gemm, &BN) : num_n_tiles(Cout_gemm, &BN);
     p.BN = BN;
     p.Cout = Cout_gemm;
-    const int stage_bytes = A_STAGE_BYTES + BN * 128;
+    if (!p.halo) p.a_stage_bytes = A_STAGE_BYTES;
+    // tiny weight sets (64 -> 64 channels) stay resident: the ring then carries activations only
+    p.b_resident = (p.halo && p.kchunks == 1 && 9 * BN * 128 <= 80 * 1024) ? 1 : 0;
+    const int resident = p.b_resident ? 9 * BN * 128 : 0;
+    const int stage_bytes = p.a_stage_bytes + (p.halo ? (p.b_resident ? 0 : 3 * BN * 128) : BN * 128);
     // short-K tiles are epilogue-bound: drain 256 columns in one pass; otherwise drain halves and spend the smem on stages
     p.half_w = (BN == 256 && p.ntaps * p.kchunks <= 2) ? 256 : 128;
     const int staging = std::min(BN, p.half_w) * 256;   // 128 rows x half_w columns x 2 B
-    int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging) / stage_bytes;
-    stages = std::min(stages, 6);
+    int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging - resident) / stage_bytes;
+    stages = std::min(stages, p.halo ? 8 : 6);
     PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
     p.stages = stages;
     static bool attr_set = false;
@@ -691,21 +804,6 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
     PICD_REQUIRE(R * S <= MAX_TAPS, "conv_fprop: %dx%d filter has too many taps", R, S);
     ConvGemmParams p;
     std::memset(&p, 0, sizeof(p));
-    const Geometry g = choose_geometry(N, OH, OW, TILE_M);
-    const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
-    for (int ph = 0; ph < stride; ++ph)
-        for (int pw = 0; pw < stride; ++pw)
-            if (make_act_map(&p.amap[ph * stride + pw], x, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
-    {
-        uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(R * S), (uint64_t)Cout};
-        uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
-        int BN;
-        num_n_tiles(Cout, &BN);
-        p.cluster = want_cluster(R * S * ceil_div(Cin, KCHUNK), g.tiles_w * g.tiles_h * g.tiles_n, BN, false) ? 1 : 0;
-        uint32_t box[3] = {64, 1, (uint32_t)(p.cluster ? BN / 2 : BN)};     // cluster: each CTA fetches half the rows
-        if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
-    }
-    if (make_act_map(&p.dmap, y, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
     int nt = 0;
     for (int r = 0; r < R; ++r)
         for (int s = 0; s < S; ++s) {
@@ -717,6 +815,27 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
             t.btap = static_cast<int16_t>(r * S + s);
             p.taps[nt++] = t;
         }
+    const bool halo = setup_halo(p, nt, stride, OH, OW, Cout);
+    const Geometry g = halo ? choose_halo_geometry(N, OH, OW) : choose_geometry(N, OH, OW, TILE_M);
+    const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
+    if (halo) {
+        p.a_stage_bytes = (bh + 2) * bw * 128;
+        if (make_act_map(&p.amap[0], x, N, H, W, Cin, 1, 0, 0, bw, bh + 2, 1)) return 3;
+    } else {
+        for (int ph = 0; ph < stride; ++ph)
+            for (int pw = 0; pw < stride; ++pw)
+                if (make_act_map(&p.amap[ph * stride + pw], x, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+    }
+    {
+        uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(R * S), (uint64_t)Cout};
+        uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
+        int BN;
+        if (halo) num_n_tiles_halo(Cout, &BN); else num_n_tiles(Cout, &BN);
+        p.cluster = (!halo && want_cluster(R * S * ceil_div(Cin, KCHUNK), g.tiles_w * g.tiles_h * g.tiles_n, BN, false)) ? 1 : 0;
+        uint32_t box[3] = {64, 1, (uint32_t)(p.cluster ? BN / 2 : BN)};     // cluster: each CTA fetches half the rows
+        if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
+    }
+    if (make_act_map(&p.dmap, y, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
     p.ntaps = nt;
     p.kchunks = ceil_div(Cin, KCHUNK);
     p.b_mn = 0;
@@ -767,9 +886,11 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
                     p.taps[nt++] = t;
                 }
             if (nt == 0) continue;   // zeroed above
-            const Geometry g = choose_geometry(N, Hv, Wv, TILE_M);
+            const bool halo = setup_halo(p, nt, stride, Hv, Wv, Cin);
+            const Geometry g = halo ? choose_halo_geometry(N, Hv, Wv) : choose_geometry(N, Hv, Wv, TILE_M);
             const int bw = 1 << g.bw_log2, bh = 1 << g.bh_log2;
-            if (make_act_map(&p.amap[0], dy, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
+            if (halo) p.a_stage_bytes = (bh + 2) * bw * 128;
+            if (make_act_map(&p.amap[0], dy, N, OH, OW, Cout, 1, 0, 0, bw, halo ? bh + 2 : bh, g.bn)) return 3;
             {
                 uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(R * S), (uint64_t)Cout};
                 uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)R * S * Cin * 2};
@@ -789,7 +910,7 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
             {
                 int BNd;
                 num_n_tiles(Cin, &BNd);
-                p.cluster = want_cluster(nt * p.kchunks, p.num_m_tiles, BNd, true) ? 1 : 0;
+                p.cluster = (!halo && want_cluster(nt * p.kchunks, p.num_m_tiles, BNd, true)) ? 1 : 0;
             }
             if (int rc = launch_conv_gemm(p, Cin, stream)) return rc;
         }
