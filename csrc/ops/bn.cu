@@ -166,7 +166,9 @@ __device__ __forceinline__ void load8f(const float* p, float (&o)[8]) {
     o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
 }
 
-__global__ void __launch_bounds__(256, 2) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
+// TACT >= 0 fixes the activation at compile time (the generic apply_act switch drags exp/erf paths and ~50 registers along)
+template <int U, int MINB, int TACT>
+__global__ void __launch_bounds__(256, MINB) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
                                                        const float* __restrict__ scale,
                                                        const float* __restrict__ shift,
                                                        const __nv_bfloat16* __restrict__ residual, int act,
@@ -182,10 +184,10 @@ __global__ void __launch_bounds__(256, 2) bn_apply_kernel(const __nv_bfloat16* _
     const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
     long long r1 = r0 + rows_per_block;
     if (r1 > P) r1 = P;
-    for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * ROW_UNROLL) {
-        Vec8 v[ROW_UNROLL], rv[ROW_UNROLL];
+    for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ty_count) * U) {
+        Vec8 v[U], rv[U];
 #pragma unroll
-        for (int u = 0; u < ROW_UNROLL; ++u) {
+        for (int u = 0; u < U; ++u) {
             const long long rr = r + static_cast<long long>(u) * ty_count;
             if (rr < r1) {
                 v[u].load(y + rr * C + cv * 8);
@@ -193,14 +195,17 @@ __global__ void __launch_bounds__(256, 2) bn_apply_kernel(const __nv_bfloat16* _
             }
         }
 #pragma unroll
-        for (int u = 0; u < ROW_UNROLL; ++u) {
+        for (int u = 0; u < U; ++u) {
             const long long rr = r + static_cast<long long>(u) * ty_count;
             if (rr < r1) {
                 float f[8], rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 v[u].unpack(f);
                 if (residual != nullptr) rv[u].unpack(rs);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) f[k] = apply_act(fmaf(f[k], sc[k], sh[k]) + rs[k], act);
+                for (int k = 0; k < 8; ++k) {
+                    const float pre = fmaf(f[k], sc[k], sh[k]) + rs[k];
+                    f[k] = TACT == ACT_NONE ? pre : (TACT == ACT_RELU ? fmaxf(pre, 0.f) : apply_act(pre, act));
+                }
                 Vec8 o;
                 o.pack(f);
                 o.store(out + rr * C + cv * 8);
@@ -439,10 +444,27 @@ extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shi
         const int rc = bn_stream_apply(y, scale, shift, residual, act, out, P, C, stream);
         if (rc >= 0) return rc;
     }
-    const ReduceShape s = stream_shape(P, C);
-    bn_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,
-        static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block);
+    static const int variant = [] { const char* e = getenv("PICD_BN_APPLY_VARIANT"); return e == nullptr ? 2 : atoi(e); }();   // 2 = 8 rows in flight (measured best)
+    ReduceShape s = stream_shape(P, C);
+#define PICD_BN_APPLY_LAUNCH_A(U, MINB, A)                                                                         \
+    bn_apply_kernel<U, MINB, A><<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(                                      \
+        static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,       \
+        static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block)
+#define PICD_BN_APPLY_LAUNCH(U, MINB)                                                                              \
+    do {                                                                                                            \
+        if (act == ACT_RELU) PICD_BN_APPLY_LAUNCH_A(U, MINB, ACT_RELU);                                             \
+        else if (act == ACT_NONE) PICD_BN_APPLY_LAUNCH_A(U, MINB, ACT_NONE);                                        \
+        else PICD_BN_APPLY_LAUNCH_A(U, MINB, -1);                                                                   \
+    } while (0)
+    if (variant == 1) PICD_BN_APPLY_LAUNCH(4, 4);
+    else if (variant == 2) {
+        const long long min_rows = 8LL * s.ty_count;
+        if (s.rows_per_block < min_rows) { s.rows_per_block = static_cast<int>(min_rows); s.grid_y = static_cast<int>((P + min_rows - 1) / min_rows); }
+        PICD_BN_APPLY_LAUNCH(8, 2);
+    } else if (variant == 3) PICD_BN_APPLY_LAUNCH(2, 6);
+    else PICD_BN_APPLY_LAUNCH(4, 2);
+#undef PICD_BN_APPLY_LAUNCH_A
+#undef PICD_BN_APPLY_LAUNCH
     PICD_LAUNCH_CHECK();
     return 0;
 }

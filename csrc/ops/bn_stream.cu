@@ -12,7 +12,7 @@
 namespace picd {
 
 constexpr int SB_CONSUMERS = 512;
-constexpr int SB_THREADS = SB_CONSUMERS + 32;
+constexpr int SB_THREADS = SB_CONSUMERS + 64;     // + producer warp + store warp
 constexpr int SB_MAX_CHUNK_BYTES = 32768;   // per tensor per stage: 32 KB when one tensor is streamed, 16 KB otherwise
 constexpr int SB_MAX_STAGES = 8;
 
@@ -44,6 +44,14 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t b
                  ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -67,7 +75,8 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(sb_raw) + 127) & ~static_cast<uintptr_t>(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + SB_MAX_STAGES;
-    uint8_t* ring = smem + 128;
+    uint64_t* done = empty + SB_MAX_STAGES;      // APPLY / BWD_APPLY: "results of this stage are in shared memory"
+    uint8_t* ring = smem + 256;
     const int stages = a.stages;
     const int n_in = a.n_in;
     const int C = a.C;
@@ -77,7 +86,9 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], SB_CONSUMERS / 32);
+            // outputs leave through bulk stores issued by the store warp, which then frees the stage on its own
+            mbar_init(&empty[s], MODE == SB_BWD_REDUCE ? SB_CONSUMERS / 32 : 1);
+            mbar_init(&done[s], SB_CONSUMERS / 32);
         }
         fence_mbar_init();
     }
@@ -105,6 +116,32 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
                     bulk_load(ring + (static_cast<size_t>(s) * n_in + t) * a.chunk_bytes, a.in[t] + row0 * C, bytes, &full[s]);
                 if (++s == stages) { s = 0; phase ^= 1; }
             }
+        }
+        return;
+    }
+    if (warp == SB_CONSUMERS / 32 + 1) {
+        // ---------------------------------------------------------------- store warp
+        // The consumers overwrite the input chunk in place with the results; one thread sends each finished stage to
+        // global memory with 1-D bulk stores (full lines, no LSU traffic) and hands the stage back to the producer once
+        // the copy engine has read it.
+        if (MODE != SB_BWD_REDUCE && lane == 0) {
+            int s = 0;
+            uint32_t phase = 0;
+            for (long long c = blockIdx.x; c < a.num_chunks; c += gridDim.x) {
+                const long long row0 = c * a.rows_per_chunk;
+                long long rows = a.P - row0;
+                if (rows > a.rows_per_chunk) rows = a.rows_per_chunk;
+                const uint32_t bytes = static_cast<uint32_t>(rows * C * 2);
+                const uint32_t base = smem_u32(ring) + static_cast<uint32_t>(s) * n_in * a.chunk_bytes;
+                mbar_wait(&done[s], phase);
+                bulk_store(a.out0 + row0 * C, base, bytes);
+                if (MODE == SB_BWD_APPLY && a.out1 != nullptr) bulk_store(a.out1 + row0 * C, base + a.chunk_bytes, bytes);
+                tma_store_commit();
+                tma_store_wait_read();
+                mbar_arrive(&empty[s]);
+                if (++s == stages) { s = 0; phase ^= 1; }
+            }
+            tma_store_wait_all();
         }
         return;
     }
@@ -147,14 +184,13 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         for (int k = 0; k < SB_MAX_CHUNK_BYTES / 16 / SB_CONSUMERS; ++k) {
             const int idx = t + k * SB_CONSUMERS;
             if (idx < nvec) {
-                const long long goff = row0 * C + static_cast<long long>(idx) * 8;
                 if (MODE == SB_APPLY) {
                     float f[8], r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                     unpack8(lds128(base + idx * 16), f);
                     if (n_in > 1) unpack8(lds128(base + cb + idx * 16), r);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) f[j] = apply_act(fmaf(f[j], sc[j], sh[j]) + r[j], a.act);
-                    *reinterpret_cast<uint4*>(a.out0 + goff) = pack8(f);
+                    sts128(base + idx * 16, pack8(f));
                 } else {
                     float g[8], yv[8];
                     unpack8(lds128(base + idx * 16), g);
@@ -180,17 +216,23 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
                             acc1[j] = fmaf(g[j] * (yv[j] - c1[j]), c2[j], acc1[j]);
                         }
                     } else {
-                        if (a.out1 != nullptr) *reinterpret_cast<uint4*>(a.out1 + goff) = pack8(g);
                         float d[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) d[j] = fmaf(sc[j], g[j], fmaf(c1[j], yv[j], c2[j]));
-                        *reinterpret_cast<uint4*>(a.out0 + goff) = pack8(d);
+                        if (a.out1 != nullptr) sts128(base + cb + idx * 16, pack8(g));     // dres takes y's slot
+                        sts128(base + idx * 16, pack8(d));                                  // dy takes dz's slot
                     }
                 }
             }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[s]);
+        if (MODE == SB_BWD_REDUCE) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        } else {
+            fence_proxy_async_smem();          // the results were written through the generic proxy; the bulk store reads them
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&done[s]);
+        }
         if (++s == stages) { s = 0; phase ^= 1; }
     }
 
@@ -225,14 +267,15 @@ static bool stream_eligible(long long P, int C) {
 
 template <int MODE>
 static int launch_stream(StreamArgs& a, cudaStream_t stream) {
-    a.chunk_bytes = a.n_in == 1 ? SB_MAX_CHUNK_BYTES : 16384;
+    static const int one_in_chunk = [] { const char* e = getenv("PICD_BN_CHUNK"); return e == nullptr ? SB_MAX_CHUNK_BYTES : atoi(e); }();
+    a.chunk_bytes = a.n_in == 1 ? one_in_chunk : 16384;
     a.rows_per_chunk = a.chunk_bytes / (a.C * 2);
     a.num_chunks = (a.P + a.rows_per_chunk - 1) / a.rows_per_chunk;
     const int stage_bytes = a.n_in * a.chunk_bytes;
     int stages = (200 * 1024) / stage_bytes;
     if (stages > SB_MAX_STAGES) stages = SB_MAX_STAGES;
     a.stages = stages;
-    int smem = stages * stage_bytes + 256;
+    int smem = stages * stage_bytes + 512;
     if (MODE == SB_BWD_REDUCE && smem < 33 * 1024) smem = 33 * 1024;
     static bool attr_set = false;
     if (!attr_set) {
