@@ -87,6 +87,23 @@ def group_basic():
     u8 = torch.randint(0, 256, (2, 16, 16, 3), dtype=torch.uint8, device=dev)
     ok &= check("normalize_u8", ops.normalize_u8(u8, torch.bfloat16), ref.normalize_u8(u8), 1e-2, g)
 
+    # channel concat / split (inception blocks) and batched top-1
+    parts = [torch.randn(3, c, 9, 7, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_()
+             for c in (64, 96, 8, 320)]
+    wide = ops.concat_channels(parts)
+    want = torch.cat([q.detach() for q in parts], 1)
+    emit({"group": g, "test": "concat_nhwc_fwd", "ok": bool(torch.equal(wide, want)) and wide.is_contiguous(memory_format=torch.channels_last)})
+    dw_ = torch.randn_like(wide)
+    wide.backward(dw_)
+    offs = [0, 64, 160, 168, 488]
+    emit({"group": g, "test": "concat_nhwc_bwd",
+          "ok": all(bool(torch.equal(q.grad, dw_[:, offs[i]:offs[i + 1]])) for i, q in enumerate(parts))})
+    for dt in (torch.float32, torch.bfloat16):
+        lg = torch.randn(1000, 7, device=dev).to(dt)
+        lb = torch.randint(0, 7, (1000,), device=dev)
+        hits = ops.top1_hits(lg, lb)
+        emit({"group": g, "test": f"top1_hits[{dt}]", "ok": bool(torch.equal(hits, 1 * (lg.argmax(1) == lb))) and hits.dtype == torch.int64})
+
     # BN family
     for (N, C, H, W, res, act) in [(8, 64, 14, 14, False, "relu"), (4, 256, 7, 7, True, "relu"), (4, 96, 9, 9, False, "none"),
                                    (2, 2048, 7, 7, True, "relu"), (4, 40, 6, 6, False, "swish"),

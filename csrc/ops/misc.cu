@@ -664,6 +664,54 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += step) out[i] = __float2bfloat16(in[i]);
 }
 
+
+// ------------------------------------------------------------------------------------ channel concat / split (NHWC)
+// Inception blocks concatenate 3-4 branch outputs along channels.  forward: dst[p, off_i + c] = src_i[p, c];
+// backward (split = 1): src_i[p, c] = dst[p, off_i + c].  One launch for all branches, 16-byte vectors.
+constexpr int CAT_MAX = 8;
+struct CatArgs {
+    __nv_bfloat16* part[CAT_MAX];
+    int c_off[CAT_MAX + 1];      // channel offset of every part inside the wide tensor (in elements); c_off[n] = Ctot
+    int n;
+};
+__global__ void __launch_bounds__(256) concat_nhwc_kernel(const CatArgs a, __nv_bfloat16* __restrict__ wide, long long P,
+                                                          int split) {
+    const int ctot = a.c_off[a.n];
+    const int vtot = ctot >> 3;
+    const long long total = P * vtot;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+        const long long row = i / vtot;
+        const int v = static_cast<int>(i - row * vtot);
+        const int c = v << 3;
+        int k = 0;
+#pragma unroll
+        for (int j = 1; j < CAT_MAX; ++j)
+            if (j < a.n && c >= a.c_off[j]) k = j;
+        const int cw = a.c_off[k + 1] - a.c_off[k];
+        uint4* pw = reinterpret_cast<uint4*>(wide + row * ctot + c);
+        uint4* pp = reinterpret_cast<uint4*>(a.part[k] + row * cw + (c - a.c_off[k]));
+        if (split) *pp = *pw; else *pw = *pp;
+    }
+}
+
+// ------------------------------------------------------------------------------------ top-1 hits
+// out[b] = 1 if argmax(logits[b, :]) == label[b] else 0 (first maximum wins, like torch.argmax); one thread per row.
+template <typename T>
+__global__ void __launch_bounds__(256) top1_hits_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
+                                                        long long* __restrict__ out, int B, int NC) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const T* row = logits + static_cast<size_t>(b) * NC;
+    float best = static_cast<float>(row[0]);
+    int arg = 0;
+    for (int c = 1; c < NC; ++c) {
+        const float v = static_cast<float>(row[c]);
+        if (v > best) { best = v; arg = c; }
+    }
+    out[b] = (arg == static_cast<int>(labels[b])) ? 1 : 0;
+}
+
 }  // namespace picd
 
 using namespace picd;
@@ -837,6 +885,33 @@ extern "C" int picd_synthetic_batch(void* img, long long* labels, int batch, int
                                     unsigned base, int out_fp32, cudaStream_t st) {
     const long long n_el = 1LL * batch * H * W * C;
     synth_kernel<<<grid_for(n_el), 256, 0, st>>>(img, labels, n_el, batch, C, num_classes, base, out_fp32);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// parts: array of n device pointers (host memory), channels: array of n channel counts (multiples of 8)
+extern "C" int picd_concat_nhwc(void* const* parts, const int* channels, int n, void* wide, long long P, int split,
+                                cudaStream_t st) {
+    PICD_REQUIRE(n >= 1 && n <= CAT_MAX, "concat: %d parts (max %d)", n, CAT_MAX);
+    CatArgs a;
+    int off = 0;
+    for (int i = 0; i < n; ++i) {
+        PICD_REQUIRE(channels[i] % 8 == 0, "concat: part %d has %d channels (must be a multiple of 8)", i, channels[i]);
+        a.part[i] = static_cast<bf16*>(parts[i]);
+        a.c_off[i] = off;
+        off += channels[i];
+    }
+    for (int i = n; i <= CAT_MAX; ++i) a.c_off[i] = off;
+    for (int i = n; i < CAT_MAX; ++i) a.part[i] = nullptr;
+    a.n = n;
+    concat_nhwc_kernel<<<grid_for(P * (off / 8)), 256, 0, st>>>(a, static_cast<bf16*>(wide), P, split);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_top1_hits(const void* logits, int is_bf16, const long long* labels, long long* out, int B, int NC,
+                              cudaStream_t st) {
+    if (B <= 0) return 0;
+    if (is_bf16) top1_hits_kernel<bf16><<<(B + 255) / 256, 256, 0, st>>>(static_cast<const bf16*>(logits), labels, out, B, NC);
+    else top1_hits_kernel<float><<<(B + 255) / 256, 256, 0, st>>>(static_cast<const float*>(logits), labels, out, B, NC);
     PICD_LAUNCH_CHECK();
     return 0;
 }

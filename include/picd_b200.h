@@ -100,6 +100,13 @@ int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, in
 int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, long long rows, int C, int act,
                  cudaStream_t stream);
 int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t stream);
+/* NHWC channel concat (split = 0) / its backward split (split = 1) of n <= 8 bf16 tensors [P, C_i] <-> [P, sum C_i];
+ * `parts` and `channels` are host arrays. */
+int picd_concat_nhwc(void* const* parts, const int* channels, int n, void* wide, long long P, int split,
+                     cudaStream_t stream);
+/* out[b] = (argmax_c logits[b, c] == labels[b]) as int64; logits bf16 or fp32 row-major [B, NC]. */
+int picd_top1_hits(const void* logits, int is_bf16, const long long* labels, long long* out, int B, int NC,
+                   cudaStream_t stream);
 int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, cudaStream_t stream);
 /* graph-replay variant: the seed is mixed with the 32-bit word at step_word (device memory) when the kernel runs */
 int picd_dropout_dyn(const void* x, void* out, long long n, float p, unsigned seed, const void* step_word,

@@ -31,7 +31,7 @@ class BasicConv2d(nn.Module):
 
 
 def _cat(xs):
-    return torch.cat(xs, 1).contiguous(memory_format=torch.channels_last)
+    return ops.concat_channels(xs)
 
 
 class InceptionA(nn.Module):
@@ -147,6 +147,10 @@ class Inception3(nn.Module):
     def __init__(self, num_classes=1000, aux_logits=True, transform_input=False, dropout=0.5):
         super().__init__()
         self.aux_logits, self.transform_input = aux_logits, transform_input
+        self.register_buffer("_ti_scale", torch.tensor([0.229 / 0.5, 0.224 / 0.5, 0.225 / 0.5]).view(1, 3, 1, 1),
+                             persistent=False)
+        self.register_buffer("_ti_shift", torch.tensor([(0.485 - 0.5) / 0.5, (0.456 - 0.5) / 0.5,
+                                                        (0.406 - 0.5) / 0.5]).view(1, 3, 1, 1), persistent=False)
         self.Conv2d_1a_3x3 = BasicConv2d(3, 32, 3, stride=2)
         self.Conv2d_2a_3x3 = BasicConv2d(32, 32, 3)
         self.Conv2d_2b_3x3 = BasicConv2d(32, 64, 3, padding=1)
@@ -171,9 +175,8 @@ class Inception3(nn.Module):
     def _transform_input(self, x):
         # torchvision applies this when pretrained weights are requested:
         # re-normalise from ImageNet mean/std to the (0.5, 0.5) convention per channel.
-        scale = x.new_tensor([0.229 / 0.5, 0.224 / 0.5, 0.225 / 0.5]).view(1, 3, 1, 1)
-        shift = x.new_tensor([(0.485 - 0.5) / 0.5, (0.456 - 0.5) / 0.5, (0.406 - 0.5) / 0.5]).view(1, 3, 1, 1)
-        return x * scale + shift
+        # the constants live in (non-persistent) buffers: no host -> device copy per step, CUDA-graph safe
+        return x * self._ti_scale.to(x.dtype) + self._ti_shift.to(x.dtype)
 
     def forward(self, x):
         if self.transform_input:

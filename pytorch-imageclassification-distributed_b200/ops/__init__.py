@@ -192,3 +192,21 @@ def normalize_u8(images_u8, dtype=torch.float32):
         from . import native
         return native.normalize_u8(images_u8, dtype)
     return ref.normalize_u8(images_u8, dtype)
+
+
+def concat_channels(xs):
+    """torch.cat(xs, dim=1) for NHWC activations (inception blocks)."""
+    xs = list(xs)
+    if use_native(xs[0]) and all(x.dtype == torch.bfloat16 for x in xs):
+        from . import native
+        return native.concat_channels(xs)
+    out = torch.cat(xs, 1)
+    return out.contiguous(memory_format=torch.channels_last) if out.dim() == 4 else out
+
+
+def top1_hits(logits, labels):
+    """Per-sample top-1 hit as int64 [N] (reference utils.py:25-27)."""
+    if logits.dim() == 2 and use_native(logits):
+        from . import native
+        return native.top1_hits(logits, labels)
+    return 1 * (logits.argmax(dim=1) == labels)

@@ -64,6 +64,8 @@ _SIG = {
     "picd_synthetic_batch": "ppiiiiiuip",
     "picd_normalize_u8": "pplii" + "p",
     "picd_cast_f32_bf16": "pplp",
+    "picd_concat_nhwc": "ppiplip",
+    "picd_top1_hits": "pippiip",
 }
 _CT = {"p": ctypes.c_void_p, "i": ctypes.c_int, "f": ctypes.c_float, "l": ctypes.c_longlong,
        "u": ctypes.c_uint, "z": ctypes.c_size_t}
@@ -907,4 +909,50 @@ def normalize_u8(images_u8, dtype):
     src = images_u8.contiguous()
     out = torch.empty((n, c, h, w), dtype=dtype, device=src.device, memory_format=torch.channels_last)
     call("picd_normalize_u8", src, out, src.numel(), c, int(dtype == torch.float32))
+    return out
+
+# --------------------------------------------------------------------------- channel concat (inception blocks, K12)
+def _concat_call(parts, wide, split):
+    n = len(parts)
+    ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in parts])
+    chans = (ctypes.c_int * n)(*[t.shape[1] for t in parts])
+    P = wide.numel() // wide.shape[1]
+    call("picd_concat_nhwc", ctypes.cast(ptrs, ctypes.c_void_p).value, ctypes.cast(chans, ctypes.c_void_p).value, n, wide, P,
+         int(split))
+
+
+class _ConcatNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *xs):
+        xs = [nhwc(x) for x in xs]
+        N, _, H, W = xs[0].shape
+        ctx.channels = [x.shape[1] for x in xs]
+        wide = empty_nhwc(N, sum(ctx.channels), H, W, xs[0].device)
+        _concat_call(xs, wide, 0)
+        return wide
+
+    @staticmethod
+    def backward(ctx, dwide):
+        dwide = nhwc(dwide)
+        N, _, H, W = dwide.shape
+        parts = [empty_nhwc(N, c, H, W, dwide.device) for c in ctx.channels]
+        _concat_call(parts, dwide, 1)
+        return tuple(parts)
+
+
+def concat_channels(xs):
+    if len(xs) > 8 or any(x.shape[1] % 8 != 0 for x in xs):
+        return torch.cat(xs, 1).contiguous(memory_format=torch.channels_last)
+    return _ConcatNHWC.apply(*xs)
+
+
+def top1_hits(logits, labels):
+    """int64 [B]: 1 where argmax(logits) == label, one launch for the whole batch."""
+    lg = logits.detach()
+    if lg.dtype not in (torch.bfloat16, torch.float32):
+        lg = lg.float()
+    lg = lg.contiguous()
+    lab = labels.to(torch.int64).contiguous()
+    out = torch.empty(lg.shape[0], dtype=torch.int64, device=lg.device)
+    call("picd_top1_hits", lg, int(lg.dtype == torch.bfloat16), lab, out, lg.shape[0], lg.shape[1])
     return out
