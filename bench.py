@@ -12,7 +12,8 @@ of CUDA events on the compute stream; the reported time is the MAX over ranks.  
 fixed, `value` is the whole-job images/sec.  Every step touches >1 GB of activations, i.e. inputs far larger than
 the 126 MB L2, so no explicit L2 flush is needed between iterations.  SM clocks / throttle reasons are sampled with
 nvidia-smi during the timed region.  `e2e` repeats the measurement through the public training API with the batch
-crossing PCIe from pinned host memory every step and the loss read back to the host every step.
+crossing PCIe from pinned host memory every step (copied one step ahead on a copy stream, see data/prefetch.py) and the
+loss read back to the host every step.
 """
 from __future__ import annotations
 
@@ -88,7 +89,7 @@ def timed_region(run_steps, steps, device, rank):
 # ------------------------------------------------------------------------------------------ our arm
 def run_b200(args):
     import torch
-    from picd_b200.data import SyntheticDeviceLoader, SyntheticHostLoader
+    from picd_b200.data import DevicePrefetcher, SyntheticDeviceLoader, SyntheticHostLoader
     from picd_b200.engine.graphed import GraphedTrainStep
     from picd_b200.engine.trainer import WeightedCrossEntropy
     from picd_b200.models import Classifier, convert_sync_batchnorm
@@ -138,10 +139,13 @@ def run_b200(args):
         sink = {"loss": 0.0}
 
         def run_e2e(n):
-            for _ in range(n):
-                images, labels = host_loader.batch(counter["i"])   # pinned uint8 -> H2D -> device normalise
-                counter["i"] += 1
-                sink["loss"] = float(step(images, labels).item())  # D2H read of the step's result
+            # pinned uint8 batch -> H2D + device normalise on the copy stream (prefetched one step ahead, like the training
+            # CLI does) -> training step -> D2H read of the step's loss
+            first = counter["i"]
+            counter["i"] += n
+            batches = (host_loader.host_batch(first + k) for k in range(n))
+            for b in DevicePrefetcher(batches, device):
+                sink["loss"] = float(step(b["image"], b["label"]).item())
 
         run_e2e(max(3, args.warmup // 2))
         ms_e, _ = timed_region(run_e2e, args.steps, device, rank)

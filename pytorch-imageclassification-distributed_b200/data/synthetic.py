@@ -73,11 +73,20 @@ class SyntheticHostLoader:
     def __len__(self):
         return self.steps_per_epoch
 
+    def host_batch(self, step: int) -> dict:
+        """The pinned uint8 batch of this step, still on the host (what a DataLoader with pin_memory yields)."""
+        i = step % len(self.images)
+        return {"image": self.images[i], "label": self.labels[i], "image_id": None}
+
     def batch(self, step: int):
         i = step % len(self.images)
         img = self.images[i].to(self.device, non_blocking=True)
         lab = self.labels[i].to(self.device, non_blocking=True)
         return ops.normalize_u8(img, self.dtype), lab
+
+    def host_iter(self, steps=None):
+        for s in range(self.steps_per_epoch if steps is None else steps):
+            yield self.host_batch(s)
 
     def __iter__(self):
         for s in range(self.steps_per_epoch):

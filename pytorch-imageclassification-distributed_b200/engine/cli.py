@@ -101,6 +101,9 @@ def main(argv: Optional[List[str]] = None) -> int:
         train_loader = make_loader(train_ds, args.batchsize, ShardedSampler(train_ds), args.num_workers)
         val_loader = make_loader(val_ds, 1 if args.batchsize == 4 else args.batchsize,
                                  ShardedSampler(val_ds), args.num_workers)      # train.py:118: batch_size=1
+        if device.type == "cuda":      # H2D copy + uint8 normalisation of batch i+1 overlap step i (data/prefetch.py)
+            from ..data import DevicePrefetcher
+            train_loader, val_loader = DevicePrefetcher(train_loader, device), DevicePrefetcher(val_loader, device)
 
     model = Classifier(args.model, num_classes, pretrained=args.pretrained, image_size=image_size,
                        small_input=small)
