@@ -153,6 +153,46 @@ def check_training(device):
     return ok
 
 
+def check_graph_training(device):
+    """CUDA-graph replay of the step across ranks: peer-flag epochs, SyncBN exchange slots and the learning rate come from
+    device memory, an eagerly launched ragged batch in between must not disturb the recorded slots."""
+    from picd_b200.engine.graphed import GraphedTrainStep
+    from picd_b200.engine.trainer import WeightedCrossEntropy
+    from picd_b200.models import Classifier, convert_sync_batchnorm
+    from picd_b200.ops import synthetic_batch
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ok = True
+    for sync in (False, True):
+        curves = {}
+        for graph in (False, True):
+            torch.manual_seed(0)
+            m = Classifier("resnet18", 7, image_size=64)
+            if sync:
+                convert_sync_batchnorm(m)
+            dp = FusedDataParallel(m.to(device), OptimizerSpec("sgd", lr=0.05, momentum=0.9))
+            dp.train()
+            step = GraphedTrainStep(dp, WeightedCrossEntropy(None), dp.optimizer, warmup=2, enabled=graph)
+            losses = []
+            for it in range(10):
+                bsz = 8 if it == 6 else 16                      # step 6 is a ragged batch: runs eagerly in both arms
+                img, lab = synthetic_batch(bsz, 3, 64, 64, 7, 0, (it % 3) * world + rank, device, torch.bfloat16)
+                losses.append(float(step(img, lab).item()))
+            flat = dp.arena.master.clone()
+            gathered = [torch.empty_like(flat) for _ in range(world)]
+            dist.all_gather(gathered, flat)
+            identical = all(torch.equal(gathered[0], t) for t in gathered)
+            curves[graph] = (losses, identical, step.replays)
+            del dp, step
+        (le, ie, _), (lg, ig, replays) = curves[False], curves[True]
+        close = all(abs(a - b) < 0.1 * max(1.0, abs(a)) for a, b in zip(le, lg))
+        good = all_ok(ie and ig and close and replays == 7 and all(l == l for l in lg), device)
+        emit({"test": f"graph_replay_train[sync_bn={sync}]", "eager": le, "graph": lg, "replays": replays,
+              "replicas_identical": bool(ie and ig), "ok": good})
+        ok &= good
+    return ok
+
+
 def sweep(device):
     """all-reduce + SGD-momentum update, fused over peer memory vs NCCL all_reduce + torch._foreach update."""
     from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
@@ -230,6 +270,7 @@ def main():
             ok &= check_fused_update(device, mode)
         ok &= check_sync_bn(device)
         ok &= check_training(device)
+        ok &= check_graph_training(device)
     if args.sweep:
         sweep(device)
     emit({"test": "SUMMARY", "world": dist.get_world_size(), "ok": bool(ok)})

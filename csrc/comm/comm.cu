@@ -207,9 +207,21 @@ __device__ __forceinline__ float xchg_sum(const PeerTable& pt, int W, long long 
     return acc;
 }
 
+// CUDA-graph replay: the launch was recorded with the epoch of the capture step and the EVEN half of its double-buffered
+// slot; *dyn_delta (rewritten by the host before every replay) says how many steps later this replay runs.
+__device__ __forceinline__ void apply_replay_delta(const unsigned* dyn_delta, int slot_floats, unsigned& epoch,
+                                                   long long& slot_off) {
+    if (dyn_delta != nullptr) {
+        epoch += *dyn_delta;
+        slot_off += (epoch & 1u) ? slot_floats : 0;
+    }
+}
+
 __global__ void __launch_bounds__(1024) p2p_allreduce_small_kernel(PeerTable pt, int rank, int W, const float* in,
                                                                    int in_replicas, float* out, int n,
-                                                                   long long slot_off, int flag_slot, unsigned epoch) {
+                                                                   long long slot_off, int flag_slot, unsigned epoch,
+                                                                   const unsigned* dyn_delta, int slot_floats) {
+    apply_replay_delta(dyn_delta, slot_floats, epoch, slot_off);
     xchg_publish_and_wait(pt, rank, W, in, n, in_replicas, slot_off, flag_slot, epoch);
     for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = xchg_sum(pt, W, slot_off, i);
 }
@@ -221,7 +233,8 @@ __global__ void __launch_bounds__(1024) bn_finalize_sync_kernel(PeerTable pt, in
                                                                 float momentum, float eps, float* scale, float* shift,
                                                                 float* mean_out, float* invstd_out, float* total_count,
                                                                 int C, long long slot_off, int flag_slot,
-                                                                unsigned epoch) {
+                                                                unsigned epoch, const unsigned* dyn_delta, int slot_floats) {
+    apply_replay_delta(dyn_delta, slot_floats, epoch, slot_off);
     float* mine = pt.xchg[rank] + slot_off;
     if (threadIdx.x == 0) mine[2 * C] = count;
     xchg_publish_and_wait(pt, rank, W, sums, 2 * C, replicas, slot_off, flag_slot, epoch);
@@ -374,7 +387,19 @@ extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_repli
                                         long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
     p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, in_replicas, out, n, slot_off, flag_slot,
-                                                       epoch);
+                                                       epoch, nullptr, 0);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// Graph-replay variants of the two small collectives: `slot_off` is the EVEN half of the slot, `epoch` the epoch at capture
+// time; the kernel adds *dyn_delta (device memory) and picks the half from the resulting parity.
+extern "C" int picd_p2p_allreduce_small_dyn(void* ctx, const float* in, int in_replicas, float* out, int n,
+                                            long long slot_off, int flag_slot, unsigned epoch, const void* dyn_delta,
+                                            int slot_floats, cudaStream_t stream) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(dyn_delta != nullptr, "p2p_allreduce_small_dyn: dyn_delta must point at a device word");
+    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, in_replicas, out, n, slot_off, flag_slot,
+                                                       epoch, static_cast<const unsigned*>(dyn_delta), slot_floats);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -386,7 +411,21 @@ extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas,
     CommCtx* c = static_cast<CommCtx*>(ctx);
     bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, replicas, count, gamma, beta, running_mean,
                                                     running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
-                                                    slot_off, flag_slot, epoch);
+                                                    slot_off, flag_slot, epoch, nullptr, 0);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int replicas, float count, const float* gamma,
+                                         const float* beta, float* running_mean, float* running_var, float momentum,
+                                         float eps, float* scale, float* shift, float* mean, float* invstd,
+                                         float* total_count, int C, long long slot_off, int flag_slot, unsigned epoch,
+                                         const void* dyn_delta, int slot_floats, cudaStream_t stream) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(dyn_delta != nullptr, "bn_finalize_sync_dyn: dyn_delta must point at a device word");
+    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, replicas, count, gamma, beta, running_mean,
+                                                    running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
+                                                    slot_off, flag_slot, epoch, static_cast<const unsigned*>(dyn_delta),
+                                                    slot_floats);
     PICD_LAUNCH_CHECK();
     return 0;
 }

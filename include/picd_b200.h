@@ -167,6 +167,14 @@ int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float coun
                           float* running_mean, float* running_var, float momentum, float eps, float* scale,
                           float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
                           int flag_slot, unsigned epoch, cudaStream_t stream);
+/* Graph-replay variants of the two small collectives: slot_off = EVEN half of the double-buffered slot, epoch = the epoch
+ * at capture time; the kernels add the device word *dyn_delta (steps since capture) and pick the half from the parity. */
+int picd_p2p_allreduce_small_dyn(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
+                                 int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, cudaStream_t stream);
+int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, float momentum, float eps, float* scale,
+                              float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
+                              int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, cudaStream_t stream);
 
 int picd_nvls_supported(void);   /* 1/0/-1: NVSwitch multicast available (probe only; the kernels use P2P loads/stores) */
 

@@ -12,13 +12,15 @@ What makes the step replayable:
   * the only step-varying host scalars -- learning rate, Adam bias corrections and the peer-flag epoch of the fused
     all-reduce kernels -- are read from a 16-byte device array that the host rewrites before each replay
     (``picd_fused_allreduce_update_dyn``);
-  * BatchNorm ``num_batches_tracked`` and the running statistics are updated by kernels, not by the host.
+  * BatchNorm ``num_batches_tracked`` and the running statistics are updated by kernels, not by the host;
+  * SyncBatchNorm's statistics exchanges (double-buffered peer-memory slots, epoch-numbered flags) are recorded on
+    slots of their own with the capture-time epoch; the kernels add a replay counter read from the same device array.
 
 Caller contract: do not keep a loss / output tensor WITH its autograd graph from an eager step alive across the call
 that records the graph (this class only hands out detached tensors).
 
-Not capturable (the step then simply runs eagerly): SyncBatchNorm (its exchange slots are double-buffered by a
-host-side epoch), ``no_sync`` accumulation, batches whose shape differs from the captured one (the ragged last batch).
+Not capturable (the step then simply runs eagerly): ``no_sync`` accumulation, batches whose shape differs from the
+captured one (the ragged last batch).
 """
 from __future__ import annotations
 
@@ -54,8 +56,6 @@ class GraphedTrainStep:
         m = self.model
         if not hasattr(m, "arena") or m.device.type != "cuda":
             return False
-        if any(getattr(x, "sync_group", False) is not False for x in m.modules()):
-            return False
         return True
 
     def _eager(self, images, labels):
@@ -87,6 +87,7 @@ class GraphedTrainStep:
         from ..ops import native
         m.capturing = True
         native.set_step_word(red.dyn[3:4])          # dropout masks follow the device-side step counter
+        red.comm.begin_capture(red.dyn)             # SyncBN collectives: slots of their own, epoch = capture epoch + delta
         try:
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self.static_loss = self._eager(self.static_images, self.static_labels)
@@ -94,6 +95,7 @@ class GraphedTrainStep:
         finally:
             m.capturing = False
             native.set_step_word(None)
+            red.comm.end_capture()
         self.launches_per_replay = int(lib.picd_launch_count() - l0)
         # recording executes nothing: undo the host-side step bookkeeping it advanced
         m.step_index, self.optimizer.step_count = step0, count0
@@ -114,7 +116,7 @@ class GraphedTrainStep:
         self.static_labels.copy_(labels, non_blocking=True)
         if m.broadcast_buffers:
             m._sync_buffers()
-        m._impl.write_dyn(m.step_index + 1)
+        m._impl.write_dyn(m.step_index + 1, self.replays)
         self.graph.replay()
         m.step_index += 1
         self.optimizer.step_count += 1

@@ -22,7 +22,8 @@ import torch.distributed as dist
 from ..ops._lib import check, require_lib
 
 SLOT_FLOATS = 2 * 2048 + 8          # (sum, sumsq) for up to 2048 channels + count
-N_SLOTS = 512                       # small-collective slots (each double-buffered)
+N_SLOTS = 1024                      # small-collective slots (each double-buffered); eager and graph-captured
+                                    # launches use disjoint slots, so a ResNet-101 needs 104 + 192 + 2 x 104 of them
 MAX_PEERS = 8
 TWO_SHOT_MIN_BYTES = 256 << 10      # below this a bucket is latency-bound: one-shot
 
@@ -128,6 +129,8 @@ class Comm:
         self._slots = {}
         self._slot_keys = []
         self._next_slot = 0
+        self.graph_dyn = None          # device float[8] while a CUDA graph of the step is recorded (word 4 = replay delta)
+        self._graph_slots = []         # slots owned by captured launches: their epochs advance once per replay
         self._f_upd = self.lib.picd_fused_allreduce_update
         self._f_upd.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 8 +
@@ -136,6 +139,15 @@ class Comm:
         self._f_upd_dyn.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 5 +
                                     [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p])
+        self._f_small_dyn = self.lib.picd_p2p_allreduce_small_dyn
+        self._f_small_dyn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                      ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p, ctypes.c_int,
+                                      ctypes.c_void_p]
+        self._f_bn_dyn = self.lib.picd_bn_finalize_sync_dyn
+        self._f_bn_dyn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float] + [ctypes.c_void_p] * 4 +
+                                   [ctypes.c_float, ctypes.c_float] + [ctypes.c_void_p] * 5 +
+                                   [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p, ctypes.c_int,
+                                    ctypes.c_void_p])
         self._f_small = self.lib.picd_p2p_allreduce_small
         self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                   ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
@@ -165,21 +177,41 @@ class Comm:
 
     # -- small collectives (SyncBN) ------------------------------------------------------------------
     def _slot(self, key) -> int:
-        s = self._slots.get(id(key))
+        k = (id(key), self.graph_dyn is not None)        # captured launches get slots of their own
+        s = self._slots.get(k)
         if s is None:
             s = self._next_slot
             self._next_slot += 1
             if s >= N_SLOTS:
                 raise RuntimeError("picd_b200: out of small-collective slots")
-            self._slots[id(key)] = s
+            self._slots[k] = s
             self._slot_keys.append(key)          # keep the key alive so its id() stays unique
         return s
 
     def _next(self, slot: int):
         e = self._slot_epoch.get(slot, 0) + 1
         self._slot_epoch[slot] = e
+        if self.graph_dyn is not None:
+            # recorded launch: pass the EVEN half and the capture-time epoch; the kernel adds the replay delta itself
+            self._graph_slots.append(slot)
+            return e, slot * 2 * SLOT_FLOATS, 2 * self.slab.max_buckets + slot
         off = (slot * 2 + (e & 1)) * SLOT_FLOATS
         return e, off, 2 * self.slab.max_buckets + slot
+
+    def begin_capture(self, dyn: torch.Tensor):
+        self.graph_dyn, self._graph_slots = dyn, []
+
+    def end_capture(self):
+        self.graph_dyn = None
+
+    def note_replay(self, index: int):
+        """Host bookkeeping for replay number `index` (0 = first): the graph's slots move one epoch per replay."""
+        if index > 0:
+            for s in self._graph_slots:
+                self._slot_epoch[s] += 1
+
+    def _delta_ptr(self):
+        return self.graph_dyn.data_ptr() + 16          # word 4 of the dyn array
 
     def bn_finalize_sync(self, sums, count, gamma, beta, rm, rv, momentum, eps, coef) -> float:
         C = gamma.numel()
@@ -187,11 +219,15 @@ class Comm:
             raise RuntimeError(f"picd_b200: SyncBN with {C} channels exceeds the exchange slot")
         e, off, fslot = self._next(self._slot(gamma))
         total = torch.empty(1, dtype=torch.float32, device=sums.device)
-        check(self._f_bn(self.ctx, sums.data_ptr(), sums.numel() // (2 * C), float(count), gamma.data_ptr(), beta.data_ptr(),
-                         None if rm is None else rm.data_ptr(), None if rv is None else rv.data_ptr(),
-                         float(momentum), float(eps), coef[0].data_ptr(), coef[1].data_ptr(), coef[2].data_ptr(),
-                         coef[3].data_ptr(), total.data_ptr(), C, off, fslot, e & 0xFFFFFFFF,
-                         torch.cuda.current_stream().cuda_stream), "picd_bn_finalize_sync")
+        args = (self.ctx, sums.data_ptr(), sums.numel() // (2 * C), float(count), gamma.data_ptr(), beta.data_ptr(),
+                None if rm is None else rm.data_ptr(), None if rv is None else rv.data_ptr(),
+                float(momentum), float(eps), coef[0].data_ptr(), coef[1].data_ptr(), coef[2].data_ptr(),
+                coef[3].data_ptr(), total.data_ptr(), C, off, fslot, e & 0xFFFFFFFF)
+        st = torch.cuda.current_stream().cuda_stream
+        if self.graph_dyn is not None:
+            check(self._f_bn_dyn(*args, self._delta_ptr(), SLOT_FLOATS, st), "picd_bn_finalize_sync_dyn")
+        else:
+            check(self._f_bn(*args, st), "picd_bn_finalize_sync")
         # every rank holds an equally sized shard (ShardedSampler pads), so the global count is known on the host
         return float(count) * self.slab.world
 
@@ -205,8 +241,13 @@ class Comm:
         holder = key if key is not None else self
         e, off, fslot = self._next(self._slot(_BwdKey.of(holder, n)))
         out = torch.empty(n, dtype=vec.dtype, device=vec.device)
-        check(self._f_small(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
-                            torch.cuda.current_stream().cuda_stream), "picd_p2p_allreduce_small")
+        st = torch.cuda.current_stream().cuda_stream
+        if self.graph_dyn is not None:
+            check(self._f_small_dyn(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
+                                    self._delta_ptr(), SLOT_FLOATS, st), "picd_p2p_allreduce_small_dyn")
+        else:
+            check(self._f_small(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF, st),
+                  "picd_p2p_allreduce_small")
         return out
 
 
@@ -234,21 +275,24 @@ class NativeReducer:
         self.side = torch.cuda.Stream(device=engine.device)
         self._epoch = 0
         self._dirty = False
-        self.dyn = None            # device float[4] (lr, bc1, bc2, epoch bits) while a step is captured / replayed
+        self.dyn = None            # device float[8] (lr, bc1, bc2, epoch bits, replay delta bits) while a step is captured / replayed
 
     def enable_dyn(self):
         if self.dyn is None:
-            self.dyn = torch.zeros(4, dtype=torch.float32, device=self.e.device)
+            self.dyn = torch.zeros(8, dtype=torch.float32, device=self.e.device)
         return self.dyn
 
-    def write_dyn(self, step: int):
-        """Refresh the step-varying scalars the captured update kernels read (host values -> device, in stream order)."""
+    def write_dyn(self, step: int, replay_index: int = 0):
+        """Refresh the step-varying scalars the captured kernels read (host values -> device, in stream order)."""
         s = self.e.spec
         b1, b2 = s.betas
-        bits = np.array([step & 0xFFFFFFFF], dtype=np.uint32).view(np.float32)[0]
-        host = torch.tensor([s.lr, 1.0 - b1 ** step, 1.0 - b2 ** step, 0.0], dtype=torch.float32)
-        host.numpy()[3] = bits                      # raw epoch bits (may not be a valid float: never touched as one)
+        words = np.array([step & 0xFFFFFFFF, replay_index & 0xFFFFFFFF], dtype=np.uint32).view(np.float32)
+        host = torch.zeros(8, dtype=torch.float32)
+        host[0], host[1], host[2] = s.lr, 1.0 - b1 ** step, 1.0 - b2 ** step
+        host.numpy()[3] = words[0]                  # raw bits (may not be valid floats: never touched as floats)
+        host.numpy()[4] = words[1]
         self.dyn.copy_(host)                        # pageable H2D: staged before the call returns, so `host` may die
+        self.comm.note_replay(replay_index)
 
     def _mode(self, b) -> int:
         if self.e.world == 1:
