@@ -97,6 +97,7 @@ def run_b200(args):
     from picd_b200.parallel import dist as D
     from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
 
+    os.environ["NCCL_DEBUG"] = os.environ.get("PICD_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout (one JSON line)
     local_rank = D.init_distributed("b200", args.local_rank)
     device = torch.device("cuda", torch.cuda.current_device())
     rank, world = D.get_rank(), D.get_world_size()

@@ -267,6 +267,19 @@ class FusedDataParallel(nn.Module):
                                 bucket_cap_bytes, self.world, self.rank)
         self.optimizer = FusedOptimizer(self)
         self._float_buffers = [b for b in module.buffers() if b.is_floating_point()]
+        self._flat_buffers = None
+        if device.type == "cuda" and self._float_buffers and all(b.dtype == torch.float32 for b in self._float_buffers):
+            # BN running statistics live in ONE flat tensor (the registered buffers become views of it): the per-forward
+            # buffer broadcast is then a single collective with no gather / scatter kernels around it
+            flat = torch.empty(sum(b.numel() for b in self._float_buffers), dtype=torch.float32, device=device)
+            off = 0
+            with torch.no_grad():
+                for b in self._float_buffers:
+                    n = b.numel()
+                    flat[off: off + n].copy_(b.reshape(-1))
+                    b.data = flat[off: off + n].view(b.shape)
+                    off += n
+            self._flat_buffers = flat
         has_sync_bn = any(getattr(m, "sync_group", False) is not False for m in module.modules())
         # P17: with SyncBN the running stats are identical on every rank already
         self.broadcast_buffers = broadcast_buffers and self.world > 1 and not has_sync_bn
@@ -297,6 +310,10 @@ class FusedDataParallel(nn.Module):
     def _sync_buffers(self):
         """Per-forward coalesced broadcast of BN running stats from rank 0."""
         if not self._float_buffers:
+            return
+        if self._flat_buffers is not None:
+            dist.broadcast(self._flat_buffers, src=dist.get_global_rank(self.group, 0) if self.group else 0,
+                           group=self.group)
             return
         flat = torch.cat([b.reshape(-1).float() for b in self._float_buffers])
         dist.broadcast(flat, src=0, group=self.group)
