@@ -95,9 +95,10 @@ __device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
 // =====================================================================================================
 //  conv / GEMM forward-style kernel: D[pixels, Cout] = sum_taps A_tap[pixels, Cin] * B_tap[Cout, Cin]^T
 // =====================================================================================================
-// kCluster: CTAs run in clusters of two that work on adjacent pixel tiles of the SAME column tile; each loads half of
-// every B (weight) tile and multicasts it to both, halving the L2->SM operand traffic of the pair (the single-CTA kernel
-// is L2-bandwidth bound on large-K tiles: ncu shows 48% tensor-pipe activity at 94 B/clk/SM of operand traffic).
+// kCluster: CTA PAIRS (tcgen05 cta_group::2).  The two CTAs of a cluster work on adjacent pixel tiles of the SAME column
+// tile as ONE 256-row UMMA: each CTA loads its own 128 pixel rows of A and HALF of every B (weight) tile, the leader
+// (cluster rank 0) issues the MMAs, each CTA drains its own 128 accumulator rows from its own TMEM.  Per CTA a k-iteration
+// then moves 16 + 16 KB instead of 16 + 32 KB through shared memory for the same tensor work (K-major B only).
 template <bool kBiasAct, bool kCluster>
 __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -105,7 +106,8 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     SmemBars* bars = reinterpret_cast<SmemBars*>(smem);
     const int BN = p.BN;
     const int stages = p.stages;
-    const int b_tap = BN * 128;                                   // one weight tap tile: BN rows x 64 k (or 64 k x BN)
+    const int b_tap = (kCluster ? BN / 2 : BN) * 128;             // one weight tap tile: BN rows x 64 k (or 64 k x BN);
+                                                                  // a CTA of a pair holds half the rows
     const int b_stage = p.halo ? (p.b_resident ? 0 : 3 * b_tap) : b_tap;
     const int a_stage = p.a_stage_bytes;
     uint8_t* sA = smem + SMEM_HEADER;
@@ -119,18 +121,19 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     if (threadIdx.x == 0) {
         for (int i = 0; i < stages; ++i) {
             mbar_init(&bars->full[i], 1);
-            mbar_init(&bars->empty[i], kCluster ? 2 : 1);     // cluster: both CTAs' MMA warps release a stage
+            mbar_init(&bars->empty[i], 1);                    // pair: the leader's commit arrives once in each CTA
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bars->tfull[i], 1);
-            mbar_init(&bars->tempty[i], 8);
+            mbar_init(&bars->tempty[i], kCluster ? 16 : 8);   // pair: the leader waits for both CTAs' epilogue warps
         }
         mbar_init(&bars->bres, 1);
         fence_mbar_init();
     }
+    if (kCluster) cluster_sync();          // both CTAs are resident before the pair-wide TMEM allocation
     if (warp == 1) {
-        tmem_alloc(&bars->tmem_base, 512);
-        tmem_relinquish();
+        if (kCluster) { tmem_alloc_pair(&bars->tmem_base, 512); tmem_relinquish_pair(); }
+        else { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
     }
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.amap[0]);
@@ -139,7 +142,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     }
     tc_fence_before();
     __syncthreads();
-    if (kCluster) cluster_sync();          // the peer's barriers exist before anything is multicast at them
+    if (kCluster) cluster_sync();          // the peer's barriers exist before anything arrives on them
     tc_fence_after();
     const uint32_t tmem_base = uniform_u32(bars->tmem_base);
 
@@ -214,26 +217,35 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                     const Tap tp = p.taps[t];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(&bars->empty[stage], phase ^ 1);
-                        mbar_arrive_expect_tx_warp(&bars->full[stage], tx_bytes);
-                        tma_load_4d_warp(sA + stage * a_stage, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
-                                    w0 + tp.dw, h0 + tp.dh, n0);
                         uint8_t* dstB = sB + stage * b_stage;
-                        if (!p.b_mn) {
-                            if (kCluster) {     // this CTA fetches rows [crank*BN/2, +BN/2) of the tile for both CTAs
-                                tma_load_3d_mc_warp(dstB + crank * (b_stage >> 1), &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
-                                               n_tile * BN + crank * (BN >> 1), 3);
-                            } else {
-                                tma_load_3d_warp(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                        if (kCluster) {
+                            // pair: the leader's barrier collects the bytes of BOTH CTAs; this CTA fetches its own pixel
+                            // rows and weight rows [crank * BN/2, +BN/2) into its own shared memory
+                            if (crank == 0) mbar_arrive_expect_tx_warp(&bars->full[stage], 2 * tx_bytes);
+                            tma_load_4d_pair_warp(sA + stage * a_stage, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
+                                                  w0 + tp.dw, h0 + tp.dh, n0);
+                            if (!p.b_mn) {
+                                tma_load_3d_pair_warp(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
+                                                      n_tile * BN + crank * (BN >> 1));
+                            } else {                     // MN-major: this CTA's half of the columns, in 64-column boxes
+                                for (int j = 0; j < BN / 128; ++j) {
+                                    int c0 = n_tile * BN + crank * (BN >> 1) + j * 64;
+                                    if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
+                                    tma_load_3d_pair_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
+                                }
                             }
                         } else {
-                            // cluster: this CTA fetches every second 64-column box (j = crank, crank + 2, ...) for both CTAs
-                            for (int j = kCluster ? crank : 0; j < BN / 64; j += kCluster ? 2 : 1) {
-                                int c0 = n_tile * BN + j * 64;
-                                if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
-                                if (kCluster)
-                                    tma_load_3d_mc_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK, 3);
-                                else
+                            mbar_arrive_expect_tx_warp(&bars->full[stage], tx_bytes);
+                            tma_load_4d_warp(sA + stage * a_stage, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
+                                             w0 + tp.dw, h0 + tp.dh, n0);
+                            if (!p.b_mn) {
+                                tma_load_3d_warp(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap, n_tile * BN);
+                            } else {
+                                for (int j = 0; j < BN / 64; ++j) {
+                                    int c0 = n_tile * BN + j * 64;
+                                    if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
                                     tma_load_3d_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
+                                }
                             }
                         }
                         if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -249,7 +261,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         uint32_t phase = 0;
         int acc = 0;
         uint32_t accphase = 0;
-        const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 0, p.b_mn);
+        const uint32_t idesc = make_idesc_bf16(kCluster ? 2 * TILE_M : TILE_M, BN, 0, p.b_mn);
         const uint64_t a_tmpl = make_smem_desc(0, 16, 1024);
         const uint64_t b_tmpl = p.b_mn ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
         const uint32_t b_kstep = p.b_mn ? (2048u >> 4) : (32u >> 4);      // descriptor units (16 B) per K=16 step
@@ -258,7 +270,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         const uint32_t b_tap_lo = static_cast<uint32_t>(b_tap) >> 4;
         const uint32_t row_lo = (static_cast<uint32_t>(bw) * 128u) >> 4;   // one pixel row of the halo box
         if (p.halo && p.b_resident) { mbar_wait(&bars->bres, 0); tc_fence_after(); }
-        for (int m = m_first; m < m_limit; m += grid_m) {
+        for (int m = m_first; m < m_limit && (!kCluster || crank == 0); m += grid_m) {     // pair: only the leader issues
             mbar_wait(&bars->tempty[acc], accphase ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * 256;
@@ -280,14 +292,17 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                 } else {
                     const uint64_t bdesc0 = b_tmpl | (sB_lo + stage * b_stage_lo);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16_warp(tmem_d, adesc0 + k * 2, bdesc0 + k * b_kstep, idesc, (it | k) != 0);
+                    for (int k = 0; k < 4; ++k) {
+                        if (kCluster) umma_bf16_pair_warp(tmem_d, adesc0 + k * 2, bdesc0 + k * b_kstep, idesc, (it | k) != 0);
+                        else umma_bf16_warp(tmem_d, adesc0 + k * 2, bdesc0 + k * b_kstep, idesc, (it | k) != 0);
+                    }
                 }
-                if (kCluster) umma_commit_mc_warp(&bars->empty[stage], 3);   // frees the stage in both CTAs
+                if (kCluster) umma_commit_pair_warp(&bars->empty[stage], 3);   // frees the stage in both CTAs
                 else umma_commit_warp(&bars->empty[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit_warp(&bars->tfull[acc]);
+            if (kCluster) umma_commit_pair_warp(&bars->tfull[acc], 3);         // both CTAs' accumulator rows are complete
+            else umma_commit_warp(&bars->tfull[acc]);
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
         }
@@ -386,7 +401,10 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                 if (hf == n_halves - 1) {                     // every accumulator column has been read
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&bars->tempty[acc]);
+                    if (lane == 0) {
+                        if (kCluster) mbar_arrive_leader(&bars->tempty[acc]);      // the leader's MMA warp waits for both CTAs
+                        else mbar_arrive(&bars->tempty[acc]);
+                    }
                 }
                 fence_proxy_async_smem();
                 named_barrier_sync(1, 256);
@@ -470,8 +488,11 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
 
     tc_fence_before();
     __syncthreads();
-    if (kCluster) cluster_sync();          // nobody leaves while the peer can still multicast into / arrive on this CTA
-    if (warp == 1) tmem_dealloc(tmem_base, 512);
+    if (kCluster) cluster_sync();          // nobody leaves while the pair's MMAs / barrier arrivals can still touch this CTA
+    if (warp == 1) {
+        if (kCluster) tmem_dealloc_pair(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
+    }
 }
 
 // =====================================================================================================
@@ -712,15 +733,17 @@ static int num_n_tiles(int C, int* BN) {
     return ceil_div(C, bn);
 }
 
-// Cluster-of-2 multicast pays when operand traffic (not the output) limits the kernel: enough K work per tile.
+// CTA pairs (cta_group::2) pay when operand traffic (not the output) limits the kernel: enough K work per tile.
 // PICD_CLUSTER=0 disables it, =1 forces it wherever it is legal, unset = heuristic.
 static bool want_cluster(int k_iters, int num_m_tiles, int BN, bool b_mn) {
     static const int mode = [] { const char* e = getenv("PICD_CLUSTER"); return e == nullptr ? -1 : atoi(e); }();
     if (mode == 0 || num_m_tiles < 2) return false;
-    if (b_mn) return false;      // MN-major B (dgrad): the box-wise split between the two CTAs gave wrong results once the
-                                 // producer became warp-convergent and measured no gain before that -> single-CTA path
+    if (b_mn && (BN % 128) != 0) return false;          // MN-major B is split between the pair in 64-column boxes
     if (mode == 1) return true;
-    return k_iters >= 4;
+    // Pairs pay when the tile is operand-bound, not HBM-bound: per CTA a k-iteration costs 2 * BN tensor cycles but moves
+    // 128 * (64 + BN/k_iters) * 2 bytes of activations -- below ~12 k-iterations of a 256-wide tile the memory system is the
+    // limit and independent CTAs schedule better (measured: the 56x56 / 28x28 ResNet layers lose 10-20% in pair mode).
+    return k_iters >= 12 && BN >= 192;
 }
 
 // halo mode keeps three weight taps per stage, so its column tiles are capped at 128 channels
@@ -740,12 +763,12 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     // tiny weight sets (64 -> 64 channels) stay resident: the ring then carries activations only
     p.b_resident = (p.halo && p.kchunks == 1 && 9 * BN * 128 <= 80 * 1024) ? 1 : 0;
     const int resident = p.b_resident ? 9 * BN * 128 : 0;
-    const int stage_bytes = p.a_stage_bytes + (p.halo ? (p.b_resident ? 0 : 3 * BN * 128) : BN * 128);
+    const int stage_bytes = p.a_stage_bytes + (p.halo ? (p.b_resident ? 0 : 3 * BN * 128) : (p.cluster ? BN / 2 : BN) * 128);
     // short-K tiles are epilogue-bound: drain 256 columns in one pass; otherwise drain halves and spend the smem on stages
     p.half_w = (BN == 256 && p.ntaps * p.kchunks <= 2) ? 256 : 128;
     const int staging = std::min(BN, p.half_w) * 256;   // 128 rows x half_w columns x 2 B
     int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging - resident) / stage_bytes;
-    stages = std::min(stages, p.halo ? 8 : 6);
+    stages = std::min(stages, (p.halo || p.cluster) ? 8 : 6);
     PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
     p.stages = stages;
     static bool attr_set = false;
