@@ -76,18 +76,45 @@ def run(args, ref_dir, timed_region, published_baseline, cfg):
     train_epoch = ns["train_epoch"]
 
     name = {"resnet50": "resnet50", "resnet101": "resnet101", "inceptionv3": "inceptionv3"}.get(args.model)
-    if name is None:
+    note = None
+    torch.manual_seed(0)
+    if name is not None:
+        model = ref_classifier.Classifier(name=name, num_classes=cfg["num_classes"])
+    elif args.model == "vit_b_16":
+        # BASELINE.json names ViT-B/16 as a target, but the reference's Classifier has no ViT branch
+        # (nn/classifier.py:11-23).  The closest reference-style arm: the reference's train_epoch + DDP wrapping around a
+        # torchvision ViT-B/16 whose head is replaced by the reference's MLP head, attribute name `encoder` as in Classifier.
+        name = "vit_b_16"
+        note = "reference train_epoch + DDP around torchvision vit_b_16 with the reference's MLP head (its Classifier has no ViT)"
+
+        class _RefStyleViT(tnn.Module):
+            def __init__(self, nc):
+                super().__init__()
+                self.encoder = tvm.vit_b_16(weights=None, image_size=args.image_size)
+                nf = self.encoder.heads.head.in_features
+                self.encoder.heads = tnn.Sequential(tnn.Linear(nf, 128), tnn.ReLU(inplace=True), tnn.Linear(128, 64),
+                                                    tnn.ReLU(inplace=True), tnn.Linear(64, 32), tnn.ReLU(inplace=True),
+                                                    tnn.Linear(32, nc))
+
+            def forward(self, images):
+                return self.encoder(images)
+
+        model = _RefStyleViT(cfg["num_classes"])
+    else:
         if rank == 0:
             print(json.dumps({"impl": "reference", "unavailable": f"the reference has no backbone named {args.model}"}))
         dist.destroy_process_group()
         return
-    torch.manual_seed(0)
-    model = ref_classifier.Classifier(name=name, num_classes=cfg["num_classes"])
     if args.sync_bn:
         model = tnn.SyncBatchNorm.convert_sync_batchnorm(model, None)              # train.py:124
     model = model.cuda()
-    optimizer = torch.optim.SGD(model.parameters(), lr=cfg["lr"], momentum=cfg["momentum"],
-                                weight_decay=cfg["weight_decay"])
+    if args.optimizer == "adamw":
+        optimizer = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=cfg["weight_decay"])
+    elif args.optimizer == "adam":
+        optimizer = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=cfg["weight_decay"])
+    else:
+        optimizer = torch.optim.SGD(model.parameters(), lr=cfg["lr"], momentum=cfg["momentum"],
+                                    weight_decay=cfg["weight_decay"])
     model = DDP(model, device_ids=[local_rank], output_device=local_rank, find_unused_parameters=False)  # train.py:128
     weight = torch.tensor(cfg["class_weights"], requires_grad=False, dtype=torch.float32).cuda()
     loss_fn = tnn.CrossEntropyLoss(weight=weight)                                   # train.py:157-158
@@ -133,8 +160,9 @@ def run(args, ref_dir, timed_region, published_baseline, cfg):
             "data": "synthetic (random tensors; random-init weights)",
             "config": {"model": f"{args.model}+MLP head ({cfg['num_classes']} classes)", "global_batch": B * world,
                        "per_gpu_batch": B, "image_size": S, "seq_len": None,
-                       "optimizer": f"sgd-momentum lr={cfg['lr']} wd={cfg['weight_decay']}", "sync_bn": args.sync_bn,
+                       "optimizer": (f"sgd-momentum lr={cfg['lr']} wd={cfg['weight_decay']}" if args.optimizer == "sgd"
+                                     else f"{args.optimizer} lr=0.001 wd={cfg['weight_decay']}"), "sync_bn": args.sync_bn,
                        "parallelism": f"ddp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": None}))
+            "clocks": clocks, "e2e": e2e, "gpu_launches": None, "note": note}))
     dist.barrier(device_ids=[local_rank])
     dist.destroy_process_group()

@@ -163,7 +163,8 @@ def run_b200(args):
             "dtype": "bf16", "data": "synthetic (generated + normalised on device; random-init weights)",
             "config": {"model": f"{args.model}+MLP head ({NUM_CLASSES} classes)", "global_batch": args.batch * world,
                        "per_gpu_batch": args.batch, "image_size": args.image_size, "seq_len": None,
-                       "optimizer": f"{args.optimizer}-momentum lr={LR} wd={WEIGHT_DECAY}", "sync_bn": args.sync_bn,
+                       "optimizer": (f"sgd-momentum lr={LR} wd={WEIGHT_DECAY}" if args.optimizer == "sgd"
+                                     else f"{args.optimizer} lr=0.001 wd={WEIGHT_DECAY}"), "sync_bn": args.sync_bn,
                        "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)",
                        "cuda_graph": bool(step.graph is not None)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss}))

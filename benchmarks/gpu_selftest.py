@@ -206,7 +206,9 @@ def group_basic():
     ok &= check("layernorm.dbeta", bt.grad, bt2.grad, 3e-2, g)
 
     # small linear
-    for (M, K, N, act) in [(16, 2048, 128, "relu"), (16, 32, 7, None), (5, 64, 32, "relu")]:
+    # the last three take the tcgen05 GEMM path with the separate activation kernels (GELU: fast erf; dbias fused in act_bwd)
+    for (M, K, N, act) in [(16, 2048, 128, "relu"), (16, 32, 7, None), (5, 64, 32, "relu"), (1024, 768, 3072, "gelu"),
+                           (788, 256, 512, "swish"), (512, 768, 768, None)]:
         x = torch.randn(M, K, device=dev).to(torch.bfloat16)
         wt = (torch.randn(N, K, device=dev) / K ** 0.5).requires_grad_()
         b = torch.randn(N, device=dev).requires_grad_()

@@ -406,10 +406,24 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SWISH = 3, ACT_SIGMOID = 4 };
+// erf-based GELU pieces from ONE exponential and ONE reciprocal (Abramowitz-Stegun 7.1.26, |error| < 1.5e-7, far below bf16
+// rounding): e = exp(-x^2/2) serves both the erf tail and the Gaussian density of the derivative.  libdevice's erff alone
+// costs more than this whole function and made the GELU kernels ALU-bound.
+__device__ __forceinline__ float gelu_cdf(float x, float& e) {          // Phi(x) = 0.5 (1 + erf(x / sqrt 2)); e = exp(-x^2 / 2)
+    const float z = fabsf(x) * 0.70710678118654752f;
+    e = __expf(-z * z);
+    const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float tail = 0.5f * poly * t * e;                              // 0.5 * erfc(z)
+    return x >= 0.f ? 1.f - tail : tail;
+}
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_RELU: return fmaxf(x, 0.f);
-        case ACT_GELU: return 0.5f * x * (1.f + erff(x * 0.70710678118654752f));
+        case ACT_GELU: { float e; return x * gelu_cdf(x, e); }
         case ACT_SWISH: return x / (1.f + __expf(-x));
         case ACT_SIGMOID: return 1.f / (1.f + __expf(-x));
         default: return x;
@@ -420,8 +434,9 @@ __device__ __forceinline__ float act_grad(float x, int act) {
     switch (act) {
         case ACT_RELU: return x > 0.f ? 1.f : 0.f;
         case ACT_GELU: {
-            float c = 0.5f * (1.f + erff(x * 0.70710678118654752f));
-            return c + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+            float e;
+            const float c = gelu_cdf(x, e);
+            return fmaf(x * 0.3989422804014327f, e, c);
         }
         case ACT_SWISH: {
             float s = 1.f / (1.f + __expf(-x));

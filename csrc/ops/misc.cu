@@ -3,6 +3,8 @@
 // All activations are NHWC bf16; reductions accumulate in fp32.
 #include "../common/picd_common.cuh"
 
+#include <algorithm>
+
 namespace picd {
 
 static int grid_for(long long work, int block = 256, int waves = 8) {
@@ -322,34 +324,101 @@ __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ log
 }
 
 // ------------------------------------------------------------------------------------ element-wise activation
+// TACT >= 0 fixes the activation at compile time (no per-element switch); two vectors per thread are in flight.
+template <int TACT>
 __global__ void __launch_bounds__(256) act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bias,
                                                       __nv_bfloat16* __restrict__ out, long long total_vecs, int C,
                                                       int act) {
     const int vecs = C >> 3;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
-        const int c0 = static_cast<int>(i % vecs) * 8;
+    for (long long i0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total_vecs; i0 += 2 * step) {
+        uint4 raw[2];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k] + (bias != nullptr ? bias[c0 + k] : 0.f), act);
-        *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
+        for (int u = 0; u < 2; ++u) {
+            const long long i = i0 + u * step;
+            raw[u] = i < total_vecs ? *reinterpret_cast<const uint4*>(x + i * 8) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const long long i = i0 + u * step;
+            if (i >= total_vecs) break;
+            float f[8];
+            unpack8(raw[u], f);
+            if (bias != nullptr) {
+                const int c0 = static_cast<int>(i % vecs) * 8;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[k] += bias[c0 + k];
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k], TACT >= 0 ? TACT : act);
+            *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
+        }
     }
 }
-// dx = dy * act'(x + bias)
+// dx = dy * act'(x + bias); optionally dbias[c] += sum over rows of dx[r, c] in the same pass (the bias gradient of the Linear
+// layer that produced x: saves re-reading dx).  Thread = one vector of 8 channels, rows strided over the block, two rows in
+// flight; shared-memory fold over the row dimension, one fp32 atomic per channel per block.
+template <int TACT>
 __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                                       const float* __restrict__ bias, __nv_bfloat16* __restrict__ dx,
-                                                      long long total_vecs, int C, int act) {
+                                                      float* __restrict__ dbias, long long P, int C, int tx_count,
+                                                      int ty_count, int rows_per_block, int act) {
+    extern __shared__ float ab_red[];     // [ty_count][tx_count][8] (only with dbias)
     const int vecs = C >> 3;
-    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
-        float g[8], f[8];
-        unpack8(*reinterpret_cast<const uint4*>(dy + i * 8), g);
-        unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
-        const int c0 = static_cast<int>(i % vecs) * 8;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, bs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const bool active = ty < ty_count && cv < vecs;
+    if (active) {
+        if (bias != nullptr) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] *= act_grad(f[k] + (bias != nullptr ? bias[c0 + k] : 0.f), act);
-        *reinterpret_cast<uint4*>(dx + i * 8) = pack8(g);
+            for (int k = 0; k < 8; ++k) bs[k] = bias[cv * 8 + k];
+        }
+        const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
+        long long r1 = r0 + rows_per_block;
+        if (r1 > P) r1 = P;
+        for (long long r = r0 + ty; r < r1; r += 2LL * ty_count) {
+            uint4 vg[2], vx[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                const bool ok = rr < r1;
+                vg[u] = ok ? *reinterpret_cast<const uint4*>(dy + rr * C + cv * 8) : make_uint4(0, 0, 0, 0);
+                vx[u] = ok ? *reinterpret_cast<const uint4*>(x + rr * C + cv * 8) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const long long rr = r + static_cast<long long>(u) * ty_count;
+                if (rr >= r1) break;
+                float g[8], f[8];
+                unpack8(vg[u], g);
+                unpack8(vx[u], f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] *= act_grad(f[k] + bs[k], TACT >= 0 ? TACT : act);
+                const uint4 o = pack8(g);
+                *reinterpret_cast<uint4*>(dx + rr * C + cv * 8) = o;
+                if (dbias != nullptr) {        // sum what the next kernels will actually read (the bf16-rounded values)
+                    float q[8];
+                    unpack8(o, q);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] += q[k];
+                }
+            }
+        }
+    }
+    if (dbias == nullptr) return;
+    if (ty < ty_count) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) ab_red[(ty * tx_count + tx) * 8 + k] = acc[k];
+    }
+    __syncthreads();
+    if (active && ty == 0) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] += ab_red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(dbias + cv * 8 + k, s[k]);
     }
 }
 
@@ -435,37 +504,66 @@ __global__ void __launch_bounds__(256) dropout_kernel(const __nv_bfloat16* __res
 }
 
 // ------------------------------------------------------------------------------------ LayerNorm (row = one warp)
+// A lane owns columns lane*8 + 256*i (i < V) of every row its warp handles: gamma / beta sit in registers for the whole
+// kernel and a row is read exactly once (it stays in registers between the statistics and the normalisation).  Warps walk
+// the rows grid-stride, two rows per iteration so that the loads of the second row overlap the reduction of the first.
+constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
+template <int V>
 __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                                                             float* __restrict__ mean_out, float* __restrict__ rstd_out,
                                                             long long M, int D, float eps) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp;
-    if (row >= M) return;
-    const __nv_bfloat16* xr = x + row * D;
-    float s = 0.f, q = 0.f;
-    for (int j = lane * 8; j < D; j += 256) {
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(xr + j), f);
+    float gm[V][8], bt[V][8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) { s += f[k]; q += f[k] * f[k]; }
+    for (int i = 0; i < V; ++i) {
+        const int j = lane * 8 + i * 256;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; bt[i][k] = (j + k < D) ? beta[j + k] : 0.f; }
     }
-    s = warp_sum(s); q = warp_sum(q);
-    const float mean = s / D;
-    const float rstd = rsqrtf(fmaxf(q / D - mean * mean, 0.f) + eps);
-    if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
-    for (int j = lane * 8; j < D; j += 256) {
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(xr + j), f);
+    const float inv_d = 1.f / D;
+    const long long nwarps = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
+    for (long long row = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp) * 2; row < M; row += nwarps * 2) {
+        uint4 raw[2][V];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = (f[k] - mean) * rstd * gamma[j + k] + beta[j + k];
-        *reinterpret_cast<uint4*>(y + row * D + j) = pack8(f);
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const int j = lane * 8 + i * 256;
+                raw[r][i] = (row + r < M && j < D) ? *reinterpret_cast<const uint4*>(x + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            if (row + r >= M) break;
+            float f[V][8];
+            float s = 0.f, q = 0.f;
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                unpack8(raw[r][i], f[i]);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { s += f[i][k]; q += f[i][k] * f[i][k]; }
+            }
+            s = warp_sum(s); q = warp_sum(q);
+            const float mean = s * inv_d;
+            const float rstd = rsqrtf(fmaxf(q * inv_d - mean * mean, 0.f) + eps);
+            if (lane == 0) { mean_out[row + r] = mean; rstd_out[row + r] = rstd; }
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const int j = lane * 8 + i * 256;
+                if (j < D) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) f[i][k] = (f[i][k] - mean) * rstd * gm[i][k] + bt[i][k];
+                    *reinterpret_cast<uint4*>(y + (row + r) * D + j) = pack8(f[i]);
+                }
+            }
+        }
     }
 }
 // dx and (atomically accumulated) dgamma/dbeta.  A lane owns the same columns (lane*8 + 256*i) for every row its warp
 // handles, so the parameter-gradient partials live in registers; they are folded across the block's warps through shared
-// memory once at the end (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).
-constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
+// memory once at the end (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).  Two rows per iteration: the
+// loads of the second row are in flight while the first one reduces.
+template <int V>
 __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                                             const float* __restrict__ gamma, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
@@ -477,51 +575,67 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
     for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) sm[j] = 0.f;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    float pg[LN_MAX_VECS][8], pb[LN_MAX_VECS][8], gm[LN_MAX_VECS][8];
+    float pg[V][8], pb[V][8], gm[V][8];
 #pragma unroll
-    for (int i = 0; i < LN_MAX_VECS; ++i) {
+    for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
 #pragma unroll
         for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; }
     }
+    const float inv_d = 1.f / D;
     const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
     long long r1 = r0 + rows_per_block;
     if (r1 > M) r1 = M;
-    for (long long row = r0 + warp; row < r1; row += nw) {
-        const float mu = mean[row], rs = rstd[row];
-        float g[LN_MAX_VECS][8], xh[LN_MAX_VECS][8];
-        float a = 0.f, b = 0.f;
+    for (long long row = r0 + warp * 2; row < r1; row += nw * 2) {
+        uint4 rg[2][V], rx[2][V];
+        float mu[2], rs[2];
 #pragma unroll
-        for (int i = 0; i < LN_MAX_VECS; ++i) {
-            const int j = lane * 8 + i * 256;
-            if (j < D) {
+        for (int r = 0; r < 2; ++r) {
+            const bool live = row + r < r1;
+            mu[r] = live ? mean[row + r] : 0.f;
+            rs[r] = live ? rstd[row + r] : 0.f;
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const int j = lane * 8 + i * 256;
+                const bool ok = live && j < D;
+                rg[r][i] = ok ? *reinterpret_cast<const uint4*>(dy + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
+                rx[r][i] = ok ? *reinterpret_cast<const uint4*>(x + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            if (row + r >= r1) break;
+            float g[V][8], xh[V][8];
+            float a = 0.f, b = 0.f;
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
                 float f[8];
-                unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g[i]);
-                unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+                unpack8(rg[r][i], g[i]);
+                unpack8(rx[r][i], f);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    xh[i][k] = (f[k] - mu) * rs;
+                    xh[i][k] = (f[k] - mu[r]) * rs[r];
                     const float gg = g[i][k] * gm[i][k];
                     a += gg; b += gg * xh[i][k];
                     pg[i][k] += g[i][k] * xh[i][k];
                     pb[i][k] += g[i][k];
                 }
             }
-        }
-        a = warp_sum(a) / D; b = warp_sum(b) / D;
+            a = warp_sum(a) * inv_d; b = warp_sum(b) * inv_d;
 #pragma unroll
-        for (int i = 0; i < LN_MAX_VECS; ++i) {
-            const int j = lane * 8 + i * 256;
-            if (j < D) {
-                float o[8];
+            for (int i = 0; i < V; ++i) {
+                const int j = lane * 8 + i * 256;
+                if (j < D) {
+                    float o[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) o[k] = rs * (g[i][k] * gm[i][k] - a - xh[i][k] * b);
-                *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
+                    for (int k = 0; k < 8; ++k) o[k] = rs[r] * (g[i][k] * gm[i][k] - a - xh[i][k] * b);
+                    *reinterpret_cast<uint4*>(dx + (row + r) * D + j) = pack8(o);
+                }
             }
         }
     }
 #pragma unroll
-    for (int i = 0; i < LN_MAX_VECS; ++i) {
+    for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
         if (j < D) {
 #pragma unroll
@@ -778,17 +892,48 @@ extern "C" int picd_cross_entropy(const float* logits, const long long* labels, 
 extern "C" int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, int C, int act, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "act: C=%d must be a multiple of 8", C);
     const long long total = rows * (C / 8);
-    act_fwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(x), bias, static_cast<bf16*>(out), total, C, act);
+#define PICD_ACT_FWD(A) act_fwd_kernel<A><<<grid_for(total / 2 + 1), 256, 0, st>>>(static_cast<const bf16*>(x), bias, static_cast<bf16*>(out), total, C, act)
+    switch (act) {
+        case ACT_RELU: PICD_ACT_FWD(ACT_RELU); break;
+        case ACT_GELU: PICD_ACT_FWD(ACT_GELU); break;
+        case ACT_SWISH: PICD_ACT_FWD(ACT_SWISH); break;
+        case ACT_SIGMOID: PICD_ACT_FWD(ACT_SIGMOID); break;
+        default: PICD_ACT_FWD(-1); break;
+    }
+#undef PICD_ACT_FWD
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// dx = dy * act'(x + bias) and, when dbias != nullptr, dbias[c] += sum_r dx[r, c] in the same pass.
+extern "C" int picd_act_bwd_bias(const void* dy, const void* x, const float* bias, void* dx, float* dbias, long long rows,
+                                 int C, int act, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "act_bwd: C=%d must be a multiple of 8", C);
+    const int vecs = C / 8;
+    const int tx = vecs < 32 ? vecs : 32, ty = 256 / tx;     // a warp covers 512 contiguous bytes of a row
+    const int gx = (vecs + tx - 1) / tx;
+    long long gy = (8LL * num_sms()) / gx;
+    if (gy < 1) gy = 1;
+    long long rpb = (rows + gy - 1) / gy;
+    if (rpb < 2LL * ty) rpb = 2LL * ty;
+    gy = (rows + rpb - 1) / rpb;
+    const size_t smem = dbias != nullptr ? static_cast<size_t>(tx) * ty * 8 * sizeof(float) : 0;
+#define PICD_ACT_BWD(A)                                                                                                     \
+    act_bwd_kernel<A><<<dim3(gx, static_cast<unsigned>(gy)), 256, smem, st>>>(static_cast<const bf16*>(dy),                  \
+        static_cast<const bf16*>(x), bias, static_cast<bf16*>(dx), dbias, rows, C, tx, ty, static_cast<int>(rpb), act)
+    switch (act) {
+        case ACT_RELU: PICD_ACT_BWD(ACT_RELU); break;
+        case ACT_GELU: PICD_ACT_BWD(ACT_GELU); break;
+        case ACT_SWISH: PICD_ACT_BWD(ACT_SWISH); break;
+        case ACT_SIGMOID: PICD_ACT_BWD(ACT_SIGMOID); break;
+        default: PICD_ACT_BWD(-1); break;
+    }
+#undef PICD_ACT_BWD
     PICD_LAUNCH_CHECK();
     return 0;
 }
 extern "C" int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, long long rows, int C, int act,
                             cudaStream_t st) {
-    const long long total = rows * (C / 8);
-    act_bwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(dy), static_cast<const bf16*>(x), bias,
-                                                    static_cast<bf16*>(dx), total, C, act);
-    PICD_LAUNCH_CHECK();
-    return 0;
+    return picd_act_bwd_bias(dy, x, bias, dx, nullptr, rows, C, act, st);
 }
 extern "C" int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t st) {
     if (C % 8 == 0) {
@@ -832,20 +977,31 @@ extern "C" int picd_dropout_dyn(const void* x, void* out, long long n, float p, 
 extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                                   long long M, int D, float eps, cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
-    layernorm_fwd_kernel<<<static_cast<unsigned>((M + 7) / 8), 256, 0, st>>>(static_cast<const bf16*>(x), gamma, beta,
-                                                                            static_cast<bf16*>(y), mean, rstd, M, D, eps);
+    const int V = (D + 255) / 256;
+    long long blocks = std::min<long long>((M + 15) / 16, 8LL * num_sms());
+    if (blocks < 1) blocks = 1;
+#define PICD_LN_FWD(VV)                                                                                              \
+    layernorm_fwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 0, st>>>(static_cast<const bf16*>(x), gamma, beta, \
+                                                                           static_cast<bf16*>(y), mean, rstd, M, D, eps)
+    if (V == 1) PICD_LN_FWD(1); else if (V == 2) PICD_LN_FWD(2); else if (V == 3) PICD_LN_FWD(3); else PICD_LN_FWD(4);
+#undef PICD_LN_FWD
     PICD_LAUNCH_CHECK();
     return 0;
 }
 extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
                                   void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
-    long long blocks = 2LL * num_sms();
+    PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
+    long long blocks = 4LL * num_sms();
     long long rpb = (M + blocks - 1) / blocks;
-    if (rpb < 8) rpb = 8;
+    if (rpb < 16) rpb = 16;
     blocks = (M + rpb - 1) / rpb;
-    layernorm_bwd_kernel<<<static_cast<unsigned>(blocks), 256, 2 * D * sizeof(float), st>>>(
-        static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta,
-        M, D, static_cast<int>(rpb));
+    const int V = (D + 255) / 256;
+#define PICD_LN_BWD(VV)                                                                                                   \
+    layernorm_bwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 2 * D * sizeof(float), st>>>(                           \
+        static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, \
+        M, D, static_cast<int>(rpb))
+    if (V == 1) PICD_LN_BWD(1); else if (V == 2) PICD_LN_BWD(2); else if (V == 3) PICD_LN_BWD(3); else PICD_LN_BWD(4);
+#undef PICD_LN_BWD
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -99,6 +99,9 @@ int picd_cross_entropy(const float* logits, const long long* labels, const float
 int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, int C, int act, cudaStream_t stream);
 int picd_act_bwd(const void* dy, const void* x, const float* bias, void* dx, long long rows, int C, int act,
                  cudaStream_t stream);
+/* picd_act_bwd that also accumulates the bias gradient dbias[c] += sum_r dx[r, c] in the same pass (dbias may be NULL). */
+int picd_act_bwd_bias(const void* dy, const void* x, const float* bias, void* dx, float* dbias, long long rows, int C,
+                      int act, cudaStream_t stream);
 int picd_colsum(const void* x, float* out, long long P, int C, cudaStream_t stream);
 /* NHWC channel concat (split = 0) / its backward split (split = 1) of n <= 8 bf16 tensors [P, C_i] <-> [P, sum C_i];
  * `parts` and `channels` are host arrays. */

@@ -53,6 +53,7 @@ _SIG = {
     "picd_cross_entropy": "pppppiip",
     "picd_act_fwd": "ppplii" + "p",
     "picd_act_bwd": "ppppliip",
+    "picd_act_bwd_bias": "pppppliip",
     "picd_colsum": "pplip",
     "picd_dropout": "pplfup",
     "picd_dropout_dyn": "pplfupp",
@@ -585,11 +586,17 @@ class _LinearTC(torch.autograd.Function):
         if dy2.dtype != torch.bfloat16:
             dy2 = dy2.to(torch.bfloat16)
         dy2 = dy2.contiguous()
+        bias_done = False
         if ctx.act not in (None, "none"):
             dpre = torch.empty_like(dy2)
-            # relu'(pre) == relu'(relu(pre)), so the saved (fused) output serves as the mask source
-            call("picd_act_bwd", dy2, pre, None, dpre, M, N, ACT[ctx.act])
+            # relu'(pre) == relu'(relu(pre)), so the saved (fused) output serves as the mask source.  The bias gradient is
+            # the column sum of dpre: accumulated by the same kernel instead of a second pass over dpre.
+            btgt = None
+            if b is not None and ctx.needs_input_grad[2] and N % 8 == 0:
+                btgt, b_routed = _grad_target(b)
+            call("picd_act_bwd_bias", dy2, pre, None, dpre, btgt, M, N, ACT[ctx.act])
             dy2 = dpre
+            bias_done = btgt is not None
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
@@ -603,7 +610,12 @@ class _LinearTC(torch.autograd.Function):
                 _mark_ready(w)
             else:
                 dw = tgt
-        if b is not None and ctx.needs_input_grad[2]:
+        if bias_done:
+            if b_routed:
+                _mark_ready(b)
+            else:
+                db = btgt
+        elif b is not None and ctx.needs_input_grad[2]:
             tgt, routed = _grad_target(b)
             call("picd_colsum", dy2, tgt, M, N)
             if routed:
