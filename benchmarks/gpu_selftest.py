@@ -140,7 +140,8 @@ def group_basic():
 
     # depthwise convolution (EfficientNet), symmetric and TF-"same" asymmetric padding
     for (N, C, H, K, stride, pad) in [(2, 32, 17, 3, 1, (1, 1, 1, 1)), (2, 96, 16, 3, 2, (0, 0, 1, 1)), (2, 144, 15, 5, 2, (2, 2, 2, 2)),
-                                      (3, 40, 9, 5, 1, (2, 2, 2, 2))]:
+                                      (3, 40, 9, 5, 1, (2, 2, 2, 2)), (2, 288, 19, 5, 2, (1, 1, 2, 2)), (2, 8, 33, 7, 1, (3, 3, 3, 3)),
+                                      (4, 528, 10, 3, 1, (1, 1, 1, 1))]:
         x = torch.randn(N, C, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         w = (torch.randn(C, 1, K, K, device=dev) / K).requires_grad_()
         xn = x.clone().requires_grad_()

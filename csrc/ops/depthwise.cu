@@ -150,6 +150,188 @@ __global__ void __launch_bounds__(256) dw_wgrad_kernel(const __nv_bfloat16* __re
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Row-structured specialisations (K = 3 / 5, stride 1 / 2: every depthwise layer of EfficientNet).  The generic kernels
+// above spend most of their instructions on 64-bit div/mod and run-time tap arithmetic (the wgrad ran at ~8% of the
+// memory roofline).  Here blockIdx.y walks (image, row) pairs, a thread owns 8 channels and strides over the pixels of a
+// row, the tap loops are compile-time, and the block's weights sit in shared memory.
+template <int K, int S>
+__global__ void __launch_bounds__(256) dw_fprop_rows_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wt,
+                                                            __nv_bfloat16* __restrict__ y, int NR, int H, int W, int C, int OH,
+                                                            int OW, int pad_t, int pad_l, int tx_count, int ty_count,
+                                                            int rows_per_block) {
+    extern __shared__ float dw_sw[];           // [K*K][tx_count*8]
+    const int vecs = C >> 3, cw = tx_count * 8;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    for (int i = threadIdx.x; i < K * K * cw; i += blockDim.x) {
+        const int tap = i / cw, c = blockIdx.x * cw + (i - tap * cw);
+        dw_sw[i] = c < C ? wt[static_cast<size_t>(tap) * C + c] : 0.f;
+    }
+    __syncthreads();
+    if (ty >= ty_count || cv >= vecs) return;
+    const float* swc = dw_sw + tx * 8;
+    int row1 = (blockIdx.y + 1) * rows_per_block;
+    if (row1 > NR) row1 = NR;
+    for (int row = blockIdx.y * rows_per_block; row < row1; ++row) {
+        const int n = row / OH, oh = row - n * OH;
+        const __nv_bfloat16* xn = x + static_cast<size_t>(n) * H * W * C + cv * 8;
+        __nv_bfloat16* yr = y + static_cast<size_t>(row) * OW * C + cv * 8;
+        for (int ow = ty; ow < OW; ow += ty_count) {
+            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                const int ih = oh * S - pad_t + r;
+                if (ih < 0 || ih >= H) continue;
+#pragma unroll
+                for (int q = 0; q < K; ++q) {
+                    const int iw = ow * S - pad_l + q;
+                    if (iw < 0 || iw >= W) continue;
+                    float f[8];
+                    dw_unpack8(*reinterpret_cast<const uint4*>(xn + (static_cast<size_t>(ih) * W + iw) * C), f);
+                    const float4 w0 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw);
+                    const float4 w1 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw + 4);
+                    acc[0] = fmaf(f[0], w0.x, acc[0]); acc[1] = fmaf(f[1], w0.y, acc[1]);
+                    acc[2] = fmaf(f[2], w0.z, acc[2]); acc[3] = fmaf(f[3], w0.w, acc[3]);
+                    acc[4] = fmaf(f[4], w1.x, acc[4]); acc[5] = fmaf(f[5], w1.y, acc[5]);
+                    acc[6] = fmaf(f[6], w1.z, acc[6]); acc[7] = fmaf(f[7], w1.w, acc[7]);
+                }
+            }
+            *reinterpret_cast<uint4*>(yr + static_cast<size_t>(ow) * C) = dw_pack8(acc);
+        }
+    }
+}
+
+// dx[n, ih, iw] = sum over taps (r, q) with (ih + pad_t - r) and (iw + pad_l - q) divisible by S of dy[n, ./S, ./S] * w[r, q]
+template <int K, int S>
+__global__ void __launch_bounds__(256) dw_dgrad_rows_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ wt,
+                                                            __nv_bfloat16* __restrict__ dx, int NR, int H, int W, int C, int OH,
+                                                            int OW, int pad_t, int pad_l, int tx_count, int ty_count,
+                                                            int rows_per_block) {
+    extern __shared__ float dw_sw[];
+    const int vecs = C >> 3, cw = tx_count * 8;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    for (int i = threadIdx.x; i < K * K * cw; i += blockDim.x) {
+        const int tap = i / cw, c = blockIdx.x * cw + (i - tap * cw);
+        dw_sw[i] = c < C ? wt[static_cast<size_t>(tap) * C + c] : 0.f;
+    }
+    __syncthreads();
+    if (ty >= ty_count || cv >= vecs) return;
+    const float* swc = dw_sw + tx * 8;
+    int row1 = (blockIdx.y + 1) * rows_per_block;
+    if (row1 > NR) row1 = NR;
+    for (int row = blockIdx.y * rows_per_block; row < row1; ++row) {     // row = n * H + ih
+        const int n = row / H, ih = row - n * H;
+        const __nv_bfloat16* gn = dy + static_cast<size_t>(n) * OH * OW * C + cv * 8;
+        __nv_bfloat16* dr = dx + static_cast<size_t>(row) * W * C + cv * 8;
+        for (int iw = ty; iw < W; iw += ty_count) {
+            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                const int th = ih + pad_t - r;
+                if (th < 0 || (S > 1 && (th % S) != 0)) continue;
+                const int oh = th / S;
+                if (oh >= OH) continue;
+#pragma unroll
+                for (int q = 0; q < K; ++q) {
+                    const int tw = iw + pad_l - q;
+                    if (tw < 0 || (S > 1 && (tw % S) != 0)) continue;
+                    const int ow = tw / S;
+                    if (ow >= OW) continue;
+                    float g[8];
+                    dw_unpack8(*reinterpret_cast<const uint4*>(gn + (static_cast<size_t>(oh) * OW + ow) * C), g);
+                    const float4 w0 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw);
+                    const float4 w1 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw + 4);
+                    acc[0] = fmaf(g[0], w0.x, acc[0]); acc[1] = fmaf(g[1], w0.y, acc[1]);
+                    acc[2] = fmaf(g[2], w0.z, acc[2]); acc[3] = fmaf(g[3], w0.w, acc[3]);
+                    acc[4] = fmaf(g[4], w1.x, acc[4]); acc[5] = fmaf(g[5], w1.y, acc[5]);
+                    acc[6] = fmaf(g[6], w1.z, acc[6]); acc[7] = fmaf(g[7], w1.w, acc[7]);
+                }
+            }
+            *reinterpret_cast<uint4*>(dr + static_cast<size_t>(iw) * C) = dw_pack8(acc);
+        }
+    }
+}
+
+// dwt[(r, q)][c] += sum over output pixels of dy[n, oh, ow, c] * x[n, oh*S - pad_t + r, ow*S - pad_l + q, c].
+// blockIdx.z = filter row r: a thread keeps the K taps of that row for its 8 channels in registers over a strip of output
+// rows, folds them across the block through shared memory and adds them with one fp32 atomic per (tap, channel) per block.
+template <int K, int S>
+__global__ void __launch_bounds__(256) dw_wgrad_rows_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                                            float* __restrict__ dwt, int NR, int H, int W, int C, int OH,
+                                                            int OW, int pad_t, int pad_l, int tx_count, int ty_count,
+                                                            int rows_per_block) {
+    extern __shared__ float dw_red[];          // [ty_count][tx_count][8]
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    const int r = blockIdx.z;
+    float acc[K][8];
+#pragma unroll
+    for (int q = 0; q < K; ++q)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[q][k] = 0.f;
+    const bool active = ty < ty_count && cv < vecs;
+    if (active) {
+        int row1 = (blockIdx.y + 1) * rows_per_block;
+        if (row1 > NR) row1 = NR;
+        for (int row = blockIdx.y * rows_per_block; row < row1; ++row) {     // row = n * OH + oh
+            const int n = row / OH, oh = row - n * OH;
+            const int ih = oh * S - pad_t + r;
+            if (ih < 0 || ih >= H) continue;
+            const __nv_bfloat16* xr = x + (static_cast<size_t>(n) * H + ih) * W * C + cv * 8;
+            const __nv_bfloat16* gr = dy + static_cast<size_t>(row) * OW * C + cv * 8;
+            for (int ow = ty; ow < OW; ow += ty_count) {
+                float g[8];
+                dw_unpack8(*reinterpret_cast<const uint4*>(gr + static_cast<size_t>(ow) * C), g);
+#pragma unroll
+                for (int q = 0; q < K; ++q) {
+                    const int iw = ow * S - pad_l + q;
+                    if (iw < 0 || iw >= W) continue;
+                    float f[8];
+                    dw_unpack8(*reinterpret_cast<const uint4*>(xr + static_cast<size_t>(iw) * C), f);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[q][k] = fmaf(g[k], f[k], acc[q][k]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+        __syncthreads();
+        if (ty < ty_count) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dw_red[(ty * tx_count + tx) * 8 + k] = acc[q][k];
+        }
+        __syncthreads();
+        if (active && ty == 0) {
+            float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += dw_red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(dwt + static_cast<size_t>(r * K + q) * C + cv * 8 + k, s[k]);
+        }
+    }
+}
+
+struct DwShape { int tx, ty, gx, gy, rpb; };
+// thread block = tx channel vectors x ty pixel lanes; blockIdx.y strips of rows sized for ~`waves` blocks per SM
+static DwShape dw_shape(int C, int rows, int waves, int gz) {
+    DwShape d;
+    const int vecs = C / 8;
+    d.tx = vecs < 32 ? vecs : 32;
+    d.ty = 256 / d.tx;
+    d.gx = (vecs + d.tx - 1) / d.tx;
+    long long gy = (static_cast<long long>(waves) * num_sms()) / (static_cast<long long>(d.gx) * gz);
+    if (gy < 1) gy = 1;
+    if (gy > rows) gy = rows;
+    d.rpb = static_cast<int>((rows + gy - 1) / gy);
+    d.gy = (rows + d.rpb - 1) / d.rpb;
+    return d;
+}
+
 static int dw_grid(long long work) {
     long long b = (work + 255) / 256;
     const long long cap = 16LL * num_sms();
@@ -166,6 +348,17 @@ using namespace picd;
 extern "C" int picd_depthwise_fprop(const void* x, const float* wt, void* y, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+#define PICD_DW_FPROP(KK, SS)                                                                                          \
+    if (K == KK && stride == SS) {                                                                                       \
+        const DwShape d = dw_shape(C, N * OH, 8, 1);                                                                      \
+        dw_fprop_rows_kernel<KK, SS><<<dim3(d.gx, d.gy), 256, KK * KK * d.tx * 8 * sizeof(float), st>>>(                   \
+            static_cast<const __nv_bfloat16*>(x), wt, static_cast<__nv_bfloat16*>(y), N * OH, H, W, C, OH, OW, pad_t, pad_l, \
+            d.tx, d.ty, d.rpb);                                                                                           \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_FPROP(3, 1) PICD_DW_FPROP(3, 2) PICD_DW_FPROP(5, 1) PICD_DW_FPROP(5, 2)
+#undef PICD_DW_FPROP
     const long long total = 1LL * N * OH * OW * (C / 8);
     dw_fprop_kernel<<<dw_grid(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), wt, static_cast<__nv_bfloat16*>(y), N, H, W,
                                                    C, OH, OW, K, stride, pad_t, pad_l);
@@ -175,6 +368,17 @@ extern "C" int picd_depthwise_fprop(const void* x, const float* wt, void* y, int
 extern "C" int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+#define PICD_DW_DGRAD(KK, SS)                                                                                          \
+    if (K == KK && stride == SS) {                                                                                       \
+        const DwShape d = dw_shape(C, N * H, 8, 1);                                                                       \
+        dw_dgrad_rows_kernel<KK, SS><<<dim3(d.gx, d.gy), 256, KK * KK * d.tx * 8 * sizeof(float), st>>>(                   \
+            static_cast<const __nv_bfloat16*>(dy), wt, static_cast<__nv_bfloat16*>(dx), N * H, H, W, C, OH, OW, pad_t, pad_l, \
+            d.tx, d.ty, d.rpb);                                                                                           \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_DGRAD(3, 1) PICD_DW_DGRAD(3, 2) PICD_DW_DGRAD(5, 1) PICD_DW_DGRAD(5, 2)
+#undef PICD_DW_DGRAD
     const long long total = 1LL * N * H * W * (C / 8);
     dw_dgrad_kernel<<<dw_grid(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), wt, static_cast<__nv_bfloat16*>(dx), N, H, W,
                                                    C, OH, OW, K, stride, pad_t, pad_l);
@@ -185,6 +389,17 @@ extern "C" int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, i
 extern "C" int picd_depthwise_wgrad(const void* x, const void* dy, float* dwt, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+#define PICD_DW_WGRAD(KK, SS)                                                                                          \
+    if (K == KK && stride == SS) {                                                                                       \
+        const DwShape d = dw_shape(C, N * OH, 4, KK);                                                                     \
+        dw_wgrad_rows_kernel<KK, SS><<<dim3(d.gx, d.gy, KK), 256, d.tx * d.ty * 8 * sizeof(float), st>>>(                  \
+            static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dwt, N * OH, H, W, C, OH, OW, pad_t,  \
+            pad_l, d.tx, d.ty, d.rpb);                                                                                    \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_WGRAD(3, 1) PICD_DW_WGRAD(3, 2) PICD_DW_WGRAD(5, 1) PICD_DW_WGRAD(5, 2)
+#undef PICD_DW_WGRAD
     const int vecs = C / 8;
     const int tx = vecs < 32 ? vecs : 32, ty = 256 / tx;
     const int gx = (vecs + tx - 1) / tx;
