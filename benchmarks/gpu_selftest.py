@@ -109,7 +109,9 @@ def group_basic():
                                    (2, 2048, 7, 7, True, "relu"), (4, 40, 6, 6, False, "swish"),
                                    # >= 4 MB: these take the TMA-streamed kernels (bn_stream.cu)
                                    (32, 64, 56, 56, False, "relu"), (16, 256, 28, 28, True, "relu"),
-                                   (64, 128, 16, 17, False, "none"), (24, 512, 14, 14, True, "relu")]:
+                                   (64, 128, 16, 17, False, "none"), (24, 512, 14, 14, True, "relu"),
+                                   # channel counts that are not powers of two (inception / efficientnet) on the streamed kernels
+                                   (32, 144, 38, 38, False, "swish"), (16, 768, 17, 17, True, "relu"), (48, 192, 35, 35, False, "relu")]:
         x = torch.randn(N, C, H, W, device=dev).mul_(1.5).add_(0.3).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         r = torch.randn(N, C, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) if res else None
         gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_()

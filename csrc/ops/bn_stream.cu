@@ -36,6 +36,7 @@ struct StreamArgs {
     int act, use_z, eval_mode;
     long long P;
     int C, rows_per_chunk, stages, chunk_bytes;
+    int n_active;                    // consumers that own a channel vector: the largest multiple of C/8 that is <= 512
     long long num_chunks;
 };
 
@@ -181,9 +182,12 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         const uint32_t base = ring_u32 + static_cast<uint32_t>(s) * n_in * a.chunk_bytes;
         const uint32_t cb = a.chunk_bytes;
 #pragma unroll
-        for (int k = 0; k < SB_MAX_CHUNK_BYTES / 16 / SB_CONSUMERS; ++k) {
-            const int idx = t + k * SB_CONSUMERS;
-            if (idx < nvec) {
+        // vector idx of the chunk belongs to channel vector idx % vecs; stepping by n_active (a multiple of vecs) keeps every
+        // thread on its own 8 channels for any C, not only powers of two
+        const int n_active = a.n_active;
+#pragma unroll 2
+        for (int idx = t; idx < nvec; idx += n_active) {
+            if (t < n_active) {
                 if (MODE == SB_APPLY) {
                     float f[8], r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                     unpack8(lds128(base + idx * 16), f);
@@ -247,7 +251,7 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
             float r0[8], r1[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) { r0[j] = 0.f; r1[j] = 0.f; }
-            for (int o = t; o < SB_CONSUMERS; o += vecs)
+            for (int o = t; o < a.n_active; o += vecs)
 #pragma unroll
                 for (int j = 0; j < 8; ++j) { r0[j] += red[o * 16 + j]; r1[j] += red[o * 16 + 8 + j]; }
             float* rep = a.sums_out + static_cast<size_t>(blockIdx.x % STAT_REPLICAS) * 2 * C;
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
 }
 
 static bool stream_eligible(long long P, int C) {
-    if (C < 64 || C > 2048 || (C & (C - 1)) != 0) return false;   // C/8 must divide the consumer count
+    if (C < 64 || C > 2048 || (C % 8) != 0) return false;          // a thread owns one 16-byte vector; >= 2 rows per chunk
     return P * C * 2 >= (4LL << 20);                                // small tensors: launch-bound either way
 }
 
@@ -270,6 +274,7 @@ static int launch_stream(StreamArgs& a, cudaStream_t stream) {
     static const int one_in_chunk = [] { const char* e = getenv("PICD_BN_CHUNK"); return e == nullptr ? SB_MAX_CHUNK_BYTES : atoi(e); }();
     a.chunk_bytes = a.n_in == 1 ? one_in_chunk : 16384;
     a.rows_per_chunk = a.chunk_bytes / (a.C * 2);
+    a.n_active = (SB_CONSUMERS / (a.C / 8)) * (a.C / 8);
     a.num_chunks = (a.P + a.rows_per_chunk - 1) / a.rows_per_chunk;
     const int stage_bytes = a.n_in * a.chunk_bytes;
     int stages = (200 * 1024) / stage_bytes;
