@@ -120,6 +120,15 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
 // shift = beta - mean*scale for the fused apply, saves mean/invstd for backward and updates the running
 // statistics with the unbiased variance (torch semantics, torch/nn/modules/_functions.py:106-115).
 __device__ __forceinline__ float fold_replicas(const float* base, int idx, int stride, int replicas) {
+    if (replicas == STAT_REPLICAS) {           // the usual case: all loads in flight at once instead of a dependent chain
+        float v[STAT_REPLICAS];
+#pragma unroll
+        for (int r = 0; r < STAT_REPLICAS; ++r) v[r] = base[static_cast<size_t>(r) * stride + idx];
+        float acc = 0.f;
+#pragma unroll
+        for (int r = 0; r < STAT_REPLICAS; ++r) acc += v[r];
+        return acc;
+    }
     float acc = 0.f;
     for (int r = 0; r < replicas; ++r) acc += base[static_cast<size_t>(r) * stride + idx];
     return acc;
@@ -491,9 +500,7 @@ extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, 
 __global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    float acc = buf[i];
-    for (int r = 1; r < replicas; ++r) acc += buf[static_cast<size_t>(r) * n + i];
-    buf[i] = acc;
+    buf[i] = fold_replicas(buf, i, n, replicas);
 }
 
 // NOTE: folds `sums` / `param_sums` in place (copy 0 receives the totals) before the streaming kernel runs.

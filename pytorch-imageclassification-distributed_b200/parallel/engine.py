@@ -368,6 +368,9 @@ class FusedDataParallel(nn.Module):
     def forward(self, *args, **kw):
         if self.broadcast_buffers and self.module.training and torch.is_grad_enabled() and not self.capturing:
             self._sync_buffers()        # (a captured step broadcasts eagerly before each replay instead)
+        if self.device.type == "cuda" and self.module.training and torch.is_grad_enabled():
+            from ..ops import native
+            native.stat_arena(self.device).begin_step()      # one memset instead of two fill kernels per BN layer
         return self.module(*args, **kw)
 
     def load_state_dict(self, state_dict, strict: bool = True, **kw):
