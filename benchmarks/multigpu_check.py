@@ -56,6 +56,10 @@ def check_fused_update(device, mode):
         lr = 0.05 if kind == "sgd" else 1e-3
         dp = FusedDataParallel(net, OptimizerSpec(kind=kind, lr=lr, momentum=0.9, weight_decay=0.01),
                                first_bucket_bytes=64 << 10, bucket_cap_bytes=1 << 20, comm=mode)
+        if mode == "nvls" and not dp._impl.comm.has_nvls:
+            emit({"test": f"fused_update[{mode},{kind}]", "skipped": "no NVSwitch multicast mapping on this host", "ok": True})
+            del dp
+            continue
         opt = (torch.optim.SGD(ref.parameters(), lr=lr, momentum=0.9, weight_decay=0.01) if kind == "sgd"
                else torch.optim.AdamW(ref.parameters(), lr=lr, weight_decay=0.01))
         for it in range(4):
@@ -198,15 +202,20 @@ def sweep(device):
     from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
     world = dist.get_world_size()
     sizes = [1 << k for k in range(8, 29, 2)]          # elements: 1 KB .. 1 GB of fp32
+    if os.environ.get("PICD_SWEEP_MIN"):
+        sizes = [n for n in sizes if n * 4 >= int(os.environ["PICD_SWEEP_MIN"])]
     for n in sizes:
         p = torch.nn.Parameter(torch.zeros(n, device=device))
         holder = torch.nn.Module()
         holder.w = p
-        for mode in ("one_shot", "two_shot"):
+        for mode in ("one_shot", "two_shot", "nvls", "nvls_ld"):
             if mode == "one_shot" and n * 4 > (64 << 20):
                 continue
             dp = FusedDataParallel(holder, OptimizerSpec("sgd", lr=0.01, momentum=0.9), first_bucket_bytes=1 << 40,
                                    bucket_cap_bytes=1 << 40, comm=mode, overlap=False)
+            if mode.startswith("nvls") and not dp._impl.comm.has_nvls:
+                del dp
+                continue
             b = dp.arena.buckets[0]
 
             def once():
@@ -266,7 +275,7 @@ def main():
     device = torch.device("cuda", torch.cuda.current_device())
     ok = True
     if not args.skip_checks:
-        for mode in ("one_shot", "two_shot", "auto"):
+        for mode in ("one_shot", "two_shot", "nvls", "auto"):
             ok &= check_fused_update(device, mode)
         ok &= check_sync_bn(device)
         ok &= check_training(device)

@@ -28,6 +28,11 @@ struct PeerTable {
     __nv_bfloat16* shadow[MAX_PEERS];
     float* xchg[MAX_PEERS];          // exchange slots for small collectives
     unsigned* flags[MAX_PEERS];
+    // NVSwitch multicast (NVLS) views of the same regions, or nullptr: a multimem.ld_reduce on mc_grad returns the sum over all
+    // ranks computed inside the switch, a multimem.st on mc_master / mc_shadow lands in every rank's copy
+    float* mc_grad;
+    float* mc_master;
+    __nv_bfloat16* mc_shadow;
 };
 
 struct OptArgs {
@@ -51,6 +56,22 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
     asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
 }
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, const uint2& v) {     // 8 raw bytes (four bf16 shadow weights)
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y))
+                 : "memory");
+}
+
 // Spin until every peer's flag word (in MY flag array) has reached `epoch`; bounded so a lost peer traps
 // instead of hanging the GPU forever.
 __device__ __forceinline__ void wait_flags(const unsigned* my_flags, int slot, int W, unsigned epoch) {
@@ -84,7 +105,10 @@ __device__ __forceinline__ float opt_update(float p, float g, float& s0, float& 
     return p - (o.lr / o.bc1) * (s0 / denom);
 }
 
-// mode: 0 = local (W == 1, no flags), 1 = one-shot, 2 = two-shot
+// mode: 0 = local (W == 1, no flags), 1 = one-shot, 2 = two-shot, 3 = two-shot through NVSwitch multicast (NVLS; 4 = NVLS
+// reduction with unicast pushes): the slice
+// owner pulls the reduced gradients with ONE multimem.ld_reduce per vector instead of W peer loads and broadcasts the updated
+// master / shadow with ONE multimem.st each instead of W peer stores
 __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable pt, int rank, int W, int mode,
                                                                      long long start, long long count,
                                                                      float* __restrict__ state0,
@@ -104,7 +128,7 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
         wait_flags(my_flags, slot_in, W, epoch);                          // ... and so are everybody else's
     }
     long long lo = start, hi = start + count;
-    if (mode == 2) {
+    if (mode >= 2) {
         const long long per = count / W;
         lo = start + per * rank;
         hi = lo + per;
@@ -125,6 +149,8 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
             const long long i = lo + (v << 2);
             if (mode == 0) {
                 g[u] = *reinterpret_cast<const float4*>(pt.grad[rank] + i);
+            } else if (mode >= 3) {
+                g[u] = multimem_ld_reduce_f4(pt.mc_grad + i);                 // the switch adds the W copies
             } else {
                 float4 part[MAX_PEERS];
 #pragma unroll
@@ -149,7 +175,10 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
             *reinterpret_cast<float4*>(state0 + i) = s0[u];
             if (opt.kind != 0) *reinterpret_cast<float4*>(state1 + i) = s1[u];
             const uint2 sh = make_uint2(pack_bf16x2(w[u].x, w[u].y), pack_bf16x2(w[u].z, w[u].w));
-            if (mode == 2) {
+            if (mode == 3) {
+                multimem_st_f4(pt.mc_master + i, w[u]);                       // one store, delivered to every rank
+                multimem_st_b64(pt.mc_shadow + i, sh);
+            } else if (mode == 2 || mode == 4) {       // mode 4: in-switch reduction, unicast pushes
 #pragma unroll
                 for (int p = 0; p < MAX_PEERS; ++p)
                     if (p < W) {
@@ -317,6 +346,14 @@ extern "C" int picd_comm_create(int rank, int world, void* const* grad, void* co
     *ctx_out = c;
     return 0;
 }
+// Registers the NVSwitch multicast views of the gradient / master / shadow regions (enables mode 3 of the bucket kernel).
+extern "C" int picd_comm_set_multicast(void* ctx, void* mc_grad, void* mc_master, void* mc_shadow) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    c->pt.mc_grad = static_cast<float*>(mc_grad);
+    c->pt.mc_master = static_cast<float*>(mc_master);
+    c->pt.mc_shadow = static_cast<__nv_bfloat16*>(mc_shadow);
+    return 0;
+}
 extern "C" int picd_comm_destroy(void* ctx) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
     if (c) {
@@ -340,7 +377,8 @@ static int fused_update_impl(void* ctx, int bucket, int mode, long long start, l
     o.kind = kind; o.lr = lr; o.momentum = momentum; o.beta1 = beta1; o.beta2 = beta2; o.eps = eps;
     o.weight_decay = weight_decay; o.bc1 = bc1; o.bc2 = bc2; o.nesterov = nesterov;
     o.grad_scale = 1.f / c->world;
-    const long long work_vecs = (mode == 2 ? count / c->world : count) / 4;
+    PICD_REQUIRE(mode < 3 || c->pt.mc_grad != nullptr, "fused_allreduce_update: NVLS mode without a multicast mapping");
+    const long long work_vecs = (mode >= 2 ? count / c->world : count) / 4;
     long long want = (work_vecs + 511) / 512;
     // Peer kernels spin on flags, so the grid must be able to become co-resident: at most 2 CTAs of 512 threads per SM.
     // Small buckets (the usual <= 25 MiB, overlapped with backward) use few CTAs to leave the SMs to the wgrads.

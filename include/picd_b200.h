@@ -154,6 +154,9 @@ int picd_ipc_open(const void* handle, void** out);
 int picd_ipc_close(void* p);
 int picd_comm_create(int rank, int world, void* const* grad, void* const* master, void* const* shadow,
                      void* const* xchg, void* const* flags, int num_buckets, void** ctx_out);
+/* NVSwitch multicast (NVLS) views of the three regions, as mapped by the host (e.g. torch symmetric memory); enables
+ * mode 3 of picd_fused_allreduce_update: multimem.ld_reduce / multimem.st instead of W peer loads / stores. */
+int picd_comm_set_multicast(void* ctx, void* mc_grad, void* mc_master, void* mc_shadow);
 int picd_comm_destroy(void* ctx);
 int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count, float* state0,
                                 float* state1, int kind, float lr, float momentum, float beta1, float beta2, float eps,

@@ -4,6 +4,8 @@
                    [gradient arena fp32 | master weights fp32 | bf16 shadow | exchange slots | flag words],
                    exported with CUDA IPC and mapped by every peer of the node (handles travel over the
                    existing torch.distributed group once, at construction).
+                   Where torch's symmetric-memory allocator is available the slab comes from it instead, which adds an
+                   NVSwitch multicast (NVLS) mapping of the same memory (``PICD_SYMM=0`` / ``PICD_NVLS=0`` opt out).
 ``NativeReducer``  launches ``picd_fused_allreduce_update`` per bucket on a side stream as soon as the bucket's
                    last gradient kernel has been queued (reference: DDP Reducer + NCCL + optimizer.step,
                    train.py:72-73).
@@ -13,6 +15,7 @@
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -26,6 +29,9 @@ N_SLOTS = 1024                      # small-collective slots (each double-buffer
                                     # launches use disjoint slots, so a ResNet-101 needs 104 + 192 + 2 x 104 of them
 MAX_PEERS = 8
 TWO_SHOT_MIN_BYTES = 256 << 10      # below this a bucket is latency-bound: one-shot
+NVLS_MIN_BYTES = 4 << 20            # from here on the in-switch reduction (multimem.ld_reduce) replaces the W peer loads, if mapped
+NVLS_ST_MAX_BYTES = 512 << 20       # above this the multimem.st broadcast is slower than unicast pushes (measured at W=8): mode 4
+NVLS_MIN_WORLD = 4                  # with 2 ranks a multicast access moves as many bytes as a peer access and is slower per SM
 
 _current: Optional["Comm"] = None
 
@@ -67,18 +73,52 @@ class SymmetricSlab:
         self.flag_words = (2 * num_buckets_hint + N_SLOTS) * MAX_PEERS
         self.nbytes = _align(self.off_flags + self.flag_words * 4)
         self.max_buckets = num_buckets_hint
-        base = ctypes.c_void_p()
-        with torch.cuda.device(device):
-            self.lib.picd_slab_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
-            check(self.lib.picd_slab_alloc(self.nbytes, ctypes.byref(base)), "picd_slab_alloc")
-        self.base = base.value
+        self.mc_base = 0          # NVSwitch multicast (NVLS) view of the slab, when the host can map one
+        self._symm = None
+        if world > 1 and os.environ.get("PICD_SYMM", "1") != "0":
+            self._try_symmetric_alloc()
+        if self._symm is None:
+            base = ctypes.c_void_p()
+            with torch.cuda.device(device):
+                self.lib.picd_slab_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
+                check(self.lib.picd_slab_alloc(self.nbytes, ctypes.byref(base)), "picd_slab_alloc")
+            self.base = base.value
         self.grad = _view(self.base + self.off_grad, total, "<f4", device, self)
         self.master = _view(self.base + self.off_master, total, "<f4", device, self)
         self.shadow = _view(self.base + self.off_shadow, total, "<i2", device, self).view(torch.bfloat16)
         self.state = [torch.zeros(total, dtype=torch.float32, device=device) for _ in range(n_state)]
-        self.peer_bases: List[int] = [self.base] * max(world, 1)
-        if world > 1:
-            self._exchange_handles()
+        if self._symm is None:
+            self.peer_bases: List[int] = [self.base] * max(world, 1)
+            if world > 1:
+                self._exchange_handles()
+
+    def _try_symmetric_alloc(self):
+        """Allocate the slab from torch's symmetric-memory allocator: besides the peer mappings (what the CUDA-IPC path
+        below provides) it returns an NVSwitch MULTICAST mapping of the same memory where the host supports NVLS, which
+        mode 3 of the bucket kernel uses (multimem.ld_reduce / multimem.st).  Collective; every rank must agree on the
+        outcome, so a failure anywhere sends all ranks to the cudaMalloc + IPC path."""
+        ok, keep = 1, None
+        try:
+            import torch.distributed._symmetric_memory as sm
+            t = sm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            t.zero_()
+            torch.cuda.synchronize(self.device)
+            h = sm.rendezvous(t, dist.group.WORLD)
+            bases = [int(p) for p in h.buffer_ptrs]
+            if len(bases) != self.world or bases[self.rank] != t.data_ptr():
+                ok = 0
+            keep = (t, h, bases)
+        except Exception:      # noqa: BLE001 -- older torch, no fabric support, container without fd passing, ...
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) != 1:
+            return
+        t, h, bases = keep
+        self._symm = (t, h)
+        self.base = t.data_ptr()
+        self.peer_bases = bases
+        self.mc_base = int(h.multicast_ptr) if os.environ.get("PICD_NVLS", "1") != "0" else 0
 
     def _exchange_handles(self):
         nb = self.lib.picd_ipc_handle_bytes()
@@ -125,6 +165,12 @@ class Comm:
                     slab.region_ptrs(slab.off_shadow), slab.region_ptrs(slab.off_xchg),
                     slab.region_ptrs(slab.off_flags), slab.max_buckets, ctypes.byref(ctx)), "picd_comm_create")
         self.ctx = ctx
+        self.has_nvls = bool(slab.mc_base)
+        if self.has_nvls:
+            f2 = self.lib.picd_comm_set_multicast
+            f2.argtypes = [ctypes.c_void_p] * 4
+            check(f2(ctx, slab.mc_base + slab.off_grad, slab.mc_base + slab.off_master, slab.mc_base + slab.off_shadow),
+                  "picd_comm_set_multicast")
         self._slot_epoch = {}
         self._slots = {}
         self._slot_keys = []
@@ -302,7 +348,15 @@ class NativeReducer:
             return 1
         if forced == "two_shot":
             return 2
-        return 2 if b.numel * 4 >= TWO_SHOT_MIN_BYTES else 1
+        if forced in ("nvls", "nvls_ld"):
+            if not self.comm.has_nvls:
+                raise RuntimeError("picd_b200: comm='nvls' but no NVSwitch multicast mapping is available")
+            return 3 if forced == "nvls" else 4
+        if b.numel * 4 < TWO_SHOT_MIN_BYTES:
+            return 1
+        if self.comm.has_nvls and self.e.world >= NVLS_MIN_WORLD and b.numel * 4 >= NVLS_MIN_BYTES:
+            return 3 if b.numel * 4 < NVLS_ST_MAX_BYTES else 4
+        return 2
 
     def launch_bucket(self, b):
         e = self.e
