@@ -12,6 +12,7 @@
 // Out-of-range key columns are masked in the softmax, out-of-range query rows are simply not stored.
 #include "../common/picd_common.cuh"
 
+#include <algorithm>
 #include <cstring>
 
 namespace picd {
@@ -187,25 +188,27 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------------ backward: dQ (+ delta)
+// Persistent: one CTA per SM walks (batch, head, query tile) items; the Q / dO / K / V tiles of item i+1 are prefetched by
+// TMA into the other half of shared memory while item i computes, and barrier setup / TMEM allocation happen once per CTA
+// (they and the load latency were ~40% of the former one-item-per-CTA kernel).  dS overwrites the Q / dO / V tiles of its own
+// item (they are dead once S and dP sit in TMEM), which is what makes two 96 KB item buffers fit.
+constexpr int ATT_DQ_ITEM_BYTES = 32768 + 16384 + 16384 + 32768;      // K | Q | dO | V   (dS aliases Q..V: 64 KB)
+struct AttDqBars {
+    uint64_t load[2], mma0, mma1;
+    uint32_t tmem_base;
+};
 __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_constant__ AttnParams p) {
     extern __shared__ uint8_t att_raw[];
     uint8_t* smem = att_align(att_raw);
-    AttBars* bars = reinterpret_cast<AttBars*>(smem);
-    uint8_t* sQ = smem + 1024;            // 16 KB
-    uint8_t* sdO = sQ + 16384;            // 16 KB
-    uint8_t* sK = sdO + 16384;            // 32 KB
-    uint8_t* sV = sK + 32768;             // 32 KB
-    uint8_t* sdS = sV + 32768;            // 64 KB
+    AttDqBars* bars = reinterpret_cast<AttDqBars*>(smem);
+    uint8_t* buf0 = smem + 1024;
     const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
     const int half = warp >> 2;          // two threads per query row: alternate 32-column chunks
-    const int mt = blockIdx.x & 1;
-    const int bh = blockIdx.x >> 1;
-    const int h = bh % p.H, b = bh / p.H;
-    const int q0 = mt * ATT_TILE;
-    if (q0 >= p.S) return;
+    const int n_tiles = (p.S + ATT_TILE - 1) / ATT_TILE;
+    const int items = p.B * p.H * n_tiles;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
+        mbar_init(&bars->load[0], 1); mbar_init(&bars->load[1], 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
         fence_mbar_init();
     }
     if (warp == 0) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
@@ -214,95 +217,121 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_consta
     tc_fence_after();
     const uint32_t tmem = uniform_u32(bars->tmem_base);
     const int HD = p.H * ATT_D;
-    const int row_base = b * p.S;
 
-    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
-        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 6);
-        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
-        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
-        mbar_wait(&bars->load, 0);
-        tc_fence_after();
-        const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
+    auto issue_loads = [&](int item, int b) {          // whole warp 0; one elected lane issues
+        const int mt = item % n_tiles, bh = item / n_tiles;
+        const int h = bh % p.H, bb = bh / p.H;
+        const int row_base = bb * p.S, q0 = mt * ATT_TILE;
+        uint8_t* sK = buf0 + b * ATT_DQ_ITEM_BYTES;
+        uint8_t* sQ = sK + 32768;
+        uint8_t* sdO = sQ + 16384;
+        uint8_t* sV = sdO + 16384;
+        mbar_arrive_expect_tx_warp(&bars->load[b], 16384 * 6);
+        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load[b], h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sdO, &p.do_map, &bars->load[b], h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sK, &p.qkv_map, &bars->load[b], HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load[b], HD + h * ATT_D, row_base + 128);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->load[b], 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load[b], 2 * HD + h * ATT_D, row_base + 128);
+    };
+
+    if (warp == 0 && static_cast<int>(blockIdx.x) < items) issue_loads(blockIdx.x, 0);
+    int it = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+        const int b = it & 1;
+        const uint32_t ld_phase = (it >> 1) & 1, mma_phase = it & 1;
+        const int mt = item % n_tiles, bh = item / n_tiles;
+        const int h = bh % p.H, bb = bh / p.H;
+        const int row_base = bb * p.S, q0 = mt * ATT_TILE;
+        uint8_t* sK = buf0 + b * ATT_DQ_ITEM_BYTES;
+        uint8_t* sQ = sK + 32768;
+        uint8_t* sdO = sQ + 16384;
+        uint8_t* sV = sdO + 16384;
+        uint8_t* sdS = sQ;                              // 64 KB over Q | dO | V
+        if (warp == 0) {
+            // the other buffer was last touched by item it-1, whose dQ MMA and stores completed before the loop came back here
+            if (item + static_cast<int>(gridDim.x) < items) issue_loads(item + gridDim.x, b ^ 1);
+            mbar_wait(&bars->load[b], ld_phase);
+            tc_fence_after();
+            const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)      // S = Q K^T  -> columns [0, 256)
-            umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
+            for (int k = 0; k < 4; ++k)      // S = Q K^T  -> columns [0, 256)
+                umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)      // dP = dO V^T -> columns [256, 512)
-            umma_bf16_warp(tmem + 256, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
-        umma_commit_warp(&bars->mma0);
-    }
-    const int row = (warp & 3) * 32 + lane;
-    const int q = q0 + row;
-    const bool qvalid = q < p.S;
-    // delta = rowsum(dO o O), straight from global memory (128 B per tensor per thread)
-    float delta = 0.f;
-    if (qvalid) {
-        const uint4* po = reinterpret_cast<const uint4*>(p.o + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
-        const uint4* pd = reinterpret_cast<const uint4*>(p.dout + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const uint4 a = po[c], d = pd[c];
-            const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
-            const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
-            delta += a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
+            for (int k = 0; k < 4; ++k)      // dP = dO V^T -> columns [256, 512)
+                umma_bf16_warp(tmem + 256, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
+            umma_commit_warp(&bars->mma0);
         }
-        if (half == 0) p.delta[(static_cast<size_t>(b) * p.H + h) * p.S + q] = delta;
-    }
-    const float lse = qvalid ? p.lse[(static_cast<size_t>(b) * p.H + h) * p.S + q] : 0.f;
-    const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    mbar_wait(&bars->mma0, 0);
-    tc_fence_after();
-    const uint32_t sdS_u32 = smem_u32(sdS);
-    for (int g = half; g < (p.n_keys + 31) >> 5; g += 2) {
-        uint32_t s[32], dp[32];
-        tmem_ld_32x32(t_row + g * 32, s);
-        tmem_ld_32x32(t_row + 256 + g * 32, dp);
-        tmem_ld_wait();
-        float f[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            const float pr = (g * 32 + i < p.S) ? exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2e, -lse)) : 0.f;
-            f[i] = qvalid ? pr * (__uint_as_float(dp[i]) - delta) * p.scale : 0.f;
-        }
-        store_row_chunk32(sdS_u32, row, g * 32, f);
-    }
-    tc_fence_before();
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
-        tc_fence_after();
-        const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
-        const int ksteps = p.n_keys >> 4;
-        for (int k = 0; k < ksteps; ++k)         // dQ = dS K  (K read MN-major), into columns [0, 64)
-            umma_bf16_warp(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
-        umma_commit_warp(&bars->mma1);
-    }
-    mbar_wait(&bars->mma1, 0);
-    tc_fence_after();
-    {
-        const int g = half;
-        uint32_t v[32];
-        tmem_ld_32x32(t_row + g * 32, v);
-        tmem_ld_wait();
+        const int row = (warp & 3) * 32 + lane;
+        const int q = q0 + row;
+        const bool qvalid = q < p.S;
+        // delta = rowsum(dO o O), straight from global memory (128 B per tensor per thread)
+        float delta = 0.f;
         if (qvalid) {
-            uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + q) * 3 * HD + h * ATT_D + g * 32);
+            const uint4* po = reinterpret_cast<const uint4*>(p.o + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
+            const uint4* pd = reinterpret_cast<const uint4*>(p.dout + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint4 w;
-                w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
-                w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
-                w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
-                w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
-                dst[c] = w;
+            for (int c = 0; c < 8; ++c) {
+                const uint4 a = po[c], d = pd[c];
+                const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+                const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
+                delta += a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
+            }
+            if (half == 0) p.delta[(static_cast<size_t>(bb) * p.H + h) * p.S + q] = delta;
+        }
+        const float lse = qvalid ? p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + q] : 0.f;
+        const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+        mbar_wait(&bars->mma0, mma_phase);
+        tc_fence_after();
+        const uint32_t sdS_u32 = smem_u32(sdS);
+        for (int g = half; g < (p.n_keys + 31) >> 5; g += 2) {
+            uint32_t s[32], dp[32];
+            tmem_ld_32x32(t_row + g * 32, s);
+            tmem_ld_32x32(t_row + 256 + g * 32, dp);
+            tmem_ld_wait();
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float pr = (g * 32 + i < p.S) ? exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2e, -lse)) : 0.f;
+                f[i] = qvalid ? pr * (__uint_as_float(dp[i]) - delta) * p.scale : 0.f;
+            }
+            store_row_chunk32(sdS_u32, row, g * 32, f);     // over Q / dO / V: the S and dP chains have completed (mma0)
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (warp == 0) {
+            tc_fence_after();
+            const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
+            const int ksteps = p.n_keys >> 4;
+            for (int k = 0; k < ksteps; ++k)         // dQ = dS K  (K read MN-major), into columns [0, 64)
+                umma_bf16_warp(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
+            umma_commit_warp(&bars->mma1);
+        }
+        mbar_wait(&bars->mma1, mma_phase);
+        tc_fence_after();
+        {
+            const int g = half;
+            uint32_t v[32];
+            tmem_ld_32x32(t_row + g * 32, v);
+            tmem_ld_wait();
+            if (qvalid) {
+                uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + q) * 3 * HD + h * ATT_D + g * 32);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 w;
+                    w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
+                    w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
+                    w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
+                    w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
+                    dst[c] = w;
+                }
             }
         }
+        tc_fence_before();
+        __syncthreads();          // every thread has read dQ out of TMEM and is done with this item's buffer
+        tc_fence_after();
     }
-    tc_fence_before();
-    __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
@@ -493,7 +522,7 @@ extern "C" int picd_attention_bwd(const void* qkv, const void* o, const void* do
     p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
     p.lse = const_cast<float*>(lse);
     p.delta = delta;
-    const int smem_dq = 1024 + 16384 * 2 + 32768 * 2 + 65536 + 1024;
+    const int smem_dq = 1024 + 2 * ATT_DQ_ITEM_BYTES + 1024;
     const int smem_kv = 2048 + 16384 * 4 + 32768 * 2 + 1024;
     static bool attr = false;
     if (!attr) {
@@ -501,7 +530,7 @@ extern "C" int picd_attention_bwd(const void* qkv, const void* o, const void* do
         PICD_CUDA(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_kv));
         attr = true;
     }
-    attn_bwd_dq_kernel<<<B * H * 2, 256, smem_dq, stream>>>(p);
+    attn_bwd_dq_kernel<<<std::min(B * H * ((S + ATT_TILE - 1) / ATT_TILE), num_sms()), 256, smem_dq, stream>>>(p);
     PICD_LAUNCH_CHECK();
     attn_bwd_dkdv_kernel<<<B * H * 2, 256, smem_kv, stream>>>(p);
     PICD_LAUNCH_CHECK();
