@@ -86,3 +86,24 @@ def test_convert_sync_batchnorm_marks_every_bn():
     # single process: falls back to local statistics and still trains
     out = m(torch.randn(2, 3, 32, 32))
     out.sum().backward()
+
+
+def test_graphed_train_step_falls_back_to_eager_on_cpu():
+    """GraphedTrainStep is the public step API of bench.py / train.py --cuda-graph; without CUDA it must simply run the
+    eager sequence (and hand out detached tensors)."""
+    import torch
+    from picd_b200.engine.graphed import GraphedTrainStep
+    from picd_b200.engine.trainer import WeightedCrossEntropy
+    from picd_b200.models import Classifier
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    torch.manual_seed(0)
+    dp = FusedDataParallel(Classifier("resnet18", 7, image_size=32, small_input=True), OptimizerSpec("sgd", lr=0.05, momentum=0.9))
+    dp.train()
+    step = GraphedTrainStep(dp, WeightedCrossEntropy(None), dp.optimizer, warmup=1)
+    assert not step.enabled
+    x, y = torch.randn(4, 3, 32, 32), torch.randint(0, 7, (4,))
+    before = dp.arena.master.clone()
+    losses = [float(step(x, y)) for _ in range(3)]
+    assert step.graph is None and step.replays == 0 and dp.step_index == 3
+    assert not step(x, y).requires_grad and not step.outputs.requires_grad
+    assert not torch.equal(before, dp.arena.master) and all(l == l for l in losses)
