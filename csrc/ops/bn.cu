@@ -182,7 +182,8 @@ __global__ void __launch_bounds__(256, MINB) bn_apply_kernel(const __nv_bfloat16
                                                        const float* __restrict__ shift,
                                                        const __nv_bfloat16* __restrict__ residual, int act,
                                                        __nv_bfloat16* __restrict__ out, long long P, int C,
-                                                       int tx_count, int ty_count, int rows_per_block) {
+                                                       int tx_count, int ty_count, int rows_per_block,
+                                                       uint8_t* __restrict__ relu_mask) {
     const int vecs = C >> 3;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
@@ -218,6 +219,14 @@ __global__ void __launch_bounds__(256, MINB) bn_apply_kernel(const __nv_bfloat16
                 Vec8 o;
                 o.pack(f);
                 o.store(out + rr * C + cv * 8);
+                if (relu_mask != nullptr) {
+                    // one bit per output: "the ReLU let it through".  The backward kernels of residual layers read this
+                    // byte per 16-byte vector instead of streaming the whole output tensor again for its sign.
+                    uint32_t bits = 0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) bits |= (f[k] > 0.f ? 1u : 0u) << k;
+                    relu_mask[rr * vecs + cv] = static_cast<uint8_t>(bits);
+                }
             }
         }
     }
@@ -396,10 +405,10 @@ static ReduceShape stream_shape(long long P, int C) {
 // TMA-streamed variants (bn_stream.cu); each returns -1 when the shape is not eligible.
 int bn_stream_apply(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
                     long long P, int C, cudaStream_t stream);
-int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale, const float* shift,
                          const float* mean, const float* invstd, int act, float* sums, long long P, int C,
                          cudaStream_t stream);
-int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
+int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale, const float* shift,
                         const float* mean, const float* invstd, int act, const float* sums, float inv_count,
                         const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
                         int eval_mode, cudaStream_t stream);
@@ -443,13 +452,14 @@ extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const 
     return 0;
 }
 
-extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
-                             void* out, long long P, int C, cudaStream_t stream) {
+// relu_mask (optional, [P * C/8] bytes + one chunk of slack): bit k of byte v = output 8*v+k is positive.
+extern "C" int picd_bn_apply_mask(const void* y, const float* scale, const float* shift, const void* residual, int act,
+                                  void* out, void* relu_mask, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_apply: C=%d must be a multiple of 8", C);
     // The TMA-streamed forward apply measured SLOWER (2.5 TB/s) than this register-streaming kernel (4.8 TB/s) --
     // one input tensor gives the ring too little work per handshake -- so it is opt-in (PICD_BN_STREAM_APPLY=1).
     static const bool stream_apply = [] { const char* e = getenv("PICD_BN_STREAM_APPLY"); return e != nullptr && e[0] == '1'; }();
-    if (stream_apply && use_stream_kernels()) {
+    if (stream_apply && use_stream_kernels() && relu_mask == nullptr) {
         const int rc = bn_stream_apply(y, scale, shift, residual, act, out, P, C, stream);
         if (rc >= 0) return rc;
     }
@@ -458,7 +468,8 @@ extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shi
 #define PICD_BN_APPLY_LAUNCH_A(U, MINB, A)                                                                         \
     bn_apply_kernel<U, MINB, A><<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(                                      \
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,       \
-        static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block)
+        static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block,                           \
+        static_cast<uint8_t*>(relu_mask))
 #define PICD_BN_APPLY_LAUNCH(U, MINB)                                                                              \
     do {                                                                                                            \
         if (act == ACT_RELU) PICD_BN_APPLY_LAUNCH_A(U, MINB, ACT_RELU);                                             \
@@ -477,13 +488,18 @@ extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shi
     PICD_LAUNCH_CHECK();
     return 0;
 }
+extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
+                             void* out, long long P, int C, cudaStream_t stream) {
+    return picd_bn_apply_mask(y, scale, shift, residual, act, out, nullptr, P, C, stream);
+}
 
-extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale,
-                                  const float* shift, const float* mean, const float* invstd, int act, float* sums,
-                                  long long P, int C, cudaStream_t stream) {
+// relu_mask (optional): the bit mask written by picd_bn_apply_mask; the streamed kernels read it instead of z.
+extern "C" int picd_bn_bwd_reduce_mask(const void* dz, const void* y, const void* z, const void* relu_mask,
+                                       const float* scale, const float* shift, const float* mean, const float* invstd,
+                                       int act, float* sums, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_reduce: C=%d must be a multiple of 8", C);
     if (use_stream_kernels()) {
-        const int rc = bn_stream_bwd_reduce(dz, y, z, scale, shift, mean, invstd, act, sums, P, C, stream);
+        const int rc = bn_stream_bwd_reduce(dz, y, z, relu_mask, scale, shift, mean, invstd, act, sums, P, C, stream);
         if (rc >= 0) return rc;
     }
     const ReduceShape s = reduce_shape(P, C);
@@ -496,6 +512,12 @@ extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, 
     return 0;
 }
 
+extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale,
+                                  const float* shift, const float* mean, const float* invstd, int act, float* sums,
+                                  long long P, int C, cudaStream_t stream) {
+    return picd_bn_bwd_reduce_mask(dz, y, z, nullptr, scale, shift, mean, invstd, act, sums, P, C, stream);
+}
+
 // In-place fold of `replicas` copies of n floats into copy 0.
 __global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -504,11 +526,11 @@ __global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
 }
 
 // NOTE: folds `sums` / `param_sums` in place (copy 0 receives the totals) before the streaming kernel runs.
-extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale,
-                                 const float* shift, const float* mean, const float* invstd, int act,
-                                 const float* sums, int sums_replicas, float inv_count, const float* param_sums,
-                                 int param_replicas, float* dgamma, float* dbeta, void* dy, void* dres, long long P,
-                                 int C, cudaStream_t stream) {
+extern "C" int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const void* relu_mask,
+                                      const float* scale, const float* shift, const float* mean, const float* invstd,
+                                      int act, const float* sums, int sums_replicas, float inv_count,
+                                      const float* param_sums, int param_replicas, float* dgamma, float* dbeta, void* dy,
+                                      void* dres, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
     if (param_sums != nullptr && param_sums != sums && param_replicas > 1) {
         fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(param_sums), 2 * C, param_replicas);
@@ -520,8 +542,8 @@ extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, c
         sums_replicas = 1;
     }
     if (use_stream_kernels()) {
-        const int rc = bn_stream_bwd_apply(dz, y, z, scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
-                                           dbeta, dy, dres, P, C, 0, stream);
+        const int rc = bn_stream_bwd_apply(dz, y, z, relu_mask, scale, shift, mean, invstd, act, sums, inv_count, param_sums,
+                                           dgamma, dbeta, dy, dres, P, C, 0, stream);
         if (rc >= 0) return rc;
     }
     const ReduceShape s = stream_shape(P, C);
@@ -533,12 +555,20 @@ extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, c
     PICD_LAUNCH_CHECK();
     return 0;
 }
+extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, int act,
+                                 const float* sums, int sums_replicas, float inv_count, const float* param_sums,
+                                 int param_replicas, float* dgamma, float* dbeta, void* dy, void* dres, long long P,
+                                 int C, cudaStream_t stream) {
+    return picd_bn_bwd_apply_mask(dz, y, z, nullptr, scale, shift, mean, invstd, act, sums, sums_replicas, inv_count, param_sums,
+                                  param_replicas, dgamma, dbeta, dy, dres, P, C, stream);
+}
 
 extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
                                 int act, void* dy, void* dres, long long P, int C, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_eval: C=%d must be a multiple of 8", C);
     if (use_stream_kernels()) {
-        const int rc = bn_stream_bwd_apply(dz, y, z, scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
+        const int rc = bn_stream_bwd_apply(dz, y, z, nullptr, scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
                                            nullptr, dy, dres, P, C, 1, stream);
         if (rc >= 0) return rc;
     }

@@ -36,6 +36,9 @@ struct StreamArgs {
     int act, use_z, eval_mode;
     long long P;
     int C, rows_per_chunk, stages, chunk_bytes;
+    const uint8_t* mask;             // BWD_*: ReLU bit mask of a residual layer (one byte per 16-byte vector), replaces in[2]
+    int use_mask, mask_chunk_bytes;  // bytes of mask per full chunk (rows_per_chunk * C/8, a multiple of 16)
+    int stage_bytes;                 // n_in * chunk_bytes (+ 1 KB-rounded mask chunk)
     int n_active;                    // consumers that own a channel vector: the largest multiple of C/8 that is <= 512
     long long num_chunks;
 };
@@ -112,9 +115,14 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
                 if (rows > a.rows_per_chunk) rows = a.rows_per_chunk;
                 const uint32_t bytes = static_cast<uint32_t>(rows * C * 2);
                 mbar_wait(&empty[s], phase ^ 1);
-                mbar_arrive_expect_tx(&full[s], bytes * n_in);
+                // mask bytes of this chunk, rounded up to the 16-byte bulk-copy granule (the mask buffer has slack at its end)
+                const uint32_t mbytes = a.use_mask ? ((static_cast<uint32_t>(rows) * (C >> 3) + 15u) & ~15u) : 0u;
+                mbar_arrive_expect_tx(&full[s], bytes * n_in + mbytes);
+                uint8_t* stage = ring + static_cast<size_t>(s) * a.stage_bytes;
                 for (int t = 0; t < n_in; ++t)
-                    bulk_load(ring + (static_cast<size_t>(s) * n_in + t) * a.chunk_bytes, a.in[t] + row0 * C, bytes, &full[s]);
+                    bulk_load(stage + static_cast<size_t>(t) * a.chunk_bytes, a.in[t] + row0 * C, bytes, &full[s]);
+                if (a.use_mask)
+                    bulk_load(stage + static_cast<size_t>(n_in) * a.chunk_bytes, a.mask + c * a.mask_chunk_bytes, mbytes, &full[s]);
                 if (++s == stages) { s = 0; phase ^= 1; }
             }
         }
@@ -133,7 +141,7 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
                 long long rows = a.P - row0;
                 if (rows > a.rows_per_chunk) rows = a.rows_per_chunk;
                 const uint32_t bytes = static_cast<uint32_t>(rows * C * 2);
-                const uint32_t base = smem_u32(ring) + static_cast<uint32_t>(s) * n_in * a.chunk_bytes;
+                const uint32_t base = smem_u32(ring) + static_cast<uint32_t>(s) * a.stage_bytes;
                 mbar_wait(&done[s], phase);
                 bulk_store(a.out0 + row0 * C, base, bytes);
                 if (MODE == SB_BWD_APPLY && a.out1 != nullptr) bulk_store(a.out1 + row0 * C, base + a.chunk_bytes, bytes);
@@ -179,7 +187,7 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         if (rows > a.rows_per_chunk) rows = a.rows_per_chunk;
         const int nvec = static_cast<int>(rows) * vecs;
         mbar_wait(&full[s], phase);
-        const uint32_t base = ring_u32 + static_cast<uint32_t>(s) * n_in * a.chunk_bytes;
+        const uint32_t base = ring_u32 + static_cast<uint32_t>(s) * a.stage_bytes;
         const uint32_t cb = a.chunk_bytes;
 #pragma unroll
         // vector idx of the chunk belongs to channel vector idx % vecs; stepping by n_active (a multiple of vecs) keeps every
@@ -200,7 +208,12 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
                     unpack8(lds128(base + idx * 16), g);
                     unpack8(lds128(base + cb + idx * 16), yv);
                     if (a.act == ACT_RELU) {
-                        if (a.use_z) {
+                        if (a.use_mask) {
+                            uint32_t mb;
+                            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(mb) : "r"(base + n_in * cb + idx));
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) g[j] = ((mb >> j) & 1u) ? g[j] : 0.f;
+                        } else if (a.use_z) {
                             float zv[8];
                             unpack8(lds128(base + 2 * cb + idx * 16), zv);
 #pragma unroll
@@ -276,7 +289,10 @@ static int launch_stream(StreamArgs& a, cudaStream_t stream) {
     a.rows_per_chunk = a.chunk_bytes / (a.C * 2);
     a.n_active = (SB_CONSUMERS / (a.C / 8)) * (a.C / 8);
     a.num_chunks = (a.P + a.rows_per_chunk - 1) / a.rows_per_chunk;
-    const int stage_bytes = a.n_in * a.chunk_bytes;
+    a.mask_chunk_bytes = a.rows_per_chunk * (a.C / 8);
+    if (a.use_mask && (a.mask_chunk_bytes % 16) != 0) return -1;       // bulk copies move 16-byte granules
+    const int stage_bytes = a.n_in * a.chunk_bytes + (a.use_mask ? ((a.mask_chunk_bytes + 1023) & ~1023) : 0);
+    a.stage_bytes = stage_bytes;
     int stages = (200 * 1024) / stage_bytes;
     if (stages > SB_MAX_STAGES) stages = SB_MAX_STAGES;
     a.stages = stages;
@@ -309,32 +325,38 @@ int bn_stream_apply(const void* y, const float* scale, const float* shift, const
     return launch_stream<SB_APPLY>(a, stream);
 }
 
-int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
-                         const float* mean, const float* invstd, int act, float* sums, long long P, int C,
-                         cudaStream_t stream) {
+// z / relu_mask: the ReLU mask source of a layer that added a residual before the activation -- the output tensor itself
+// (a third streamed input) or, preferably, the bit mask written by the forward apply (1/16 of the bytes).
+static void set_mask_source(StreamArgs& a, const void* z, const void* relu_mask, int act) {
+    a.in[2] = static_cast<const __nv_bfloat16*>(z);
+    a.mask = static_cast<const uint8_t*>(relu_mask);
+    a.use_mask = (relu_mask != nullptr && act == ACT_RELU) ? 1 : 0;
+    a.use_z = (!a.use_mask && z != nullptr && act == ACT_RELU) ? 1 : 0;
+    a.n_in = a.use_z ? 3 : 2;
+}
+
+int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
+                         const float* shift, const float* mean, const float* invstd, int act, float* sums, long long P,
+                         int C, cudaStream_t stream) {
     if (!stream_eligible(P, C)) return -1;
     StreamArgs a{};
     a.in[0] = static_cast<const __nv_bfloat16*>(dz);
     a.in[1] = static_cast<const __nv_bfloat16*>(y);
-    a.in[2] = static_cast<const __nv_bfloat16*>(z);
-    a.use_z = (z != nullptr && act == ACT_RELU) ? 1 : 0;
-    a.n_in = a.use_z ? 3 : 2;
+    set_mask_source(a, z, relu_mask, act);
     a.scale = scale; a.shift = shift; a.mean = mean; a.invstd = invstd; a.act = act;
     a.sums_out = sums; a.P = P; a.C = C;
     return launch_stream<SB_BWD_REDUCE>(a, stream);
 }
 
-int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const float* scale, const float* shift,
-                        const float* mean, const float* invstd, int act, const float* sums, float inv_count,
-                        const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
-                        int eval_mode, cudaStream_t stream) {
+int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
+                        const float* shift, const float* mean, const float* invstd, int act, const float* sums,
+                        float inv_count, const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres,
+                        long long P, int C, int eval_mode, cudaStream_t stream) {
     if (!stream_eligible(P, C)) return -1;
     StreamArgs a{};
     a.in[0] = static_cast<const __nv_bfloat16*>(dz);
     a.in[1] = static_cast<const __nv_bfloat16*>(y);
-    a.in[2] = static_cast<const __nv_bfloat16*>(z);
-    a.use_z = (z != nullptr && act == ACT_RELU) ? 1 : 0;
-    a.n_in = a.use_z ? 3 : 2;
+    set_mask_source(a, z, relu_mask, act);
     a.out0 = static_cast<__nv_bfloat16*>(dy);
     a.out1 = static_cast<__nv_bfloat16*>(dres);
     a.scale = scale; a.shift = shift; a.mean = mean; a.invstd = invstd; a.act = act;

@@ -74,6 +74,18 @@ int picd_bn_finalize(const float* sums, int replicas, float count, const float* 
                      float* invstd, int C, cudaStream_t stream);
 int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                         float eps, float* scale, float* shift, int C, cudaStream_t stream);
+/* ReLU bit mask for layers that add a residual before the activation: picd_bn_apply_mask additionally writes one byte per
+ * 16-byte output vector (bit k = output 8*v+k is positive) into relu_mask, which must hold P*C/8 bytes plus 4 KB of slack;
+ * the *_mask backward entry points read it instead of streaming z again (z is still used by the small-tensor kernels). */
+int picd_bn_apply_mask(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
+                       void* relu_mask, long long P, int C, cudaStream_t stream);
+int picd_bn_bwd_reduce_mask(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
+                            const float* shift, const float* mean, const float* invstd, int act, float* sums, long long P,
+                            int C, cudaStream_t stream);
+int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
+                           const float* shift, const float* mean, const float* invstd, int act, const float* sums,
+                           int sums_replicas, float inv_count, const float* param_sums, int param_replicas, float* dgamma,
+                           float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream);
 int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
                   long long P, int C, cudaStream_t stream);
 int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,

@@ -14,6 +14,7 @@ the bucket's fused all-reduce + update can start right behind the wgrad launch.
 from __future__ import annotations
 
 import ctypes
+import os
 import math
 from typing import Optional, Tuple
 
@@ -43,6 +44,9 @@ _SIG = {
     "picd_bn_finalize": "pifppppffppppip",
     "picd_bn_eval_coeffs": "ppppfppip",
     "picd_bn_apply": "ppppiplip",
+    "picd_bn_apply_mask": "ppppipplip",
+    "picd_bn_bwd_reduce_mask": "ppppppppiplip",
+    "picd_bn_bwd_apply_mask": "ppppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_reduce": "pppppppiplip",
     "picd_bn_bwd_apply": "pppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_eval": "pppppipplip",
@@ -396,6 +400,9 @@ class _BNCfg:
     __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group", "fork", "fork_role")
 
 
+_USE_RELU_MASK = os.environ.get("PICD_BN_MASK", "1") != "0"      # A/B switch: 0 = backward re-reads z for the ReLU sign
+
+
 def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
     C = gamma.numel()
     P = y.numel() // C
@@ -408,7 +415,12 @@ def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
         total = float(count)
     z = torch.empty_like(y)
     res = None if residual is None else nhwc(residual)
-    call("picd_bn_apply", y, coef[0], coef[1], res, ACT[cfg.act], z, P, C)
+    # residual + ReLU: the backward needs the sign of the OUTPUT (it cannot be recomputed from y alone).  A bit mask
+    # (1/16 of the tensor) saves the backward kernels from streaming z again.
+    ctx.relu_mask = None
+    if res is not None and cfg.act == "relu" and cfg.training and _USE_RELU_MASK:    # (grad mode is off inside Function.forward)
+        ctx.relu_mask = torch.empty(P * (C // 8) + 4096, dtype=torch.uint8, device=y.device)
+    call("picd_bn_apply_mask", y, coef[0], coef[1], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
     ctx.bn_total, ctx.bn_act, ctx.bn_training = total, cfg.act, cfg.training
     ctx.bn_sync, ctx.has_res = cfg.sync_group, residual is not None
     return z, coef
@@ -427,11 +439,12 @@ def _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, need_dres):
         call("picd_bn_bwd_eval", dz, y, zmask, coef[0], coef[1], act, dy, dres, P, C)
         return dy, dres, None, None
     sums2 = stat_buffer(C, y.device)
-    call("picd_bn_bwd_reduce", dz, y, zmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
+    rmask = getattr(ctx, "relu_mask", None) if zmask is not None else None
+    call("picd_bn_bwd_reduce_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
     gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C)
     gt, g_routed = _grad_target(gamma)
     bt, b_routed = _grad_target(beta)
-    call("picd_bn_bwd_apply", dz, y, zmask, coef[0], coef[1], coef[2], coef[3], act, gsums, gsums.numel() // (2 * C),
+    call("picd_bn_bwd_apply_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, gsums, gsums.numel() // (2 * C),
          1.0 / ctx.bn_total, sums2, STAT_REPLICAS, gt, bt, dy, dres, P, C)
     if g_routed:
         _mark_ready(gamma)
