@@ -54,3 +54,27 @@ def test_folder_dataset_and_real_loader(tmp_path):
     from picd_b200 import ops
     x = ops.normalize_u8(raw.unsqueeze(0))
     assert x.shape == (1, 3, 32, 32) and abs(float(x.mean())) < 3
+
+
+def test_bucket_variant_selection_policy():
+    """The per-bucket choice between one-shot / two-shot / NVLS variants of the fused all-reduce kernel is host logic
+    (parallel/native_comm.NativeReducer._mode): check it without a GPU by calling it on a stand-in object."""
+    from types import SimpleNamespace
+    from picd_b200.parallel import native_comm as nc
+
+    def mode(world, nbytes, has_nvls, forced="auto"):
+        fake = SimpleNamespace(e=SimpleNamespace(world=world, comm=forced), comm=SimpleNamespace(has_nvls=has_nvls))
+        return nc.NativeReducer._mode(fake, SimpleNamespace(numel=nbytes // 4))
+
+    assert mode(1, 1 << 30, True) == 0                                   # single GPU: local update, no flags
+    assert mode(8, 64 << 10, True) == 1                                  # latency-bound bucket: one-shot
+    assert mode(8, 1 << 20, True) == 2                                   # below the NVLS threshold: two-shot P2P
+    assert mode(8, 25 << 20, True) == 3                                  # DDP-sized bucket on an NVLS host
+    assert mode(8, 1 << 30, True) == 4                                   # huge bucket: in-switch reduce, unicast pushes
+    assert mode(8, 25 << 20, False) == 2                                 # no multicast mapping
+    assert mode(2, 25 << 20, True) == 2                                  # two ranks: multicast moves the same bytes
+    assert mode(8, 64 << 10, True, forced="two_shot") == 2 and mode(8, 1 << 30, True, forced="one_shot") == 1
+    assert mode(8, 1 << 20, True, forced="nvls") == 3 and mode(8, 1 << 20, True, forced="nvls_ld") == 4
+    import pytest
+    with pytest.raises(RuntimeError):
+        mode(8, 1 << 20, False, forced="nvls")
