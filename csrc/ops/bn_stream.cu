@@ -285,7 +285,10 @@ static bool stream_eligible(long long P, int C) {
 template <int MODE>
 static int launch_stream(StreamArgs& a, cudaStream_t stream) {
     static const int one_in_chunk = [] { const char* e = getenv("PICD_BN_CHUNK"); return e == nullptr ? SB_MAX_CHUNK_BYTES : atoi(e); }();
-    a.chunk_bytes = a.n_in == 1 ? one_in_chunk : 16384;
+    // per-chunk handshakes bound the kernels, not bytes (two 16 KB tensors and three 16 KB tensors per chunk took the same
+    // time): two streamed tensors get 32 KB chunks (3 stages), three keep 16 KB (4 stages)
+    static const int two_in_chunk = [] { const char* e = getenv("PICD_BN_CHUNK_MULTI"); return e == nullptr ? 32768 : atoi(e); }();
+    a.chunk_bytes = a.n_in == 1 ? one_in_chunk : (a.n_in == 2 ? two_in_chunk : 16384);
     a.rows_per_chunk = a.chunk_bytes / (a.C * 2);
     a.n_active = (SB_CONSUMERS / (a.C / 8)) * (a.C / 8);
     a.num_chunks = (a.P + a.rows_per_chunk - 1) / a.rows_per_chunk;
