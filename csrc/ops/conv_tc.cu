@@ -16,10 +16,14 @@
 //     lands them), split-K over pixel ranges, fp32 accumulation in TMEM, vector red.add into the fp32
 //     gradient arena.
 //
-// conv_gemm_kernel: persistent, warp-specialised (warp0 TMA producer, warp1 MMA issuer, warps2-5 epilogue),
-// 3-4 stage smem ring, double-buffered 128xBN fp32 accumulator in TMEM, epilogue converts to bf16 into a
-// 128B-swizzled staging tile that one thread stores with TMA while all four warps accumulate per-channel
-// sum / sum-of-squares for BatchNorm from the same staging tile (fused BN statistics).
+// conv_gemm_kernel: persistent, warp-specialised (warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue), 4-8 stage
+// smem ring, double-buffered 128xBN fp32 accumulator in TMEM, epilogue converts to bf16 into a 128B-swizzled staging tile
+// that one thread stores with TMA (or TMA reduce-add) while all eight warps accumulate per-channel sum / sum-of-squares for
+// BatchNorm from the same staging tile (fused BN statistics).  Variants selected per launch:
+//   * halo mode (3x3, stride 1): one activation box with a halo row above/below per column shift, the three dh taps are
+//     descriptor shifts inside it; tiny weight sets stay resident in shared memory;
+//   * CTA pairs (tcgen05 cta_group::2): two SMs execute one M=256 UMMA, each loading its own pixel rows and half of B;
+//   * producer and MMA loops are warp-convergent (elect.sync inside the asm) so that operands live in uniform registers.
 #include "../common/picd_common.cuh"
 
 #include <algorithm>
