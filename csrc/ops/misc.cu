@@ -569,11 +569,7 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
                                                             const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                             long long M, int D, int rows_per_block) {
-    extern __shared__ float sm[];   // [2][D]
-    float* sg = sm;
-    float* sb = sm + D;
-    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) sm[j] = 0.f;
-    __syncthreads();
+    extern __shared__ float sm[];   // [warps][2][V*256]: every warp parks its partial sums, no shared-memory atomics
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     float pg[V][8], pb[V][8], gm[V][8];
 #pragma unroll
@@ -634,18 +630,27 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
             }
         }
     }
+    // fold the block's warps: warp w writes its partials to sm[w], then every thread sums a few columns over the warps and
+    // issues one global atomic per column (the former version did 2 x 8 x V shared-memory atomics per thread, 8-way contended)
+    constexpr int W2 = V * 256;
+    float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
-        if (j < D) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { atomicAdd(sg + j + k, pg[i][k]); atomicAdd(sb + j + k, pb[i][k]); }
-        }
+        *reinterpret_cast<float4*>(mine + j) = make_float4(pg[i][0], pg[i][1], pg[i][2], pg[i][3]);
+        *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
+        *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
+        *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
     }
     __syncthreads();
     for (int j = threadIdx.x; j < D; j += blockDim.x) {
-        atomicAdd(dgamma + j, sg[j]);
-        atomicAdd(dbeta + j, sb[j]);
+        float a = 0.f, b = 0.f;
+        for (int w = 0; w < nw; ++w) {
+            a += sm[static_cast<size_t>(w) * 2 * W2 + j];
+            b += sm[static_cast<size_t>(w) * 2 * W2 + W2 + j];
+        }
+        atomicAdd(dgamma + j, a);
+        atomicAdd(dbeta + j, b);
     }
 }
 
@@ -991,13 +996,18 @@ extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float
 extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
                                   void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
-    long long blocks = 4LL * num_sms();
+    static bool attr_set = false;
+    if (!attr_set) {       // V = 4 parks 8 warps x 2 x 1024 floats = 64 KB
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        attr_set = true;
+    }
+    long long blocks = 2LL * num_sms();
     long long rpb = (M + blocks - 1) / blocks;
     if (rpb < 16) rpb = 16;
     blocks = (M + rpb - 1) / rpb;
     const int V = (D + 255) / 256;
 #define PICD_LN_BWD(VV)                                                                                                   \
-    layernorm_bwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 2 * D * sizeof(float), st>>>(                           \
+    layernorm_bwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 8 * 2 * VV * 256 * sizeof(float), st>>>(                           \
         static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, \
         M, D, static_cast<int>(rpb))
     if (V == 1) PICD_LN_BWD(1); else if (V == 2) PICD_LN_BWD(2); else if (V == 3) PICD_LN_BWD(3); else PICD_LN_BWD(4);
