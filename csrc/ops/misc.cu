@@ -325,21 +325,23 @@ __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ log
 
 // ------------------------------------------------------------------------------------ element-wise activation
 // TACT >= 0 fixes the activation at compile time (no per-element switch); two vectors per thread are in flight.
+constexpr int ACT_UNROLL = 2;      // independent 16-byte vectors (rows) in flight per thread in the activation kernels (4 measured slower: GELU backward is ALU-bound)
+// TACT >= 0 fixes the activation at compile time (no per-element switch).
 template <int TACT>
 __global__ void __launch_bounds__(256) act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bias,
                                                       __nv_bfloat16* __restrict__ out, long long total_vecs, int C,
                                                       int act) {
     const int vecs = C >> 3;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total_vecs; i0 += 2 * step) {
-        uint4 raw[2];
+    for (long long i0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total_vecs; i0 += ACT_UNROLL * step) {
+        uint4 raw[ACT_UNROLL];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < ACT_UNROLL; ++u) {
             const long long i = i0 + u * step;
             raw[u] = i < total_vecs ? *reinterpret_cast<const uint4*>(x + i * 8) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < ACT_UNROLL; ++u) {
             const long long i = i0 + u * step;
             if (i >= total_vecs) break;
             float f[8];
@@ -356,7 +358,7 @@ __global__ void __launch_bounds__(256) act_fwd_kernel(const __nv_bfloat16* __res
     }
 }
 // dx = dy * act'(x + bias); optionally dbias[c] += sum over rows of dx[r, c] in the same pass (the bias gradient of the Linear
-// layer that produced x: saves re-reading dx).  Thread = one vector of 8 channels, rows strided over the block, two rows in
+// layer that produced x: saves re-reading dx).  Thread = one vector of 8 channels, rows strided over the block, ACT_UNROLL rows in
 // flight; shared-memory fold over the row dimension, one fp32 atomic per channel per block.
 template <int TACT>
 __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
@@ -377,17 +379,17 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __res
         const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
         long long r1 = r0 + rows_per_block;
         if (r1 > P) r1 = P;
-        for (long long r = r0 + ty; r < r1; r += 2LL * ty_count) {
-            uint4 vg[2], vx[2];
+        for (long long r = r0 + ty; r < r1; r += static_cast<long long>(ACT_UNROLL) * ty_count) {
+            uint4 vg[ACT_UNROLL], vx[ACT_UNROLL];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < ACT_UNROLL; ++u) {
                 const long long rr = r + static_cast<long long>(u) * ty_count;
                 const bool ok = rr < r1;
                 vg[u] = ok ? *reinterpret_cast<const uint4*>(dy + rr * C + cv * 8) : make_uint4(0, 0, 0, 0);
                 vx[u] = ok ? *reinterpret_cast<const uint4*>(x + rr * C + cv * 8) : make_uint4(0, 0, 0, 0);
             }
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < ACT_UNROLL; ++u) {
                 const long long rr = r + static_cast<long long>(u) * ty_count;
                 if (rr >= r1) break;
                 float g[8], f[8];
@@ -897,7 +899,7 @@ extern "C" int picd_cross_entropy(const float* logits, const long long* labels, 
 extern "C" int picd_act_fwd(const void* x, const float* bias, void* out, long long rows, int C, int act, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "act: C=%d must be a multiple of 8", C);
     const long long total = rows * (C / 8);
-#define PICD_ACT_FWD(A) act_fwd_kernel<A><<<grid_for(total / 2 + 1), 256, 0, st>>>(static_cast<const bf16*>(x), bias, static_cast<bf16*>(out), total, C, act)
+#define PICD_ACT_FWD(A) act_fwd_kernel<A><<<grid_for(total / ACT_UNROLL + 1), 256, 0, st>>>(static_cast<const bf16*>(x), bias, static_cast<bf16*>(out), total, C, act)
     switch (act) {
         case ACT_RELU: PICD_ACT_FWD(ACT_RELU); break;
         case ACT_GELU: PICD_ACT_FWD(ACT_GELU); break;
@@ -919,7 +921,7 @@ extern "C" int picd_act_bwd_bias(const void* dy, const void* x, const float* bia
     long long gy = (8LL * num_sms()) / gx;
     if (gy < 1) gy = 1;
     long long rpb = (rows + gy - 1) / gy;
-    if (rpb < 2LL * ty) rpb = 2LL * ty;
+    if (rpb < static_cast<long long>(ACT_UNROLL) * ty) rpb = static_cast<long long>(ACT_UNROLL) * ty;
     gy = (rows + rpb - 1) / rpb;
     const size_t smem = dbias != nullptr ? static_cast<size_t>(tx) * ty * 8 * sizeof(float) : 0;
 #define PICD_ACT_BWD(A)                                                                                                     \
