@@ -16,6 +16,27 @@ import torch.nn as nn
 from .. import ops
 
 
+# BatchNorm's ``num_batches_tracked`` counters: on CUDA the per-layer ``+= 1`` (one tiny kernel per BN layer per step, 53 for
+# ResNet-50) is deferred and applied by ONE multi-tensor add at the end of the model's forward pass.
+_pending_counters = []
+
+
+def _count_batch(bn) -> None:
+    t = bn.num_batches_tracked
+    if t.is_cuda:
+        _pending_counters.append(t)
+    else:
+        t += 1
+
+
+def flush_batch_counters() -> None:
+    """Apply the deferred ``num_batches_tracked += 1`` updates (called at the end of Classifier / backbone /
+    FusedDataParallel forwards and before a BatchNorm state dict is read)."""
+    if _pending_counters:
+        torch._foreach_add_(_pending_counters, 1)
+        _pending_counters.clear()
+
+
 def _pair(v):
     return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
 
@@ -62,9 +83,13 @@ class BatchNorm2d(nn.Module):
 
     def forward(self, x, act=None, residual=None):
         if self.training:
-            self.num_batches_tracked += 1
+            _count_batch(self)
         return ops.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var,
                               self.training, self.momentum, self.eps, self.sync_group, act, residual)
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        flush_batch_counters()
+        return super()._save_to_state_dict(destination, prefix, keep_vars)
 
     def extra_repr(self):
         return f"{self.num_features}, eps={self.eps}, momentum={self.momentum}, sync={self.sync_group}"
@@ -93,7 +118,7 @@ def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", r
     """Fused act(BN(conv(x)) + residual) using the parameters of a Conv2d/BatchNorm2d pair.  ``padding`` overrides the
     conv's own (used for TF-"same" layers: a (top, left, bottom, right) tuple)."""
     if bn.training:
-        bn.num_batches_tracked += 1
+        _count_batch(bn)
     return ops.conv_bn_act(
         x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
         stride=conv.stride, padding=conv.padding if padding is None else padding, groups=conv.groups,

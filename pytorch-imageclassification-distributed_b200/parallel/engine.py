@@ -371,7 +371,10 @@ class FusedDataParallel(nn.Module):
         if self.device.type == "cuda" and self.module.training and torch.is_grad_enabled():
             from ..ops import native
             native.stat_arena(self.device).begin_step()      # one memset instead of two fill kernels per BN layer
-        return self.module(*args, **kw)
+        out = self.module(*args, **kw)
+        from ..models.layers import flush_batch_counters
+        flush_batch_counters()          # deferred BatchNorm num_batches_tracked updates: one multi-tensor add
+        return out
 
     def load_state_dict(self, state_dict, strict: bool = True, **kw):
         out = super().load_state_dict(state_dict, strict=strict, **kw)

@@ -83,3 +83,17 @@ def test_graph_replay_dropout_mask_changes():
     assert not torch.equal(outs[0], outs[1]) and not torch.equal(outs[1], outs[2])
     for o in outs:
         assert 0.4 < float((o == 0).float().mean()) < 0.6
+
+
+def test_batch_counters_deferred_but_exact():
+    """num_batches_tracked is bumped by one multi-tensor add per forward (eager and replayed) and is exact when read."""
+    import torch
+    _, _, step, dp = _run(True, steps=7)
+    sd = dp.state_dict()
+    counts = {k: int(v) for k, v in sd.items() if k.endswith("num_batches_tracked")}
+    assert counts and set(counts.values()) == {7}, counts
+    bn = dp.module.encoder.bn1
+    dp.eval()
+    with torch.no_grad():
+        dp(torch.randn(2, 3, 64, 64, device="cuda").to(torch.bfloat16))
+    assert int(bn.num_batches_tracked) == 7            # eval forwards do not count
