@@ -26,8 +26,13 @@ class BasicConv2d(nn.Module):
         nn.init.trunc_normal_(self.conv.weight, mean=0.0, std=std, a=-2, b=2)
         self.bn = BatchNorm2d(cout, eps=0.001)
 
-    def forward(self, x):
-        return conv_bn_act(x, self.conv, self.bn, "relu")
+    def forward(self, x, grad_fork=None):
+        return conv_bn_act(x, self.conv, self.bn, "relu", grad_fork=grad_fork)
+
+
+def _acc(fk):
+    """grad_fork argument of a branch whose input gradient is ADDED into the one deposited by the block's last branch."""
+    return None if fk is None else (fk, "accumulate")
 
 
 def _cat(xs):
@@ -46,10 +51,13 @@ class InceptionA(nn.Module):
         self.branch_pool = BasicConv2d(cin, pool_features, 1)
 
     def forward(self, x):
-        b1 = self.branch1x1(x)
-        b5 = self.branch5x5_2(self.branch5x5_1(x))
-        b3 = self.branch3x3dbl_3(self.branch3x3dbl_2(self.branch3x3dbl_1(x)))
-        bp = self.branch_pool(ops.avg_pool2d(x, 3, 1, 1))
+        # the block input feeds four branches: the pooling branch (created last, so its backward runs first) deposits its
+        # input gradient, the three 1x1 convs add theirs into it with TMA reduce-add stores (ops.fork_n)
+        (x1, x2, x3, x4), fk = ops.fork_n(x, 4)
+        b1 = self.branch1x1(x1, _acc(fk))
+        b5 = self.branch5x5_2(self.branch5x5_1(x2, _acc(fk)))
+        b3 = self.branch3x3dbl_3(self.branch3x3dbl_2(self.branch3x3dbl_1(x3, _acc(fk))))
+        bp = self.branch_pool(ops.avg_pool2d(x4, 3, 1, 1, grad_fork=fk))
         return _cat([b1, b5, b3, bp])
 
 
@@ -62,9 +70,10 @@ class InceptionB(nn.Module):
         self.branch3x3dbl_3 = BasicConv2d(96, 96, 3, stride=2)
 
     def forward(self, x):
-        b3 = self.branch3x3(x)
-        bd = self.branch3x3dbl_3(self.branch3x3dbl_2(self.branch3x3dbl_1(x)))
-        return _cat([b3, bd, ops.max_pool2d(x, 3, 2)])
+        (x1, x2, x3), fk = ops.fork_n(x, 3)
+        b3 = self.branch3x3(x1, _acc(fk))
+        bd = self.branch3x3dbl_3(self.branch3x3dbl_2(self.branch3x3dbl_1(x2, _acc(fk))))
+        return _cat([b3, bd, ops.max_pool2d(x3, 3, 2, grad_fork=fk)])
 
 
 class InceptionC(nn.Module):
@@ -82,11 +91,12 @@ class InceptionC(nn.Module):
         self.branch_pool = BasicConv2d(cin, 192, 1)
 
     def forward(self, x):
-        b1 = self.branch1x1(x)
-        b7 = self.branch7x7_3(self.branch7x7_2(self.branch7x7_1(x)))
+        (x1, x2, x3, x4), fk = ops.fork_n(x, 4)
+        b1 = self.branch1x1(x1, _acc(fk))
+        b7 = self.branch7x7_3(self.branch7x7_2(self.branch7x7_1(x2, _acc(fk))))
         bd = self.branch7x7dbl_5(self.branch7x7dbl_4(self.branch7x7dbl_3(
-            self.branch7x7dbl_2(self.branch7x7dbl_1(x)))))
-        bp = self.branch_pool(ops.avg_pool2d(x, 3, 1, 1))
+            self.branch7x7dbl_2(self.branch7x7dbl_1(x3, _acc(fk))))))
+        bp = self.branch_pool(ops.avg_pool2d(x4, 3, 1, 1, grad_fork=fk))
         return _cat([b1, b7, bd, bp])
 
 
@@ -101,9 +111,10 @@ class InceptionD(nn.Module):
         self.branch7x7x3_4 = BasicConv2d(192, 192, 3, stride=2)
 
     def forward(self, x):
-        b3 = self.branch3x3_2(self.branch3x3_1(x))
-        b7 = self.branch7x7x3_4(self.branch7x7x3_3(self.branch7x7x3_2(self.branch7x7x3_1(x))))
-        return _cat([b3, b7, ops.max_pool2d(x, 3, 2)])
+        (x1, x2, x3), fk = ops.fork_n(x, 3)
+        b3 = self.branch3x3_2(self.branch3x3_1(x1, _acc(fk)))
+        b7 = self.branch7x7x3_4(self.branch7x7x3_3(self.branch7x7x3_2(self.branch7x7x3_1(x2, _acc(fk)))))
+        return _cat([b3, b7, ops.max_pool2d(x3, 3, 2, grad_fork=fk)])
 
 
 class InceptionE(nn.Module):
@@ -120,12 +131,15 @@ class InceptionE(nn.Module):
         self.branch_pool = BasicConv2d(cin, 192, 1)
 
     def forward(self, x):
-        b1 = self.branch1x1(x)
-        b3 = self.branch3x3_1(x)
-        b3 = _cat([self.branch3x3_2a(b3), self.branch3x3_2b(b3)])
-        bd = self.branch3x3dbl_2(self.branch3x3dbl_1(x))
-        bd = _cat([self.branch3x3dbl_3a(bd), self.branch3x3dbl_3b(bd)])
-        bp = self.branch_pool(ops.avg_pool2d(x, 3, 1, 1))
+        (x1, x2, x3, x4), fk = ops.fork_n(x, 4)
+        b1 = self.branch1x1(x1, _acc(fk))
+        b3 = self.branch3x3_1(x2, _acc(fk))
+        (b3a, b3b), fk3 = ops.fork_n(b3, 2)        # inner two-way forks: the second conv deposits, the first accumulates
+        b3 = _cat([self.branch3x3_2a(b3a, _acc(fk3)), self.branch3x3_2b(b3b, None if fk3 is None else (fk3, "deposit_dx"))])
+        bd = self.branch3x3dbl_2(self.branch3x3dbl_1(x3, _acc(fk)))
+        (bda, bdb), fkd = ops.fork_n(bd, 2)
+        bd = _cat([self.branch3x3dbl_3a(bda, _acc(fkd)), self.branch3x3dbl_3b(bdb, None if fkd is None else (fkd, "deposit_dx"))])
+        bp = self.branch_pool(ops.avg_pool2d(x4, 3, 1, 1, grad_fork=fk))
         return _cat([b1, b3, bd, bp])
 
 

@@ -40,6 +40,16 @@ def fork(x):
     return x, x, None
 
 
+def fork_n(x, n: int):
+    """n-way version of :func:`fork` for blocks whose input feeds several branches (inception).  Returns
+    ``(aliases, fork)``; the branch that is created last passes ``grad_fork=(fork, "deposit_dx")`` (or, for a pooling
+    op, ``grad_fork=fork``), the others ``(fork, "accumulate")``."""
+    if x.is_cuda and not _force_torch() and torch.is_grad_enabled() and x.requires_grad:
+        from . import native
+        return native.fork_n(x, n)
+    return [x] * n, None
+
+
 def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, padding=0, groups=1,
                 training=True, momentum=0.1, eps=1e-5, act="relu", residual=None, sync_group=False,
                 grad_fork=None):
@@ -112,17 +122,17 @@ def activation(x, act):
     return ref.activation(x, act)
 
 
-def max_pool2d(x, kernel_size, stride, padding=0, ceil_mode=False):
+def max_pool2d(x, kernel_size, stride, padding=0, ceil_mode=False, grad_fork=None):
     if use_native(x) and not ceil_mode:
         from . import native
-        return native.pool2d(x, kernel_size, stride, padding, mode="max")
+        return native.pool2d(x, kernel_size, stride, padding, mode="max", grad_fork=grad_fork)
     return ref.max_pool2d(x, kernel_size, stride, padding, ceil_mode)
 
 
-def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True):
+def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True, grad_fork=None):
     if use_native(x) and count_include_pad:
         from . import native
-        return native.pool2d(x, kernel_size, stride, padding, mode="avg")
+        return native.pool2d(x, kernel_size, stride, padding, mode="avg", grad_fork=grad_fork)
     return ref.avg_pool2d(x, kernel_size, stride, padding, count_include_pad)
 
 

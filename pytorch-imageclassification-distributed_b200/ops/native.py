@@ -291,22 +291,35 @@ class GradFork:
 
 class _ForkFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x):
-        return x.view_as(x), x.view_as(x)
+    def forward(ctx, x, n):
+        return tuple(x.view_as(x) for _ in range(n))
 
     @staticmethod
-    def backward(ctx, g1, g2):
-        if g1 is None or g2 is None:
-            return g1 if g2 is None else g2
-        if g1.data_ptr() == g2.data_ptr():
-            return g1                       # the dgrad already accumulated into the deposited tensor
-        return g1 + g2
+    def backward(ctx, *gs):
+        # branches whose dgrad accumulated into the deposited tensor all hand back that same tensor: count it once
+        uniq = {}
+        for g in gs:
+            if g is not None:
+                uniq.setdefault(g.data_ptr(), g)
+        vals = list(uniq.values())
+        if not vals:
+            return None, None
+        out = vals[0]
+        for g in vals[1:]:
+            out = out + g
+        return out, None
 
 
 def fork(x):
     """(x1, x2, fork): two autograd-distinct aliases of x plus the side channel that lets their gradients be fused."""
-    x1, x2 = _ForkFn.apply(x)
+    x1, x2 = _ForkFn.apply(x, 2)
     return x1, x2, GradFork()
+
+
+def fork_n(x, n: int):
+    """n autograd-distinct aliases of x + the side channel (inception blocks: one activation feeds 3-4 branches).  The
+    branch created LAST deposits its input gradient (its backward runs first), the others add theirs into it."""
+    return list(_ForkFn.apply(x, n)), GradFork()
 
 
 def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool, accumulate_into=None):
@@ -481,8 +494,7 @@ class _ConvBnAct(torch.autograd.Function):
         if fork_ is not None:
             if role == "deposit_dx" and dx is not None:
                 fork_.partner = dx
-            elif role == "accumulate":
-                fork_.partner = None
+            # (the deposited tensor stays registered: with more than two branches several dgrads add into it)
         return dx, dw, dgamma, dbeta, dres, None
 
 
@@ -740,7 +752,8 @@ def linear(x, w, b, act):
 # --------------------------------------------------------------------------- pooling
 class _Pool2d(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, k, s, p, mode):
+    def forward(ctx, x, k, s, p, mode, fork_=None):
+        ctx.fork = fork_
         x = nhwc(x)
         N, C, H, W = x.shape
         kh, kw = _pair(k)
@@ -758,13 +771,15 @@ class _Pool2d(torch.autograd.Function):
         arg = ctx.saved_tensors[0] if mode == 0 else None
         dx = empty_nhwc(N, C, H, W, dy.device)
         call("picd_pool_bwd", nhwc(dy), arg, dx, N, H, W, C, OH, OW, kh, kw, s, p, mode)
-        return dx, None, None, None, None
+        if ctx.fork is not None:
+            ctx.fork.partner = dx            # sibling branches' dgrads add into this tensor (see fork_n)
+        return dx, None, None, None, None, None
 
 
-def pool2d(x, k, s, p, mode):
+def pool2d(x, k, s, p, mode, grad_fork=None):
     if x.shape[1] % 8 != 0:
         return (ref.max_pool2d if mode == "max" else ref.avg_pool2d)(x, k, s, p)
-    return _Pool2d.apply(x, k, s, p, 0 if mode == "max" else 1)
+    return _Pool2d.apply(x, k, s, p, 0 if mode == "max" else 1, grad_fork)
 
 
 class _GlobalAvgPool(torch.autograd.Function):
