@@ -833,6 +833,46 @@ __global__ void __launch_bounds__(256) top1_hits_kernel(const T* __restrict__ lo
     out[b] = (arg == static_cast<int>(labels[b])) ? 1 : 0;
 }
 
+// Specialisation for the stems of the CNN backbones (3 input channels, stride 2 -> 12 packed channels padded to 16): one
+// thread = one packed cell, all index arithmetic compile-time or 32-bit (the generic kernel spends ~80 integer instructions
+// per element on run-time div/mod by C and s).
+template <typename T>
+__global__ void __launch_bounds__(256) pack_s2d_c3s2_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ out, int H, int W,
+                                                            int Hp, int Wp, int pad_h, int pad_w, int normalize) {
+    const int n = blockIdx.x / Hp, ii = blockIdx.x - n * Hp;
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, inv_std[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
+    const T* xn = x + static_cast<size_t>(n) * H * W * 3;
+    __nv_bfloat16* orow = out + (static_cast<size_t>(n) * Hp + ii) * Wp * 16;
+    for (int j = threadIdx.x; j < Wp; j += blockDim.x) {
+        float f[16];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const int ih = ii * 2 + a - pad_h;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const int iw = j * 2 + b - pad_w;
+                const bool ok = ih >= 0 && ih < H && iw >= 0 && iw < W;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float v = 0.f;
+                    if (ok) {
+                        v = static_cast<float>(xn[(static_cast<size_t>(ih) * W + iw) * 3 + c]);
+                        if (normalize) v = (v * (1.f / 255.f) - mean[c]) * inv_std[c];
+                    }
+                    f[(a * 2 + b) * 3 + c] = v;
+                }
+            }
+        }
+        f[12] = f[13] = f[14] = f[15] = 0.f;
+        float lo[8], hi[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { lo[k] = f[k]; hi[k] = f[8 + k]; }
+        uint4* dst = reinterpret_cast<uint4*>(orow + static_cast<size_t>(j) * 16);
+        dst[0] = pack8(lo);
+        dst[1] = pack8(hi);
+    }
+}
+
 }  // namespace picd
 
 using namespace picd;
@@ -1040,6 +1080,16 @@ extern "C" int picd_pack_s2d(const void* x, void* out, int N, int H, int W, int 
                              int pad_w, int src_u8, cudaStream_t st) {
     PICD_REQUIRE(Cp % 8 == 0, "pack_s2d: packed channel count %d must be a multiple of 8", Cp);
     const long long total = 1LL * N * Hp * Wp * (Cp / 8);
+    if (C == 3 && s == 2 && Cp == 16) {
+        if (src_u8)
+            pack_s2d_c3s2_kernel<uint8_t><<<N * Hp, 128, 0, st>>>(static_cast<const uint8_t*>(x), static_cast<bf16*>(out), H, W, Hp, Wp,
+                                                                  pad_h, pad_w, 1);
+        else
+            pack_s2d_c3s2_kernel<bf16><<<N * Hp, 128, 0, st>>>(static_cast<const bf16*>(x), static_cast<bf16*>(out), H, W, Hp, Wp, pad_h,
+                                                               pad_w, 0);
+        PICD_LAUNCH_CHECK();
+        return 0;
+    }
     if (src_u8)
         pack_s2d_kernel<uint8_t><<<grid_for(total), 256, 0, st>>>(static_cast<const uint8_t*>(x), static_cast<bf16*>(out), N, H, W, C,
                                                                   Hp, Wp, Cp, s, pad_h, pad_w, 1);
