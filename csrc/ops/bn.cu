@@ -176,21 +176,69 @@ __device__ __forceinline__ void load8f(const float* p, float (&o)[8]) {
 }
 
 // TACT >= 0 fixes the activation at compile time (the generic apply_act switch drags exp/erf paths and ~50 registers along)
+// Optional fused finalize: when fin.sums != nullptr every block first turns the (replicated) batch sums of ITS channel slab
+// into scale / shift in shared memory -- 32 loads per thread -- and the blocks of the first row strip also publish scale,
+// shift, mean, invstd (the backward needs them) and update the running statistics.  That removes the separate
+// bn_finalize launch and one kernel-to-kernel dependency per BatchNorm layer.
+struct BnFinalizeArgs {
+    const float* sums;          // [replicas][2][C] or nullptr (then scale / shift are read from global memory)
+    int replicas;
+    float count, momentum, eps;
+    const float* gamma;
+    const float* beta;
+    float* running_mean;
+    float* running_var;
+    float* mean_out;
+    float* invstd_out;
+};
+
 template <int U, int MINB, int TACT>
 __global__ void __launch_bounds__(256, MINB) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
-                                                       const float* __restrict__ scale,
-                                                       const float* __restrict__ shift,
+                                                       float* __restrict__ scale,
+                                                       float* __restrict__ shift,
                                                        const __nv_bfloat16* __restrict__ residual, int act,
                                                        __nv_bfloat16* __restrict__ out, long long P, int C,
                                                        int tx_count, int ty_count, int rows_per_block,
-                                                       uint8_t* __restrict__ relu_mask) {
+                                                       uint8_t* __restrict__ relu_mask, const BnFinalizeArgs fin) {
     const int vecs = C >> 3;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
+    __shared__ float s_coef[2][2048];         // scale / shift of the block's channel slab (tx_count * 8 <= 2048 channels)
+    if (fin.sums != nullptr) {
+        for (int cl = threadIdx.x; cl < tx_count * 8; cl += blockDim.x) {
+            const int c = blockIdx.x * tx_count * 8 + cl;
+            if (c >= C) break;
+            const float mean = fold_replicas(fin.sums, c, 2 * C, fin.replicas) / fin.count;
+            float var = fold_replicas(fin.sums, C + c, 2 * C, fin.replicas) / fin.count - mean * mean;
+            var = fmaxf(var, 0.f);
+            const float invstd = rsqrtf(var + fin.eps);
+            const float scv = fin.gamma[c] * invstd;
+            const float shv = fin.beta[c] - mean * scv;
+            s_coef[0][cl] = scv;
+            s_coef[1][cl] = shv;
+            if (blockIdx.y == 0) {
+                scale[c] = scv;
+                shift[c] = shv;
+                fin.mean_out[c] = mean;
+                fin.invstd_out[c] = invstd;
+                if (fin.running_mean != nullptr) {
+                    const float unbiased = fin.count > 1.f ? var * (fin.count / (fin.count - 1.f)) : var;
+                    fin.running_mean[c] = (1.f - fin.momentum) * fin.running_mean[c] + fin.momentum * mean;
+                    fin.running_var[c] = (1.f - fin.momentum) * fin.running_var[c] + fin.momentum * unbiased;
+                }
+            }
+        }
+        __syncthreads();
+    }
     if (ty >= ty_count || cv >= vecs) return;
     float sc[8], sh[8];
-    load8f(scale + cv * 8, sc);
-    load8f(shift + cv * 8, sh);
+    if (fin.sums != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { sc[k] = s_coef[0][tx * 8 + k]; sh[k] = s_coef[1][tx * 8 + k]; }
+    } else {
+        load8f(scale + cv * 8, sc);
+        load8f(shift + cv * 8, sh);
+    }
     const long long r0 = static_cast<long long>(blockIdx.y) * rows_per_block;
     long long r1 = r0 + rows_per_block;
     if (r1 > P) r1 = P;
@@ -453,13 +501,13 @@ extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const 
 }
 
 // relu_mask (optional, [P * C/8] bytes + one chunk of slack): bit k of byte v = output 8*v+k is positive.
-extern "C" int picd_bn_apply_mask(const void* y, const float* scale, const float* shift, const void* residual, int act,
-                                  void* out, void* relu_mask, long long P, int C, cudaStream_t stream) {
+static int bn_apply_impl(const void* y, float* scale, float* shift, const void* residual, int act, void* out,
+                         void* relu_mask, long long P, int C, const BnFinalizeArgs& fin, cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_apply: C=%d must be a multiple of 8", C);
     // The TMA-streamed forward apply measured SLOWER (2.5 TB/s) than this register-streaming kernel (4.8 TB/s) --
     // one input tensor gives the ring too little work per handshake -- so it is opt-in (PICD_BN_STREAM_APPLY=1).
     static const bool stream_apply = [] { const char* e = getenv("PICD_BN_STREAM_APPLY"); return e != nullptr && e[0] == '1'; }();
-    if (stream_apply && use_stream_kernels() && relu_mask == nullptr) {
+    if (stream_apply && use_stream_kernels() && relu_mask == nullptr && fin.sums == nullptr) {
         const int rc = bn_stream_apply(y, scale, shift, residual, act, out, P, C, stream);
         if (rc >= 0) return rc;
     }
@@ -469,7 +517,7 @@ extern "C" int picd_bn_apply_mask(const void* y, const float* scale, const float
     bn_apply_kernel<U, MINB, A><<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(                                      \
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,       \
         static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block,                           \
-        static_cast<uint8_t*>(relu_mask))
+        static_cast<uint8_t*>(relu_mask), fin)
 #define PICD_BN_APPLY_LAUNCH(U, MINB)                                                                              \
     do {                                                                                                            \
         if (act == ACT_RELU) PICD_BN_APPLY_LAUNCH_A(U, MINB, ACT_RELU);                                             \
@@ -488,9 +536,27 @@ extern "C" int picd_bn_apply_mask(const void* y, const float* scale, const float
     PICD_LAUNCH_CHECK();
     return 0;
 }
+extern "C" int picd_bn_apply_mask(const void* y, const float* scale, const float* shift, const void* residual, int act,
+                                  void* out, void* relu_mask, long long P, int C, cudaStream_t stream) {
+    BnFinalizeArgs fin{};
+    return bn_apply_impl(y, const_cast<float*>(scale), const_cast<float*>(shift), residual, act, out, relu_mask, P, C, fin, stream);
+}
 extern "C" int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act,
                              void* out, long long P, int C, cudaStream_t stream) {
     return picd_bn_apply_mask(y, scale, shift, residual, act, out, nullptr, P, C, stream);
+}
+// picd_bn_finalize + picd_bn_apply_mask in ONE launch: sums = `replicas` copies of [sum(C), sumsq(C)] over `count` elements
+// per channel; scale / shift / mean / invstd are outputs (kept for the backward), running statistics are updated.
+extern "C" int picd_bn_finalize_apply(const void* y, const float* sums, int replicas, float count, const float* gamma,
+                                      const float* beta, float* running_mean, float* running_var, float momentum, float eps,
+                                      float* scale, float* shift, float* mean, float* invstd, const void* residual, int act,
+                                      void* out, void* relu_mask, long long P, int C, cudaStream_t stream) {
+    PICD_REQUIRE(sums != nullptr, "bn_finalize_apply: sums must not be null");
+    BnFinalizeArgs fin{};
+    fin.sums = sums; fin.replicas = replicas; fin.count = count; fin.momentum = momentum; fin.eps = eps;
+    fin.gamma = gamma; fin.beta = beta; fin.running_mean = running_mean; fin.running_var = running_var;
+    fin.mean_out = mean; fin.invstd_out = invstd;
+    return bn_apply_impl(y, scale, shift, residual, act, out, relu_mask, P, C, fin, stream);
 }
 
 // relu_mask (optional): the bit mask written by picd_bn_apply_mask; the streamed kernels read it instead of z.

@@ -86,6 +86,12 @@ int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const v
                            const float* shift, const float* mean, const float* invstd, int act, const float* sums,
                            int sums_replicas, float inv_count, const float* param_sums, int param_replicas, float* dgamma,
                            float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream);
+/* picd_bn_finalize + picd_bn_apply_mask in one launch (per-replica BatchNorm in training): scale / shift / mean / invstd
+ * are OUTPUTS (the backward entry points take them), running statistics are updated in place. */
+int picd_bn_finalize_apply(const void* y, const float* sums, int replicas, float count, const float* gamma, const float* beta,
+                           float* running_mean, float* running_var, float momentum, float eps, float* scale, float* shift,
+                           float* mean, float* invstd, const void* residual, int act, void* out, void* relu_mask, long long P,
+                           int C, cudaStream_t stream);
 int picd_bn_apply(const void* y, const float* scale, const float* shift, const void* residual, int act, void* out,
                   long long P, int C, cudaStream_t stream);
 int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, const float* scale, const float* shift,

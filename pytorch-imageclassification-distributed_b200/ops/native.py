@@ -45,6 +45,7 @@ _SIG = {
     "picd_bn_eval_coeffs": "ppppfppip",
     "picd_bn_apply": "ppppiplip",
     "picd_bn_apply_mask": "ppppipplip",
+    "picd_bn_finalize_apply": "ppifppppffpppppipplip",
     "picd_bn_bwd_reduce_mask": "ppppppppiplip",
     "picd_bn_bwd_apply_mask": "ppppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_reduce": "pppppppiplip",
@@ -413,13 +414,21 @@ class _BNCfg:
     __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group", "fork", "fork_role")
 
 
+# Opt-in: let the apply kernel compute scale / shift from the batch sums itself (picd_bn_finalize_apply).  Measured SLOWER
+# (+0.3 ms per ResNet-50 step): the prologue runs in each of the ~1000 blocks of every apply launch, which costs more than
+# the one tiny bn_finalize kernel it saves.
+_FUSE_FINALIZE = os.environ.get("PICD_BN_FUSE_FINALIZE", "0") == "1"
 _USE_RELU_MASK = os.environ.get("PICD_BN_MASK", "1") != "0"      # A/B switch: 0 = backward re-reads z for the ReLU sign
 
 
 def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
     C = gamma.numel()
     P = y.numel() // C
-    if cfg.training:
+    fuse_finalize = cfg.training and _sync_world(cfg.sync_group) <= 1 and _FUSE_FINALIZE
+    if fuse_finalize:          # per-replica BN: the apply kernel turns the batch sums into coefficients itself
+        coef = torch.empty(4, C, dtype=torch.float32, device=y.device)
+        total = float(count)
+    elif cfg.training:
         coef, total = _bn_forward_coeffs(sums, count, gamma, beta, cfg.rm, cfg.rv, cfg.momentum, cfg.eps,
                                          cfg.sync_group)
     else:
@@ -433,7 +442,11 @@ def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
     ctx.relu_mask = None
     if res is not None and cfg.act == "relu" and cfg.training and _USE_RELU_MASK:    # (grad mode is off inside Function.forward)
         ctx.relu_mask = torch.empty(P * (C // 8) + 4096, dtype=torch.uint8, device=y.device)
-    call("picd_bn_apply_mask", y, coef[0], coef[1], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
+    if fuse_finalize:
+        call("picd_bn_finalize_apply", y, sums, sums.numel() // (2 * C), total, gamma, beta, cfg.rm, cfg.rv, float(cfg.momentum),
+             float(cfg.eps), coef[0], coef[1], coef[2], coef[3], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
+    else:
+        call("picd_bn_apply_mask", y, coef[0], coef[1], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
     ctx.bn_total, ctx.bn_act, ctx.bn_training = total, cfg.act, cfg.training
     ctx.bn_sync, ctx.has_res = cfg.sync_group, residual is not None
     return z, coef
