@@ -468,8 +468,9 @@ extern "C" int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int repli
     return 0;
 }
 
-// NVLS probe: does the device expose NVSwitch multicast objects (cuMulticastCreate & friends)?  picd_b200 does not use
-// them yet (one-/two-shot peer loads/stores only); the probe lets hosts report it.  Returns 1 / 0, or -1 if unknown.
+// NVLS probe: does the device expose NVSwitch multicast objects (cuMulticastCreate & friends)?  The multicast MAPPING used by
+// mode 3 / 4 of the bucket kernel is created by the host (picd_comm_set_multicast); this only reports the device capability.
+// Returns 1 / 0, or -1 if unknown.
 extern "C" int picd_nvls_supported() {
     typedef CUresult (*GetAttrFn)(int*, CUdevice_attribute, CUdevice);
     void* fn = nullptr;

@@ -376,8 +376,9 @@ class NativeReducer:
 
 
 def nvls_supported() -> int:
-    """1 / 0 / -1: whether the device exposes NVSwitch multicast (NVLS).  Informational: the engine uses one-/two-shot
-    peer loads and stores; an NVLS variant (multimem.ld_reduce / multimem.st) is future work."""
+    """1 / 0 / -1: whether the device exposes NVSwitch multicast (NVLS).  Informational: whether the engine actually
+    uses its NVLS kernel variant depends on a multicast MAPPING of the slab being available (``Comm.has_nvls``, obtained
+    through torch's symmetric-memory allocator in ``SymmetricSlab._try_symmetric_alloc``)."""
     lib = require_lib()
     lib.picd_nvls_supported.restype = ctypes.c_int
     return int(lib.picd_nvls_supported())
