@@ -1,7 +1,7 @@
 // NVLink peer-memory communication fused with compute (BASELINE.json north-star).
 //
-// Every rank owns one cudaMalloc slab (gradient arena | fp32 masters | bf16 shadows | exchange slots | flags)
-// that is exported with CUDA IPC and mapped by all peers of the node.  Kernels then dereference peer pointers
+// Every rank owns one slab (gradient arena | fp32 masters | bf16 shadows | exchange slots | flags) that all peers of the node
+// map: cudaMalloc + CUDA IPC, or torch's symmetric-memory allocator when available (which adds an NVSwitch multicast view).  Kernels then dereference peer pointers
 // directly; NVSwitch gives every pair full bandwidth, so there is no ring and no NCCL call on the hot path.
 //
 //   fused_allreduce_update_kernel  (one launch per gradient bucket, side stream, overlapped with backward)
@@ -10,6 +10,9 @@
 //                     scales by 1/W, runs SGD-momentum / Adam / AdamW on the fp32 master (optimizer state is
 //                     touched only by the slice owner), and PUSHES the new fp32 master + bf16 shadow to all peers
 //       one-shot    : every rank sums the whole (small, latency-bound) bucket and updates its own replica
+//       NVLS        : two-shot through the NVSwitch multicast mapping of the slab (when the host provides one): the slice
+//                     owner pulls the in-switch reduced gradients with multimem.ld_reduce and broadcasts master + shadow with
+//                     multimem.st (mode 3), or keeps the unicast pushes (mode 4, faster above ~512 MB)
 //       barrier-out : once every peer has read my gradients and pushed my weights, re-zero my gradient bucket
 //   bn_finalize_sync_kernel        SyncBatchNorm statistics: publish (sum, sumsq, count), wait, sum all peers'
 //                                   slots in rank order, finalize scale/shift/running stats -- one launch, no NCCL
