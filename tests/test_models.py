@@ -107,3 +107,23 @@ def test_graphed_train_step_falls_back_to_eager_on_cpu():
     assert step.graph is None and step.replays == 0 and dp.step_index == 3
     assert not step(x, y).requires_grad and not step.outputs.requires_grad
     assert not torch.equal(before, dp.arena.master) and all(l == l for l in losses)
+
+
+def test_cpu_fallbacks_of_small_ops():
+    """concat_channels / top1_hits / fork_n run through the torch path on CPU tensors with the same semantics."""
+    import torch
+    from picd_b200 import ops
+    from picd_b200.utils import Accuracy
+    a = torch.randn(2, 8, 5, 5).contiguous(memory_format=torch.channels_last)
+    b = torch.randn(2, 16, 5, 5).contiguous(memory_format=torch.channels_last)
+    c = ops.concat_channels([a, b])
+    assert torch.equal(c, torch.cat([a, b], 1)) and c.is_contiguous(memory_format=torch.channels_last)
+    logits = torch.tensor([[0.1, 0.9, 0.0], [2.0, 1.0, 0.0], [0.0, 0.0, 0.5]])
+    labels = torch.tensor([1, 1, 2])
+    hits = ops.top1_hits(logits, labels)
+    assert hits.tolist() == [1, 0, 1] and hits.dtype == torch.int64 and torch.equal(Accuracy(logits, labels), hits)
+    x = torch.randn(1, 8, 4, 4, requires_grad=True)
+    parts, fk = ops.fork_n(x, 3)
+    assert fk is None and len(parts) == 3 and all(p is x for p in parts)
+    x1, x2, fk2 = ops.fork(x)
+    assert fk2 is None and x1 is x and x2 is x
