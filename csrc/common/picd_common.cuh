@@ -128,15 +128,6 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uin
         "r"(c3)
         : "memory");
 }
-// Multicast variants: the box lands at the same shared-memory offset of every CTA in `mask`, and each destination CTA's
-// mbarrier (same offset) receives the complete_tx.
-__device__ __forceinline__ void tma_load_3d_mc(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
-                                               uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(mask)
-        : "memory");
-}
 
 // ---- warp-convergent issue ----------------------------------------------------------------
 // The *_warp variants below are called by ALL 32 lanes of a converged warp; `elect.sync` inside the asm block lets one
@@ -178,18 +169,6 @@ __device__ __forceinline__ void tma_load_4d_warp(void* dst, const CUtensorMap* m
         "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n\t}"
         ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
         "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_3d_mc_warp(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
-                                                    uint32_t mask) {
-    // the CTA mask travels as a 32-bit operand and is narrowed inside the block (a 16-bit "h" operand in a loop made
-    // ptxas recycle a live uniform register for it)
-    asm volatile(
-        "{\n\t.reg .pred e;\n\t.reg .b16 m;\n\t"
-        "cvt.u16.u32 m, %6;\n\t"
-        "elect.sync _|e, 0xffffffff;\n\t"
-        "@e cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], m;\n\t}"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(mask)
         : "memory");
 }
 
