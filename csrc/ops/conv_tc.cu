@@ -61,7 +61,7 @@ struct ConvGemmParams {
     const float* bias;    // [Cout] or nullptr
     int act;
     int half_w;           // columns drained per staging pass: 128 (deep operand ring) or 256 (short-K tiles, one pass)
-    int cluster;          // 1: launched as clusters of 2 with multicast B tiles (set by the host launcher)
+    int cluster;          // 1: launched as CTA pairs (clusters of 2, cta_group::2): each CTA loads its own half of every B tile
     int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
     // halo mode (3x3, stride 1): one activation box with a one-row halo above and below is loaded per (k-chunk, dw) and
     // the three dh taps read it through descriptors shifted by whole pixel rows -> 3 instead of 9 A loads per k-chunk.
