@@ -162,7 +162,7 @@ def run(args, ref_dir, timed_region, published_baseline, cfg):
                        "per_gpu_batch": B, "image_size": S, "seq_len": None,
                        "optimizer": (f"sgd-momentum lr={cfg['lr']} wd={cfg['weight_decay']}" if args.optimizer == "sgd"
                                      else f"{args.optimizer} lr=0.001 wd={cfg['weight_decay']}"), "sync_bn": args.sync_bn,
-                       "parallelism": f"ddp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": None, "note": note}))
     dist.barrier(device_ids=[local_rank])
     dist.destroy_process_group()

@@ -97,7 +97,6 @@ def run_b200(args):
     from picd_b200.parallel import dist as D
     from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
 
-    os.environ["NCCL_DEBUG"] = os.environ.get("PICD_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout (one JSON line)
     local_rank = D.init_distributed("b200", args.local_rank)
     device = torch.device("cuda", torch.cuda.current_device())
     rank, world = D.get_rank(), D.get_world_size()
@@ -154,6 +153,22 @@ def run_b200(args):
                "h2d_bytes_per_step": host_loader.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e / args.steps}
 
+    # replica identity (what DDP guarantees, train.py:128), checked OUTSIDE the timed regions: every rank hashes its fp32
+    # masters (BN running statistics are rank-local between two forwards unless SyncBN is on, exactly as under DDP's
+    # per-forward buffer broadcast) and the hashes are compared across ranks
+    replicas_identical = None
+    if world > 1:
+        import hashlib
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        h = hashlib.sha1(dp.arena.master.detach().cpu().numpy().tobytes())
+        if args.sync_bn:
+            for b in dp.module.buffers():
+                h.update(b.detach().cpu().numpy().tobytes())
+        box = [None] * world
+        dist.all_gather_object(box, h.hexdigest())
+        replicas_identical = all(v == box[0] for v in box)
+
     if rank == 0:
         pub = published_baseline()
         print(json.dumps({
@@ -165,9 +180,9 @@ def run_b200(args):
                        "per_gpu_batch": args.batch, "image_size": args.image_size, "seq_len": None,
                        "optimizer": (f"sgd-momentum lr={LR} wd={WEIGHT_DECAY}" if args.optimizer == "sgd"
                                      else f"{args.optimizer} lr=0.001 wd={WEIGHT_DECAY}"), "sync_bn": args.sync_bn,
-                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)",
-                       "cuda_graph": bool(step.graph is not None)},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss}))
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (>1 GB activations per step)"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss,
+            "cuda_graph": bool(step.graph is not None), "replicas_identical": replicas_identical}))
     D.barrier()
     D.shutdown()
 

@@ -96,7 +96,9 @@ def check_sync_bn(device):
     # a slab (and therefore a communicator) exists once any model is wrapped
     holder = FusedDataParallel(torch.nn.Linear(8, 8).to(device), OptimizerSpec("sgd", lr=0.0))
     ok = True
-    for (N, C, H) in [(4, 64, 8), (2, 256, 7), (3, 2048, 3)]:
+    # the last case gives every rank a DIFFERENT batch size (a ragged last batch through a non-padding loader): the global
+    # element count then has to come from the exchange, forward and backward (torch/nn/modules/_functions.py:59-62,170-179)
+    for (N, C, H) in [(4, 64, 8), (2, 256, 7), (3, 2048, 3), (2 + rank, 128, 6)]:
         g = torch.Generator().manual_seed(7 + rank)
         x = (torch.randn(N, C, H, H, generator=g) * (1 + rank) + 0.2 * rank).to(device)
         xb = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
@@ -150,11 +152,57 @@ def check_training(device):
         gathered = [torch.empty_like(flat) for _ in range(world)]
         dist.all_gather(gathered, flat)
         identical = all(torch.equal(gathered[0], t) for t in gathered)
-        good = identical and all(l == l and l < 50 for l in losses)
-        emit({"test": f"resnet18_train[sync_bn={sync}]", "losses": losses, "replicas_identical": identical, "ok": good})
+        # BN running statistics: rank 0's copy is pushed to every peer by the step's last bucket kernel (DDP's per-forward
+        # buffer broadcast); with SyncBN they are identical by construction
+        bufs = dp._flat_buffers.clone()
+        bg = [torch.empty_like(bufs) for _ in range(world)]
+        dist.all_gather(bg, bufs)
+        bufs_identical = all(torch.equal(bg[0], t) for t in bg) and bool(bufs.abs().sum() > 0)
+        good = identical and bufs_identical and all(l == l and l < 50 for l in losses)
+        emit({"test": f"resnet18_train[sync_bn={sync}]", "losses": losses, "replicas_identical": identical,
+              "buffers_identical": bufs_identical, "ok": good})
         ok &= good
         del dp
     return ok
+
+
+def check_optimizer_checkpoint(device):
+    """Save at step k, reload into a FRESH engine, continue: must equal the uninterrupted run bit for bit.  Two-shot buckets
+    keep the AdamW moments sharded by slice owner, so this only works if state_dict() assembles the owners' slices."""
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank, world = dist.get_rank(), dist.get_world_size()
+
+    def build():
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.ReLU(), torch.nn.Linear(512, 1024),
+                                  torch.nn.ReLU(), torch.nn.Linear(1024, 8)).to(device)
+        return FusedDataParallel(net, OptimizerSpec(kind="adamw", lr=1e-3, weight_decay=0.01), first_bucket_bytes=64 << 10,
+                                 bucket_cap_bytes=1 << 20, comm="two_shot")
+
+    def steps(dp, lo, hi):
+        for it in range(lo, hi):
+            g = torch.Generator(device="cpu").manual_seed(100 * it + rank)
+            dp(torch.randn(32, 256, generator=g).to(device)).square().mean().backward()
+            dp.optimizer.step()
+        torch.cuda.synchronize()
+
+    a = build()
+    steps(a, 0, 3)
+    weights = {k: v.detach().clone() for k, v in a.state_dict().items()}
+    opt = a.optimizer.state_dict()                         # collective
+    steps(a, 3, 6)
+    want = a.arena.master.clone()
+    del a
+    b = build()
+    b.load_state_dict(weights)
+    b.optimizer.load_state_dict(opt)
+    steps(b, 3, 6)
+    same = all_ok(bool(torch.equal(b.arena.master, want)), device)
+    nz = [float(t.abs().sum()) > 0 for t in opt["state"]]
+    emit({"test": "optimizer_checkpoint[two_shot,adamw]", "resumed_equals_uninterrupted": same, "state_nonzero": nz,
+          "ok": same and all(nz)})
+    del b
+    return same and all(nz)
 
 
 def check_graph_training(device):
@@ -186,6 +234,10 @@ def check_graph_training(device):
             gathered = [torch.empty_like(flat) for _ in range(world)]
             dist.all_gather(gathered, flat)
             identical = all(torch.equal(gathered[0], t) for t in gathered)
+            bufs = dp._flat_buffers.clone()
+            bg = [torch.empty_like(bufs) for _ in range(world)]
+            dist.all_gather(bg, bufs)
+            identical = identical and all(torch.equal(bg[0], t) for t in bg)      # running statistics follow rank 0's
             curves[graph] = (losses, identical, step.replays)
             del dp, step
         (le, ie, _), (lg, ig, replays) = curves[False], curves[True]
@@ -279,6 +331,7 @@ def main():
             ok &= check_fused_update(device, mode)
         ok &= check_sync_bn(device)
         ok &= check_training(device)
+        ok &= check_optimizer_checkpoint(device)
         ok &= check_graph_training(device)
     if args.sweep:
         sweep(device)

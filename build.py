@@ -21,7 +21,6 @@ OUT = os.path.join(PKG, "lib", "libpicd_b200.so")
 OBJ_DIR = os.path.join(ROOT, "build", "obj")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"]
 
 
@@ -40,7 +39,6 @@ def _compile(src: str, obj: str, verbose: bool) -> None:
     if src.endswith(".cpp"):
         cmd = [NVCC, "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-x", "c++", "-c", src, "-o", obj]
     if verbose:
-        cmd.insert(-4, "-Xptxas") if False else None
         print(" ".join(cmd), flush=True)
     subprocess.run(cmd, check=True)
 

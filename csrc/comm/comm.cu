@@ -31,6 +31,7 @@ struct PeerTable {
     __nv_bfloat16* shadow[MAX_PEERS];
     float* xchg[MAX_PEERS];          // exchange slots for small collectives
     unsigned* flags[MAX_PEERS];
+    float* bufs[MAX_PEERS];          // module buffers (BatchNorm running statistics) kept identical to rank 0's, or nullptr
     // NVSwitch multicast (NVLS) views of the same regions, or nullptr: a multimem.ld_reduce on mc_grad returns the sum over all
     // ranks computed inside the switch, a multimem.st on mc_master / mc_shadow lands in every rank's copy
     float* mc_grad;
@@ -75,14 +76,25 @@ __device__ __forceinline__ void multimem_st_b64(void* mc, const uint2& v) {     
                  : "memory");
 }
 
-// Spin until every peer's flag word (in MY flag array) has reached `epoch`; bounded so a lost peer traps
-// instead of hanging the GPU forever.
+// Spin until every peer's flag word (in MY flag array) has reached `epoch`; bounded so a lost peer traps instead of hanging
+// the GPU forever.  The bound (nanoseconds of %globaltimer) comes from the host: PICD_FLAG_TIMEOUT_S, default 600 s -- the
+// same order as the process-group timeout, so a rank that is merely slow (first batch of an epoch, a filesystem stall, a
+// debugger) does not take its peers' contexts down.
+__device__ long long g_flag_timeout_ns = 600LL * 1000000000LL;
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ void wait_flags(const unsigned* my_flags, int slot, int W, unsigned epoch) {
     if (threadIdx.x < W) {
         const unsigned* f = my_flags + slot * MAX_PEERS + threadIdx.x;
-        const long long t0 = clock64();
-        while (static_cast<int>(ld_acquire_sys(f) - epoch) < 0) {
-            if (clock64() - t0 > 40000000000LL) __trap();     // ~20 s
+        if (static_cast<int>(ld_acquire_sys(f) - epoch) < 0) {
+            const unsigned long long t0 = globaltimer_ns();
+            const unsigned long long budget = static_cast<unsigned long long>(g_flag_timeout_ns);
+            while (static_cast<int>(ld_acquire_sys(f) - epoch) < 0) {
+                if (globaltimer_ns() - t0 > budget) __trap();
+            }
         }
     }
     __syncthreads();
@@ -118,7 +130,7 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
                                                                      float* __restrict__ state1, OptArgs opt,
                                                                      int slot_in, int slot_out, unsigned epoch,
                                                                      unsigned* block_counter,
-                                                                     const float* __restrict__ dyn) {
+                                                                     const float* __restrict__ dyn, long long bcast_n) {
     if (dyn != nullptr) {
         // step-varying scalars come from device memory so that a captured CUDA graph can be replayed step after step:
         // (lr, 1 - beta1^t, 1 - beta2^t, flag epoch as raw bits), rewritten by the host before each replay
@@ -197,13 +209,30 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
     }
     if (mode == 0) return;
 
+    // DDP's per-forward buffer broadcast (torch/nn/parallel/distributed.py:2214-2257) without a collective
+    // call: the step's LAST bucket carries it.  Past the barrier-in every rank has finished this step's forward, so rank 0's
+    // running statistics are final and nobody touches theirs before the next forward; rank 0 pushes its copy into every
+    // peer's slab, and the barrier-out below publishes it.
+    if (bcast_n > 0 && rank == 0) {
+        const float* src = pt.bufs[0];
+        for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < (bcast_n >> 2); v += stride) {
+            const float4 b = *reinterpret_cast<const float4*>(src + (v << 2));
+#pragma unroll
+            for (int p = 1; p < MAX_PEERS; ++p)
+                if (p < W) *reinterpret_cast<float4*>(pt.bufs[p] + (v << 2)) = b;
+        }
+    }
+
     // barrier-out: the last block of this grid tells the peers that this rank is done reading and pushing
     __shared__ unsigned s_last;
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        // self-resetting ticket: launches of one bucket are stream-ordered, so the counter is 0 whenever a grid starts, for
+        // any grid size (the calibration sweep reuses a bucket with different sizes and modes)
         const unsigned old = atomicAdd(block_counter, 1u);
-        s_last = ((old + 1u) % gridDim.x == 0u) ? 1u : 0u;
+        s_last = (old + 1u == gridDim.x) ? 1u : 0u;
+        if (s_last) atomicExch(block_counter, 0u);
     }
     __syncthreads();
     if (s_last) signal_peers(pt, slot_out, rank, W, epoch);
@@ -294,6 +323,7 @@ struct CommCtx {
     PeerTable pt;
     int rank, world;
     unsigned* counters;     // per-bucket block counters (device)
+    long long bufs_n;       // floats in each rank's module-buffer region (0 = none registered)
 };
 
 }  // namespace picd
@@ -344,6 +374,7 @@ extern "C" int picd_comm_create(int rank, int world, void* const* grad, void* co
     }
     c->rank = rank;
     c->world = world;
+    c->bufs_n = 0;
     PICD_CUDA(cudaMalloc(&c->counters, sizeof(unsigned) * (num_buckets + 1)));
     PICD_CUDA(cudaMemset(c->counters, 0, sizeof(unsigned) * (num_buckets + 1)));
     *ctx_out = c;
@@ -355,6 +386,23 @@ extern "C" int picd_comm_set_multicast(void* ctx, void* mc_grad, void* mc_master
     c->pt.mc_grad = static_cast<float*>(mc_grad);
     c->pt.mc_master = static_cast<float*>(mc_master);
     c->pt.mc_shadow = static_cast<__nv_bfloat16*>(mc_shadow);
+    return 0;
+}
+// Registers the per-rank module-buffer regions (n floats each, a multiple of 4, inside the peer-mapped slabs): a bucket launch
+// with bcast_buffers != 0 then copies rank 0's region into every peer's.
+extern "C" int picd_comm_set_buffers(void* ctx, void* const* bufs, long long n) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(n >= 0 && (n % 4) == 0, "comm_set_buffers: n=%lld must be a non-negative multiple of 4", n);
+    for (int i = 0; i < c->world; ++i) c->pt.bufs[i] = static_cast<float*>(bufs[i]);
+    c->bufs_n = n;
+    return 0;
+}
+// Upper bound, in seconds, on how long a kernel spins for a peer's flag before it traps (default 600; env PICD_FLAG_TIMEOUT_S
+// is read by the Python engine and passed here).  Applies to every communicator of the current device.
+extern "C" int picd_comm_set_flag_timeout(double seconds) {
+    PICD_REQUIRE(seconds > 0.0, "comm_set_flag_timeout: %f s", seconds);
+    const long long ns = static_cast<long long>(seconds * 1e9);
+    PICD_CUDA(cudaMemcpyToSymbol(g_flag_timeout_ns, &ns, sizeof(ns)));
     return 0;
 }
 extern "C" int picd_comm_destroy(void* ctx) {
@@ -371,8 +419,10 @@ extern "C" int picd_comm_destroy(void* ctx) {
 static int fused_update_impl(void* ctx, int bucket, int mode, long long start, long long count,
                              float* state0, float* state1, int kind, float lr, float momentum,
                              float beta1, float beta2, float eps, float weight_decay, float bc1,
-                             float bc2, int nesterov, unsigned epoch, int blocks, const float* dyn, cudaStream_t stream) {
+                             float bc2, int nesterov, unsigned epoch, int blocks, const float* dyn, int bcast_buffers,
+                             cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(!bcast_buffers || c->bufs_n == 0 || c->pt.bufs[0] != nullptr, "fused_allreduce_update: buffers not registered");
     PICD_REQUIRE(count % (4 * c->world) == 0, "fused_allreduce_update: bucket of %lld elements does not split into "
                  "16-byte slices over %d ranks", count, c->world);
     if (c->world == 1) mode = 0;
@@ -400,7 +450,8 @@ static int fused_update_impl(void* ctx, int bucket, int mode, long long start, l
         if (blocks > max_resident) blocks = max_resident;
     }
     fused_allreduce_update_kernel<<<blocks, 512, 0, stream>>>(c->pt, c->rank, c->world, mode, start, count, state0, state1, o,
-                                                              2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket, dyn);
+                                                              2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket, dyn,
+                                                              (bcast_buffers && c->world > 1) ? c->bufs_n : 0LL);
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -408,9 +459,10 @@ static int fused_update_impl(void* ctx, int bucket, int mode, long long start, l
 extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count,
                                            float* state0, float* state1, int kind, float lr, float momentum,
                                            float beta1, float beta2, float eps, float weight_decay, float bc1,
-                                           float bc2, int nesterov, unsigned epoch, int blocks, cudaStream_t stream) {
+                                           float bc2, int nesterov, unsigned epoch, int blocks, int bcast_buffers,
+                                           cudaStream_t stream) {
     return fused_update_impl(ctx, bucket, mode, start, count, state0, state1, kind, lr, momentum, beta1, beta2, eps,
-                             weight_decay, bc1, bc2, nesterov, epoch, blocks, nullptr, stream);
+                             weight_decay, bc1, bc2, nesterov, epoch, blocks, nullptr, bcast_buffers, stream);
 }
 
 // Graph-replay variant: lr, the two Adam bias corrections and the flag epoch are read from the device array
@@ -418,10 +470,30 @@ extern "C" int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long
 extern "C" int picd_fused_allreduce_update_dyn(void* ctx, int bucket, int mode, long long start, long long count,
                                                float* state0, float* state1, int kind, float momentum, float beta1,
                                                float beta2, float eps, float weight_decay, int nesterov, int blocks,
-                                               const float* dyn, cudaStream_t stream) {
+                                               const float* dyn, int bcast_buffers, cudaStream_t stream) {
     PICD_REQUIRE(dyn != nullptr, "fused_allreduce_update_dyn: dyn must point at 4 device floats");
     return fused_update_impl(ctx, bucket, mode, start, count, state0, state1, kind, 0.f, momentum, beta1, beta2, eps,
-                             weight_decay, 1.f, 1.f, nesterov, 0u, blocks, dyn, stream);
+                             weight_decay, 1.f, 1.f, nesterov, 0u, blocks, dyn, bcast_buffers, stream);
+}
+
+// First kernel of a captured training step: advances the step-varying words of the dyn array ON THE DEVICE, so a replay needs
+// no host-to-device copy at all.  dyn = {lr, 1 - beta1^t, 1 - beta2^t, t (flag epoch / dropout step, raw bits), replay index
+// (raw bits)}: t and the replay index are incremented, the two Adam bias corrections recomputed from t; lr is only written by
+// the host when the schedule changes it.
+__global__ void dyn_advance_kernel(float* dyn, float beta1, float beta2) {
+    if (threadIdx.x == 0) {
+        const unsigned t = __float_as_uint(dyn[3]) + 1u;
+        dyn[3] = __uint_as_float(t);
+        dyn[4] = __uint_as_float(__float_as_uint(dyn[4]) + 1u);
+        dyn[1] = 1.f - powf(beta1, static_cast<float>(t));
+        dyn[2] = 1.f - powf(beta2, static_cast<float>(t));
+    }
+}
+extern "C" int picd_dyn_advance(float* dyn, float beta1, float beta2, cudaStream_t stream) {
+    PICD_REQUIRE(dyn != nullptr, "dyn_advance: dyn must point at 8 device floats");
+    dyn_advance_kernel<<<1, 32, 0, stream>>>(dyn, beta1, beta2);
+    PICD_LAUNCH_CHECK();
+    return 0;
 }
 
 extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n,

@@ -363,8 +363,9 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(
     const float* __restrict__ invstd, int act, const float* __restrict__ sums, float inv_count,
     const float* __restrict__ param_sums, float* dgamma, float* dbeta, __nv_bfloat16* __restrict__ dy,
     __nv_bfloat16* __restrict__ dres, long long P, int C, int tx_count, int ty_count, int rows_per_block,
-    int eval_mode, int sums_replicas, int param_replicas) {
+    int eval_mode, int sums_replicas, int param_replicas, const float* __restrict__ count_dev) {
     const int vecs = C >> 3;
+    if (count_dev != nullptr) inv_count = 1.f / __ldg(count_dev);     // SyncBN: the exchanged global element count
     if (blockIdx.x == 0 && blockIdx.y == 0 && dgamma != nullptr) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             dbeta[c] += fold_replicas(param_sums, c, 2 * C, param_replicas);
@@ -459,7 +460,7 @@ int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const voi
 int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale, const float* shift,
                         const float* mean, const float* invstd, int act, const float* sums, float inv_count,
                         const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
-                        int eval_mode, cudaStream_t stream);
+                        int eval_mode, const float* count_dev, cudaStream_t stream);
 static bool use_stream_kernels() {
     static const bool on = [] { const char* e = getenv("PICD_BN_STREAM"); return e == nullptr || e[0] != '0'; }();
     return on;
@@ -592,11 +593,15 @@ __global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
 }
 
 // NOTE: folds `sums` / `param_sums` in place (copy 0 receives the totals) before the streaming kernel runs.
-extern "C" int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const void* relu_mask,
-                                      const float* scale, const float* shift, const float* mean, const float* invstd,
-                                      int act, const float* sums, int sums_replicas, float inv_count,
-                                      const float* param_sums, int param_replicas, float* dgamma, float* dbeta, void* dy,
-                                      void* dres, long long P, int C, cudaStream_t stream) {
+// count_dev (nullable): device pointer to the GLOBAL per-channel element count; when given it replaces inv_count.  SyncBatchNorm's
+// forward exchange publishes the true total, so ranks with different batch sizes (a ragged last batch) scale dX correctly
+// (torch/nn/modules/_functions.py:59-62,170-179).
+extern "C" int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const void* z, const void* relu_mask,
+                                          const float* scale, const float* shift, const float* mean, const float* invstd,
+                                          int act, const float* sums, int sums_replicas, float inv_count,
+                                          const float* count_dev, const float* param_sums, int param_replicas,
+                                          float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
+                                          cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
     if (param_sums != nullptr && param_sums != sums && param_replicas > 1) {
         fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(param_sums), 2 * C, param_replicas);
@@ -609,7 +614,7 @@ extern "C" int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void*
     }
     if (use_stream_kernels()) {
         const int rc = bn_stream_bwd_apply(dz, y, z, relu_mask, scale, shift, mean, invstd, act, sums, inv_count, param_sums,
-                                           dgamma, dbeta, dy, dres, P, C, 0, stream);
+                                           dgamma, dbeta, dy, dres, P, C, 0, count_dev, stream);
         if (rc >= 0) return rc;
     }
     const ReduceShape s = stream_shape(P, C);
@@ -617,9 +622,17 @@ extern "C" int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void*
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
         dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
-        s.rows_per_block, 0, sums_replicas, param_replicas);
+        s.rows_per_block, 0, sums_replicas, param_replicas, count_dev);
     PICD_LAUNCH_CHECK();
     return 0;
+}
+extern "C" int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const void* relu_mask,
+                                      const float* scale, const float* shift, const float* mean, const float* invstd,
+                                      int act, const float* sums, int sums_replicas, float inv_count,
+                                      const float* param_sums, int param_replicas, float* dgamma, float* dbeta, void* dy,
+                                      void* dres, long long P, int C, cudaStream_t stream) {
+    return picd_bn_bwd_apply_mask_cnt(dz, y, z, relu_mask, scale, shift, mean, invstd, act, sums, sums_replicas, inv_count,
+                                      nullptr, param_sums, param_replicas, dgamma, dbeta, dy, dres, P, C, stream);
 }
 extern "C" int picd_bn_bwd_apply(const void* dz, const void* y, const void* z, const float* scale,
                                  const float* shift, const float* mean, const float* invstd, int act,
@@ -635,7 +648,7 @@ extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, co
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_eval: C=%d must be a multiple of 8", C);
     if (use_stream_kernels()) {
         const int rc = bn_stream_bwd_apply(dz, y, z, nullptr, scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
-                                           nullptr, dy, dres, P, C, 1, stream);
+                                           nullptr, dy, dres, P, C, 1, nullptr, stream);
         if (rc >= 0) return rc;
     }
     const ReduceShape s = stream_shape(P, C);
@@ -643,7 +656,7 @@ extern "C" int picd_bn_bwd_eval(const void* dz, const void* y, const void* z, co
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, nullptr, nullptr, act, nullptr, 0.f, nullptr, nullptr,
         nullptr, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
-        s.rows_per_block, 1, 1, 1);
+        s.rows_per_block, 1, 1, 1, nullptr);
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -33,6 +33,7 @@ struct StreamArgs {
     float* dgamma;
     float* dbeta;
     float inv_count;
+    const float* count_dev;          // BWD_APPLY, nullable: device-side global element count (SyncBN), replaces inv_count
     int act, use_z, eval_mode;
     long long P;
     int C, rows_per_chunk, stages, chunk_bytes;
@@ -172,10 +173,11 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         float mu[8], is[8], s1[8], s2[8];
         ld8f(a.mean + cv * 8, mu); ld8f(a.invstd + cv * 8, is);
         ld8f(a.sums + cv * 8, s1); ld8f(a.sums + C + cv * 8, s2);
+        const float inv_count = a.count_dev != nullptr ? 1.f / __ldg(a.count_dev) : a.inv_count;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            c1[k] = -sc[k] * is[k] * s2[k] * a.inv_count;
-            c2[k] = -sc[k] * s1[k] * a.inv_count - c1[k] * mu[k];
+            c1[k] = -sc[k] * is[k] * s2[k] * inv_count;
+            c2[k] = -sc[k] * s1[k] * inv_count - c1[k] * mu[k];
         }
     }
     const uint32_t ring_u32 = smem_u32(ring);
@@ -189,7 +191,6 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         mbar_wait(&full[s], phase);
         const uint32_t base = ring_u32 + static_cast<uint32_t>(s) * a.stage_bytes;
         const uint32_t cb = a.chunk_bytes;
-#pragma unroll
         // vector idx of the chunk belongs to channel vector idx % vecs; stepping by n_active (a multiple of vecs) keeps every
         // thread on its own 8 channels for any C, not only powers of two
         const int n_active = a.n_active;
@@ -354,7 +355,7 @@ int bn_stream_bwd_reduce(const void* dz, const void* y, const void* z, const voi
 int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
                         const float* shift, const float* mean, const float* invstd, int act, const float* sums,
                         float inv_count, const float* param_sums, float* dgamma, float* dbeta, void* dy, void* dres,
-                        long long P, int C, int eval_mode, cudaStream_t stream) {
+                        long long P, int C, int eval_mode, const float* count_dev, cudaStream_t stream) {
     if (!stream_eligible(P, C)) return -1;
     StreamArgs a{};
     a.in[0] = static_cast<const __nv_bfloat16*>(dz);
@@ -364,7 +365,7 @@ int bn_stream_bwd_apply(const void* dz, const void* y, const void* z, const void
     a.out1 = static_cast<__nv_bfloat16*>(dres);
     a.scale = scale; a.shift = shift; a.mean = mean; a.invstd = invstd; a.act = act;
     a.sums = sums; a.inv_count = inv_count; a.param_sums = param_sums; a.dgamma = dgamma; a.dbeta = dbeta;
-    a.eval_mode = eval_mode; a.P = P; a.C = C;
+    a.eval_mode = eval_mode; a.count_dev = count_dev; a.P = P; a.C = C;
     return launch_stream<SB_BWD_APPLY>(a, stream);
 }
 

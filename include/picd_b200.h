@@ -21,7 +21,9 @@ enum { PICD_ACT_NONE = 0, PICD_ACT_RELU = 1, PICD_ACT_GELU = 2, PICD_ACT_SWISH =
 /* optimizer kinds */
 enum { PICD_OPT_SGD = 0, PICD_OPT_ADAM = 1, PICD_OPT_ADAMW = 2 };
 /* all-reduce variants */
-enum { PICD_AR_LOCAL = 0, PICD_AR_ONE_SHOT = 1, PICD_AR_TWO_SHOT = 2 };
+enum { PICD_AR_LOCAL = 0, PICD_AR_ONE_SHOT = 1, PICD_AR_TWO_SHOT = 2,
+       PICD_AR_NVLS = 3,      /* two-shot through the NVSwitch multicast mapping: multimem.ld_reduce + multimem.st */
+       PICD_AR_NVLS_LD = 4 }; /* in-switch reduction (multimem.ld_reduce), unicast pushes */
 
 const char* picd_last_error(void);
 int picd_version(void);
@@ -86,6 +88,13 @@ int picd_bn_bwd_apply_mask(const void* dz, const void* y, const void* z, const v
                            const float* shift, const float* mean, const float* invstd, int act, const float* sums,
                            int sums_replicas, float inv_count, const float* param_sums, int param_replicas, float* dgamma,
                            float* dbeta, void* dy, void* dres, long long P, int C, cudaStream_t stream);
+/* As picd_bn_bwd_apply_mask; count_dev (nullable) points at the GLOBAL per-channel element count in device memory and then
+ * replaces inv_count (SyncBatchNorm with unequal per-rank batches, torch/nn/modules/_functions.py:59-62,170-179). */
+int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const void* z, const void* relu_mask, const float* scale,
+                               const float* shift, const float* mean, const float* invstd, int act, const float* sums,
+                               int sums_replicas, float inv_count, const float* count_dev, const float* param_sums,
+                               int param_replicas, float* dgamma, float* dbeta, void* dy, void* dres, long long P, int C,
+                               cudaStream_t stream);
 /* picd_bn_finalize + picd_bn_apply_mask in one launch (per-replica BatchNorm in training): scale / shift / mean / invstd
  * are OUTPUTS (the backward entry points take them), running statistics are updated in place. */
 int picd_bn_finalize_apply(const void* y, const float* sums, int replicas, float count, const float* gamma, const float* beta,
@@ -175,16 +184,26 @@ int picd_comm_create(int rank, int world, void* const* grad, void* const* master
 /* NVSwitch multicast (NVLS) views of the three regions, as mapped by the host (e.g. torch symmetric memory); enables
  * mode 3 of picd_fused_allreduce_update: multimem.ld_reduce / multimem.st instead of W peer loads / stores. */
 int picd_comm_set_multicast(void* ctx, void* mc_grad, void* mc_master, void* mc_shadow);
+/* Per-rank module-buffer regions (BatchNorm running statistics; n floats each, n % 4 == 0) inside the peer-mapped slabs.
+ * A bucket launch with bcast_buffers != 0 copies rank 0's region into every peer's between its two flag barriers: DDP's
+ * per-forward buffer broadcast (torch/nn/parallel/distributed.py:2214-2257 via train.py:49,128) without a collective call. */
+int picd_comm_set_buffers(void* ctx, void* const* bufs, long long n);
+/* Seconds a kernel may spin on a peer's flag before it traps (default 600); applies to the current device. */
+int picd_comm_set_flag_timeout(double seconds);
 int picd_comm_destroy(void* ctx);
 int picd_fused_allreduce_update(void* ctx, int bucket, int mode, long long start, long long count, float* state0,
                                 float* state1, int kind, float lr, float momentum, float beta1, float beta2, float eps,
                                 float weight_decay, float bc1, float bc2, int nesterov, unsigned epoch, int blocks,
-                                cudaStream_t stream);
+                                int bcast_buffers, cudaStream_t stream);
 /* Same bucket update for CUDA-graph replay: the step-varying scalars (lr, 1-beta1^t, 1-beta2^t, flag epoch as raw bits)
  * are read from the device array dyn[4] when the kernel runs, so one captured launch serves every later step. */
 int picd_fused_allreduce_update_dyn(void* ctx, int bucket, int mode, long long start, long long count, float* state0,
                                     float* state1, int kind, float momentum, float beta1, float beta2, float eps,
-                                    float weight_decay, int nesterov, int blocks, const float* dyn, cudaStream_t stream);
+                                    float weight_decay, int nesterov, int blocks, const float* dyn, int bcast_buffers,
+                                    cudaStream_t stream);
+/* First kernel of a captured step: increments dyn[3] (step / flag epoch, raw bits) and dyn[4] (replay index, raw bits) and
+ * recomputes dyn[1], dyn[2] = 1 - beta^t on the device, so that a graph replay needs no host-to-device copy. */
+int picd_dyn_advance(float* dyn, float beta1, float beta2, cudaStream_t stream);
 int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
                              int flag_slot, unsigned epoch, cudaStream_t stream);
 int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
@@ -205,7 +224,8 @@ int picd_nvls_supported(void);   /* 1/0/-1: NVSwitch multicast available (probe 
 /* ---- runtime ---------------------------------------------------------------------------------------------- */
 /* reverse-order bucket plan (torch DDP Reducer semantics); host function */
 int picd_plan_buckets(const int64_t* padded_sizes, int n_params, int64_t first_bytes, int64_t cap_bytes,
-                      int elem_bytes, int64_t* starts, int64_t* ends, int* param_bucket, int max_buckets);
+                      int elem_bytes, int64_t unit /* every bucket end is a multiple of this many elements */,
+                      int64_t* starts, int64_t* ends, int* param_bucket, int max_buckets);
 
 #ifdef __cplusplus
 }

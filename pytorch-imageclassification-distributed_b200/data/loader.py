@@ -23,7 +23,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 import torch
-from torch.utils.data import DataLoader, Dataset
+from torch.utils.data import DataLoader, Dataset, get_worker_info
 
 from ..ops.reference import IMAGENET_MEAN, IMAGENET_STD
 from ..parallel.sampler import ShardedSampler
@@ -85,7 +85,22 @@ class ImageDataset(Dataset):
         names = class_names if class_names is not None else sorted(
             d.name for d in self.image_dir.iterdir() if d.is_dir()) if self.image_dir.is_dir() else []
         self.mapping: Dict[str, int] = {n: i for i, n in enumerate(names)}   # fix D5
-        self._rng = random.Random()
+        self.seed = seed
+        self._rng: Optional[random.Random] = None     # created lazily, once per process: see _augment_rng
+        self._rng_owner = None
+
+    def _augment_rng(self) -> random.Random:
+        """Augmentation RNG of THIS process.  DataLoader workers are forks of the parent, so an RNG created in __init__
+        would be copied into every worker and all of them would draw the same rot90 / flip / colour decisions.  torch
+        gives each worker a distinct seed (base_seed + worker id, re-drawn per epoch from the global generator that
+        ``--seed`` seeds), which is what the reference's use of the global ``random`` module relies on; the main process
+        (num_workers=0) derives its stream from ``seed``."""
+        info = get_worker_info()
+        key = (os.getpid(), None if info is None else info.seed)
+        if self._rng is None or self._rng_owner != key:
+            self._rng = random.Random(self.seed * 1000003 + 17 if info is None else info.seed)
+            self._rng_owner = key
+        return self._rng
 
     def __len__(self):
         return len(self.image_files)
@@ -108,7 +123,7 @@ class ImageDataset(Dataset):
         return {"image": tensor, "label": label, "image_id": image_id}
 
     def augument(self, image: np.ndarray) -> np.ndarray:     # (sic) upstream spelling kept
-        r = self._rng
+        r = self._augment_rng()
         image = np.rot90(image, k=r.randrange(4))
         if r.random() > 0.5:
             image = image[::-1, ...]

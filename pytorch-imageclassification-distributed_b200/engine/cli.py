@@ -59,8 +59,12 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--seed", default=0, type=int)
     p.add_argument("--calibrate-comm", action="store_true",
                    help="measure one-shot vs two-shot all-reduce at start-up and pick the switch-over bucket size")
-    p.add_argument("--cuda-graph", action="store_true",
-                   help="record the training step once and replay it as a CUDA graph (b200 backend, no SyncBN)")
+    p.add_argument("--cuda-graph", dest="cuda_graph", action="store_true", default=None,
+                   help="record the training step once and replay it as a CUDA graph (default on the b200 backend on "
+                        "CUDA, SyncBatchNorm included; batches of another shape, e.g. a ragged last one, run eagerly)")
+    p.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false")
+    p.add_argument("--progress", action="store_true",
+                   help="rank 0 shows the reference's tqdm bar with the running loss instead of printed lines")
     return p
 
 
@@ -80,6 +84,13 @@ def main(argv: Optional[List[str]] = None) -> int:
     local_rank = D.init_distributed(args.backend, args.local_rank)
     use_cuda = torch.cuda.is_available() and args.backend != "gloo"
     device = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
+    if args.dtype == "fp32" and use_cuda:
+        # the sm_100a kernels are bf16-in / fp32-accumulate (fp32 masters, statistics and optimizer); there is no
+        # fp32/tf32 tensor-core path, and silently training in bf16 under an fp32 flag would be a lie
+        raise SystemExit("--dtype fp32 is only available on the CPU/gloo path (--backend gloo); the CUDA kernels "
+                         "compute in bf16 with fp32 accumulation, masters and optimizer state")
+    if args.cuda_graph is None:
+        args.cuda_graph = use_cuda and args.backend == "b200"
     torch.manual_seed(args.seed)
     image_size = args.image_size or (299 if args.model == "inceptionv3" else 224)
     small = image_size <= 64
@@ -134,7 +145,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     history, best = fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device,
                         name=args.model, epochs=args.epochs, start_epoch=start_epoch, best_score=best_score,
                         ckpt_dir=args.ckpt_dir, log_interval=args.log_interval, tracer=tracer,
-                        max_steps=args.max_steps, cuda_graph=args.cuda_graph)
+                        max_steps=args.max_steps, cuda_graph=args.cuda_graph, progress=args.progress)
     if args.trace:
         tracer.log(event="summary", phases=tracer.summary(), history=history, best=best)
         tracer.close()

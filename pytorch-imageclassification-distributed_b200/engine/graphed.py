@@ -9,9 +9,11 @@ What makes the step replayable:
   * all kernels run on the stream that is current when the op is called (the ctypes bindings pass
     ``torch.cuda.current_stream()``), tensor maps travel by value in the launch parameters, activations come from the
     graph's private memory pool, gradients / weights live in the static parameter arena;
-  * the only step-varying host scalars -- learning rate, Adam bias corrections and the peer-flag epoch of the fused
-    all-reduce kernels -- are read from a 16-byte device array that the host rewrites before each replay
-    (``picd_fused_allreduce_update_dyn``);
+  * the only step-varying scalars -- learning rate, Adam bias corrections and the peer-flag epoch of the fused
+    all-reduce kernels -- are read from a small device array (``picd_fused_allreduce_update_dyn``) whose step-dependent
+    words the graph's first kernel advances itself (``picd_dyn_advance``); the host writes it only when the learning
+    rate changes or an eager step ran in between, so a replay involves no host-to-device copy besides the batch;
+  * DDP's per-forward buffer broadcast rides in the last bucket kernel (peer stores), so no NCCL call surrounds a replay;
   * BatchNorm ``num_batches_tracked`` and the running statistics are updated by kernels, not by the host;
   * SyncBatchNorm's statistics exchanges (double-buffered peer-memory slots, epoch-numbered flags) are recorded on
     slots of their own with the capture-time epoch; the kernels add a replay counter read from the same device array.
@@ -90,6 +92,7 @@ class GraphedTrainStep:
         red.comm.begin_capture(red.dyn)             # SyncBN collectives: slots of their own, epoch = capture epoch + delta
         try:
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                red.advance_dyn()                   # step counter / flag epoch / bias corrections move on the device
                 self.static_loss = self._eager(self.static_images, self.static_labels)
                 self.static_outputs = self.outputs
         finally:
@@ -114,9 +117,7 @@ class GraphedTrainStep:
         m = self.model
         self.static_images.copy_(images, non_blocking=True)
         self.static_labels.copy_(labels, non_blocking=True)
-        if m.broadcast_buffers:
-            m._sync_buffers()
-        m._impl.write_dyn(m.step_index + 1, self.replays)
+        m._impl.sync_dyn(m.step_index + 1, self.replays)     # no H2D copy unless the host's view of (lr, step) moved
         self.graph.replay()
         m.step_index += 1
         self.optimizer.step_count += 1

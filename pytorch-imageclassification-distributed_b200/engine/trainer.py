@@ -60,14 +60,31 @@ def _to_device(batch, device):
 
 def train_epoch(epoch: int, model, loss_fn, optimizer, loader, device, log_interval: int = 50,
                 tracer: Optional[Tracer] = None, max_steps: Optional[int] = None,
-                printer: Callable[[str], None] = print, step_fn=None) -> float:
+                printer: Callable[[str], None] = print, step_fn=None, progress: bool = False) -> float:
     """``step_fn`` (an :class:`picd_b200.engine.graphed.GraphedTrainStep`) replaces the forward/backward/step sequence
-    with one CUDA-graph replay per batch; the loop around it is unchanged."""
+    with one CUDA-graph replay per batch; the loop around it is unchanged.  ``progress``: rank 0 shows the reference's
+    tqdm bar (train.py:39-42) whose description ``Epoch: e; Loss val|(avg)`` (train.py:67-68) is refreshed from the
+    device-side meter every ``log_interval`` steps (every step with ``log_interval=1``, like the reference) instead of
+    a printed line."""
     model.train()
     losses = AverageMeter()
     tracer = tracer or Tracer(enabled=False)
     t0, seen = time.time(), 0
-    for index, batch in enumerate(loader):
+    bar = None
+    iterator = loader
+    if progress and D.is_main():
+        try:
+            from tqdm import tqdm
+            total = None
+            try:
+                total = len(loader) if max_steps is None else min(len(loader), max_steps)
+            except TypeError:
+                total = max_steps
+            bar = tqdm(loader, total=total)
+            iterator = bar
+        except ImportError:
+            bar = None
+    for index, batch in enumerate(iterator):
         if max_steps is not None and index >= max_steps:
             break
         with tracer.range("h2d"):
@@ -94,8 +111,14 @@ def train_epoch(epoch: int, model, loss_fn, optimizer, loader, device, log_inter
             if D.is_main():
                 val, ssum = packed.tolist()
                 rate = seen * D.get_world_size() / max(time.time() - t0, 1e-9)
-                printer(f"Epoch: {epoch}; step {index + 1}; Loss {val:.4f}|({ssum / losses.count:.4f}); "
-                        f"{rate:.1f} img/s")
+                if bar is not None:
+                    bar.set_description(f"Epoch: {epoch}; Loss {val:.4f}|({ssum / losses.count:.4f})")
+                    bar.set_postfix_str(f"{rate:.1f} img/s")
+                else:
+                    printer(f"Epoch: {epoch}; step {index + 1}; Loss {val:.4f}|({ssum / losses.count:.4f}); "
+                            f"{rate:.1f} img/s")
+    if bar is not None:
+        bar.close()
     if losses.count == 0:
         return float("nan")
     avg = D.reduce_tensor(torch.as_tensor(losses.avg, dtype=torch.float32, device=device), average=True)
@@ -127,7 +150,8 @@ def val_epoch(epoch: int, model, loader, device, printer: Callable[[str], None] 
 def fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device, *, name: str,
         epochs: int = 100, start_epoch: int = 0, best_score: float = 0.0, ckpt_dir: str = "dtmodel/cp",
         save_every: int = 5, log_interval: int = 50, tracer: Optional[Tracer] = None,
-        max_steps: Optional[int] = None, printer: Callable[[str], None] = print, cuda_graph: bool = False):
+        max_steps: Optional[int] = None, printer: Callable[[str], None] = print, cuda_graph: bool = False,
+        progress: bool = False):
     """The reference's epoch driver (train.py:161-188) with start_epoch honoured (fix D10).  ``cuda_graph`` replays the
     training step from a captured CUDA graph where the model allows it (see engine/graphed.py)."""
     history = []
@@ -143,9 +167,12 @@ def fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device, 
         elif hasattr(train_loader, "set_epoch"):
             train_loader.set_epoch(epoch)
         loss = train_epoch(epoch, model, loss_fn, optimizer, train_loader, device, log_interval,
-                           tracer, max_steps, printer, step_fn)
+                           tracer, max_steps, printer, step_fn, progress)
         scheduler.step()                                          # train.py:166
         acc = val_epoch(epoch, model, val_loader, device, printer, max_steps)
+        # the optimizer state is sharded by slice owner on the peer-memory engine: assembling it is a collective, so
+        # every rank takes part even though only rank 0 writes the file
+        opt_state = optimizer.state_dict() if epoch % save_every == 0 else None
         if D.is_main():
             if acc > best_score:
                 printer(f"Model improved to {acc} so storing checkpoint")
@@ -153,7 +180,7 @@ def fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device, 
                 save_checkpoint(model, epoch, best_score, ckpt_dir, name, BEST)
             if epoch % save_every == 0:
                 save_checkpoint(model, epoch, best_score, ckpt_dir, name, LATEST,
-                                extra={"optimizer": optimizer.state_dict(),
+                                extra={"optimizer": opt_state,
                                        "scheduler": scheduler.state_dict()})
         best_score = float(D.broadcast_object(best_score, 0))
         history.append({"epoch": epoch, "loss": loss, "val_accuracy": acc})

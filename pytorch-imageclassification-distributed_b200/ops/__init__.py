@@ -2,9 +2,12 @@
 tensors and to the pure-torch oracle (:mod:`.reference`) otherwise.
 
 There is exactly one device code path (no multi-backend dispatch): a CUDA tensor
-either runs the hand-written kernel or raises -- it never silently falls back to
-cuDNN/ATen.  ``PICD_FORCE_TORCH=1`` is an explicit debugging switch that runs the
-oracle on the GPU for A/B comparison.
+runs the hand-written kernel.  The few shapes no model of this repository reaches and no
+kernel covers (generic grouped convolutions, ``ceil_mode`` max-pooling, average pooling
+that excludes the padding, attention with a head size other than 64 or more than 256
+tokens) run the library operator and say so ONCE on stderr (``PICD_STRICT=1`` turns
+that into an error) -- never silently.  ``PICD_FORCE_TORCH=1`` is an explicit debugging
+switch that runs the oracle on the GPU for A/B comparison.
 """
 from __future__ import annotations
 
@@ -19,6 +22,19 @@ from ._lib import lib_available, lib_path, require_lib  # noqa: F401
 
 def _force_torch() -> bool:
     return os.environ.get("PICD_FORCE_TORCH", "0") == "1"
+
+
+_warned = set()
+
+
+def _library_fallback(what: str) -> None:
+    """A CUDA tensor is about to run a library (ATen / cuDNN) operator because no sm_100a kernel covers this shape."""
+    if os.environ.get("PICD_STRICT", "0") == "1":
+        raise NotImplementedError(f"picd_b200: no native kernel for {what} (PICD_STRICT=1)")
+    if what not in _warned:
+        _warned.add(what)
+        import sys
+        print(f"picd_b200: WARNING: {what} has no sm_100a kernel here; running the library operator", file=sys.stderr)
 
 
 def use_native(x: torch.Tensor) -> bool:
@@ -77,7 +93,8 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, paddi
         if groups == x.shape[1] == w.shape[0] and w.shape[1] == 1 and w.shape[2] == w.shape[3] and groups % 8 == 0:
             y = native.depthwise_conv2d(x, w, stride, padding)       # native stencil kernel (csrc/ops/depthwise.cu)
         else:
-            y = ref.conv2d(x, w, None, stride, padding, groups)      # generic grouped conv: library
+            _library_fallback(f"grouped convolution (groups={groups}, not depthwise)")
+            y = ref.conv2d(x, w, None, stride, padding, groups)
         return native.bn_act(y, gamma, beta, running_mean, running_var, training=training,
                              momentum=momentum, eps=eps, act=act, residual=residual,
                              sync_group=sync_group)
@@ -90,6 +107,8 @@ def conv2d(x, w, bias=None, stride=1, padding=0, groups=1):
     if use_native(x) and groups == 1:
         from . import native
         return native.conv2d(x, w, bias, stride, padding)
+    if x.is_cuda and not _force_torch():
+        _library_fallback(f"conv2d with groups={groups}")
     return ref.conv2d(x, w, bias, stride, padding, groups)
 
 
@@ -126,6 +145,8 @@ def max_pool2d(x, kernel_size, stride, padding=0, ceil_mode=False, grad_fork=Non
     if use_native(x) and not ceil_mode:
         from . import native
         return native.pool2d(x, kernel_size, stride, padding, mode="max", grad_fork=grad_fork)
+    if x.is_cuda and not _force_torch():
+        _library_fallback("max_pool2d(ceil_mode=True)")
     return ref.max_pool2d(x, kernel_size, stride, padding, ceil_mode)
 
 
@@ -133,6 +154,8 @@ def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True, grad_f
     if use_native(x) and count_include_pad:
         from . import native
         return native.pool2d(x, kernel_size, stride, padding, mode="avg", grad_fork=grad_fork)
+    if x.is_cuda and not _force_torch():
+        _library_fallback("avg_pool2d(count_include_pad=False)")
     return ref.avg_pool2d(x, kernel_size, stride, padding, count_include_pad)
 
 
@@ -160,6 +183,7 @@ def layer_norm(x, gamma, beta, eps=1e-6):
 def attention(q, k, v, scale=None):
     if use_native(q):
         from . import native
+        _library_fallback(f"attention with head dim {q.shape[-1]} / {q.shape[-2]} tokens (native: 64 / <= 256)")
         return native.attention(q, k, v, scale)
     return ref.attention(q, k, v, scale)
 

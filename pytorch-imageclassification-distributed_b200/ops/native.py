@@ -48,6 +48,7 @@ _SIG = {
     "picd_bn_finalize_apply": "ppifppppffpppppipplip",
     "picd_bn_bwd_reduce_mask": "ppppppppiplip",
     "picd_bn_bwd_apply_mask": "ppppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
+    "picd_bn_bwd_apply_mask_cnt": "ppppppppi" + "pif" + "p" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_reduce": "pppppppiplip",
     "picd_bn_bwd_apply": "pppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_eval": "pppppipplip",
@@ -382,8 +383,8 @@ def _bn_forward_coeffs(sums, count, gamma, beta, rm, rv, momentum, eps, sync_gro
         from ..parallel import native_comm
         comm = native_comm.current_comm()
         if comm is not None:
-            tot = comm.bn_finalize_sync(sums, count, gamma, beta, rm, rv, momentum, eps, coef)
-            return coef, tot
+            tot, tot_dev = comm.bn_finalize_sync(sums, count, gamma, beta, rm, rv, momentum, eps, coef)
+            return coef, (tot, tot_dev)
         # no peer-mapped slab (e.g. model not wrapped yet): NCCL fallback for the statistics only
         import torch.distributed as dist
         packed = torch.cat([sums.view(-1, 2 * C).sum(0), sums.new_tensor([float(count)])])
@@ -393,7 +394,7 @@ def _bn_forward_coeffs(sums, count, gamma, beta, rm, rv, momentum, eps, sync_gro
         total = float(total_t.item())
     call("picd_bn_finalize", sums, sums.numel() // (2 * C), total, gamma, beta, rm, rv, float(momentum), float(eps),
          coef[0], coef[1], coef[2], coef[3], C)
-    return coef, total
+    return coef, (total, None)
 
 
 def _bn_allreduce_bwd(sums2, sync_group, C):
@@ -425,12 +426,13 @@ def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
     C = gamma.numel()
     P = y.numel() // C
     fuse_finalize = cfg.training and _sync_world(cfg.sync_group) <= 1 and _FUSE_FINALIZE
+    total_dev = None           # SyncBN: the exchanged global element count, in device memory
     if fuse_finalize:          # per-replica BN: the apply kernel turns the batch sums into coefficients itself
         coef = torch.empty(4, C, dtype=torch.float32, device=y.device)
         total = float(count)
     elif cfg.training:
-        coef, total = _bn_forward_coeffs(sums, count, gamma, beta, cfg.rm, cfg.rv, cfg.momentum, cfg.eps,
-                                         cfg.sync_group)
+        coef, (total, total_dev) = _bn_forward_coeffs(sums, count, gamma, beta, cfg.rm, cfg.rv, cfg.momentum, cfg.eps,
+                                                      cfg.sync_group)
     else:
         coef = torch.empty(4, C, dtype=torch.float32, device=y.device)
         call("picd_bn_eval_coeffs", gamma, beta, cfg.rm, cfg.rv, float(cfg.eps), coef[0], coef[1], C)
@@ -447,7 +449,7 @@ def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
              float(cfg.eps), coef[0], coef[1], coef[2], coef[3], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
     else:
         call("picd_bn_apply_mask", y, coef[0], coef[1], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
-    ctx.bn_total, ctx.bn_act, ctx.bn_training = total, cfg.act, cfg.training
+    ctx.bn_total, ctx.bn_act, ctx.bn_training, ctx.bn_total_dev = total, cfg.act, cfg.training, total_dev
     ctx.bn_sync, ctx.has_res = cfg.sync_group, residual is not None
     return z, coef
 
@@ -470,8 +472,9 @@ def _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, need_dres):
     gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C)
     gt, g_routed = _grad_target(gamma)
     bt, b_routed = _grad_target(beta)
-    call("picd_bn_bwd_apply_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, gsums, gsums.numel() // (2 * C),
-         1.0 / ctx.bn_total, sums2, STAT_REPLICAS, gt, bt, dy, dres, P, C)
+    call("picd_bn_bwd_apply_mask_cnt", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, gsums,
+         gsums.numel() // (2 * C), 1.0 / ctx.bn_total, getattr(ctx, "bn_total_dev", None), sums2, STAT_REPLICAS, gt, bt, dy,
+         dres, P, C)
     if g_routed:
         _mark_ready(gamma)
     if b_routed:

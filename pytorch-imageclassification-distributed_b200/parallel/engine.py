@@ -60,12 +60,26 @@ class Bucket:
 
 
 def plan_buckets(padded_sizes: Sequence[int], first_bytes: int = FIRST_BUCKET_BYTES,
-                 cap_bytes: int = BUCKET_CAP_BYTES, elem_bytes: int = 4) -> List[Tuple[int, int, List[int]]]:
+                 cap_bytes: int = BUCKET_CAP_BYTES, elem_bytes: int = 4, unit: int = 1,
+                 native: Optional[bool] = None) -> List[Tuple[int, int, List[int]]]:
     """Greedy contiguous bucketing over parameters already sorted in *expected gradient
     arrival order* (reverse registration).  The first bucket closes at ``first_bytes`` so
-    communication starts early, later ones at ``cap_bytes``.  Returns
-    ``(start_elem, end_elem, [param indices])`` per bucket.  ``csrc/runtime/bucket_planner.cpp``
-    is the native twin of this function (same result, used by non-Python hosts)."""
+    communication starts early, later ones at ``cap_bytes``.  Every bucket's
+    end is rounded up to a multiple of ``unit`` elements (``lcm(64, 4 * world)``): the
+    two-shot kernel splits a bucket into ``world`` slices of whole 16-byte vectors, so a
+    bucket must divide evenly for ANY world size (3, 5, 6, 7 included), not only powers of
+    two.  Returns ``(start_elem, end_elem, [param indices])`` per bucket; the gap between a
+    bucket's last parameter and its end is padding.
+
+    ``csrc/runtime/bucket_planner.cpp`` (``picd_plan_buckets``) is the native implementation
+    and is the one used whenever the kernel library is loadable; this Python body is the
+    fallback for a tree without a build and the oracle of ``tests/test_bucket_planner.py``."""
+    if native is None or native:
+        out = _plan_buckets_native(padded_sizes, first_bytes, cap_bytes, elem_bytes, unit)
+        if out is not None:
+            return out
+        if native:
+            raise RuntimeError("picd_b200: native bucket planner requested but the library is not loadable")
     out: List[Tuple[int, int, List[int]]] = []
     start, cur, members = 0, 0, []
     limit = first_bytes
@@ -73,11 +87,42 @@ def plan_buckets(padded_sizes: Sequence[int], first_bytes: int = FIRST_BUCKET_BY
         members.append(i)
         cur += n
         if (cur - start) * elem_bytes >= limit:
+            cur = start + _round_up(cur - start, unit)
             out.append((start, cur, members))
             start, members, limit = cur, [], cap_bytes
     if members:
+        cur = start + _round_up(cur - start, unit)
         out.append((start, cur, members))
     return out
+
+
+def _plan_buckets_native(padded_sizes, first_bytes, cap_bytes, elem_bytes, unit):
+    """``picd_plan_buckets`` through ctypes; None when the library cannot be loaded (CPU-only checkout without a build)."""
+    import ctypes
+    from ..ops._lib import lib_available, require_lib
+    if not lib_available():
+        return None
+    lib = require_lib()
+    if not hasattr(lib, "picd_plan_buckets"):
+        return None
+    n = len(padded_sizes)
+    if n == 0:
+        return []
+    f = lib.picd_plan_buckets
+    i64p = ctypes.POINTER(ctypes.c_int64)
+    f.argtypes = [i64p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int64, i64p, i64p,
+                  ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    f.restype = ctypes.c_int
+    sizes = (ctypes.c_int64 * n)(*[int(v) for v in padded_sizes])
+    starts, ends = (ctypes.c_int64 * n)(), (ctypes.c_int64 * n)()
+    owner = (ctypes.c_int * n)()
+    nb = f(sizes, n, int(first_bytes), int(cap_bytes), int(elem_bytes), int(max(unit, 1)), starts, ends, owner, n)
+    if nb < 0:
+        raise RuntimeError("picd_plan_buckets failed")
+    members: List[List[int]] = [[] for _ in range(nb)]
+    for i in range(n):
+        members[owner[i]].append(i)
+    return [(int(starts[b]), int(ends[b]), members[b]) for b in range(nb)]
 
 
 def _round_up(n: int, a: int) -> int:
@@ -141,27 +186,28 @@ class ParamArena:
     """Flat master / gradient / shadow / optimizer-state buffers with per-parameter views."""
 
     def __init__(self, params: Iterable[nn.Parameter], device: torch.device, spec: OptimizerSpec,
-                 first_bytes=FIRST_BUCKET_BYTES, cap_bytes=BUCKET_CAP_BYTES, world: int = 1, rank: int = 0):
+                 first_bytes=FIRST_BUCKET_BYTES, cap_bytes=BUCKET_CAP_BYTES, world: int = 1, rank: int = 0,
+                 buffer_floats: int = 0):
         plist = [p for p in params if p.requires_grad]
         self.params: List[nn.Parameter] = list(reversed(plist))     # expected gradient arrival order
         self.device, self.spec, self.world, self.rank = device, spec, world, rank
-        self.offsets, sizes = [], []
-        off = 0
-        for p in self.params:
-            self.offsets.append(off)
-            n = _round_up(p.numel(), ALIGN)
-            sizes.append(n)
-            off += n
-        # pad the total so that every bucket splits evenly across ranks in 16-byte units
-        self.total = _round_up(off, ALIGN * max(world, 1))
-        self.buckets = [Bucket(i, s, e, m) for i, (s, e, m) in
-                        enumerate(plan_buckets(sizes, first_bytes, cap_bytes))]
-        if self.buckets:
-            self.buckets[-1].end = self.total
+        sizes = [_round_up(p.numel(), ALIGN) for p in self.params]
+        # every bucket must split into `world` slices of whole 16-byte vectors (two-shot / NVLS kernels), for any world size
+        self.unit = math.lcm(ALIGN, 4 * max(world, 1))
+        plan = plan_buckets(sizes, first_bytes, cap_bytes, unit=self.unit)
+        self.buckets = [Bucket(i, s, e, m) for i, (s, e, m) in enumerate(plan)]
+        self.offsets = [0] * len(self.params)
+        for b in self.buckets:
+            off = b.start
+            for pi in b.params:
+                self.offsets[pi] = off
+                off += sizes[pi]
+        self.total = self.buckets[-1].end if self.buckets else 0
         self.native = None
         if device.type == "cuda":
             from . import native_comm
-            self.native = native_comm.SymmetricSlab(self.total, spec.n_state, device, world, rank)
+            self.native = native_comm.SymmetricSlab(self.total, spec.n_state, device, world, rank,
+                                                    buffer_floats=buffer_floats)
             self.master, self.grad, self.shadow = self.native.master, self.native.grad, self.native.shadow
             self.state = self.native.state
         else:
@@ -232,16 +278,19 @@ class FusedOptimizer:
         self.step_count += 1
 
     def state_dict(self):
+        """COLLECTIVE when world > 1 on CUDA: in the two-shot / NVLS bucket kernels only the slice owner ever writes the
+        momentum / Adam moments of its 1/W slice (csrc/comm/comm.cu), so the complete state is assembled by all-gathering
+        the owners' slices bucket by bucket.  Every rank must call it; every rank gets the full tensors."""
         a = self.engine.arena
         return {"kind": self.spec.kind, "lr": self.spec.lr, "step": self.engine.step_index,
-                "state": [s.detach().cpu() for s in a.state]}
+                "state": [s.detach().cpu() for s in self.engine.gather_sharded(a.state)]}
 
     def load_state_dict(self, sd):
         a = self.engine.arena
         self.spec.lr = sd["lr"]
         self.engine.step_index = sd["step"]
         for dst, src in zip(a.state, sd["state"]):
-            dst.copy_(src)
+            dst.copy_(src)            # every rank keeps the full tensor; a slice owner only ever reads its own part
 
 
 # ----------------------------------------------------------------------------- the engine
@@ -263,15 +312,19 @@ class FusedDataParallel(nn.Module):
         except StopIteration:
             device = torch.device("cpu")
         self.device = device
-        self.arena = ParamArena(module.parameters(), device, self.spec, first_bucket_bytes,
-                                bucket_cap_bytes, self.world, self.rank)
-        self.optimizer = FusedOptimizer(self)
+        self._verify_replicas()
         self._float_buffers = [b for b in module.buffers() if b.is_floating_point()]
+        flat_ok = device.type == "cuda" and self._float_buffers and all(b.dtype == torch.float32 for b in self._float_buffers)
+        nbuf = sum(b.numel() for b in self._float_buffers) if flat_ok else 0
+        self.arena = ParamArena(module.parameters(), device, self.spec, first_bucket_bytes,
+                                bucket_cap_bytes, self.world, self.rank, buffer_floats=nbuf)
+        self.optimizer = FusedOptimizer(self)
         self._flat_buffers = None
-        if device.type == "cuda" and self._float_buffers and all(b.dtype == torch.float32 for b in self._float_buffers):
-            # BN running statistics live in ONE flat tensor (the registered buffers become views of it): the per-forward
-            # buffer broadcast is then a single collective with no gather / scatter kernels around it
-            flat = torch.empty(sum(b.numel() for b in self._float_buffers), dtype=torch.float32, device=device)
+        if flat_ok:
+            # BN running statistics live in ONE flat region of the peer-mapped slab (the registered buffers become views of
+            # it): the per-forward buffer broadcast of DDP is then a plain copy of rank 0's region into the
+            # peers', done by the step's last bucket kernel between its two flag barriers -- no collective call per step
+            flat = self.arena.native.bufs[:nbuf]
             off = 0
             with torch.no_grad():
                 for b in self._float_buffers:
@@ -297,6 +350,48 @@ class FusedDataParallel(nn.Module):
         else:
             self._impl = _TorchReducer(self)
 
+    # -- replica consistency (DDP ctor: _verify_param_shape_across_processes) --
+    def _verify_replicas(self):
+        """Every rank must wrap the same parameter list (count, shapes, dtypes, trainability) with the same update rule:
+        the arena offsets, the bucket plan and the peer-pointer arithmetic of the bucket kernels are derived from it, so
+        a mismatch would corrupt peers' memory or hang the first collective.  torch DDP raises in its constructor
+        (torch/nn/parallel/distributed.py:881, reached from train.py:128); so does this, before anything is allocated."""
+        if self.world == 1:
+            return
+        import hashlib
+        h = hashlib.sha1()
+        n = 0
+        for p in self.module.parameters():
+            if p.requires_grad:
+                h.update(repr((tuple(p.shape), str(p.dtype))).encode())
+                n += 1
+        mine = (n, h.hexdigest(), self.spec.kind)
+        box = [None] * self.world
+        dist.all_gather_object(box, mine, group=self.group)
+        bad = [r for r, v in enumerate(box) if v != box[0]]
+        if bad:
+            raise RuntimeError(
+                f"picd_b200: replicas disagree on the model: rank 0 wraps {box[0][0]} trainable parameters "
+                f"(shape digest {box[0][1][:12]}, optimizer {box[0][2]}), rank(s) {bad} differ "
+                f"(e.g. rank {bad[0]}: {box[bad[0]][0]} parameters, digest {box[bad[0]][1][:12]}, optimizer "
+                f"{box[bad[0]][2]}).  All ranks must build the same network before FusedDataParallel wraps it.")
+
+    def gather_sharded(self, flats):
+        """Full copies of per-element buffers that the bucket kernels keep SHARDED by slice owner (optimizer state): for
+        every bucket reduced in two-shot / NVLS mode rank r holds the valid values of slice r only.  Collective."""
+        outs = [f.detach().clone() for f in flats]
+        impl = getattr(self, "_impl", None)
+        if self.world == 1 or self.device.type != "cuda" or impl is None or not hasattr(impl, "_mode"):
+            return outs
+        for b in self.arena.buckets:
+            if impl._mode(b) < 2:
+                continue                      # one-shot buckets: every rank updates the whole bucket
+            per = b.numel // self.world
+            lo = b.start + per * self.rank
+            for f, o in zip(flats, outs):
+                dist.all_gather_into_tensor(o[b.start: b.end], f[lo: lo + per].contiguous(), group=self.group)
+        return outs
+
     # -- initial replica sync (DDP ctor: _sync_module_states, SURVEY.md N3) ------------------
     def _broadcast_initial_state(self):
         if self.world == 1:
@@ -308,12 +403,9 @@ class FusedDataParallel(nn.Module):
             dist.broadcast(b, src=0, group=self.group)
 
     def _sync_buffers(self):
-        """Per-forward coalesced broadcast of BN running stats from rank 0."""
+        """Per-forward coalesced broadcast of BN running stats from rank 0 -- CPU / gloo path only; on
+        CUDA the step's last bucket kernel pushes rank 0's buffers over NVLink (csrc/comm/comm.cu, ``bcast_n``)."""
         if not self._float_buffers:
-            return
-        if self._flat_buffers is not None:
-            dist.broadcast(self._flat_buffers, src=dist.get_global_rank(self.group, 0) if self.group else 0,
-                           group=self.group)
             return
         flat = torch.cat([b.reshape(-1).float() for b in self._float_buffers])
         dist.broadcast(flat, src=0, group=self.group)
@@ -366,8 +458,9 @@ class FusedDataParallel(nn.Module):
 
     # -- nn.Module plumbing -------------------------------------------------------------------
     def forward(self, *args, **kw):
-        if self.broadcast_buffers and self.module.training and torch.is_grad_enabled() and not self.capturing:
-            self._sync_buffers()        # (a captured step broadcasts eagerly before each replay instead)
+        if self.broadcast_buffers and self._flat_buffers is None and self.module.training and torch.is_grad_enabled() \
+                and not self.capturing:
+            self._sync_buffers()        # CPU / gloo (and CUDA modules with non-fp32 buffers): a collective per forward
         if self.device.type == "cuda" and self.module.training and torch.is_grad_enabled():
             from ..ops import native
             native.stat_arena(self.device).begin_step()      # one memset instead of two fill kernels per BN layer

@@ -59,7 +59,7 @@ def _view(ptr: int, n: int, typestr: str, device, owner) -> torch.Tensor:
 
 class SymmetricSlab:
     def __init__(self, total: int, n_state: int, device: torch.device, world: int, rank: int,
-                 num_buckets_hint: int = 256):
+                 num_buckets_hint: int = 256, buffer_floats: int = 0):
         self.lib = require_lib()
         self.total, self.device, self.world, self.rank = total, device, world, rank
         if world > MAX_PEERS:
@@ -71,7 +71,10 @@ class SymmetricSlab:
         self.off_xchg = _align(self.off_shadow + total * 2)
         self.off_flags = _align(self.off_xchg + N_SLOTS * 2 * SLOT_FLOATS * 4)
         self.flag_words = (2 * num_buckets_hint + N_SLOTS) * MAX_PEERS
-        self.nbytes = _align(self.off_flags + self.flag_words * 4)
+        # module buffers (BatchNorm running statistics): rank 0's copy is pushed into the peers' by the step's last bucket kernel
+        self.buffer_floats = (int(buffer_floats) + 3) // 4 * 4
+        self.off_bufs = _align(self.off_flags + self.flag_words * 4)
+        self.nbytes = _align(self.off_bufs + self.buffer_floats * 4)
         self.max_buckets = num_buckets_hint
         self.mc_base = 0          # NVSwitch multicast (NVLS) view of the slab, when the host can map one
         self._symm = None
@@ -87,6 +90,7 @@ class SymmetricSlab:
         self.master = _view(self.base + self.off_master, total, "<f4", device, self)
         self.shadow = _view(self.base + self.off_shadow, total, "<i2", device, self).view(torch.bfloat16)
         self.state = [torch.zeros(total, dtype=torch.float32, device=device) for _ in range(n_state)]
+        self.bufs = _view(self.base + self.off_bufs, self.buffer_floats, "<f4", device, self) if self.buffer_floats else None
         if self._symm is None:
             self.peer_bases: List[int] = [self.base] * max(world, 1)
             if world > 1:
@@ -171,6 +175,15 @@ class Comm:
             f2.argtypes = [ctypes.c_void_p] * 4
             check(f2(ctx, slab.mc_base + slab.off_grad, slab.mc_base + slab.off_master, slab.mc_base + slab.off_shadow),
                   "picd_comm_set_multicast")
+        if slab.buffer_floats:
+            f3 = self.lib.picd_comm_set_buffers
+            f3.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong]
+            check(f3(ctx, slab.region_ptrs(slab.off_bufs), slab.buffer_floats), "picd_comm_set_buffers")
+        timeout_s = float(os.environ.get("PICD_FLAG_TIMEOUT_S", "600"))
+        f4 = self.lib.picd_comm_set_flag_timeout
+        f4.argtypes = [ctypes.c_double]
+        with torch.cuda.device(slab.device):
+            check(f4(timeout_s), "picd_comm_set_flag_timeout")
         self._slot_epoch = {}
         self._slots = {}
         self._slot_keys = []
@@ -180,11 +193,13 @@ class Comm:
         self._f_upd = self.lib.picd_fused_allreduce_update
         self._f_upd.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 8 +
-                                [ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p])
+                                [ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_int, ctypes.c_void_p])
         self._f_upd_dyn = self.lib.picd_fused_allreduce_update_dyn
         self._f_upd_dyn.argtypes = ([ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong,
                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 5 +
-                                    [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p])
+                                    [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p])
+        self._f_adv = self.lib.picd_dyn_advance
+        self._f_adv.argtypes = [ctypes.c_void_p, ctypes.c_float, ctypes.c_float, ctypes.c_void_p]
         self._f_small_dyn = self.lib.picd_p2p_allreduce_small_dyn
         self._f_small_dyn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p, ctypes.c_int,
@@ -205,20 +220,20 @@ class Comm:
 
     # -- gradient buckets ---------------------------------------------------------------------------
     def fused_update(self, bucket_index: int, mode: int, start: int, count: int, state, spec, step: int,
-                     epoch: int, blocks: int = 0, dyn: Optional[torch.Tensor] = None):
+                     epoch: int, blocks: int = 0, dyn: Optional[torch.Tensor] = None, bcast_buffers: bool = False):
         s0 = state[0].data_ptr()
         s1 = state[1].data_ptr() if len(state) > 1 else None
         b1, b2 = spec.betas
         if dyn is not None:      # CUDA-graph capture: lr / bias corrections / epoch are read from `dyn` at run time
             check(self._f_upd_dyn(self.ctx, bucket_index, mode, start, count, s0, s1, spec.KINDS[spec.kind],
                                   spec.momentum, b1, b2, spec.eps, spec.weight_decay, int(spec.nesterov), blocks,
-                                  dyn.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                                  dyn.data_ptr(), int(bcast_buffers), torch.cuda.current_stream().cuda_stream),
                   "picd_fused_allreduce_update_dyn")
             return
         bc1, bc2 = 1.0 - b1 ** step, 1.0 - b2 ** step
         check(self._f_upd(self.ctx, bucket_index, mode, start, count, s0, s1, spec.KINDS[spec.kind], spec.lr,
                           spec.momentum, b1, b2, spec.eps, spec.weight_decay, bc1, bc2, int(spec.nesterov),
-                          epoch & 0xFFFFFFFF, blocks, torch.cuda.current_stream().cuda_stream),
+                          epoch & 0xFFFFFFFF, blocks, int(bcast_buffers), torch.cuda.current_stream().cuda_stream),
               "picd_fused_allreduce_update")
 
     # -- small collectives (SyncBN) ------------------------------------------------------------------
@@ -274,8 +289,10 @@ class Comm:
             check(self._f_bn_dyn(*args, self._delta_ptr(), SLOT_FLOATS, st), "picd_bn_finalize_sync_dyn")
         else:
             check(self._f_bn(*args, st), "picd_bn_finalize_sync")
-        # every rank holds an equally sized shard (ShardedSampler pads), so the global count is known on the host
-        return float(count) * self.slab.world
+        # `total` (device) is the exchanged GLOBAL count: the backward scales with it, so ranks may hold different batch
+        # sizes (a ragged last batch through a non-padding loader); the host-side float is only an estimate for callers
+        # that want a number without a sync
+        return float(count) * self.slab.world, total
 
     def allreduce_small(self, vec: torch.Tensor, n: Optional[int] = None, key=None) -> torch.Tensor:
         """Sum ``n`` floats over all ranks.  ``vec`` may hold several replicas of the payload ([R, n]); they are
@@ -321,6 +338,7 @@ class NativeReducer:
         self.side = torch.cuda.Stream(device=engine.device)
         self._epoch = 0
         self._dirty = False
+        self._launched = 0         # buckets launched so far in the current step
         self.dyn = None            # device float[8] (lr, bc1, bc2, epoch bits, replay delta bits) while a step is captured / replayed
 
     def enable_dyn(self):
@@ -328,16 +346,29 @@ class NativeReducer:
             self.dyn = torch.zeros(8, dtype=torch.float32, device=self.e.device)
         return self.dyn
 
-    def write_dyn(self, step: int, replay_index: int = 0):
-        """Refresh the step-varying scalars the captured kernels read (host values -> device, in stream order)."""
+    def advance_dyn(self):
+        """Recorded as the FIRST kernel of a captured step: the device itself moves the step counter / flag epoch, the
+        replay index and the Adam bias corrections forward (``picd_dyn_advance``), so a replay needs no H2D copy."""
+        b1, b2 = self.e.spec.betas
+        check(self.comm._f_adv(self.dyn.data_ptr(), b1, b2, torch.cuda.current_stream().cuda_stream), "picd_dyn_advance")
+
+    def sync_dyn(self, step: int, replay_index: int = 0):
+        """Make sure the captured kernels of the coming replay see (lr, step, replay index): the device advances step and
+        replay index by itself, so the host only writes when its own bookkeeping says the device copy is off -- the first
+        replay, after an eagerly executed step in between (ragged batch), or when the scheduler changed the learning rate.
+        The write is a small synchronous copy of the values ONE BEFORE the wanted ones (the graph's first kernel adds one)."""
         s = self.e.spec
-        b1, b2 = s.betas
-        words = np.array([step & 0xFFFFFFFF, replay_index & 0xFFFFFFFF], dtype=np.uint32).view(np.float32)
-        host = torch.zeros(8, dtype=torch.float32)
-        host[0], host[1], host[2] = s.lr, 1.0 - b1 ** step, 1.0 - b2 ** step
-        host.numpy()[3] = words[0]                  # raw bits (may not be valid floats: never touched as floats)
-        host.numpy()[4] = words[1]
-        self.dyn.copy_(host)                        # pageable H2D: staged before the call returns, so `host` may die
+        want = (step & 0xFFFFFFFF, replay_index & 0xFFFFFFFF, float(s.lr))
+        if getattr(self, "_dyn_next", None) != want:
+            b1, b2 = s.betas
+            host = np.zeros(8, dtype=np.float32)
+            host[0] = s.lr
+            prev = max(step - 1, 0)
+            host[1], host[2] = 1.0 - b1 ** prev, 1.0 - b2 ** prev
+            host.view(np.uint32)[3] = (step - 1) & 0xFFFFFFFF       # raw bits (never touched as floats)
+            host.view(np.uint32)[4] = (replay_index - 1) & 0xFFFFFFFF
+            self.dyn.copy_(torch.from_numpy(host))
+        self._dyn_next = ((step + 1) & 0xFFFFFFFF, (replay_index + 1) & 0xFFFFFFFF, float(s.lr))
         self.comm.note_replay(replay_index)
 
     def _mode(self, b) -> int:
@@ -364,12 +395,17 @@ class NativeReducer:
         ev = torch.cuda.Event()
         ev.record(cur)
         self.side.wait_event(ev)
+        self._launched += 1
+        # the step's last bucket also carries rank 0's module buffers to the peers (DDP's per-forward buffer broadcast)
+        bcast = e.broadcast_buffers and e._flat_buffers is not None and self._launched == len(e.arena.buckets)
         with torch.cuda.stream(self.side):
             self.comm.fused_update(b.index, self._mode(b), b.start, b.numel, e.arena.state, e.spec,
-                                   e.step_index + 1, e.step_index + 1, dyn=self.dyn if e.capturing else None)
+                                   e.step_index + 1, e.step_index + 1, dyn=self.dyn if e.capturing else None,
+                                   bcast_buffers=bcast)
         self._dirty = True
 
     def finish(self):
+        self._launched = 0
         if self._dirty:
             torch.cuda.current_stream(self.e.device).wait_stream(self.side)
             self._dirty = False

@@ -54,6 +54,20 @@ for sync, kind in ((False, "sgd"), (True, "adam")):
         rvs = [torch.empty_like(rv) for _ in range(world)]
         dist.all_gather(rvs, rv)
         assert all(torch.equal(rvs[0], r) for r in rvs)
+# DDP's constructor check (torch/nn/parallel/distributed.py:881): replicas that disagree on the model raise on EVERY rank
+# instead of corrupting each other's arenas
+torch.manual_seed(0)
+odd = Classifier("resnet18", 5 if rank == 0 else 6, small_input=True)
+try:
+    FusedDataParallel(odd, OptimizerSpec("sgd"))
+    raise SystemExit("replica mismatch was not detected")
+except RuntimeError as e:
+    assert "replicas disagree" in str(e), e
+
+# optimizer-state checkpoint is a collective that returns the full state on every rank, and reloads
+sd = dp.optimizer.state_dict()
+assert len(sd["state"]) == 2 and all(t.numel() == dp.arena.total for t in sd["state"])
+dp.optimizer.load_state_dict(sd)
 barrier()
 if rank == 0:
     print("DIST_WORKER_OK")

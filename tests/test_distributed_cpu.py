@@ -8,8 +8,8 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _torchrun(args, port, timeout=600):
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+def _torchrun(args, port, timeout=600, nproc=2):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr",
            "127.0.0.1", "--master-port", str(port)] + args
     env = dict(os.environ, OMP_NUM_THREADS="2", PYTHONPATH=ROOT)
     return subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
@@ -17,6 +17,13 @@ def _torchrun(args, port, timeout=600):
 
 def test_engine_two_ranks_gloo():
     r = _torchrun([os.path.join(ROOT, "tests", "_dist_worker.py")], 29531)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "DIST_WORKER_OK" in r.stdout
+
+
+def test_engine_three_ranks_gloo():
+    """A world size that is not a power of two (buckets must split evenly for W = 3, 5, 6, 7 as well)."""
+    r = _torchrun([os.path.join(ROOT, "tests", "_dist_worker.py")], 29533, nproc=3)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "DIST_WORKER_OK" in r.stdout
 

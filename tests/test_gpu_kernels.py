@@ -35,6 +35,16 @@ def test_tcgen05_conv_fprop_dgrad_wgrad():
     assert gpu_selftest.group_conv()
 
 
+def test_fused_paths_compose_like_the_fp32_oracle():
+    import gpu_selftest
+    assert gpu_selftest.group_compose()
+
+
+def test_native_path_trains_to_accuracy():
+    import gpu_selftest
+    assert gpu_selftest.group_converge()
+
+
 def test_models_match_torch_reference():
     import gpu_selftest
     assert gpu_selftest.group_model()
