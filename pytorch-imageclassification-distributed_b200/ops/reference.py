@@ -130,6 +130,12 @@ def max_pool2d(x, kernel_size, stride, padding=0, ceil_mode=False):
 
 
 def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True):
+    if x.is_cuda and x.dim() == 4 and not x.is_contiguous():
+        # torch 2.11's CUDA avg_pool2d BACKWARD for channels_last inputs ignores the padding offset (measured on B200: a
+        # unit gradient at output (0, 0) of a 3x3/s1/p1 pool lands on inputs [0..2, 0..2] instead of [0..1, 0..1]; the
+        # NCHW kernel and picd_pool_bwd agree with the definition).  The oracle therefore pools in NCHW.
+        y = F.avg_pool2d(x.contiguous(), kernel_size, stride, padding, count_include_pad=count_include_pad)
+        return y.contiguous(memory_format=torch.channels_last)
     return F.avg_pool2d(x, kernel_size, stride, padding, count_include_pad=count_include_pad)
 
 
