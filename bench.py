@@ -137,15 +137,23 @@ def run_b200(args):
     if not args.no_e2e:
         host_loader = SyntheticHostLoader(args.batch, args.image_size, NUM_CLASSES, 1 << 30, device, seed=1)
         sink = {"loss": 0.0}
+        from picd_b200.utils import LaggedScalarReader
+        reader = LaggedScalarReader(device, lag=1)
 
         def run_e2e(n):
             # pinned uint8 batch -> H2D + device normalise on the copy stream (prefetched one step ahead, like the training
-            # CLI does) -> training step -> D2H read of the step's loss
+            # CLI does) -> training step -> D2H read of EVERY step's loss into pinned memory, consumed one step late so that
+            # the host never waits for the step it has just enqueued (utils/lagged.py); the last value is read before
+            # the region ends
             first = counter["i"]
             counter["i"] += n
             batches = (host_loader.host_batch(first + k) for k in range(n))
             for b in DevicePrefetcher(batches, device):
-                sink["loss"] = float(step(b["image"], b["label"]).item())
+                v = reader.push(step(b["image"], b["label"]))
+                if v is not None:
+                    sink["loss"] = v
+            for v in reader.flush():
+                sink["loss"] = v
 
         run_e2e(max(3, args.warmup // 2))
         ms_e, _ = timed_region(run_e2e, args.steps, device, rank)

@@ -350,6 +350,9 @@ CONV_CASES = [
     # 3x3 stride-1 shapes that take the halo path (one activation box per column shift, resident weights for 64->64)
     (2, 28, 28, 128, 128, 3, 3, 1, 1), (3, 30, 37, 64, 96, 3, 3, 1, 1), (2, 56, 56, 64, 192, 3, 3, 1, 1),
     (2, 28, 28, 192, 64, 3, 3, 1, 1), (5, 33, 29, 64, 64, 3, 3, 1, 1),
+    # dgrads whose OUTPUT is wide (two 256-column tiles; CTA pairs) -- the fused BN-backward reduction walks both passes
+    (4, 14, 14, 512, 512, 3, 3, 1, 1), (8, 28, 28, 512, 128, 1, 1, 1, 0), (4, 28, 28, 512, 512, 3, 3, 2, 1),
+    (4, 14, 14, 1024, 256, 1, 1, 1, 0), (3, 7, 7, 2048, 512, 1, 1, 1, 0), (2, 57, 55, 256, 64, 1, 1, 1, 0),
 ]
 
 
@@ -390,6 +393,38 @@ def group_conv():
             yf = y2.float()
             ok &= check(tag + ".stats_sum", stats[:Cout], yf.sum((0, 2, 3)), 1e-2, g)
             ok &= check(tag + ".stats_sumsq", stats[Cout:], (yf * yf).sum((0, 2, 3)), 1e-2, g)
+        # dgrad with the fused BatchNorm-backward reduction of the upstream layer (picd_conv_dgrad_bnreduce): dx must be
+        # bit-identical to the plain dgrad, the sums must match the fp32 evaluation on that dx
+        if not first:
+            for relu in (True, False):
+                gen = torch.Generator(device="cpu").manual_seed(11)
+                y_up = (torch.randn(N, Cin, H, W, generator=gen) * 1.5 + 0.3).to(dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+                coef = torch.stack([torch.randn(Cin, generator=gen), torch.randn(Cin, generator=gen) * 0.5,
+                                    torch.randn(Cin, generator=gen) * 0.3 + 0.3, torch.rand(Cin, generator=gen) + 0.5]).to(dev)
+                rec = native.BnRecord()
+                rec.y, rec.coef, rec.relu, rec.eligible = y_up, coef, relu, True
+                _, info = native._conv_forward(x, w.detach(), stride, pad, None, None, None)
+                dyb = dy.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+                keep = os.environ.get("PICD_FUSE_BN_REDUCE")
+                os.environ["PICD_FUSE_BN_REDUCE"] = "all"      # also the shapes the engine leaves to the separate kernel
+                try:
+                    dx_f, _ = native._conv_backward(info, dyb, w.detach(), True, False, src_bn=rec)
+                finally:
+                    if keep is None:
+                        os.environ.pop("PICD_FUSE_BN_REDUCE")
+                    else:
+                        os.environ["PICD_FUSE_BN_REDUCE"] = keep
+                dx_p, _ = native._conv_backward(info, dyb, w.detach(), True, False)
+                same = bool(torch.equal(dx_f, dx_p)) and rec.sums is not None
+                ok &= emit_ok({"group": g, "test": tag + f".dgrad_bnreduce[relu={relu}].dx_identical", "ok": same})
+                if rec.sums is not None:
+                    sums = rec.sums.view(-1, 2 * Cin).sum(0)
+                    yf, gf = y_up.float(), dx_p.float()
+                    sc, sh, mu, istd = [c.view(1, -1, 1, 1) for c in coef]
+                    gm = gf * ((yf * sc + sh) > 0) if relu else gf
+                    ok &= check(tag + f".dgrad_bnreduce[relu={relu}].sum_g", sums[:Cin], gm.sum((0, 2, 3)), 1e-2, g)
+                    ok &= check(tag + f".dgrad_bnreduce[relu={relu}].sum_g_xhat", sums[Cin:],
+                                (gm * (yf - mu) * istd).sum((0, 2, 3)), 1e-2, g)
     return ok
 
 

@@ -3,6 +3,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace picd {
@@ -10,6 +11,11 @@ namespace picd {
 static thread_local char g_error[1024] = "";
 static unsigned long long g_launches = 0;
 void count_launch() { __atomic_add_fetch(&g_launches, 1ULL, __ATOMIC_RELAXED); }
+
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("PICD_PDL"); return e == nullptr || e[0] != '0'; }();
+    return on;
+}
 
 void set_error(const char* fmt, ...) {
     va_list ap;

@@ -85,6 +85,7 @@ constexpr int ROW_UNROLL = 4;   // rows in flight per thread (memory-level paral
 __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ stats,
                                                        long long P, int C, int tx_count, int ty_count,
                                                        int rows_per_block) {
+    pdl_sync();
     const int vecs = C >> 3;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
@@ -138,6 +139,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, int replicas,
                                    const float* __restrict__ beta, float* running_mean, float* running_var,
                                    float momentum, float eps, float* scale, float* shift, float* mean_out,
                                    float* invstd_out, int C) {
+    pdl_sync();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float mean = fold_replicas(sums, c, 2 * C, replicas) / count;
@@ -159,6 +161,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, int replicas,
 __global__ void bn_eval_coeffs_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ running_mean, const float* __restrict__ running_var,
                                       float eps, float* scale, float* shift, int C) {
+    pdl_sync();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float sc = gamma[c] * rsqrtf(running_var[c] + eps);
@@ -200,6 +203,7 @@ __global__ void __launch_bounds__(256, MINB) bn_apply_kernel(const __nv_bfloat16
                                                        __nv_bfloat16* __restrict__ out, long long P, int C,
                                                        int tx_count, int ty_count, int rows_per_block,
                                                        uint8_t* __restrict__ relu_mask, const BnFinalizeArgs fin) {
+    pdl_sync();
     const int vecs = C >> 3;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
@@ -306,6 +310,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const __nv_bfloat
                                                             const float* __restrict__ invstd, int act,
                                                             float* __restrict__ sums, long long P, int C, int tx_count,
                                                             int ty_count, int rows_per_block) {
+    pdl_sync();
     const int vecs = C >> 3;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
@@ -364,6 +369,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(
     const float* __restrict__ param_sums, float* dgamma, float* dbeta, __nv_bfloat16* __restrict__ dy,
     __nv_bfloat16* __restrict__ dres, long long P, int C, int tx_count, int ty_count, int rows_per_block,
     int eval_mode, int sums_replicas, int param_replicas, const float* __restrict__ count_dev) {
+    pdl_sync();
     const int vecs = C >> 3;
     if (count_dev != nullptr) inv_count = 1.f / __ldg(count_dev);     // SyncBN: the exchanged global element count
     if (blockIdx.x == 0 && blockIdx.y == 0 && dgamma != nullptr) {
@@ -474,8 +480,8 @@ extern "C" int picd_bn_stats(const void* x, float* stats, long long P, int C, cu
     PICD_REQUIRE(C % 8 == 0, "bn_stats: C=%d must be a multiple of 8", C);
     const ReduceShape s = reduce_shape(P, C);
     const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
-    bn_stats_kernel<<<dim3(s.grid_x, s.grid_y), 256, smem, stream>>>(static_cast<const __nv_bfloat16*>(x), stats, P, C,
-                                                                     s.tx_count, s.ty_count, s.rows_per_block);
+    PICD_CUDA(launch_pdl(bn_stats_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
+                         static_cast<const __nv_bfloat16*>(x), stats, P, C, s.tx_count, s.ty_count, s.rows_per_block));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -486,8 +492,8 @@ extern "C" int picd_stat_replicas() { return STAT_REPLICAS; }
 extern "C" int picd_bn_finalize(const float* sums, int replicas, float count, const float* gamma, const float* beta,
                                 float* running_mean, float* running_var, float momentum, float eps, float* scale,
                                 float* shift, float* mean, float* invstd, int C, cudaStream_t stream) {
-    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums, replicas, count, gamma, beta, running_mean, running_var,
-                                                            momentum, eps, scale, shift, mean, invstd, C);
+    PICD_CUDA(launch_pdl(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, sums, replicas, count, gamma, beta,
+                         running_mean, running_var, momentum, eps, scale, shift, mean, invstd, C));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -495,8 +501,8 @@ extern "C" int picd_bn_finalize(const float* sums, int replicas, float count, co
 extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
                                    const float* running_var, float eps, float* scale, float* shift, int C,
                                    cudaStream_t stream) {
-    bn_eval_coeffs_kernel<<<(C + 127) / 128, 128, 0, stream>>>(gamma, beta, running_mean, running_var, eps, scale,
-                                                               shift, C);
+    PICD_CUDA(launch_pdl(bn_eval_coeffs_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, gamma, beta, running_mean,
+                         running_var, eps, scale, shift, C));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -515,10 +521,10 @@ static int bn_apply_impl(const void* y, float* scale, float* shift, const void* 
     static const int variant = [] { const char* e = getenv("PICD_BN_APPLY_VARIANT"); return e == nullptr ? 2 : atoi(e); }();   // 2 = 8 rows in flight (measured best)
     ReduceShape s = stream_shape(P, C);
 #define PICD_BN_APPLY_LAUNCH_A(U, MINB, A)                                                                         \
-    bn_apply_kernel<U, MINB, A><<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(                                      \
+    PICD_CUDA(launch_pdl(bn_apply_kernel<U, MINB, A>, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,               \
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,       \
         static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block,                           \
-        static_cast<uint8_t*>(relu_mask), fin)
+        static_cast<uint8_t*>(relu_mask), fin))
 #define PICD_BN_APPLY_LAUNCH(U, MINB)                                                                              \
     do {                                                                                                            \
         if (act == ACT_RELU) PICD_BN_APPLY_LAUNCH_A(U, MINB, ACT_RELU);                                             \
@@ -571,10 +577,10 @@ extern "C" int picd_bn_bwd_reduce_mask(const void* dz, const void* y, const void
     }
     const ReduceShape s = reduce_shape(P, C);
     const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
-    bn_bwd_reduce_kernel<<<dim3(s.grid_x, s.grid_y), 256, smem, stream>>>(
+    PICD_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, P, C, s.tx_count, s.ty_count,
-        s.rows_per_block);
+        s.rows_per_block));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -587,6 +593,7 @@ extern "C" int picd_bn_bwd_reduce(const void* dz, const void* y, const void* z, 
 
 // In-place fold of `replicas` copies of n floats into copy 0.
 __global__ void fold_replicas_kernel(float* buf, int n, int replicas) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     buf[i] = fold_replicas(buf, i, n, replicas);
@@ -604,11 +611,13 @@ extern "C" int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const v
                                           cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
     if (param_sums != nullptr && param_sums != sums && param_replicas > 1) {
-        fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(param_sums), 2 * C, param_replicas);
+        PICD_CUDA(launch_pdl(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(param_sums),
+                             2 * C, param_replicas));
         param_replicas = 1;
     }
     if (sums_replicas > 1) {
-        fold_replicas_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(const_cast<float*>(sums), 2 * C, sums_replicas);
+        PICD_CUDA(launch_pdl(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(sums), 2 * C,
+                             sums_replicas));
         if (param_sums == sums) param_replicas = 1;
         sums_replicas = 1;
     }
@@ -618,11 +627,11 @@ extern "C" int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const v
         if (rc >= 0) return rc;
     }
     const ReduceShape s = stream_shape(P, C);
-    bn_bwd_apply_kernel<<<dim3(s.grid_x, s.grid_y), 256, 0, stream>>>(
+    PICD_CUDA(launch_pdl(bn_bwd_apply_kernel, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
         dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,
-        s.rows_per_block, 0, sums_replicas, param_replicas, count_dev);
+        s.rows_per_block, 0, sums_replicas, param_replicas, count_dev));
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(SB_THREADS, 1) bn_stream_kernel(const StreamAr
         }
         fence_mbar_init();
     }
+    pdl_sync();        // the previous kernel (finalize / fold / the producer of the streamed tensors) has completed
     if (MODE == SB_BWD_APPLY && blockIdx.x == 0 && a.dgamma != nullptr) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             a.dbeta[c] += a.param_sums[c];
@@ -311,7 +312,7 @@ static int launch_stream(StreamArgs& a, cudaStream_t stream) {
     }
     long long grid = num_sms();
     if (grid > a.num_chunks) grid = a.num_chunks;
-    bn_stream_kernel<MODE><<<static_cast<unsigned>(grid), SB_THREADS, smem, stream>>>(a);
+    PICD_CUDA(launch_pdl(bn_stream_kernel<MODE>, dim3(static_cast<unsigned>(grid)), dim3(SB_THREADS), smem, stream, a));
     PICD_LAUNCH_CHECK();
     return 0;
 }

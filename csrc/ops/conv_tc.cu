@@ -38,6 +38,8 @@ constexpr int KCHUNK = 64;                   // bf16 elements per 128B swizzle r
 constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
 constexpr int SMEM_HEADER = 2048;           // mbarriers + TMEM base (first 512 B), bias tile of the CTA (1 KB at +512)
 constexpr int SMEM_BIAS_OFF = 512;
+constexpr int SMEM_HEADER_BNR = 5120;       // bn_reduce launches: + scale / shift / mean of the CTA's 256 channels (3 x 1 KB at +2048)
+constexpr int SMEM_COEF_OFF = 2048;
 constexpr int MAX_DYN_SMEM = 232448;         // 227 KB
 
 struct Tap {
@@ -69,6 +71,17 @@ struct ConvGemmParams {
     int halo;
     int a_stage_bytes;    // bytes of one A stage: 16 KB, or (bh + 2) * bw * 128 in halo mode
     int b_resident;       // halo mode, tiny weights: all 9 B taps are loaded once per CTA and stay in shared memory
+    int header_bytes;     // shared-memory header: SMEM_HEADER, or SMEM_HEADER_BNR when BatchNorm coefficient vectors are staged
+    // ---- fused BatchNorm-backward reduction (dgrad launches) --------------------------------------------------
+    // The tile this kernel stores is dz of the UPSTREAM conv+BN(+ReLU) layer.  With that layer's raw conv output y (ymap,
+    // same geometry as dmap: one extra TMA load per output pass) and its BN coefficients the epilogue accumulates
+    // sum(g) and sum(g * xhat), g = dz * [y*scale+shift > 0], xhat = (y - mean) * invstd, from the bf16-rounded values it
+    // stores -- exactly what bn_bwd_reduce would compute from a second pass over dz and y, which therefore disappears.
+    int bn_reduce;        // 0 / 1; the sums go to `stats` ([STAT_REPLICAS][2][Cout], same layout as the forward statistics)
+    int r_relu;           // upstream activation is ReLU (mask recomputed from y) or identity
+    int ybufs;            // y tiles in flight + 1: the tile of pass k + ybufs - 1 is requested when pass k starts (1..4)
+    CUtensorMap ymap;
+    const float* r_scale; const float* r_shift; const float* r_mean; const float* r_invstd;
 };
 
 struct WgradParams {
@@ -89,6 +102,7 @@ struct SmemBars {
     uint64_t tfull[2];
     uint64_t tempty[2];
     uint64_t bres;        // halo mode with resident weights: "all taps have landed"
+    uint64_t ybar[4];     // bn_reduce: "the upstream y tile of an output pass has landed" (one per y buffer)
     uint32_t tmem_base;
 };
 
@@ -114,10 +128,11 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                                                                   // a CTA of a pair holds half the rows
     const int b_stage = p.halo ? (p.b_resident ? 0 : 3 * b_tap) : b_tap;
     const int a_stage = p.a_stage_bytes;
-    uint8_t* sA = smem + SMEM_HEADER;
+    uint8_t* sA = smem + p.header_bytes;
     uint8_t* sB = sA + stages * a_stage;
     uint8_t* sBres = sB + stages * b_stage;                       // 9 resident taps (halo + b_resident only)
     uint8_t* sOut = sBres + (p.b_resident ? 9 * b_tap : 0);
+    uint8_t* sY = sOut + (BN < p.half_w ? BN : p.half_w) * 256;   // bn_reduce: upstream y tile of the current pass (same shape as sOut)
 
     const int warp = uniform_warp_id();      // provably warp-uniform: the role branches below stay convergent
     const int lane = threadIdx.x & 31;
@@ -132,6 +147,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
             mbar_init(&bars->tempty[i], kCluster ? 16 : 8);   // pair: the leader waits for both CTAs' epilogue warps
         }
         mbar_init(&bars->bres, 1);
+        for (int i = 0; i < 4; ++i) mbar_init(&bars->ybar[i], 1);
         fence_mbar_init();
     }
     if (kCluster) cluster_sync();          // both CTAs are resident before the pair-wide TMEM allocation
@@ -143,12 +159,14 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         tma_prefetch_desc(&p.amap[0]);
         tma_prefetch_desc(&p.bmap);
         tma_prefetch_desc(&p.dmap);
+        if (p.bn_reduce) tma_prefetch_desc(&p.ymap);
     }
     tc_fence_before();
     __syncthreads();
     if (kCluster) cluster_sync();          // the peer's barriers exist before anything arrives on them
     tc_fence_after();
     const uint32_t tmem_base = uniform_u32(bars->tmem_base);
+    pdl_sync();        // everything above overlapped the previous kernel's tail; from here on its results are visible
 
     const int numN = p.numN;
     const int crank = kCluster ? static_cast<int>(uniform_u32(cluster_ctarank())) : 0;
@@ -167,6 +185,17 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         for (int i = threadIdx.x; i < BN; i += blockDim.x) {
             const int c = n_tile * BN + i;
             sBias[i] = (p.bias != nullptr && c < p.Cout) ? p.bias[c] : 0.f;
+        }
+        __syncthreads();
+    }
+    float* sCoef = reinterpret_cast<float*>(smem + SMEM_COEF_OFF);       // [3][256]: scale, shift, mean of the upstream BN
+    if (p.bn_reduce) {
+        for (int i = threadIdx.x; i < BN; i += blockDim.x) {
+            const int c = n_tile * BN + i;
+            const bool in = c < p.Cout;
+            sCoef[i] = in ? p.r_scale[c] : 0.f;
+            sCoef[256 + i] = in ? p.r_shift[c] : 0.f;
+            sCoef[512 + i] = in ? p.r_mean[c] : 0.f;
         }
         __syncthreads();
     }
@@ -330,6 +359,34 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         const int n_halves = (BN + hw - 1) >> hw_log2;
         int acc = 0;
         uint32_t accphase = 0;
+        // bn_reduce: the y tiles are requested ybufs - 1 passes ahead of their use (an output pass of a short-K layer lasts
+        // less than one DRAM round trip).  Thread tid_e == 0 walks the same (tile, pass) sequence with a cursor of its own.
+        const uint32_t ysize = static_cast<uint32_t>(BN < hw ? BN : hw) * 256u;
+        int pf_m = m_first, pf_hf = 0;
+        uint32_t pf_cnt = 0, ycons = 0;
+        auto issue_y = [&]() {
+            if (pf_m >= m_limit) return;
+            if (pf_m < p.num_m_tiles) {
+                const int ptw = pf_m % p.tiles_w;
+                const int pth = (pf_m / p.tiles_w) % p.tiles_h;
+                const int ptn = pf_m / (p.tiles_w * p.tiles_h);
+                const int pcols = (BN - pf_hf * hw) < hw ? (BN - pf_hf * hw) : hw;
+                uint8_t* dst = sY + (pf_cnt % p.ybufs) * ysize;
+                uint64_t* bar = &bars->ybar[pf_cnt % p.ybufs];
+                uint32_t ybytes = 0;
+                for (int j = 0; j < (pcols >> 6); ++j)
+                    if (n_tile * BN + pf_hf * hw + j * 64 < p.Cout) ybytes += 16384;
+                mbar_arrive_expect_tx(bar, ybytes);
+                for (int j = 0; j < (pcols >> 6); ++j) {
+                    const int c0 = n_tile * BN + pf_hf * hw + j * 64;
+                    if (c0 < p.Cout) tma_load_4d(dst + j * 16384, &p.ymap, bar, c0, ptw * bw, pth * bh, ptn * bn);
+                }
+                ++pf_cnt;
+            }
+            if (++pf_hf == n_halves) { pf_hf = 0; pf_m += grid_m; }
+        };
+        if (p.bn_reduce && tid_e == 0)
+            for (int i = 0; i + 1 < p.ybufs; ++i) issue_y();
         const int iw = row & (bw - 1);
         const int ih = (row >> p.bw_log2) & (bh - 1);
         const int in_ = row >> (p.bw_log2 + p.bh_log2);
@@ -390,6 +447,9 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                 tmem_ld_32x32(t_row + (g0 + colhalf) * 32, va);       // in flight while the staging buffer drains
                 if (tid_e == 0) tma_store_wait_read();        // the previous TMA store has drained the staging buffer
                 named_barrier_sync(1, 256);
+                // everybody is past the statistics of the previous pass, so the y buffer it used is free: request the tile
+                // of the pass ybufs - 1 ahead into it
+                if (p.bn_reduce && tid_e == 0) issue_y();
 #pragma unroll 1
                 for (int j = 0; j < ngt; j += 2) {            // software pipeline: the next group loads while this one converts
                     const int gg = 2 * j + colhalf;
@@ -422,7 +482,61 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                     }
                     tma_store_commit();
                 }
-                if (p.stats != nullptr) {
+                if (p.bn_reduce && tile_ok) {
+                    // BatchNorm-backward sums of the upstream layer: g = dz * relu'(y*scale+shift) from the staged bf16 tile,
+                    // y from the tile TMA just delivered; thread -> (8-channel chunk, row group) as for the forward statistics
+                    const int nch = hcols >> 3;
+                    const int my_ch = tid_e & (nch - 1);
+                    const int rows_per_rg = nch >> 1;
+                    const int r0 = (tid_e / nch) * rows_per_rg;
+                    const uint32_t chunk_off = (my_ch >> 3) * 16384;
+                    const uint32_t stat_chunk = static_cast<uint32_t>(my_ch & 7);
+                    const uint32_t y_u32 = smem_u32(sY) + (ycons % p.ybufs) * ysize;
+                    float sc[8], sh[8], mu[8];
+                    {
+                        const uint32_t cbase = smem_u32(sCoef) + (hf * hw + my_ch * 8) * 4;
+#pragma unroll
+                        for (int i = 0; i < 8; i += 4) {
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(sc[i]), "=f"(sc[i + 1]), "=f"(sc[i + 2]), "=f"(sc[i + 3]) : "r"(cbase + i * 4));
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(sh[i]), "=f"(sh[i + 1]), "=f"(sh[i + 2]), "=f"(sh[i + 3]) : "r"(cbase + 1024 + i * 4));
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(mu[i]), "=f"(mu[i + 1]), "=f"(mu[i + 2]), "=f"(mu[i + 3]) : "r"(cbase + 2048 + i * 4));
+                        }
+                    }
+                    if (!p.r_relu) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { sc[i] = 0.f; sh[i] = 1.f; }      // mask always true
+                    }
+                    float s[8], qq[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] = 0.f; qq[i] = 0.f; }
+                    mbar_wait(&bars->ybar[ycons % p.ybufs], (ycons / p.ybufs) & 1u);
+                    ++ycons;
+#pragma unroll 2
+                    for (int r = r0; r < r0 + rows_per_rg; ++r) {
+                        const uint32_t off = chunk_off + r * 128 + ((stat_chunk ^ (r & 7)) << 4);
+                        uint32_t w4[4], y4[4];
+                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(w4[0]), "=r"(w4[1]), "=r"(w4[2]), "=r"(w4[3]) : "r"(sOut_u32 + off));
+                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(y4[0]), "=r"(y4[1]), "=r"(y4[2]), "=r"(y4[3]) : "r"(y_u32 + off));
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 f = unpack_bf16x2(w4[i]);
+                            const float2 yv = unpack_bf16x2(y4[i]);
+                            const float g0 = fmaf(yv.x, sc[2 * i], sh[2 * i]) > 0.f ? f.x : 0.f;
+                            const float g1 = fmaf(yv.y, sc[2 * i + 1], sh[2 * i + 1]) > 0.f ? f.y : 0.f;
+                            s[2 * i] += g0; qq[2 * i] = fmaf(g0, yv.x - mu[2 * i], qq[2 * i]);
+                            s[2 * i + 1] += g1; qq[2 * i + 1] = fmaf(g1, yv.y - mu[2 * i + 1], qq[2 * i + 1]);
+                        }
+                    }
+                    if (hf == 0) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { stS[0][i] += s[i]; stQ[0][i] += qq[i]; }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { stS[1][i] += s[i]; stQ[1][i] += qq[i]; }
+                    }
+                } else if (p.stats != nullptr && !p.bn_reduce) {
                     // per-channel sum / sumsq of the bf16-rounded outputs (what BatchNorm will actually read): every thread
                     // owns one 16-byte chunk (8 channels) over a group of rows, read back from the staging tile with v4 loads
                     const int nch = hcols >> 3;                            // 8, 16 or 32 chunks per row
@@ -484,7 +598,11 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                         b += red[(g * 2 + 1) * hcols + tid_e];
                     }
                     const int c = n_tile * BN + hf * hw + tid_e;
-                    if (c < p.Cout) { atomicAdd(st + c, a); atomicAdd(st + p.Cout + c, b); }
+                    if (c < p.Cout) {
+                        if (p.bn_reduce) b *= p.r_invstd[c];          // sum(g * (y - mean)) -> sum(g * xhat)
+                        atomicAdd(st + c, a);
+                        atomicAdd(st + p.Cout + c, b);
+                    }
                 }
             }
         }
@@ -536,6 +654,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = uniform_u32(bars->tmem_base);
+    pdl_sync();
 
     const int inner = p.ngroups * p.numM * p.numN;
     const int split = blockIdx.x / inner;
@@ -769,9 +888,24 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     const int resident = p.b_resident ? 9 * BN * 128 : 0;
     const int stage_bytes = p.a_stage_bytes + (p.halo ? (p.b_resident ? 0 : 3 * BN * 128) : (p.cluster ? BN / 2 : BN) * 128);
     // short-K tiles are epilogue-bound: drain 256 columns in one pass; otherwise drain halves and spend the smem on stages
-    p.half_w = (BN == 256 && p.ntaps * p.kchunks <= 2) ? 256 : 128;
+    p.half_w = (BN == 256 && p.ntaps * p.kchunks <= 2 && !p.bn_reduce) ? 256 : 128;
     const int staging = std::min(BN, p.half_w) * 256;   // 128 rows x half_w columns x 2 B
-    int stages = (MAX_DYN_SMEM - 1024 - SMEM_HEADER - staging - resident) / stage_bytes;
+    p.header_bytes = p.bn_reduce ? SMEM_HEADER_BNR : SMEM_HEADER;
+    // bn_reduce: 1-3 more staging-sized buffers receive the upstream y tiles, requested ybufs - 1 output passes ahead; deep
+    // prefetch where shared memory allows it without starving the operand ring
+    p.ybufs = 0;
+    if (p.bn_reduce) {
+        const char* fe = getenv("PICD_YBUFS");             // tuning override, read per call (benchmarks flip it in-process)
+        const int forced = fe == nullptr ? 0 : atoi(fe);
+        // measured (benchmarks/fused_reduce_layers.py): a second buffer pays only for short-K tiles, whose output pass is
+        // shorter than a DRAM round trip (56x56 64 <- 256 1x1: 0.123 -> 0.103 ms); elsewhere the operand ring needs the
+        // shared memory more (14x14 256 <- 256 3x3: 0.057 -> 0.059 -> 0.072 ms with 1 / 2 / 3 buffers)
+        const int k_iters = p.halo ? 3 * p.kchunks : p.ntaps * p.kchunks;
+        p.ybufs = 1;
+        if (k_iters <= 4 && (MAX_DYN_SMEM - 1024 - p.header_bytes - staging * 3 - resident) / stage_bytes >= 3) p.ybufs = 2;
+        if (forced >= 1 && forced <= 4) p.ybufs = forced;
+    }
+    int stages = (MAX_DYN_SMEM - 1024 - p.header_bytes - staging * (1 + p.ybufs) - resident) / stage_bytes;
     stages = std::min(stages, (p.halo || p.cluster) ? 8 : 6);
     PICD_REQUIRE(stages >= 2, "conv_gemm: tile does not fit shared memory (BN=%d)", BN);
     p.stages = stages;
@@ -794,11 +928,13 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
         cfg.blockDim = dim3(320);
         cfg.dynamicSmemBytes = MAX_DYN_SMEM;
         cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = pdl_enabled() ? 2 : 1;
         if (bias_act) PICD_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<true, true>, p));
         else PICD_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<false, true>, p));
         count_launch();
@@ -809,9 +945,9 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
     grid = std::max(p.numN, grid / p.numN * p.numN);
     // request the whole smem so that exactly one CTA (and one 512-column TMEM allocation) lives on an SM
     if (bias_act)
-        conv_gemm_kernel<true, false><<<grid, 320, MAX_DYN_SMEM, stream>>>(p);
+        PICD_CUDA(launch_pdl(conv_gemm_kernel<true, false>, dim3(grid), dim3(320), MAX_DYN_SMEM, stream, p));
     else
-        conv_gemm_kernel<false, false><<<grid, 320, MAX_DYN_SMEM, stream>>>(p);
+        PICD_CUDA(launch_pdl(conv_gemm_kernel<false, false>, dim3(grid), dim3(320), MAX_DYN_SMEM, stream, p));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -874,11 +1010,20 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
     return launch_conv_gemm(p, Cout, stream);
 }
 
+// Fused BatchNorm-backward reduction of a dgrad launch (see ConvGemmParams::bn_reduce): dx is dz of the upstream BN layer.
+struct BnReduceArgs {
+    const void* y;            // the upstream layer's raw conv output, [N,H,W,Cin] bf16 (same shape as dx)
+    const float* scale; const float* shift; const float* mean; const float* invstd;     // [Cin]
+    float* sums;              // [STAT_REPLICAS][2][Cin], zeroed by the caller
+    int relu;                 // the upstream activation is ReLU (else identity)
+};
+
 // dx[N,H,W,Cin] = conv_transpose(dy[N,OH,OW,Cout], w[Cout,R,S,Cin]).  Weights are read through an MN-major
 // descriptor, i.e. the same tensor as fprop.  Stride 2 = one launch per output parity class.
 static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
                            int R, int S, int stride, int pad_h, int pad_w, int OH, int OW, int accumulate,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const BnReduceArgs* bnr = nullptr) {
+    PICD_REQUIRE(bnr == nullptr || !accumulate, "conv_dgrad: the fused BN reduction needs the FINAL gradient, not a partial sum");
     PICD_REQUIRE(stride == 1 || stride == 2, "conv_dgrad: stride %d unsupported", stride);
     PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_dgrad: channels must be multiples of 8");
     // If some output parity class receives no tap (e.g. 1x1 stride-2), zero dx once BEFORE any class is written.
@@ -925,6 +1070,12 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
                 if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
             }
             if (make_act_map(&p.dmap, dx, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+            if (bnr != nullptr) {
+                if (make_act_map(&p.ymap, bnr->y, N, H, W, Cin, stride, ph, pw, bw, bh, g.bn)) return 3;
+                p.bn_reduce = 1;
+                p.r_relu = bnr->relu;
+                p.r_scale = bnr->scale; p.r_shift = bnr->shift; p.r_mean = bnr->mean; p.r_invstd = bnr->invstd;
+            }
             p.ntaps = nt;
             p.kchunks = ceil_div(Cout, KCHUNK);
             p.b_mn = 1;
@@ -932,7 +1083,7 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
             p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
             p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
             p.W = Wv; p.H = Hv; p.N = N;
-            p.stats = nullptr; p.bias = nullptr; p.act = ACT_NONE;
+            p.stats = bnr != nullptr ? bnr->sums : nullptr; p.bias = nullptr; p.act = ACT_NONE;
             p.reduce_add = accumulate;
             {
                 int BNd;
@@ -958,6 +1109,19 @@ extern "C" int picd_conv_dgrad_accumulate(const void* dy, const void* w, void* d
     return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, 1, stream);
 }
 
+// dx = conv_transpose(dy, w) where dx is the gradient dz flowing into an upstream conv + BatchNorm(+ReLU) layer: the epilogue
+// also accumulates that layer's BatchNorm-backward sums sum(g), sum(g * xhat) (g = dz masked by the ReLU, recomputed from
+// y_up * scale + shift) into sums[STAT_REPLICAS][2][Cin] -- the separate bn_bwd_reduce pass over dz and y_up disappears
+// (torch/nn/modules/_functions.py:144-153 batch_norm_backward_reduce).  Stride-2 dgrads with an empty parity class leave zeros
+// there, which contribute nothing.
+extern "C" int picd_conv_dgrad_bnreduce(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                        int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                                        const void* y_up, const float* scale, const float* shift, const float* mean,
+                                        const float* invstd, int relu, float* sums, cudaStream_t stream) {
+    PICD_REQUIRE(y_up != nullptr && sums != nullptr, "conv_dgrad_bnreduce: y_up / sums must not be null");
+    BnReduceArgs b{y_up, scale, shift, mean, invstd, sums, relu};
+    return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, 0, stream, &b);
+}
 // dw[Cout,R,S,Cin] (fp32) += sum over pixels of dy (x) x.  The caller provides a zeroed (or accumulating) buffer.
 extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
                                int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
@@ -1041,7 +1205,7 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
         PICD_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
         attr_set = true;
     }
-    conv_wgrad_kernel<<<inner * ksplit, 192, smem_launch, stream>>>(p);
+    PICD_CUDA(launch_pdl(conv_wgrad_kernel, dim3(inner * ksplit), dim3(192), smem_launch, stream, p));
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -41,6 +41,14 @@ int picd_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W
 /* dx += ...: same as picd_conv_dgrad but ADDS into the existing bf16 dx with TMA reduce-add (residual-gradient fusion) */
 int picd_conv_dgrad_accumulate(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R,
                                int S, int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
+/* dgrad whose output is the gradient dz flowing into an upstream conv + BatchNorm(+ReLU) layer: the epilogue also reduces
+ * that layer's BatchNorm-backward sums sum(g), sum(g * xhat) into sums[STAT_REPLICAS][2][Cin] (zeroed by the caller), g = dz
+ * masked by the upstream ReLU (recomputed from y_up * scale + shift).  Replaces the separate batch_norm_backward_reduce pass
+ * (torch/nn/modules/_functions.py:144-153 via train.py:72). */
+int picd_conv_dgrad_bnreduce(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
+                             int stride, int pad_h, int pad_w, int OH, int OW, const void* y_up, const float* scale,
+                             const float* shift, const float* mean, const float* invstd, int relu, float* sums,
+                             cudaStream_t stream);
 /* dw (fp32, [Cout,R,S,Cin]) += ...; accumulates with red.add, so it can target the gradient arena directly */
 int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
                     int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);

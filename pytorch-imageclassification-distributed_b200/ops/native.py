@@ -31,6 +31,7 @@ _SIG = {
     "picd_conv_fprop": "pppppi" + "i" * 12 + "p",
     "picd_conv_dgrad": "ppp" + "i" * 12 + "p",
     "picd_conv_dgrad_accumulate": "ppp" + "i" * 12 + "p",
+    "picd_conv_dgrad_bnreduce": "ppp" + "i" * 12 + "ppppp" + "i" + "p" + "p",
     "picd_conv_wgrad": "ppp" + "i" * 12 + "p",
     "picd_attention_fwd": "pppiiip",
     "picd_attention_bwd": "ppppppiiip",
@@ -324,9 +325,49 @@ def fork_n(x, n: int):
     return list(_ForkFn.apply(x, n)), GradFork()
 
 
-def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool, accumulate_into=None):
+class BnRecord:
+    """What a conv + BatchNorm(+ReLU) layer leaves behind for whoever produces the gradient of its OUTPUT.
+
+    The BatchNorm backward needs two per-channel sums over (dz, y) before it can write dy.  When the layer's output feeds
+    exactly one convolution, that convolution's dgrad kernel -- the kernel that writes dz -- can accumulate the sums in
+    its epilogue (``picd_conv_dgrad_bnreduce``): it only needs this layer's raw conv output ``y`` and BN coefficients, which
+    this record carries from forward to backward.  The producer fills ``sums`` and remembers which tensor it wrote
+    (``dz``); the layer's own backward uses the sums only if autograd hands it exactly that tensor (a second consumer
+    of the activation would make autograd sum gradients into a new tensor, and the separate reduction kernel runs).
+
+    Residual layers (two consumers, ReLU behind the skip add) keep the separate reduction: a form of the dgrad that loads
+    the skip branch's gradient tile, adds, stores and reduces with the forward's ReLU bit mask was built and measured
+    SLOWER than TMA reduce-add + bn_bwd_reduce (3.2 vs 2.3 ms per ResNet-50 step over the 16 layers): three staged tiles
+    per output pass make the epilogue, not HBM, the limit of these short-K 1x1 dgrads."""
+    __slots__ = ("y", "coef", "relu", "eligible", "sums", "dz")
+
+    def __init__(self):
+        self.y = self.coef = self.sums = self.dz = None
+        self.relu, self.eligible = False, False
+
+
+_FUSE_BN_REDUCE = os.environ.get("PICD_FUSE_BN_REDUCE", "1") != "0"     # A/B switch
+
+
+def _fused_reduce_pays(i: _ConvInfo) -> bool:
+    """Where the fused reduction beats dgrad + bn_bwd_reduce (benchmarks/fused_reduce_layers.py, ResNet-50 shapes at batch
+    256: 2.65 -> 2.34 ms per step over the 32 eligible layers).  It loses where the dgrad is already bound by its epilogue:
+    stride-2 dgrads (four parity launches, each paying the extra tile traffic: 0.119 -> 0.129 ms) and 3x3 layers with
+    64-wide tiles (0.120 -> 0.128 ms)."""
+    if os.environ.get("PICD_FUSE_BN_REDUCE") == "all":
+        return True
+    if i.stride != 1:
+        return False
+    if i.R * i.S > 1 and i.Cin <= 64:
+        return False
+    return True
+
+
+def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool, accumulate_into=None,
+                   src_bn: Optional["BnRecord"] = None):
     """Returns (dx or None, dw tensor or None).  dw is None when it was routed into the arena.  ``accumulate_into``:
-    an existing bf16 NHWC tensor of dx's shape that dx is added to (and which is returned as dx)."""
+    an existing bf16 NHWC tensor of dx's shape that dx is added to (and which is returned as dx).  ``src_bn``: record of
+    the conv+BN layer that produced this conv's input -- its BatchNorm-backward sums are then reduced by the dgrad."""
     i = info
     dx = None
     if need_dx:
@@ -337,6 +378,14 @@ def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: 
             dx = accumulate_into
             call("picd_conv_dgrad_accumulate", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph,
                  i.pw, i.OH, i.OW)
+        elif _FUSE_BN_REDUCE and src_bn is not None and src_bn.eligible and src_bn.y is not None and \
+                tuple(src_bn.y.shape) == (i.N, i.Cin, i.H, i.W) and _fused_reduce_pays(i):
+            dx = empty_nhwc(i.N, i.Cin, i.H, i.W, dy.device)
+            coef = src_bn.coef
+            sums = stat_buffer(i.Cin, dy.device)
+            call("picd_conv_dgrad_bnreduce", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                 i.OH, i.OW, src_bn.y, coef[0], coef[1], coef[2], coef[3], int(src_bn.relu), sums)
+            src_bn.sums, src_bn.dz = sums, dx
         else:
             dx = empty_nhwc(i.N, i.Cin, i.H, i.W, dy.device)
             call("picd_conv_dgrad", dy, i.w_sh, dx, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
@@ -412,7 +461,8 @@ def _bn_allreduce_bwd(sums2, sync_group, C):
 
 
 class _BNCfg:
-    __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group", "fork", "fork_role")
+    __slots__ = ("stride", "padding", "training", "momentum", "eps", "act", "rm", "rv", "sync_group", "fork", "fork_role",
+                 "rec", "src_rec")
 
 
 # Opt-in: let the apply kernel compute scale / shift from the batch sums itself (picd_bn_finalize_apply).  Measured SLOWER
@@ -451,6 +501,12 @@ def _bn_apply_fwd(ctx, y, gamma, beta, residual, cfg: _BNCfg, sums, count):
         call("picd_bn_apply_mask", y, coef[0], coef[1], res, ACT[cfg.act], z, ctx.relu_mask, P, C)
     ctx.bn_total, ctx.bn_act, ctx.bn_training, ctx.bn_total_dev = total, cfg.act, cfg.training, total_dev
     ctx.bn_sync, ctx.has_res = cfg.sync_group, residual is not None
+    rec = getattr(cfg, "rec", None)
+    ctx.bn_rec = rec
+    if rec is not None:
+        # the consumer's dgrad may reduce this layer's backward sums when the ReLU mask can be recomputed from y alone
+        rec.y, rec.coef, rec.relu = y, coef, cfg.act == "relu"
+        rec.eligible = bool(cfg.training and residual is None and cfg.act in ("relu", "none") and C % 8 == 0)
     return z, coef
 
 
@@ -466,9 +522,16 @@ def _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, need_dres):
     if not ctx.bn_training:
         call("picd_bn_bwd_eval", dz, y, zmask, coef[0], coef[1], act, dy, dres, P, C)
         return dy, dres, None, None
-    sums2 = stat_buffer(C, y.device)
     rmask = getattr(ctx, "relu_mask", None) if zmask is not None else None
-    call("picd_bn_bwd_reduce_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
+    rec = getattr(ctx, "bn_rec", None)
+    if rec is not None and rec.sums is not None and rec.dz is not None and rec.dz.data_ptr() == dz.data_ptr() and \
+            rec.dz.shape == dz.shape:
+        sums2 = rec.sums            # reduced by the dgrad kernel that wrote dz (picd_conv_dgrad_bnreduce)
+    else:
+        sums2 = stat_buffer(C, y.device)
+        call("picd_bn_bwd_reduce_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
+    if rec is not None:
+        rec.y = rec.coef = rec.sums = rec.dz = None
     gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C)
     gt, g_routed = _grad_target(gamma)
     bt, b_routed = _grad_target(beta)
@@ -495,6 +558,7 @@ class _ConvBnAct(torch.autograd.Function):
         ctx.save_for_backward(w, gamma, beta, y, z, coef)
         ctx.x_needs_grad = x.requires_grad
         ctx.fork, ctx.fork_role = getattr(cfg, "fork", None), getattr(cfg, "fork_role", None)
+        ctx.src_rec = getattr(cfg, "src_rec", None)
         return z
 
     @staticmethod
@@ -506,7 +570,8 @@ class _ConvBnAct(torch.autograd.Function):
         if fork_ is not None and role == "deposit_res" and dres is not None:
             fork_.partner = dres
         acc = fork_.partner if (fork_ is not None and role == "accumulate") else None
-        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1], accumulate_into=acc)
+        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1], accumulate_into=acc,
+                                src_bn=ctx.src_rec if fork_ is None else None)
         if fork_ is not None:
             if role == "deposit_dx" and dx is not None:
                 fork_.partner = dx
@@ -520,7 +585,14 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride, padding
     cfg.stride, cfg.padding, cfg.training, cfg.momentum, cfg.eps = stride, padding, training, momentum, eps
     cfg.act, cfg.rm, cfg.rv, cfg.sync_group = act or "none", running_mean, running_var, sync_group
     cfg.fork, cfg.fork_role = grad_fork if grad_fork is not None else (None, None)
-    return _ConvBnAct.apply(x, w, gamma, beta, residual, cfg)
+    # BatchNorm-backward reduction fused into the consumer's dgrad (BnRecord): this layer publishes a record on its output,
+    # and picks up the record of the layer that produced its input
+    cfg.rec = BnRecord() if (training and torch.is_grad_enabled()) else None
+    cfg.src_rec = getattr(x, "_bn_rec", None)
+    out = _ConvBnAct.apply(x, w, gamma, beta, residual, cfg)
+    if cfg.rec is not None:
+        out._bn_rec = cfg.rec
+    return out
 
 
 class _BnAct(torch.autograd.Function):
@@ -549,6 +621,7 @@ def bn_act(y, gamma, beta, running_mean, running_var, *, training, momentum, eps
     cfg = _BNCfg()
     cfg.stride = cfg.padding = None
     cfg.fork = cfg.fork_role = None
+    cfg.rec = cfg.src_rec = None
     cfg.training, cfg.momentum, cfg.eps = training, momentum, eps
     cfg.act, cfg.rm, cfg.rv, cfg.sync_group = act or "none", running_mean, running_var, sync_group
     return _BnAct.apply(y, gamma, beta, residual, cfg)

@@ -4,3 +4,4 @@ from .checkpoint import (BEST, LATEST, checkpoint_path, load_checkpoint, prefixe
 from .meters import Accuracy, AverageMeter
 
 __all__ = [n for n in dir() if not n.startswith("_")]
+from .lagged import LaggedScalarReader  # noqa: E402,F401
