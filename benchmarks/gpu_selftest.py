@@ -286,6 +286,12 @@ def group_gemm():
         dw = torch.zeros(N, K, dtype=torch.float32, device=dev)
         native.call("picd_gemm_tn_f32", dy, a, dw, M, N, K)
         ok &= check(f"gemm_tn[{M},{N},{K}]", dw, dy.float().t() @ a.float(), 1.5e-2, g)
+        # wgrad + bias gradient (ones-tile MMA) in one kernel
+        dw2 = torch.zeros(N, K, dtype=torch.float32, device=dev)
+        db = torch.zeros(N, dtype=torch.float32, device=dev)
+        native.call("picd_gemm_tn_f32_bias", dy, a, dw2, db, M, N, K)
+        ok &= check(f"gemm_tn_bias[{M},{N},{K}].dw", dw2, dy.float().t() @ a.float(), 1.5e-2, g)
+        ok &= check(f"gemm_tn_bias[{M},{N},{K}].db", db, dy.float().sum(0), 1e-2, g)
     # throughput of the big ones
     for (M, N, K) in [(8192, 8192, 8192), (50432, 3072, 768), (50432, 768, 3072)]:
         a = torch.randn(M, K, device=dev).to(torch.bfloat16)

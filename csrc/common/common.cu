@@ -12,9 +12,11 @@ static thread_local char g_error[1024] = "";
 static unsigned long long g_launches = 0;
 void count_launch() { __atomic_add_fetch(&g_launches, 1ULL, __ATOMIC_RELAXED); }
 
-bool pdl_enabled() {
-    static const bool on = [] { const char* e = getenv("PICD_PDL"); return e == nullptr || e[0] != '0'; }();
-    return on;
+bool pdl_enabled(int cls) {
+    // default: every class.  Measured: -0.12 ms per ResNet-50 step (19.35 -> 19.2), neutral within noise on the ViT-B/16 step
+    // (21.26 - 21.55 ms for any mask on a power-capped box)
+    static const int mask = [] { const char* e = getenv("PICD_PDL"); return e == nullptr ? 15 : atoi(e); }();
+    return (mask & cls) != 0;
 }
 
 void set_error(const char* fmt, ...) {

@@ -58,9 +58,10 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // prologue and then block in pdl_wait() until the previous grid has COMPLETED and its memory is visible.  Rule for every such
 // kernel: no global-memory access before pdl_wait().  Works inside CUDA-graph capture (programmatic edges).  PICD_PDL=0
 // launches everything the classic way (A/B switch).
-bool pdl_enabled();
+enum PdlClass { PDL_CONV = 1, PDL_BN = 2, PDL_ATTN = 4, PDL_ROWWISE = 8 };     // PICD_PDL = bit mask of the classes that use it
+bool pdl_enabled(int cls = PDL_CONV);
 #ifdef __CUDACC__
-template <typename... Params, typename... Args>
+template <int CLS = PDL_CONV, typename... Params, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {
     cudaLaunchConfig_t cfg{};
@@ -72,7 +73,7 @@ inline cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, 
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = pdl_enabled(CLS) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
 }
 #endif

@@ -24,6 +24,8 @@ constexpr int ATT_MAX_S = 256;
 struct AttnParams {
     CUtensorMap qkv_map;     // [B*S rows, 3*H*64 cols] bf16, box (64, 128)
     CUtensorMap do_map;      // [B*S rows, H*64 cols]  bf16, box (64, 128)   (backward)
+    CUtensorMap qkv_map64;   // the same tensors with 64-row boxes (query sub-tiles of the dK / dV kernel)
+    CUtensorMap do_map64;
     __nv_bfloat16* o;        // fwd out / bwd in   [B*S, H*64]
     const __nv_bfloat16* dout;
     __nv_bfloat16* dqkv;     // [B*S, 3*H*64]
@@ -38,6 +40,15 @@ struct AttBars {
     uint32_t tmem_base;
 };
 
+// 2^x on the SFU in ONE instruction.  exp2f() without fast-math expands to a range check + scaling around ex2.approx (denormal
+// results), which the softmax does not need: every argument is <= 0 after the row maximum / log-sum-exp is subtracted, and
+// results below 2^-126 flush to zero, which is what a bf16 probability becomes anyway.  ncu showed these kernels issue-bound
+// (34 % issue utilisation with 16 warps, the rest latency), so instruction count matters.
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ uint8_t* att_align(uint8_t* p) {
     return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~static_cast<uintptr_t>(1023));
 }
@@ -93,6 +104,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = uniform_u32(bars->tmem_base);
+    pdl_sync();
     const int HD = p.H * ATT_D;
     const int row_base = b * p.S;
 
@@ -122,9 +134,14 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
         uint32_t v[32];
         tmem_ld_32x32(t_row + g * 32, v);
         tmem_ld_wait();
+        if (g * 32 + 32 <= p.S) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (g * 32 + i < p.S) mx = fmaxf(mx, __uint_as_float(v[i]));
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (g * 32 + i < p.S) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
     }
     s_red[half * 128 + row] = mx;
     __syncthreads();                       // also: every S read of pass 1 is done
@@ -138,11 +155,18 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
         tmem_ld_32x32(t_row + g * 32, v);
         tmem_ld_wait();
         float f[32];
+        if (g * 32 + 32 <= p.S) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            const float e = (g * 32 + i < p.S) ? exp2f(fmaf(__uint_as_float(v[i]), p.scale_log2e, -m2)) : 0.f;
-            f[i] = e;
-            l += e;
+            for (int i = 0; i < 32; ++i) {
+                f[i] = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -m2));
+                l += f[i];
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                f[i] = (g * 32 + i < p.S) ? fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -m2)) : 0.f;
+                l += f[i];
+            }
         }
         store_row_chunk32(sP_u32, row, g * 32, f);       // overwrites Q/K: the S = Q K^T chain has completed (mma0)
     }
@@ -188,168 +212,218 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------------ backward: dQ (+ delta)
-// Persistent: one CTA per SM walks (batch, head, query tile) items; the Q / dO / K / V tiles of item i+1 are prefetched by
-// TMA into the other half of shared memory while item i computes, and barrier setup / TMEM allocation happen once per CTA
-// (they and the load latency were ~40% of the former one-item-per-CTA kernel).  dS overwrites the Q / dO / V tiles of its own
-// item (they are dead once S and dP sit in TMEM), which is what makes two 96 KB item buffers fit.
-constexpr int ATT_DQ_ITEM_BYTES = 32768 + 16384 + 16384 + 32768;      // K | Q | dO | V   (dS aliases Q..V: 64 KB)
+// One CTA per (batch, head, 128-query tile), TWO CTAs per SM.  The former version kept S = Q K^T and dP = dO V^T side by side in
+// TMEM (2 x 256 columns = the whole TMEM, one CTA per SM) and ran its phases -- load, MMA, exp, MMA, store: ~10 us of latency
+// per item -- back to back with nothing to overlap them but a prefetch.  Here S and dP share ONE set of columns: the
+// probabilities P = exp2(S * c - lse) are packed to bf16 and parked in registers (two threads per row, <= 64 registers each)
+// while the dP MMA overwrites S; dS = P o (dP - delta) * scale then goes to shared memory over the dead Q / dO / V tiles and
+// dQ = dS K lands in the same columns again.  256 TMEM columns and 98 KB of shared memory per CTA: two CTAs per SM hide
+// each other's latency chain.
 struct AttDqBars {
-    uint64_t load[2], mma0, mma1;
+    uint64_t load, mma0, mma1, mma2;
     uint32_t tmem_base;
 };
-__global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_constant__ AttnParams p) {
+__device__ __forceinline__ void store_row_chunk32_bits(uint32_t tile_u32, int row, int col0, const uint32_t (&f)[32]) {
+    const uint32_t dst = tile_u32 + (col0 >> 6) * 16384 + row * 128;
+    const uint32_t half = static_cast<uint32_t>((col0 >> 5) & 1) * 64;
+    const uint32_t rx = static_cast<uint32_t>(row & 7) << 4;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const uint32_t a0 = pack_bf16x2(__uint_as_float(f[8 * c + 0]), __uint_as_float(f[8 * c + 1]));
+        const uint32_t a1 = pack_bf16x2(__uint_as_float(f[8 * c + 2]), __uint_as_float(f[8 * c + 3]));
+        const uint32_t a2 = pack_bf16x2(__uint_as_float(f[8 * c + 4]), __uint_as_float(f[8 * c + 5]));
+        const uint32_t a3 = pack_bf16x2(__uint_as_float(f[8 * c + 6]), __uint_as_float(f[8 * c + 7]));
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + ((half + c * 16) ^ rx)), "r"(a0), "r"(a1), "r"(a2),
+                     "r"(a3)
+                     : "memory");
+    }
+}
+__global__ void __launch_bounds__(256, 2) attn_bwd_dq_kernel(const __grid_constant__ AttnParams p) {
     extern __shared__ uint8_t att_raw[];
     uint8_t* smem = att_align(att_raw);
     AttDqBars* bars = reinterpret_cast<AttDqBars*>(smem);
-    uint8_t* buf0 = smem + 1024;
+    uint8_t* sK = smem + 1024;            // 32 KB
+    uint8_t* sQ = sK + 32768;             // 16 KB
+    uint8_t* sdO = sQ + 16384;            // 16 KB
+    uint8_t* sV = sdO + 16384;            // 32 KB
+    uint8_t* sdS = sQ;                    // 64 KB over Q | dO | V once S and dP have been computed
     const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
     const int half = warp >> 2;          // two threads per query row: alternate 32-column chunks
     const int n_tiles = (p.S + ATT_TILE - 1) / ATT_TILE;
-    const int items = p.B * p.H * n_tiles;
+    const int item = blockIdx.x;
+    const int mt = item % n_tiles, bh = item / n_tiles;
+    const int h = bh % p.H, bb = bh / p.H;
+    const int row_base = bb * p.S, q0 = mt * ATT_TILE;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars->load[0], 1); mbar_init(&bars->load[1], 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
+        mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1); mbar_init(&bars->mma2, 1);
         fence_mbar_init();
+        tma_prefetch_desc(&p.qkv_map); tma_prefetch_desc(&p.do_map);
     }
-    if (warp == 0) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+    if (warp == 0) { tmem_alloc(&bars->tmem_base, 256); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = uniform_u32(bars->tmem_base);
+    pdl_sync();
     const int HD = p.H * ATT_D;
 
-    auto issue_loads = [&](int item, int b) {          // whole warp 0; one elected lane issues
-        const int mt = item % n_tiles, bh = item / n_tiles;
-        const int h = bh % p.H, bb = bh / p.H;
-        const int row_base = bb * p.S, q0 = mt * ATT_TILE;
-        uint8_t* sK = buf0 + b * ATT_DQ_ITEM_BYTES;
-        uint8_t* sQ = sK + 32768;
-        uint8_t* sdO = sQ + 16384;
-        uint8_t* sV = sdO + 16384;
-        mbar_arrive_expect_tx_warp(&bars->load[b], 16384 * 6);
-        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load[b], h * ATT_D, row_base + q0);
-        tma_load_2d_warp(sdO, &p.do_map, &bars->load[b], h * ATT_D, row_base + q0);
-        tma_load_2d_warp(sK, &p.qkv_map, &bars->load[b], HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load[b], HD + h * ATT_D, row_base + 128);
-        tma_load_2d_warp(sV, &p.qkv_map, &bars->load[b], 2 * HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load[b], 2 * HD + h * ATT_D, row_base + 128);
-    };
+    if (warp == 0) {          // whole warp, one elected lane issues
+        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 6);
+        tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
+        tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
+        mbar_wait(&bars->load, 0);
+        tc_fence_after();
+        const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)      // S = Q K^T
+            umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma0);
+    }
+    const int row = (warp & 3) * 32 + lane;
+    const int q = q0 + row;
+    const bool qvalid = q < p.S;
+    // delta = rowsum(dO o O), straight from global memory (128 B per tensor per thread); overlaps the loads and the S MMA
+    float delta = 0.f;
+    if (qvalid) {
+        const uint4* po = reinterpret_cast<const uint4*>(p.o + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
+        const uint4* pd = reinterpret_cast<const uint4*>(p.dout + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const uint4 a = po[c], d = pd[c];
+            const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+            const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
+            delta += a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
+        }
+        if (half == 0) p.delta[(static_cast<size_t>(bb) * p.H + h) * p.S + q] = delta;
+    }
+    const float lse = qvalid ? p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + q] : 0.f;
+    const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const int nchunks = (p.n_keys + 31) >> 5;
 
-    if (warp == 0 && static_cast<int>(blockIdx.x) < items) issue_loads(blockIdx.x, 0);
-    int it = 0;
-    for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
-        const int b = it & 1;
-        const uint32_t ld_phase = (it >> 1) & 1, mma_phase = it & 1;
-        const int mt = item % n_tiles, bh = item / n_tiles;
-        const int h = bh % p.H, bb = bh / p.H;
-        const int row_base = bb * p.S, q0 = mt * ATT_TILE;
-        uint8_t* sK = buf0 + b * ATT_DQ_ITEM_BYTES;
-        uint8_t* sQ = sK + 32768;
-        uint8_t* sdO = sQ + 16384;
-        uint8_t* sV = sdO + 16384;
-        uint8_t* sdS = sQ;                              // 64 KB over Q | dO | V
-        if (warp == 0) {
-            // the other buffer was last touched by item it-1, whose dQ MMA and stores completed before the loop came back here
-            if (item + static_cast<int>(gridDim.x) < items) issue_loads(item + gridDim.x, b ^ 1);
-            mbar_wait(&bars->load[b], ld_phase);
-            tc_fence_after();
-            const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
+    // ---- phase 1: P = exp2(S * c - lse), packed to bf16 and kept in registers
+    uint32_t pk[4][16];
+    mbar_wait(&bars->mma0, 0);
+    tc_fence_after();
 #pragma unroll
-            for (int k = 0; k < 4; ++k)      // S = Q K^T  -> columns [0, 256)
-                umma_bf16_warp(tmem, desc_kmajor(smem_u32(sQ), k), desc_kmajor(smem_u32(sK), k), idesc, k != 0);
-#pragma unroll
-            for (int k = 0; k < 4; ++k)      // dP = dO V^T -> columns [256, 512)
-                umma_bf16_warp(tmem + 256, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
-            umma_commit_warp(&bars->mma0);
-        }
-        const int row = (warp & 3) * 32 + lane;
-        const int q = q0 + row;
-        const bool qvalid = q < p.S;
-        // delta = rowsum(dO o O), straight from global memory (128 B per tensor per thread)
-        float delta = 0.f;
-        if (qvalid) {
-            const uint4* po = reinterpret_cast<const uint4*>(p.o + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
-            const uint4* pd = reinterpret_cast<const uint4*>(p.dout + static_cast<size_t>(row_base + q) * HD + h * ATT_D);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const uint4 a = po[c], d = pd[c];
-                const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
-                const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
-                delta += a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
-            }
-            if (half == 0) p.delta[(static_cast<size_t>(bb) * p.H + h) * p.S + q] = delta;
-        }
-        const float lse = qvalid ? p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + q] : 0.f;
-        const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-        mbar_wait(&bars->mma0, mma_phase);
-        tc_fence_after();
-        const uint32_t sdS_u32 = smem_u32(sdS);
-        for (int g = half; g < (p.n_keys + 31) >> 5; g += 2) {
-            uint32_t s[32], dp[32];
-            tmem_ld_32x32(t_row + g * 32, s);
-            tmem_ld_32x32(t_row + 256 + g * 32, dp);
+    for (int j = 0; j < 4; ++j) {
+        const int g = half + 2 * j;
+        if (g < nchunks) {
+            uint32_t sv[32];
+            tmem_ld_32x32(t_row + g * 32, sv);
             tmem_ld_wait();
-            float f[32];
+            if (g * 32 + 32 <= p.S) {            // every key of this chunk exists: no per-element predicate
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float pr = (g * 32 + i < p.S) ? exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2e, -lse)) : 0.f;
-                f[i] = qvalid ? pr * (__uint_as_float(dp[i]) - delta) * p.scale : 0.f;
-            }
-            store_row_chunk32(sdS_u32, row, g * 32, f);     // over Q / dO / V: the S and dP chains have completed (mma0)
-        }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        __syncthreads();
-        if (warp == 0) {
-            tc_fence_after();
-            const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
-            const int ksteps = p.n_keys >> 4;
-            for (int k = 0; k < ksteps; ++k)         // dQ = dS K  (K read MN-major), into columns [0, 64)
-                umma_bf16_warp(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
-            umma_commit_warp(&bars->mma1);
-        }
-        mbar_wait(&bars->mma1, mma_phase);
-        tc_fence_after();
-        {
-            const int g = half;
-            uint32_t v[32];
-            tmem_ld_32x32(t_row + g * 32, v);
-            tmem_ld_wait();
-            if (qvalid) {
-                uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + q) * 3 * HD + h * ATT_D + g * 32);
+                for (int i = 0; i < 16; ++i)
+                    pk[j][i] = pack_bf16x2(fast_exp2(fmaf(__uint_as_float(sv[2 * i]), p.scale_log2e, -lse)),
+                                           fast_exp2(fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2e, -lse)));
+            } else {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint4 w;
-                    w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
-                    w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
-                    w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
-                    w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
-                    dst[c] = w;
+                for (int i = 0; i < 16; ++i) {
+                    const float p0 = (g * 32 + 2 * i < p.S) ? fast_exp2(fmaf(__uint_as_float(sv[2 * i]), p.scale_log2e, -lse)) : 0.f;
+                    const float p1 = (g * 32 + 2 * i + 1 < p.S) ? fast_exp2(fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2e, -lse)) : 0.f;
+                    pk[j][i] = pack_bf16x2(p0, p1);
                 }
             }
         }
-        tc_fence_before();
-        __syncthreads();          // every thread has read dQ out of TMEM and is done with this item's buffer
-        tc_fence_after();
     }
-    if (warp == 0) tmem_dealloc(tmem, 512);
+    tc_fence_before();
+    __syncthreads();                     // every S column has been read: the dP MMA may overwrite them
+    if (warp == 0) {
+        tc_fence_after();
+        const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)      // dP = dO V^T, into the columns S occupied
+            umma_bf16_warp(tmem, desc_kmajor(smem_u32(sdO), k), desc_kmajor(smem_u32(sV), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma1);
+    }
+    // ---- phase 2: dS = P o (dP - delta) * scale -> shared memory (over Q | dO | V: every MMA that read them has completed)
+    mbar_wait(&bars->mma1, 0);
+    tc_fence_after();
+    const uint32_t sdS_u32 = smem_u32(sdS);
+    const float sc_row = qvalid ? p.scale : 0.f;         // rows beyond the sequence produce dS = 0
+    const float nds = -delta * sc_row;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int g = half + 2 * j;
+        if (g < nchunks) {
+            uint32_t dp[32];
+            tmem_ld_32x32(t_row + g * 32, dp);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {       // dS = P * (dP - delta) * scale = P * fma(dP, scale, -delta * scale)
+                const float2 pr = unpack_bf16x2(pk[j][i]);
+                dp[2 * i] = __float_as_uint(pr.x * fmaf(__uint_as_float(dp[2 * i]), sc_row, nds));
+                dp[2 * i + 1] = __float_as_uint(pr.y * fmaf(__uint_as_float(dp[2 * i + 1]), sc_row, nds));
+            }
+            store_row_chunk32_bits(sdS_u32, row, g * 32, dp);
+        }
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
+        const int ksteps = p.n_keys >> 4;
+        for (int k = 0; k < ksteps; ++k)         // dQ = dS K  (K read MN-major), into columns [0, 64)
+            umma_bf16_warp(tmem, desc_kmajor(sdS_u32, k), desc_mnmajor(smem_u32(sK), k), idesc, k != 0);
+        umma_commit_warp(&bars->mma2);
+    }
+    mbar_wait(&bars->mma2, 0);
+    tc_fence_after();
+    {
+        const int g = half;
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + g * 32, v);
+        tmem_ld_wait();
+        if (qvalid) {
+            uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + q) * 3 * HD + h * ATT_D + g * 32);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
+                w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
+                w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
+                w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
+                dst[c] = w;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 // ------------------------------------------------------------------------------------------------ backward: dK, dV
-__global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_constant__ AttnParams p) {
+// One CTA per (batch, head, 128-key tile); the queries are walked in SUB-TILES OF 64.  With 128-query tiles the kernel needed
+// 384 TMEM columns (S^T, dP^T, dV, dK) and 134 KB of shared memory, i.e. one CTA per SM running its load -> MMA -> exp -> MMA
+// phases strictly one after the other (2.9 ms of a 23 ms ViT-B/16 step).  64-query sub-tiles need 4 x 64 = 256 columns and
+// 100 KB, so TWO CTAs share an SM and fill each other's phase gaps; the Q / dO sub-tile of the next iteration is prefetched
+// into a second 16 KB buffer while the current one computes.
+constexpr int ATT_QSUB = 64;
+struct AttKvBars {
+    uint64_t load[2], mma0, mma1;
+    uint32_t tmem_base;
+};
+__global__ void __launch_bounds__(256, 2) attn_bwd_dkdv_kernel(const __grid_constant__ AttnParams p) {
     extern __shared__ uint8_t att_raw[];
     uint8_t* smem = att_align(att_raw);
-    AttBars* bars = reinterpret_cast<AttBars*>(smem);
-    float* s_lse = reinterpret_cast<float*>(smem + 128);     // 128 floats
-    float* s_delta = s_lse + 128;                            // 128 floats  (ends at 128 + 1024 = 1152 < 2048)
+    AttKvBars* bars = reinterpret_cast<AttKvBars*>(smem);
+    float* s_lse = reinterpret_cast<float*>(smem + 128);     // [2][64]
+    float* s_delta = s_lse + 2 * ATT_QSUB;                   // [2][64]  (ends at 128 + 1024 < 2048)
     uint8_t* sK = smem + 2048;            // 16 KB  (this CTA's key tile)
     uint8_t* sV = sK + 16384;             // 16 KB
-    uint8_t* sQ = sV + 16384;             // 16 KB  (current query tile)
-    uint8_t* sdO = sQ + 16384;            // 16 KB
-    uint8_t* sPT = sdO + 16384;           // 32 KB  P^T  [keys x queries]
-    uint8_t* sdST = sPT + 32768;          // 32 KB  dS^T [keys x queries]
+    uint8_t* sQ = sV + 16384;             // 2 x 8 KB  (query sub-tile, double buffered)
+    uint8_t* sdO = sQ + 16384;            // 2 x 8 KB
+    uint8_t* sPT = sdO + 16384;           // 16 KB  P^T  [128 keys x 64 queries]
+    uint8_t* sdST = sPT + 16384;          // 16 KB  dS^T [128 keys x 64 queries]
     const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
-    const int half = warp >> 2;          // two threads per key row: alternate 32-query chunks
+    const int half = warp >> 2;          // two threads per key row: one 32-query chunk each
     const int kt = blockIdx.x & 1;
     const int bh = blockIdx.x >> 1;
     const int h = bh % p.H, b = bh / p.H;
@@ -357,125 +431,141 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkdv_kernel(const __grid_cons
     if (k0 >= p.S) return;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
+        mbar_init(&bars->load[0], 1); mbar_init(&bars->load[1], 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
         fence_mbar_init();
+        tma_prefetch_desc(&p.qkv_map); tma_prefetch_desc(&p.qkv_map64); tma_prefetch_desc(&p.do_map64);
     }
-    if (warp == 0) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+    if (warp == 0) { tmem_alloc(&bars->tmem_base, 256); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = uniform_u32(bars->tmem_base);
+    pdl_sync();
     const int HD = p.H * ATT_D;
     const int row_base = b * p.S;
     const int row = (warp & 3) * 32 + lane;      // key index inside the tile
     const int key = k0 + row;
     const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    const int n_qtiles = (p.S + ATT_TILE - 1) / ATT_TILE;
-    uint32_t ph = 0;
+    const int n_sub = (p.S + ATT_QSUB - 1) / ATT_QSUB;
+    const size_t stat_base = (static_cast<size_t>(b) * p.H + h) * p.S;
 
-    for (int qt = 0; qt < n_qtiles; ++qt) {
-        const int q0 = qt * ATT_TILE;
-        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
-            mbar_arrive_expect_tx_warp(&bars->load, qt == 0 ? 16384 * 4 : 16384 * 2);
-            if (qt == 0) {
-                tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + k0);
-                tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + k0);
-            }
-            tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
-            tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
+    auto issue_sub = [&](int qt) {       // whole warp 0; one elected lane issues
+        const int bsel = qt & 1;
+        mbar_arrive_expect_tx_warp(&bars->load[bsel], qt == 0 ? 16384 * 2 + 8192 * 2 : 8192 * 2);
+        if (qt == 0) {
+            tma_load_2d_warp(sK, &p.qkv_map, &bars->load[0], HD + h * ATT_D, row_base + k0);
+            tma_load_2d_warp(sV, &p.qkv_map, &bars->load[0], 2 * HD + h * ATT_D, row_base + k0);
         }
-        // per-query log-sum-exp and delta of this query tile (written by the forward / dQ kernels)
-        if (threadIdx.x < ATT_TILE) {
+        tma_load_2d_warp(sQ + bsel * 8192, &p.qkv_map64, &bars->load[bsel], h * ATT_D, row_base + qt * ATT_QSUB);
+        tma_load_2d_warp(sdO + bsel * 8192, &p.do_map64, &bars->load[bsel], h * ATT_D, row_base + qt * ATT_QSUB);
+    };
+    if (warp == 0) issue_sub(0);
+
+    for (int qt = 0; qt < n_sub; ++qt) {
+        const int bsel = qt & 1;
+        const int q0 = qt * ATT_QSUB;
+        const uint32_t ld_phase = (qt >> 1) & 1, ph = qt & 1;
+        // the other Q / dO buffer was last read by the dV / dK MMAs of sub-tile qt - 1, which completed (mma1) before this
+        // iteration started: prefetch sub-tile qt + 1 into it
+        if (warp == 0 && qt + 1 < n_sub) issue_sub(qt + 1);
+        if (threadIdx.x < ATT_QSUB) {
             const int qq = q0 + threadIdx.x;
-            const size_t off = (static_cast<size_t>(b) * p.H + h) * p.S + qq;
-            s_lse[threadIdx.x] = qq < p.S ? p.lse[off] : 0.f;
-            s_delta[threadIdx.x] = qq < p.S ? p.delta[off] : 0.f;
+            s_lse[bsel * ATT_QSUB + threadIdx.x] = qq < p.S ? p.lse[stat_base + qq] : INFINITY;
+            s_delta[bsel * ATT_QSUB + threadIdx.x] = qq < p.S ? -p.delta[stat_base + qq] * p.scale : 0.f;     // -delta * scale
         }
-        __syncthreads();
-        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
-            mbar_wait(&bars->load, ph);
+        if (warp == 0) {
+            mbar_wait(&bars->load[bsel], ld_phase);
             tc_fence_after();
-            const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_TILE, 0, 0);
+            const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_QSUB, 0, 0);
+            const uint32_t q_u32 = smem_u32(sQ + bsel * 8192), do_u32 = smem_u32(sdO + bsel * 8192);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)      // S^T = K Q^T   -> columns [0, 128)
-                umma_bf16_warp(tmem, desc_kmajor(smem_u32(sK), k), desc_kmajor(smem_u32(sQ), k), idesc, k != 0);
+            for (int k = 0; k < 4; ++k)      // S^T = K Q^T   -> columns [0, 64)
+                umma_bf16_warp(tmem, desc_kmajor(smem_u32(sK), k), desc_kmajor(q_u32, k), idesc, k != 0);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)      // dP^T = V dO^T -> columns [128, 256)
-                umma_bf16_warp(tmem + 128, desc_kmajor(smem_u32(sV), k), desc_kmajor(smem_u32(sdO), k), idesc, k != 0);
+            for (int k = 0; k < 4; ++k)      // dP^T = V dO^T -> columns [64, 128)
+                umma_bf16_warp(tmem + 64, desc_kmajor(smem_u32(sV), k), desc_kmajor(do_u32, k), idesc, k != 0);
             umma_commit_warp(&bars->mma0);
         }
+        __syncthreads();                     // s_lse / s_delta of this sub-tile are visible
         mbar_wait(&bars->mma0, ph);
         tc_fence_after();
         const uint32_t sPT_u32 = smem_u32(sPT), sdST_u32 = smem_u32(sdST);
-#pragma unroll 1
-        for (int g = half; g < 4; g += 2) {
-            uint32_t s[32], dp[32];
-            tmem_ld_32x32(t_row + g * 32, s);
-            tmem_ld_32x32(t_row + 128 + g * 32, dp);
+        {
+            const int g = half;              // 32 queries per thread
+            uint32_t sv[32], dp[32];
+            tmem_ld_32x32(t_row + g * 32, sv);
+            tmem_ld_32x32(t_row + 64 + g * 32, dp);
             tmem_ld_wait();
-            float fp[32], fd[32];
+            const uint32_t lse_u32 = smem_u32(s_lse + bsel * ATT_QSUB + g * 32);
+            const uint32_t del_u32 = smem_u32(s_delta + bsel * ATT_QSUB + g * 32);
+            // s_lse holds +inf for queries beyond the sequence (exp2(-inf) = 0) and this row's scale is 0 for keys beyond
+            // it, so the loop needs no per-element predicate; per-query constants come as 16-byte broadcast loads
+            const float kscale = key < p.S ? p.scale_log2e : 0.f;
+            const float koff = key < p.S ? 0.f : -INFINITY;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int qq = g * 32 + i;
-                const bool ok = (q0 + qq < p.S) && (key < p.S);
-                const float pr = ok ? exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2e, -s_lse[qq])) : 0.f;
-                fp[i] = pr;
-                fd[i] = pr * (__uint_as_float(dp[i]) - s_delta[qq]) * p.scale;
+            for (int i = 0; i < 32; i += 4) {
+                float l4[4], d4[4];
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(l4[0]), "=f"(l4[1]), "=f"(l4[2]), "=f"(l4[3]) : "r"(lse_u32 + i * 4));
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(d4[0]), "=f"(d4[1]), "=f"(d4[2]), "=f"(d4[3]) : "r"(del_u32 + i * 4));
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float pr = fast_exp2(fmaf(__uint_as_float(sv[i + e]), kscale, koff - l4[e]));
+                    sv[i + e] = __float_as_uint(pr);
+                    dp[i + e] = __float_as_uint(pr * fmaf(__uint_as_float(dp[i + e]), p.scale, d4[e]));
+                }
             }
-            store_row_chunk32(sPT_u32, row, g * 32, fp);
-            store_row_chunk32(sdST_u32, row, g * 32, fd);
+            store_row_chunk32_bits(sPT_u32, row, g * 32, sv);
+            store_row_chunk32_bits(sdST_u32, row, g * 32, dp);
         }
         tc_fence_before();
         fence_proxy_async_smem();
         __syncthreads();
-        if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
+        if (warp == 0) {
             tc_fence_after();
             const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
+            const uint32_t q_u32 = smem_u32(sQ + bsel * 8192), do_u32 = smem_u32(sdO + bsel * 8192);
 #pragma unroll
-            for (int k = 0; k < 8; ++k)      // dV += P^T dO   (dO read MN-major) -> columns [256, 320)
-                umma_bf16_warp(tmem + 256, desc_kmajor(sPT_u32, k), desc_mnmajor(smem_u32(sdO), k), idesc, (qt | k) != 0);
+            for (int k = 0; k < 4; ++k)      // dV += P^T dO   (dO read MN-major) -> columns [128, 192)
+                umma_bf16_warp(tmem + 128, desc_kmajor(sPT_u32, k), desc_mnmajor(do_u32, k), idesc, (qt | k) != 0);
 #pragma unroll
-            for (int k = 0; k < 8; ++k)      // dK += dS^T Q   (Q read MN-major)  -> columns [320, 384)
-                umma_bf16_warp(tmem + 320, desc_kmajor(sdST_u32, k), desc_mnmajor(smem_u32(sQ), k), idesc, (qt | k) != 0);
+            for (int k = 0; k < 4; ++k)      // dK += dS^T Q   (Q read MN-major)  -> columns [192, 256)
+                umma_bf16_warp(tmem + 192, desc_kmajor(sdST_u32, k), desc_mnmajor(q_u32, k), idesc, (qt | k) != 0);
             umma_commit_warp(&bars->mma1);
         }
-        mbar_wait(&bars->mma1, ph);      // sQ / sdO / sPT / sdST may be overwritten by the next query tile
+        mbar_wait(&bars->mma1, ph);      // sPT / sdST and this Q / dO buffer may be overwritten from here on
         tc_fence_after();
-        ph ^= 1;
         __syncthreads();
     }
     // ---- store dK (slot 1 of dqkv) and dV (slot 2)
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
-        {
-            const int g = half;
-            uint32_t v[32];
-            tmem_ld_32x32(t_row + (which == 0 ? 320 : 256) + g * 32, v);
-            tmem_ld_wait();
-            if (key < p.S) {
-                uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + key) * 3 * HD + (which + 1) * HD +
-                                                      h * ATT_D + g * 32);
+        const int g = half;
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + (which == 0 ? 192 : 128) + g * 32, v);
+        tmem_ld_wait();
+        if (key < p.S) {
+            uint4* dst = reinterpret_cast<uint4*>(p.dqkv + static_cast<size_t>(row_base + key) * 3 * HD + (which + 1) * HD +
+                                                  h * ATT_D + g * 32);
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint4 w;
-                    w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
-                    w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
-                    w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
-                    w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
-                    dst[c] = w;
-                }
+            for (int c = 0; c < 4; ++c) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]), __uint_as_float(v[8 * c + 1]));
+                w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]));
+                w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]));
+                w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]));
+                dst[c] = w;
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, 512);
+    if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
-static int make_2d_map(CUtensorMap* m, const void* base, long long rows, int cols) {
+static int make_2d_map(CUtensorMap* m, const void* base, long long rows, int cols, int box_rows = 128) {
     uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
     uint64_t strides[1] = {(uint64_t)cols * 2};
-    uint32_t box[2] = {64, 128};
+    uint32_t box[2] = {64, (uint32_t)box_rows};
     return make_tensor_map(m, base, 2, 2, dims, strides, box, true);
 }
 
@@ -505,7 +595,7 @@ extern "C" int picd_attention_fwd(const void* qkv, void* o, float* lse, int B, i
         PICD_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr = true;
     }
-    attn_fwd_kernel<<<B * H * 2, 256, smem, stream>>>(p);
+    PICD_CUDA(launch_pdl<PDL_ATTN>(attn_fwd_kernel, dim3(B * H * 2), dim3(256), smem, stream, p));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -517,22 +607,24 @@ extern "C" int picd_attention_bwd(const void* qkv, const void* o, const void* do
     AttnParams p;
     if (fill_params(p, qkv, B, S, H)) return 3;
     if (make_2d_map(&p.do_map, dout, static_cast<long long>(B) * S, H * ATT_D)) return 3;
+    if (make_2d_map(&p.do_map64, dout, static_cast<long long>(B) * S, H * ATT_D, ATT_QSUB)) return 3;
+    if (make_2d_map(&p.qkv_map64, qkv, static_cast<long long>(B) * S, 3 * H * ATT_D, ATT_QSUB)) return 3;
     p.o = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(o));
     p.dout = static_cast<const __nv_bfloat16*>(dout);
     p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
     p.lse = const_cast<float*>(lse);
     p.delta = delta;
-    const int smem_dq = 1024 + 2 * ATT_DQ_ITEM_BYTES + 1024;
-    const int smem_kv = 2048 + 16384 * 4 + 32768 * 2 + 1024;
+    const int smem_dq = 1024 + 32768 + 16384 + 16384 + 32768 + 1024;       // 98 KB: two CTAs per SM
+    const int smem_kv = 2048 + 16384 * 6 + 1024;       // 99 KB: two CTAs per SM
     static bool attr = false;
     if (!attr) {
         PICD_CUDA(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
         PICD_CUDA(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_kv));
         attr = true;
     }
-    attn_bwd_dq_kernel<<<std::min(B * H * ((S + ATT_TILE - 1) / ATT_TILE), num_sms()), 256, smem_dq, stream>>>(p);
+    PICD_CUDA(launch_pdl<PDL_ATTN>(attn_bwd_dq_kernel, dim3(B * H * ((S + ATT_TILE - 1) / ATT_TILE)), dim3(256), smem_dq, stream, p));
     PICD_LAUNCH_CHECK();
-    attn_bwd_dkdv_kernel<<<B * H * 2, 256, smem_kv, stream>>>(p);
+    PICD_CUDA(launch_pdl<PDL_ATTN>(attn_bwd_dkdv_kernel, dim3(B * H * 2), dim3(256), smem_kv, stream, p));
     PICD_LAUNCH_CHECK();
     return 0;
 }

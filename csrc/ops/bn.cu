@@ -480,7 +480,7 @@ extern "C" int picd_bn_stats(const void* x, float* stats, long long P, int C, cu
     PICD_REQUIRE(C % 8 == 0, "bn_stats: C=%d must be a multiple of 8", C);
     const ReduceShape s = reduce_shape(P, C);
     const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
-    PICD_CUDA(launch_pdl(bn_stats_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_stats_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
                          static_cast<const __nv_bfloat16*>(x), stats, P, C, s.tx_count, s.ty_count, s.rows_per_block));
     PICD_LAUNCH_CHECK();
     return 0;
@@ -492,7 +492,7 @@ extern "C" int picd_stat_replicas() { return STAT_REPLICAS; }
 extern "C" int picd_bn_finalize(const float* sums, int replicas, float count, const float* gamma, const float* beta,
                                 float* running_mean, float* running_var, float momentum, float eps, float* scale,
                                 float* shift, float* mean, float* invstd, int C, cudaStream_t stream) {
-    PICD_CUDA(launch_pdl(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, sums, replicas, count, gamma, beta,
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, sums, replicas, count, gamma, beta,
                          running_mean, running_var, momentum, eps, scale, shift, mean, invstd, C));
     PICD_LAUNCH_CHECK();
     return 0;
@@ -501,7 +501,7 @@ extern "C" int picd_bn_finalize(const float* sums, int replicas, float count, co
 extern "C" int picd_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
                                    const float* running_var, float eps, float* scale, float* shift, int C,
                                    cudaStream_t stream) {
-    PICD_CUDA(launch_pdl(bn_eval_coeffs_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, gamma, beta, running_mean,
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_eval_coeffs_kernel, dim3((C + 127) / 128), dim3(128), 0, stream, gamma, beta, running_mean,
                          running_var, eps, scale, shift, C));
     PICD_LAUNCH_CHECK();
     return 0;
@@ -521,7 +521,7 @@ static int bn_apply_impl(const void* y, float* scale, float* shift, const void* 
     static const int variant = [] { const char* e = getenv("PICD_BN_APPLY_VARIANT"); return e == nullptr ? 2 : atoi(e); }();   // 2 = 8 rows in flight (measured best)
     ReduceShape s = stream_shape(P, C);
 #define PICD_BN_APPLY_LAUNCH_A(U, MINB, A)                                                                         \
-    PICD_CUDA(launch_pdl(bn_apply_kernel<U, MINB, A>, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,               \
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_apply_kernel<U, MINB, A>, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,               \
         static_cast<const __nv_bfloat16*>(y), scale, shift, static_cast<const __nv_bfloat16*>(residual), act,       \
         static_cast<__nv_bfloat16*>(out), P, C, s.tx_count, s.ty_count, s.rows_per_block,                           \
         static_cast<uint8_t*>(relu_mask), fin))
@@ -577,7 +577,7 @@ extern "C" int picd_bn_bwd_reduce_mask(const void* dz, const void* y, const void
     }
     const ReduceShape s = reduce_shape(P, C);
     const size_t smem = static_cast<size_t>(s.tx_count) * s.ty_count * 16 * sizeof(float);
-    PICD_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_bwd_reduce_kernel, dim3(s.grid_x, s.grid_y), dim3(256), smem, stream,
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, P, C, s.tx_count, s.ty_count,
         s.rows_per_block));
@@ -611,12 +611,12 @@ extern "C" int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const v
                                           cudaStream_t stream) {
     PICD_REQUIRE(C % 8 == 0, "bn_bwd_apply: C=%d must be a multiple of 8", C);
     if (param_sums != nullptr && param_sums != sums && param_replicas > 1) {
-        PICD_CUDA(launch_pdl(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(param_sums),
+        PICD_CUDA(launch_pdl<PDL_BN>(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(param_sums),
                              2 * C, param_replicas));
         param_replicas = 1;
     }
     if (sums_replicas > 1) {
-        PICD_CUDA(launch_pdl(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(sums), 2 * C,
+        PICD_CUDA(launch_pdl<PDL_BN>(fold_replicas_kernel, dim3((2 * C + 255) / 256), dim3(256), 0, stream, const_cast<float*>(sums), 2 * C,
                              sums_replicas));
         if (param_sums == sums) param_replicas = 1;
         sums_replicas = 1;
@@ -627,7 +627,7 @@ extern "C" int picd_bn_bwd_apply_mask_cnt(const void* dz, const void* y, const v
         if (rc >= 0) return rc;
     }
     const ReduceShape s = stream_shape(P, C);
-    PICD_CUDA(launch_pdl(bn_bwd_apply_kernel, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_bwd_apply_kernel, dim3(s.grid_x, s.grid_y), dim3(256), 0, stream,
         static_cast<const __nv_bfloat16*>(dz), static_cast<const __nv_bfloat16*>(y),
         static_cast<const __nv_bfloat16*>(z), scale, shift, mean, invstd, act, sums, inv_count, param_sums, dgamma,
         dbeta, static_cast<__nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dres), P, C, s.tx_count, s.ty_count,

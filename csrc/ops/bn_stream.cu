@@ -312,7 +312,7 @@ static int launch_stream(StreamArgs& a, cudaStream_t stream) {
     }
     long long grid = num_sms();
     if (grid > a.num_chunks) grid = a.num_chunks;
-    PICD_CUDA(launch_pdl(bn_stream_kernel<MODE>, dim3(static_cast<unsigned>(grid)), dim3(SB_THREADS), smem, stream, a));
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_stream_kernel<MODE>, dim3(static_cast<unsigned>(grid)), dim3(SB_THREADS), smem, stream, a));
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -94,6 +94,11 @@ struct WgradParams {
     int BN, numN, numM, ksplit, num_p_tiles, stages;
     int tiles_w, tiles_h, bw_log2, bh_log2;
     int G, cin_blocks, ngroups;   // taps per CTA (their B tiles sit side by side along N), 64-channel blocks per tap
+    // bias gradient db[cout] += sum over pixels of dy[pixel, cout] on the tensor cores: the CTAs that own the first tap / first
+    // input-channel tile multiply their dy tiles by a constant tile of ONES as well (one extra N = 16 MMA per k-step into 16
+    // spare TMEM columns) -- the separate column-sum pass over dy disappears.
+    float* dbias;                 // [Cout] fp32, accumulated with atomics; nullptr = no bias
+    int tmem_cols;                // 256, or 512 when BN + 16 spare columns do not fit
 };
 
 struct SmemBars {
@@ -630,6 +635,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     const int b_stage = BN * 128;
     uint8_t* sA = smem + SMEM_HEADER;
     uint8_t* sB = sA + stages * A_STAGE_BYTES;
+    uint8_t* sOnes = sB + stages * b_stage;          // 8 KB of bf16 1.0 (dbias only): a [64 x 64] B tile in any layout
 
     const int warp = uniform_warp_id();
     const int lane = threadIdx.x & 31;
@@ -642,8 +648,12 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
         mbar_init(&bars->tfull[0], 1);
         fence_mbar_init();
     }
+    if (p.dbias != nullptr) {
+        for (int i = threadIdx.x; i < 2048; i += blockDim.x) reinterpret_cast<uint32_t*>(sOnes)[i] = 0x3F803F80u;
+        fence_proxy_async_smem();
+    }
     if (warp == 1) {
-        tmem_alloc(&bars->tmem_base, 256);
+        tmem_alloc(&bars->tmem_base, p.tmem_cols);
         tmem_relinquish();
     }
     if (warp == 0 && lane == 0) {
@@ -662,6 +672,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     const int nt = rem % p.numN; rem /= p.numN;
     const int mt = rem % p.numM; rem /= p.numM;
     const int group = rem;                      // taps [group*G, group*G + G) share this CTA's dy tiles
+    const bool do_bias = p.dbias != nullptr && nt == 0 && group == 0;     // one CTA per (k-split, cout tile) sums dy
     const int pt_begin = static_cast<int>((static_cast<long long>(p.num_p_tiles) * split) / p.ksplit);
     const int pt_end = static_cast<int>((static_cast<long long>(p.num_p_tiles) * (split + 1)) / p.ksplit);
     const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
@@ -710,8 +721,10 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t idesc = make_idesc_bf16(TILE_M, BN, 1, 1);
+            const uint32_t idesc_ones = make_idesc_bf16(TILE_M, 16, 1, 1);
             const uint64_t tmpl = make_smem_desc(0, 8192, 1024);
             const uint32_t sA_lo = smem_u32(sA) >> 4, sB_lo = smem_u32(sB) >> 4;
+            const uint64_t onesdesc0 = tmpl | (smem_u32(sOnes) >> 4);
             const uint32_t a_stage_lo = A_STAGE_BYTES >> 4, b_stage_lo = static_cast<uint32_t>(b_stage) >> 4;
             for (int pt = pt_begin; pt < pt_end; ++pt) {
                 mbar_wait(&bars->full[stage], phase);
@@ -722,6 +735,12 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
                 for (int k = 0; k < 4; ++k)
                     umma_bf16_warp(tmem_base, adesc0 + k * (2048 >> 4), bdesc0 + k * (2048 >> 4), idesc,
                                    (pt > pt_begin) || (k != 0));
+                if (do_bias) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)      // dy^T x ones: every one of the 16 result columns is the bias gradient
+                        umma_bf16_warp(tmem_base + BN, adesc0 + k * (2048 >> 4), onesdesc0 + k * (2048 >> 4), idesc_ones,
+                                       (pt > pt_begin) || (k != 0));
+                }
                 umma_commit_warp(&bars->empty[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
@@ -735,6 +754,12 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
             mbar_wait(&bars->tfull[0], 0);
             tc_fence_after();
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            if (do_bias) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + BN, v);
+                tmem_ld_wait();
+                if (cout < p.Cout) atomicAdd(p.dbias + cout, __uint_as_float(v[0]));
+            }
             for (int g = 0; g < BN / 32; ++g) {
                 uint32_t v[32];
                 tmem_ld_32x32(t_row + g * 32, v);
@@ -763,7 +788,7 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 256);
+    if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
 // =====================================================================================================
@@ -1123,9 +1148,8 @@ extern "C" int picd_conv_dgrad_bnreduce(const void* dy, const void* w, void* dx,
     return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, 0, stream, &b);
 }
 // dw[Cout,R,S,Cin] (fp32) += sum over pixels of dy (x) x.  The caller provides a zeroed (or accumulating) buffer.
-extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
-                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
-                               cudaStream_t stream) {
+static int conv_wgrad_impl(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int Cin, int Cout,
+                           int R, int S, int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream) {
     PICD_REQUIRE(stride == 1 || stride == 2, "conv_wgrad: stride %d unsupported", stride);
     PICD_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv_wgrad: channels must be multiples of 8");
     PICD_REQUIRE(R * S <= MAX_TAPS, "conv_wgrad: too many taps");
@@ -1150,6 +1174,7 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
         }
     p.ntaps = nt;
     p.dw = dw; p.Cout = Cout; p.Cin = Cin; p.taps_total = R * S;
+    p.dbias = dbias;
     int BN;
     p.numN = num_n_tiles(Cin, &BN);
     p.cin_blocks = ceil_div(Cin, 64);
@@ -1177,14 +1202,16 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
     p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h;
     p.bw_log2 = g.bw_log2; p.bh_log2 = g.bh_log2;
     const int stage_bytes = A_STAGE_BYTES + BN * 128;
+    const int ones_bytes = dbias != nullptr ? 8192 : 0;
+    p.tmem_cols = (dbias != nullptr && BN + 32 > 256) ? 512 : 256;      // the epilogue reads 32 columns from column BN on
     // small tiles: shallow ring, two CTAs per SM (2 x 256 TMEM columns) so one CTA's red.add epilogue overlaps
     // the other's main loop; wide tiles: one CTA per SM with a deep ring.
     int smem_launch;
     if (BN <= 128) {
         p.stages = (BN <= 64) ? 4 : 3;
-        smem_launch = p.stages * stage_bytes + SMEM_HEADER + 1024;
+        smem_launch = p.stages * stage_bytes + SMEM_HEADER + 1024 + ones_bytes;
     } else {
-        p.stages = std::min(6, (MAX_DYN_SMEM - 1024 - SMEM_HEADER) / stage_bytes);
+        p.stages = std::min(6, (MAX_DYN_SMEM - 1024 - SMEM_HEADER - ones_bytes) / stage_bytes);
         smem_launch = MAX_DYN_SMEM;
     }
     const int inner = p.ngroups * p.numM * p.numN;
@@ -1210,6 +1237,18 @@ extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, 
     return 0;
 }
 
+extern "C" int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
+                               int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                               cudaStream_t stream) {
+    return conv_wgrad_impl(x, dy, dw, nullptr, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, stream);
+}
+// Same, plus the bias gradient db[Cout] (fp32, accumulated) = column sums of dy, computed by the same kernel with a ones-tile MMA.
+extern "C" int picd_conv_wgrad_bias(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int Cin,
+                                    int Cout, int R, int S, int stride, int pad_h, int pad_w, int OH, int OW,
+                                    cudaStream_t stream) {
+    return conv_wgrad_impl(x, dy, dw, dbias, N, H, W, Cin, Cout, R, S, stride, pad_h, pad_w, OH, OW, stream);
+}
+
 // D[M,N] = act(A[M,K] * B[N,K]^T + bias): the Linear forward (and, with swapped roles, every GEMM whose
 // operands are K-major).  All bf16 row-major, fp32 accumulate.
 extern "C" int picd_gemm_nt(const void* a, const void* b, void* d, const float* bias, int act, int M, int N_, int K,
@@ -1224,4 +1263,9 @@ extern "C" int picd_gemm_nn(const void* a, const void* b, void* d, int M, int N_
 extern "C" int picd_gemm_tn_f32(const void* a_dy, const void* b_x, float* d, int M, int N_, int K,
                                 cudaStream_t stream) {
     return picd_conv_wgrad(b_x, a_dy, d, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
+}
+// Linear wgrad + bias gradient in one kernel: D[N,K] += A^T B and dbias[N] += column sums of A (= dY).
+extern "C" int picd_gemm_tn_f32_bias(const void* a_dy, const void* b_x, float* d, float* dbias, int M, int N_, int K,
+                                     cudaStream_t stream) {
+    return conv_wgrad_impl(b_x, a_dy, d, dbias, 1, 1, M, K, N_, 1, 1, 1, 0, 0, 1, M, stream);
 }

@@ -514,7 +514,12 @@ template <int V>
 __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                                                             float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                            long long M, int D, float eps) {
+                                                            long long M, int D, float eps,
+                                                            const __nv_bfloat16* __restrict__ res,
+                                                            __nv_bfloat16* __restrict__ sum_out) {
+    // res / sum_out (both or neither): the transformer's residual add fused in -- the row normalised is s = bf16(x + res),
+    // which is also written to sum_out (the residual stream); one pass instead of an add kernel followed by this one
+    pdl_sync();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float gm[V][8], bt[V][8];
 #pragma unroll
@@ -534,6 +539,23 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
                 const int j = lane * 8 + i * 256;
                 raw[r][i] = (row + r < M && j < D) ? *reinterpret_cast<const uint4*>(x + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
             }
+        if (res != nullptr) {
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int i = 0; i < V; ++i) {
+                    const int j = lane * 8 + i * 256;
+                    if (row + r < M && j < D) {
+                        float a[8], b[8];
+                        unpack8(raw[r][i], a);
+                        unpack8(*reinterpret_cast<const uint4*>(res + (row + r) * D + j), b);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) a[k] += b[k];
+                        raw[r][i] = pack8(a);               // the bf16-rounded sum is what gets normalised (and re-read by the backward)
+                        *reinterpret_cast<uint4*>(sum_out + (row + r) * D + j) = raw[r][i];
+                    }
+                }
+        }
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             if (row + r >= M) break;
@@ -570,15 +592,21 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
                                                             const float* __restrict__ gamma, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                            long long M, int D, int rows_per_block) {
-    extern __shared__ float sm[];   // [warps][2][V*256]: every warp parks its partial sums, no shared-memory atomics
+                                                            long long M, int D, int rows_per_block,
+                                                            const __nv_bfloat16* __restrict__ add_in,
+                                                            float* __restrict__ dcol) {
+    // add_in (nullable): gradient arriving over the residual stream; the kernel writes dx = LayerNorm-backward + add_in, i.e. the
+    // gradient sum autograd would otherwise compute with a separate add kernel.  dcol (nullable, [D]): column sums of that
+    // final dx -- the bias gradient of the Linear layer whose output fed the residual add (its dY IS this dx).
+    extern __shared__ float sm[];   // [warps][3][V*256]: every warp parks its partial sums, no shared-memory atomics
+    pdl_sync();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    float pg[V][8], pb[V][8], gm[V][8];
+    float pg[V][8], pb[V][8], pc[V][8], gm[V][8];
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; }
+        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; pc[i][k] = 0.f; gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; }
     }
     const float inv_d = 1.f / D;
     const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
@@ -627,7 +655,20 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
                     float o[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) o[k] = rs[r] * (g[i][k] * gm[i][k] - a - xh[i][k] * b);
-                    *reinterpret_cast<uint4*>(dx + (row + r) * D + j) = pack8(o);
+                    if (add_in != nullptr) {
+                        float ad[8];
+                        unpack8(*reinterpret_cast<const uint4*>(add_in + (row + r) * D + j), ad);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) o[k] += ad[k];
+                    }
+                    const uint4 packed = pack8(o);
+                    *reinterpret_cast<uint4*>(dx + (row + r) * D + j) = packed;
+                    if (dcol != nullptr) {
+                        float ob[8];
+                        unpack8(packed, ob);               // sum what the consumer GEMMs will read (bf16-rounded)
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) pc[i][k] += ob[k];
+                    }
                 }
             }
         }
@@ -635,7 +676,7 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
     // fold the block's warps: warp w writes its partials to sm[w], then every thread sums a few columns over the warps and
     // issues one global atomic per column (the former version did 2 x 8 x V shared-memory atomics per thread, 8-way contended)
     constexpr int W2 = V * 256;
-    float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
+    float* mine = sm + static_cast<size_t>(warp) * 3 * W2;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
@@ -643,16 +684,20 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
         *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
         *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
         *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
+        *reinterpret_cast<float4*>(mine + 2 * W2 + j) = make_float4(pc[i][0], pc[i][1], pc[i][2], pc[i][3]);
+        *reinterpret_cast<float4*>(mine + 2 * W2 + j + 4) = make_float4(pc[i][4], pc[i][5], pc[i][6], pc[i][7]);
     }
     __syncthreads();
     for (int j = threadIdx.x; j < D; j += blockDim.x) {
-        float a = 0.f, b = 0.f;
+        float a = 0.f, b = 0.f, c = 0.f;
         for (int w = 0; w < nw; ++w) {
-            a += sm[static_cast<size_t>(w) * 2 * W2 + j];
-            b += sm[static_cast<size_t>(w) * 2 * W2 + W2 + j];
+            a += sm[static_cast<size_t>(w) * 3 * W2 + j];
+            b += sm[static_cast<size_t>(w) * 3 * W2 + W2 + j];
+            c += sm[static_cast<size_t>(w) * 3 * W2 + 2 * W2 + j];
         }
         atomicAdd(dgamma + j, a);
         atomicAdd(dbeta + j, b);
+        if (dcol != nullptr) atomicAdd(dcol + j, c);
     }
 }
 
@@ -1021,26 +1066,39 @@ extern "C" int picd_dropout_dyn(const void* x, void* out, long long n, float p, 
     PICD_LAUNCH_CHECK();
     return 0;
 }
-extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
-                                  long long M, int D, float eps, cudaStream_t st) {
+// s = x + res (bf16) -> sum_out, y = LayerNorm(s): the residual add of a transformer block fused into the LayerNorm that
+// follows it.  res == nullptr: plain LayerNorm of x (sum_out unused).
+extern "C" int picd_add_layernorm_fwd(const void* x, const void* res, const float* gamma, const float* beta, void* sum_out,
+                                      void* y, float* mean, float* rstd, long long M, int D, float eps, cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
+    PICD_REQUIRE((res == nullptr) == (sum_out == nullptr), "add_layernorm: res and sum_out go together");
     const int V = (D + 255) / 256;
     long long blocks = std::min<long long>((M + 15) / 16, 8LL * num_sms());
     if (blocks < 1) blocks = 1;
 #define PICD_LN_FWD(VV)                                                                                              \
-    layernorm_fwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 0, st>>>(static_cast<const bf16*>(x), gamma, beta, \
-                                                                           static_cast<bf16*>(y), mean, rstd, M, D, eps)
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(layernorm_fwd_kernel<VV>, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st,            \
+                         static_cast<const bf16*>(x), gamma, beta, static_cast<bf16*>(y), mean, rstd, M, D, eps,     \
+                         static_cast<const bf16*>(res), static_cast<bf16*>(sum_out)))
     if (V == 1) PICD_LN_FWD(1); else if (V == 2) PICD_LN_FWD(2); else if (V == 3) PICD_LN_FWD(3); else PICD_LN_FWD(4);
 #undef PICD_LN_FWD
     PICD_LAUNCH_CHECK();
     return 0;
 }
-extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
-                                  void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
+extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                                  long long M, int D, float eps, cudaStream_t st) {
+    return picd_add_layernorm_fwd(x, nullptr, gamma, beta, nullptr, y, mean, rstd, M, D, eps, st);
+}
+// dx = LayerNorm-backward(dy, x) + add_in (nullable: the gradient arriving over the residual stream); dcol (nullable, [D],
+// accumulated): column sums of dx = the bias gradient of the Linear whose output was added into the residual stream.
+extern "C" int picd_layernorm_bwd_add(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                                      const void* add_in, void* dx, float* dgamma, float* dbeta, float* dcol, long long M,
+                                      int D, cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
     static bool attr_set = false;
-    if (!attr_set) {       // V = 4 parks 8 warps x 2 x 1024 floats = 64 KB
-        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    if (!attr_set) {       // V = 4 parks 8 warps x 3 x 1024 floats = 96 KB
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_set = true;
     }
     long long blocks = 2LL * num_sms();
@@ -1049,13 +1107,18 @@ extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* ga
     blocks = (M + rpb - 1) / rpb;
     const int V = (D + 255) / 256;
 #define PICD_LN_BWD(VV)                                                                                                   \
-    layernorm_bwd_kernel<VV><<<static_cast<unsigned>(blocks), 256, 8 * 2 * VV * 256 * sizeof(float), st>>>(                           \
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(layernorm_bwd_kernel<VV>, dim3(static_cast<unsigned>(blocks)), dim3(256),                         \
+        8 * 3 * VV * 256 * sizeof(float), st,                                                                             \
         static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, \
-        M, D, static_cast<int>(rpb))
+        M, D, static_cast<int>(rpb), static_cast<const bf16*>(add_in), dcol))
     if (V == 1) PICD_LN_BWD(1); else if (V == 2) PICD_LN_BWD(2); else if (V == 3) PICD_LN_BWD(3); else PICD_LN_BWD(4);
 #undef PICD_LN_BWD
     PICD_LAUNCH_CHECK();
     return 0;
+}
+extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                                  void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
+    return picd_layernorm_bwd_add(dy, x, gamma, mean, rstd, nullptr, dx, dgamma, dbeta, nullptr, M, D, st);
 }
 extern "C" int picd_small_linear_fwd(const void* x, const float* w, const float* bias, void* y, int M, int N, int K, int act,
                                      int out_fp32, cudaStream_t st) {

@@ -49,6 +49,11 @@ int picd_conv_dgrad_bnreduce(const void* dy, const void* w, void* dx, int N, int
                              int stride, int pad_h, int pad_w, int OH, int OW, const void* y_up, const float* scale,
                              const float* shift, const float* mean, const float* invstd, int relu, float* sums,
                              cudaStream_t stream);
+/* Same as picd_conv_wgrad / picd_gemm_tn_f32 plus the bias gradient dbias[Cout] += column sums of dy, computed by the same kernel
+ * (one extra N = 16 MMA per k-step against a tile of ones): no separate pass over dy. */
+int picd_conv_wgrad_bias(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int Cin, int Cout, int R,
+                         int S, int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
+int picd_gemm_tn_f32_bias(const void* a_dy, const void* b_x, float* d, float* dbias, int M, int N, int K, cudaStream_t stream);
 /* dw (fp32, [Cout,R,S,Cin]) += ...; accumulates with red.add, so it can target the gradient arena directly */
 int picd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
                     int stride, int pad_h, int pad_w, int OH, int OW, cudaStream_t stream);
@@ -149,6 +154,14 @@ int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, 
 /* graph-replay variant: the seed is mixed with the 32-bit word at step_word (device memory) when the kernel runs */
 int picd_dropout_dyn(const void* x, void* out, long long n, float p, unsigned seed, const void* step_word,
                      cudaStream_t stream);
+/* Transformer residual add fused into the LayerNorm that follows it: s = x + res (bf16) -> sum_out, y = LayerNorm(s).
+ * Backward: dx = LayerNorm-backward(dy, s) + add_in (gradient arriving over the residual stream, nullable); dcol (nullable,
+ * accumulated): column sums of dx = bias gradient of the Linear whose output was `res`. */
+int picd_add_layernorm_fwd(const void* x, const void* res, const float* gamma, const float* beta, void* sum_out, void* y,
+                           float* mean, float* rstd, long long M, int D, float eps, cudaStream_t stream);
+int picd_layernorm_bwd_add(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                           const void* add_in, void* dx, float* dgamma, float* dbeta, float* dcol, long long M, int D,
+                           cudaStream_t stream);
 int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                        long long M, int D, float eps, cudaStream_t stream);
 int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,

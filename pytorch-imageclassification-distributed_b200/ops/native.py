@@ -41,6 +41,8 @@ _SIG = {
     "picd_gemm_nt": "ppppiiiip",
     "picd_gemm_nn": "pppiiip",
     "picd_gemm_tn_f32": "pppiiip",
+    "picd_gemm_tn_f32_bias": "ppppiiip",
+    "picd_conv_wgrad_bias": "pppp" + "i" * 12 + "p",
     "picd_bn_stats": "pplip",
     "picd_bn_finalize": "pifppppffppppip",
     "picd_bn_eval_coeffs": "ppppfppip",
@@ -66,6 +68,8 @@ _SIG = {
     "picd_dropout_dyn": "pplfupp",
     "picd_layernorm_fwd": "pppppplifp",
     "picd_layernorm_bwd": "pppppppplip",
+    "picd_add_layernorm_fwd": "pppppppplifp",
+    "picd_layernorm_bwd_add": "pppppppppplip",
     "picd_small_linear_fwd": "ppppiiiiip",
     "picd_small_linear_bwd": "pppppppp" + "iiiiii" + "p",
     "picd_pack_s2d": "pp" + "i" * 11 + "p",
@@ -364,7 +368,7 @@ def _fused_reduce_pays(i: _ConvInfo) -> bool:
 
 
 def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: bool, need_dw: bool, accumulate_into=None,
-                   src_bn: Optional["BnRecord"] = None):
+                   src_bn: Optional["BnRecord"] = None, dbias: Optional[torch.Tensor] = None):
     """Returns (dx or None, dw tensor or None).  dw is None when it was routed into the arena.  ``accumulate_into``:
     an existing bf16 NHWC tensor of dx's shape that dx is added to (and which is returned as dx).  ``src_bn``: record of
     the conv+BN layer that produced this conv's input -- its BatchNorm-backward sums are then reduced by the dgrad."""
@@ -395,8 +399,12 @@ def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: 
         if i.packed:
             dwp = torch.zeros((i.Cout, i.Cp, i.R, i.S), dtype=torch.float32, device=dy.device).contiguous(
                 memory_format=torch.channels_last)
-            call("picd_conv_wgrad", i.x, dy, dwp, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
-                 i.OH, i.OW)
+            if dbias is not None:
+                call("picd_conv_wgrad_bias", i.x, dy, dwp, dbias, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                     i.OH, i.OW)
+            else:
+                call("picd_conv_wgrad", i.x, dy, dwp, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                     i.OH, i.OW)
             g = _unpack_wgrad(dwp, i.orig_w_shape, i.s_pack, i.R, i.S)
             tgt, routed = _grad_target(w, True)
             if routed:
@@ -405,8 +413,12 @@ def _conv_backward(info: _ConvInfo, dy: torch.Tensor, w: torch.Tensor, need_dx: 
                 dw_ret = g.contiguous(memory_format=torch.channels_last)
         else:
             tgt, routed = _grad_target(w, True)
-            call("picd_conv_wgrad", i.x, dy, tgt, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
-                 i.OH, i.OW)
+            if dbias is not None:
+                call("picd_conv_wgrad_bias", i.x, dy, tgt, dbias, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                     i.OH, i.OW)
+            else:
+                call("picd_conv_wgrad", i.x, dy, tgt, i.N, i.H, i.W, i.Cin, i.Cout, i.R, i.S, i.stride, i.ph, i.pw,
+                     i.OH, i.OW)
             dw_ret = None if routed else tgt
         if dw_ret is None:
             _mark_ready(w)
@@ -641,16 +653,20 @@ class _Conv2d(torch.autograd.Function):
         w, bias = ctx.saved_tensors
         need = ctx.needs_input_grad
         dy = nhwc(dy)
-        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1])
         db = None
+        btgt, b_routed = (None, False)
         if bias is not None and need[2]:
-            tgt, routed = _grad_target(bias)
-            C = bias.numel()
-            call("picd_colsum", dy, tgt, dy.numel() // C, C)
-            if routed:
+            btgt, b_routed = _grad_target(bias)
+        fused_bias = btgt is not None and need[1]          # the wgrad kernel sums dy for the bias as well
+        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1], dbias=btgt if fused_bias else None)
+        if btgt is not None:
+            if not fused_bias:
+                C = bias.numel()
+                call("picd_colsum", dy, btgt, dy.numel() // C, C)
+            if b_routed:
                 _mark_ready(bias)
             else:
-                db = tgt
+                db = btgt
         return dx, dw, db, None, None
 
 
@@ -720,7 +736,8 @@ def _use_tc(M, N, K):
 
 class _LinearTC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, b, act):
+    def forward(ctx, x, w, b, act, external_bias_grad=False):
+        ctx.external_bias_grad = bool(external_bias_grad)     # the consumer of this output reduces db (add_layer_norm)
         K = w.shape[1]
         N = w.shape[0]
         x2 = x.reshape(-1, K)
@@ -767,7 +784,13 @@ class _LinearTC(torch.autograd.Function):
         dw = db = None
         if ctx.needs_input_grad[1]:
             tgt, routed = _grad_target(w)
-            call("picd_gemm_tn_f32", dy2, x2, tgt, M, N, K)
+            if (not bias_done) and b is not None and ctx.needs_input_grad[2] and not ctx.external_bias_grad:
+                # bias gradient = column sums of dY: the wgrad kernel computes them with a ones-tile MMA (no extra pass)
+                btgt, b_routed = _grad_target(b)
+                call("picd_gemm_tn_f32_bias", dy2, x2, tgt, btgt, M, N, K)
+                bias_done = True
+            else:
+                call("picd_gemm_tn_f32", dy2, x2, tgt, M, N, K)
             if routed:
                 _mark_ready(w)
             else:
@@ -777,14 +800,14 @@ class _LinearTC(torch.autograd.Function):
                 _mark_ready(b)
             else:
                 db = btgt
-        elif b is not None and ctx.needs_input_grad[2]:
+        elif b is not None and ctx.needs_input_grad[2] and not ctx.external_bias_grad:
             tgt, routed = _grad_target(b)
             call("picd_colsum", dy2, tgt, M, N)
             if routed:
                 _mark_ready(b)
             else:
                 db = tgt
-        return dx, dw, db, None
+        return dx, dw, db, None, None
 
 
 class _LinearSmall(torch.autograd.Function):
@@ -827,11 +850,11 @@ class _LinearSmall(torch.autograd.Function):
             (None if (b is None or b_routed) else bt), None
 
 
-def linear(x, w, b, act):
+def linear(x, w, b, act, external_bias_grad=False):
     N, K = w.shape
     M = x.numel() // K
     if _use_tc(M, N, K):
-        return _LinearTC.apply(x, w, b, act)
+        return _LinearTC.apply(x, w, b, act, external_bias_grad and act in (None, "none"))
     if act in (None, "none", "relu"):
         return _LinearSmall.apply(x, w, b, act)
     # swish / sigmoid / gelu on tiny tensors (squeeze-excite vectors): native linear, element-wise torch activation
@@ -1027,6 +1050,54 @@ def layer_norm(x, gamma, beta, eps):
     if x.shape[-1] % 8 != 0 or x.shape[-1] > 1024:
         return ref.layer_norm(x, gamma, beta, eps)
     return _LayerNorm.apply(x, gamma, beta, eps)
+
+
+class _AddLayerNorm(torch.autograd.Function):
+    """(s, y) = (x + delta, LayerNorm(x + delta)) in one kernel; the backward adds the gradient of ``s`` (the residual
+    stream) to the LayerNorm backward in one kernel as well and hands the SAME tensor to both inputs.  ``delta_bias``: bias
+    of the Linear that produced ``delta`` -- its gradient is the column sum of that tensor, reduced by the same kernel."""
+
+    @staticmethod
+    def forward(ctx, x, delta, gamma, beta, eps, delta_bias):
+        D = x.shape[-1]
+        x2 = x.reshape(-1, D)
+        d2 = delta.reshape(-1, D)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        if d2.dtype != torch.bfloat16:
+            d2 = d2.to(torch.bfloat16)
+        x2, d2 = x2.contiguous(), d2.contiguous()
+        M = x2.shape[0]
+        ssum, y = torch.empty_like(x2), torch.empty_like(x2)
+        stats = torch.empty(2, M, dtype=torch.float32, device=x.device)
+        call("picd_add_layernorm_fwd", x2, d2, gamma, beta, ssum, y, stats[0], stats[1], M, D, float(eps))
+        ctx.shape = x.shape
+        ctx.save_for_backward(ssum, gamma, beta, stats, delta_bias)
+        return ssum.view(x.shape), y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, ds, dy):
+        ssum, gamma, beta, stats, delta_bias = ctx.saved_tensors
+        M, D = ssum.shape
+        if dy is None:
+            dy = torch.zeros_like(ssum)
+        dy2 = dy.reshape(M, D).to(torch.bfloat16).contiguous()
+        ds2 = None if ds is None else ds.reshape(M, D).to(torch.bfloat16).contiguous()
+        dx = torch.empty_like(ssum)
+        gt, g_routed = _grad_target(gamma)
+        bt, b_routed = _grad_target(beta)
+        ct, c_routed = (None, False) if delta_bias is None else _grad_target(delta_bias)
+        call("picd_layernorm_bwd_add", dy2, ssum, gamma, stats[0], stats[1], ds2, dx, gt, bt, ct, M, D)
+        for prm, routed in ((gamma, g_routed), (beta, b_routed), (delta_bias, c_routed)):
+            if routed:
+                _mark_ready(prm)
+        dxv = dx.view(ctx.shape)
+        return dxv, dxv, (None if g_routed else gt), (None if b_routed else bt), None, \
+            (None if (delta_bias is None or c_routed) else ct)
+
+
+def add_layer_norm(x, delta, gamma, beta, eps, delta_bias=None):
+    return _AddLayerNorm.apply(x, delta, gamma, beta, eps, delta_bias)
 
 
 class _AttentionPacked(torch.autograd.Function):
