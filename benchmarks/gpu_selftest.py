@@ -214,6 +214,28 @@ def group_basic():
     ok &= check("layernorm.dgamma", gm.grad, gm2.grad, 3e-2, g)
     ok &= check("layernorm.dbeta", bt.grad, bt2.grad, 3e-2, g)
 
+    # residual add fused into LayerNorm (transformer blocks): (s, y) = (x + d, LN(x + d)); both outputs carry gradient
+    for (M, D) in [(50, 768), (333, 256), (64, 1024)]:
+        x = torch.randn(M, D, device=dev).to(torch.bfloat16)
+        d = torch.randn(M, D, device=dev).to(torch.bfloat16)
+        gm, bt = (torch.rand(D, device=dev) + 0.5).requires_grad_(), torch.randn(D, device=dev).requires_grad_()
+        xn, dn = x.clone().requires_grad_(), d.clone().requires_grad_()
+        sn, yn = ops.add_layer_norm(xn, dn, gm, bt, 1e-6)
+        gs, gy = torch.randn_like(sn), torch.randn_like(yn)
+        torch.autograd.backward([sn, yn], [gs, gy])
+        xr, dr = x.float().requires_grad_(), d.float().requires_grad_()
+        gm2, bt2 = gm.detach().clone().requires_grad_(), bt.detach().clone().requires_grad_()
+        sr = (xr + dr).to(torch.bfloat16).float() + 0 * (xr + dr)       # the kernel normalises the bf16-rounded sum
+        sr = xr + dr
+        yr = F.layer_norm(sr, (D,), gm2, bt2, 1e-6)
+        torch.autograd.backward([sr, yr], [gs.float(), gy.float()])
+        ok &= check(f"add_layernorm[{M},{D}].sum", sn, sr, 1e-2, g)
+        ok &= check(f"add_layernorm[{M},{D}].y", yn, yr, 2e-2, g)
+        ok &= check(f"add_layernorm[{M},{D}].dx", xn.grad, xr.grad, 3e-2, g)
+        ok &= check(f"add_layernorm[{M},{D}].ddelta", dn.grad, dr.grad, 3e-2, g)
+        ok &= check(f"add_layernorm[{M},{D}].dgamma", gm.grad, gm2.grad, 3e-2, g)
+        ok &= check(f"add_layernorm[{M},{D}].dbeta", bt.grad, bt2.grad, 3e-2, g)
+
     # small linear
     # the last three take the tcgen05 GEMM path with the separate activation kernels (GELU: fast erf; dbias fused in act_bwd)
     for (M, K, N, act) in [(16, 2048, 128, "relu"), (16, 32, 7, None), (5, 64, 32, "relu"), (1024, 768, 3072, "gelu"),
@@ -292,6 +314,30 @@ def group_gemm():
         native.call("picd_gemm_tn_f32_bias", dy, a, dw2, db, M, N, K)
         ok &= check(f"gemm_tn_bias[{M},{N},{K}].dw", dw2, dy.float().t() @ a.float(), 1.5e-2, g)
         ok &= check(f"gemm_tn_bias[{M},{N},{K}].db", db, dy.float().sum(0), 1e-2, g)
+    # transformer MLP chain: Linear+GELU -> Linear.  The second layer's dgrad multiplies by gelu'(pre) in its epilogue
+    # (picd_gemm_nn_actgrad) and both bias gradients come out of the wgrad kernels (ones-tile MMA)
+    from picd_b200 import ops
+    for (M, D, Hd, act) in [(1576, 768, 3072, "gelu"), (640, 256, 512, "swish")]:
+        torch.manual_seed(3)
+        x = torch.randn(M, D, device=dev).to(torch.bfloat16)
+        w1 = (torch.randn(Hd, D, device=dev) / D ** 0.5).requires_grad_()
+        b1 = (torch.randn(Hd, device=dev) * 0.1).requires_grad_()
+        w2 = (torch.randn(D, Hd, device=dev) / Hd ** 0.5).requires_grad_()
+        b2 = (torch.randn(D, device=dev) * 0.1).requires_grad_()
+        xn = x.clone().requires_grad_()
+        y = ops.linear(ops.linear(xn, w1, b1, act), w2, b2, None)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr = x.float().requires_grad_()
+        p2 = [t.detach().clone().requires_grad_() for t in (w1, b1, w2, b2)]
+        hr = torch.nn.functional.linear(xr, p2[0].to(torch.bfloat16).float(), p2[1])
+        hr = torch.nn.functional.gelu(hr) if act == "gelu" else torch.nn.functional.silu(hr)
+        yr = torch.nn.functional.linear(hr, p2[2].to(torch.bfloat16).float(), p2[3])
+        yr.backward(dy.float())
+        ok &= check(f"mlp[{M},{D},{Hd},{act}].fwd", y, yr, 2e-2, g)
+        ok &= check(f"mlp[{M},{D},{Hd},{act}].dx", xn.grad, xr.grad, 3e-2, g)
+        for nm, a_, b_ in zip(("dw1", "db1", "dw2", "db2"), (w1, b1, w2, b2), p2):
+            ok &= check(f"mlp[{M},{D},{Hd},{act}].{nm}", a_.grad, b_.grad, 3e-2, g)
     # throughput of the big ones
     for (M, N, K) in [(8192, 8192, 8192), (50432, 3072, 768), (50432, 768, 3072)]:
         a = torch.randn(M, K, device=dev).to(torch.bfloat16)

@@ -672,9 +672,13 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
     const int nt = rem % p.numN; rem /= p.numN;
     const int mt = rem % p.numM; rem /= p.numM;
     const int group = rem;                      // taps [group*G, group*G + G) share this CTA's dy tiles
-    const bool do_bias = p.dbias != nullptr && nt == 0 && group == 0;     // one CTA per (k-split, cout tile) sums dy
     const int pt_begin = static_cast<int>((static_cast<long long>(p.num_p_tiles) * split) / p.ksplit);
     const int pt_end = static_cast<int>((static_cast<long long>(p.num_p_tiles) * (split + 1)) / p.ksplit);
+    // the CTAs of the first tap group share the bias work: input-channel tile nt sums dy over the pixel tiles pt with
+    // pt % numN == nt (one CTA doing all of it finished ~10 % after its siblings and set the kernel's tail)
+    const bool bias_cta = p.dbias != nullptr && group == 0;
+    const int bias_first = pt_begin + ((nt - pt_begin % p.numN) + p.numN) % p.numN;      // first pt >= pt_begin with pt % numN == nt
+    const bool do_bias = bias_cta && bias_first < pt_end;
     const int bw = 1 << p.bw_log2, bh = 1 << p.bh_log2;
     const int bn = 64 >> (p.bw_log2 + p.bh_log2);
 
@@ -735,11 +739,11 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_kernel(const __grid_constan
                 for (int k = 0; k < 4; ++k)
                     umma_bf16_warp(tmem_base, adesc0 + k * (2048 >> 4), bdesc0 + k * (2048 >> 4), idesc,
                                    (pt > pt_begin) || (k != 0));
-                if (do_bias) {
+                if (do_bias && (pt - bias_first) % p.numN == 0 && pt >= bias_first) {
 #pragma unroll
                     for (int k = 0; k < 4; ++k)      // dy^T x ones: every one of the 16 result columns is the bias gradient
                         umma_bf16_warp(tmem_base + BN, adesc0 + k * (2048 >> 4), onesdesc0 + k * (2048 >> 4), idesc_ones,
-                                       (pt > pt_begin) || (k != 0));
+                                       (pt > bias_first) || (k != 0));
                 }
                 umma_commit_warp(&bars->empty[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }

@@ -509,6 +509,10 @@ __global__ void __launch_bounds__(256) dropout_kernel(const __nv_bfloat16* __res
 // A lane owns columns lane*8 + 256*i (i < V) of every row its warp handles: gamma / beta sit in registers for the whole
 // kernel and a row is read exactly once (it stays in registers between the statistics and the normalisation).  Warps walk
 // the rows grid-stride, two rows per iteration so that the loads of the second row overlap the reduction of the first.
+__device__ __forceinline__ void ld8f(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
 constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
 template <int V>
 __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
@@ -588,95 +592,75 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
 // memory once at the end (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).  Two rows per iteration: the
 // loads of the second row are in flight while the first one reduces.
 template <int V>
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                                                            const float* __restrict__ gamma, const float* __restrict__ mean,
-                                                            const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
-                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                            long long M, int D, int rows_per_block,
-                                                            const __nv_bfloat16* __restrict__ add_in,
-                                                            float* __restrict__ dcol) {
+__global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                               const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                               const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                               long long M, int D, int rows_per_block,
+                                                               const __nv_bfloat16* __restrict__ add_in) {
     // add_in (nullable): gradient arriving over the residual stream; the kernel writes dx = LayerNorm-backward + add_in, i.e. the
-    // gradient sum autograd would otherwise compute with a separate add kernel.  dcol (nullable, [D]): column sums of that
-    // final dx -- the bias gradient of the Linear layer whose output fed the residual add (its dY IS this dx).
-    extern __shared__ float sm[];   // [warps][3][V*256]: every warp parks its partial sums, no shared-memory atomics
+    // gradient sum autograd would otherwise compute with a separate add kernel.
+    // Register diet (two blocks per SM instead of one at 199 registers): a row is read TWICE -- pass A accumulates the two row
+    // sums and the parameter-gradient partials on the fly, pass B re-reads dy / x (L1 hits: a row is 3 KB) and writes dx -- so
+    // that no per-row array survives between the passes; gamma is re-read from L1 as well.
+    extern __shared__ float sm[];   // [warps][2][V*256]: every warp parks its partial sums, no shared-memory atomics
     pdl_sync();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    float pg[V][8], pb[V][8], pc[V][8], gm[V][8];
+    float pg[V][8], pb[V][8];
 #pragma unroll
-    for (int i = 0; i < V; ++i) {
-        const int j = lane * 8 + i * 256;
+    for (int i = 0; i < V; ++i)
 #pragma unroll
-        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; pc[i][k] = 0.f; gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; }
-    }
+        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; }
     const float inv_d = 1.f / D;
     const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
     long long r1 = r0 + rows_per_block;
     if (r1 > M) r1 = M;
-    for (long long row = r0 + warp * 2; row < r1; row += nw * 2) {
-        uint4 rg[2][V], rx[2][V];
-        float mu[2], rs[2];
+    for (long long row = r0 + warp; row < r1; row += nw) {
+        const float mu = mean[row], rs = rstd[row];
+        float a = 0.f, b = 0.f;
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            const bool live = row + r < r1;
-            mu[r] = live ? mean[row + r] : 0.f;
-            rs[r] = live ? rstd[row + r] : 0.f;
-#pragma unroll
-            for (int i = 0; i < V; ++i) {
-                const int j = lane * 8 + i * 256;
-                const bool ok = live && j < D;
-                rg[r][i] = ok ? *reinterpret_cast<const uint4*>(dy + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
-                rx[r][i] = ok ? *reinterpret_cast<const uint4*>(x + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            if (row + r >= r1) break;
-            float g[V][8], xh[V][8];
-            float a = 0.f, b = 0.f;
-#pragma unroll
-            for (int i = 0; i < V; ++i) {
-                float f[8];
-                unpack8(rg[r][i], g[i]);
-                unpack8(rx[r][i], f);
+        for (int i = 0; i < V; ++i) {
+            const int j = lane * 8 + i * 256;
+            if (j < D) {
+                float g[8], f[8], gm[8];
+                unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
+                unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+                ld8f(gamma + j, gm);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    xh[i][k] = (f[k] - mu[r]) * rs[r];
-                    const float gg = g[i][k] * gm[i][k];
-                    a += gg; b += gg * xh[i][k];
-                    pg[i][k] += g[i][k] * xh[i][k];
-                    pb[i][k] += g[i][k];
+                    const float xh = (f[k] - mu) * rs;
+                    const float gg = g[k] * gm[k];
+                    a += gg; b = fmaf(gg, xh, b);
+                    pg[i][k] = fmaf(g[k], xh, pg[i][k]);
+                    pb[i][k] += g[k];
                 }
             }
-            a = warp_sum(a) * inv_d; b = warp_sum(b) * inv_d;
+        }
+        a = warp_sum(a) * inv_d; b = warp_sum(b) * inv_d;
 #pragma unroll
-            for (int i = 0; i < V; ++i) {
-                const int j = lane * 8 + i * 256;
-                if (j < D) {
-                    float o[8];
+        for (int i = 0; i < V; ++i) {
+            const int j = lane * 8 + i * 256;
+            if (j < D) {
+                float g[8], f[8], gm[8], o[8];
+                unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
+                unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
+                ld8f(gamma + j, gm);
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) o[k] = rs[r] * (g[i][k] * gm[i][k] - a - xh[i][k] * b);
-                    if (add_in != nullptr) {
-                        float ad[8];
-                        unpack8(*reinterpret_cast<const uint4*>(add_in + (row + r) * D + j), ad);
+                for (int k = 0; k < 8; ++k) o[k] = rs * (g[k] * gm[k] - a - (f[k] - mu) * rs * b);
+                if (add_in != nullptr) {
+                    float ad[8];
+                    unpack8(*reinterpret_cast<const uint4*>(add_in + row * D + j), ad);
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) o[k] += ad[k];
-                    }
-                    const uint4 packed = pack8(o);
-                    *reinterpret_cast<uint4*>(dx + (row + r) * D + j) = packed;
-                    if (dcol != nullptr) {
-                        float ob[8];
-                        unpack8(packed, ob);               // sum what the consumer GEMMs will read (bf16-rounded)
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) pc[i][k] += ob[k];
-                    }
+                    for (int k = 0; k < 8; ++k) o[k] += ad[k];
                 }
+                *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
             }
         }
     }
     // fold the block's warps: warp w writes its partials to sm[w], then every thread sums a few columns over the warps and
     // issues one global atomic per column (the former version did 2 x 8 x V shared-memory atomics per thread, 8-way contended)
     constexpr int W2 = V * 256;
-    float* mine = sm + static_cast<size_t>(warp) * 3 * W2;
+    float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
@@ -684,20 +668,16 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
         *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
         *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
         *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
-        *reinterpret_cast<float4*>(mine + 2 * W2 + j) = make_float4(pc[i][0], pc[i][1], pc[i][2], pc[i][3]);
-        *reinterpret_cast<float4*>(mine + 2 * W2 + j + 4) = make_float4(pc[i][4], pc[i][5], pc[i][6], pc[i][7]);
     }
     __syncthreads();
     for (int j = threadIdx.x; j < D; j += blockDim.x) {
-        float a = 0.f, b = 0.f, c = 0.f;
+        float a = 0.f, b = 0.f;
         for (int w = 0; w < nw; ++w) {
-            a += sm[static_cast<size_t>(w) * 3 * W2 + j];
-            b += sm[static_cast<size_t>(w) * 3 * W2 + W2 + j];
-            c += sm[static_cast<size_t>(w) * 3 * W2 + 2 * W2 + j];
+            a += sm[static_cast<size_t>(w) * 2 * W2 + j];
+            b += sm[static_cast<size_t>(w) * 2 * W2 + W2 + j];
         }
         atomicAdd(dgamma + j, a);
         atomicAdd(dbeta + j, b);
-        if (dcol != nullptr) atomicAdd(dcol + j, c);
     }
 }
 
@@ -1088,17 +1068,14 @@ extern "C" int picd_layernorm_fwd(const void* x, const float* gamma, const float
                                   long long M, int D, float eps, cudaStream_t st) {
     return picd_add_layernorm_fwd(x, nullptr, gamma, beta, nullptr, y, mean, rstd, M, D, eps, st);
 }
-// dx = LayerNorm-backward(dy, x) + add_in (nullable: the gradient arriving over the residual stream); dcol (nullable, [D],
-// accumulated): column sums of dx = the bias gradient of the Linear whose output was added into the residual stream.
+// dx = LayerNorm-backward(dy, x) + add_in (nullable: the gradient arriving over the residual stream).
 extern "C" int picd_layernorm_bwd_add(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
-                                      const void* add_in, void* dx, float* dgamma, float* dbeta, float* dcol, long long M,
-                                      int D, cudaStream_t st) {
+                                      const void* add_in, void* dx, float* dgamma, float* dbeta, long long M, int D,
+                                      cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
     static bool attr_set = false;
-    if (!attr_set) {       // V = 4 parks 8 warps x 3 x 1024 floats = 96 KB
-        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    if (!attr_set) {       // V = 4 parks 8 warps x 2 x 1024 floats = 64 KB
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         attr_set = true;
     }
     long long blocks = 2LL * num_sms();
@@ -1108,9 +1085,9 @@ extern "C" int picd_layernorm_bwd_add(const void* dy, const void* x, const float
     const int V = (D + 255) / 256;
 #define PICD_LN_BWD(VV)                                                                                                   \
     PICD_CUDA(launch_pdl<PDL_ROWWISE>(layernorm_bwd_kernel<VV>, dim3(static_cast<unsigned>(blocks)), dim3(256),                         \
-        8 * 3 * VV * 256 * sizeof(float), st,                                                                             \
+        8 * 2 * VV * 256 * sizeof(float), st,                                                                             \
         static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, \
-        M, D, static_cast<int>(rpb), static_cast<const bf16*>(add_in), dcol))
+        M, D, static_cast<int>(rpb), static_cast<const bf16*>(add_in)))
     if (V == 1) PICD_LN_BWD(1); else if (V == 2) PICD_LN_BWD(2); else if (V == 3) PICD_LN_BWD(3); else PICD_LN_BWD(4);
 #undef PICD_LN_BWD
     PICD_LAUNCH_CHECK();
@@ -1118,7 +1095,7 @@ extern "C" int picd_layernorm_bwd_add(const void* dy, const void* x, const float
 }
 extern "C" int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
                                   void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t st) {
-    return picd_layernorm_bwd_add(dy, x, gamma, mean, rstd, nullptr, dx, dgamma, dbeta, nullptr, M, D, st);
+    return picd_layernorm_bwd_add(dy, x, gamma, mean, rstd, nullptr, dx, dgamma, dbeta, M, D, st);
 }
 extern "C" int picd_small_linear_fwd(const void* x, const float* w, const float* bias, void* y, int M, int N, int K, int act,
                                      int out_fp32, cudaStream_t st) {

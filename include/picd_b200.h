@@ -155,13 +155,11 @@ int picd_dropout(const void* x, void* out, long long n, float p, unsigned seed, 
 int picd_dropout_dyn(const void* x, void* out, long long n, float p, unsigned seed, const void* step_word,
                      cudaStream_t stream);
 /* Transformer residual add fused into the LayerNorm that follows it: s = x + res (bf16) -> sum_out, y = LayerNorm(s).
- * Backward: dx = LayerNorm-backward(dy, s) + add_in (gradient arriving over the residual stream, nullable); dcol (nullable,
- * accumulated): column sums of dx = bias gradient of the Linear whose output was `res`. */
+ * Backward: dx = LayerNorm-backward(dy, s) + add_in (gradient arriving over the residual stream, nullable). */
 int picd_add_layernorm_fwd(const void* x, const void* res, const float* gamma, const float* beta, void* sum_out, void* y,
                            float* mean, float* rstd, long long M, int D, float eps, cudaStream_t stream);
 int picd_layernorm_bwd_add(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
-                           const void* add_in, void* dx, float* dgamma, float* dbeta, float* dcol, long long M, int D,
-                           cudaStream_t stream);
+                           const void* add_in, void* dx, float* dgamma, float* dbeta, long long M, int D, cudaStream_t stream);
 int picd_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                        long long M, int D, float eps, cudaStream_t stream);
 int picd_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,

@@ -139,8 +139,8 @@ class Linear(nn.Module):
         else:
             self.register_parameter("bias", None)
 
-    def forward(self, x, external_bias_grad: bool = False):
-        return ops.linear(x, self.weight, self.bias, self.act, external_bias_grad)
+    def forward(self, x):
+        return ops.linear(x, self.weight, self.bias, self.act)
 
     def extra_repr(self):
         return f"{self.in_features}, {self.out_features}, bias={self.bias is not None}, act={self.act}"

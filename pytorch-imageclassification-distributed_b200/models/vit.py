@@ -28,11 +28,11 @@ class SelfAttention(nn.Module):
         self.out_proj = Linear(dim, dim)
         nn.init.zeros_(self.out_proj.bias)
 
-    def forward(self, x, external_bias_grad: bool = False):
+    def forward(self, x):
         b, s, d = x.shape
         qkv = ops.linear(x.reshape(b * s, d), self.in_proj_weight, self.in_proj_bias)    # [b*s, 3d], packed q|k|v
         o = ops.attention_packed(qkv, b, s, self.heads)                                    # [b*s, d]
-        return self.out_proj(o, external_bias_grad).view(b, s, d)
+        return self.out_proj(o).view(b, s, d)
 
 
 class MLPBlock(nn.Sequential):
@@ -62,18 +62,12 @@ class EncoderBlock(nn.Module):
     def forward_fused(self, x, h, next_ln):
         """Same block with the two residual adds fused into the LayerNorms that follow them (``ops.add_layer_norm``):
         ``x`` is the residual stream, ``h = ln_1(x)`` was produced by the previous block's second add, and this block's
-        second add is fused with ``next_ln`` (the next block's ``ln_1`` or the encoder's final LayerNorm).  Without
-        dropout the bias gradients of ``out_proj`` / the second MLP layer are reduced by the same backward kernels."""
+        second add is fused with ``next_ln`` (the next block's ``ln_1`` or the encoder's final LayerNorm)."""
         b, s, d = x.shape
-        drop = self.training and self.dropout.p > 0.0
-        ext = ops.fuses_add_layer_norm(x) and not drop
-        a = self.self_attention(h, external_bias_grad=ext)
-        x, h = ops.add_layer_norm(x, self.dropout(a), self.ln_2.weight, self.ln_2.bias, self.ln_2.eps,
-                                  self.self_attention.out_proj.bias if ext else None)
-        y = self.mlp[0](h.reshape(b * s, d))
-        y = self.mlp[2](self.mlp[1](y))
-        y = self.mlp[4](self.mlp[3](y, ext)).view(b, s, d)
-        return ops.add_layer_norm(x, y, next_ln.weight, next_ln.bias, next_ln.eps, self.mlp[3].bias if ext else None)
+        a = self.dropout(self.self_attention(h))
+        x, h = ops.add_layer_norm(x, a, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps)
+        y = self.mlp(h.reshape(b * s, d)).view(b, s, d)
+        return ops.add_layer_norm(x, y, next_ln.weight, next_ln.bias, next_ln.eps)
 
 
 class Encoder(nn.Module):

@@ -125,28 +125,20 @@ def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum, ep
     return ref.activation(z, act)
 
 
-def linear(x, w, b=None, act: Optional[str] = None, external_bias_grad: bool = False):
-    """``external_bias_grad``: the caller promises to pass ``b`` as ``delta_bias`` to :func:`add_layer_norm` together with
-    this output, whose backward kernel then reduces the bias gradient (native path only; ignored elsewhere)."""
+def linear(x, w, b=None, act: Optional[str] = None):
     if use_native(x):
         from . import native
-        return native.linear(x, w, b, act, external_bias_grad)
+        return native.linear(x, w, b, act)
     return ref.linear(x, w, b, act)
 
 
-def fuses_add_layer_norm(x) -> bool:
-    """True when :func:`add_layer_norm` runs the fused kernels for this tensor (and so may own a bias gradient)."""
-    return x.is_cuda and not _force_torch() and x.shape[-1] % 8 == 0 and x.shape[-1] <= 1024
-
-
-def add_layer_norm(x, delta, gamma, beta, eps=1e-6, delta_bias=None):
-    """Transformer residual step: returns ``(x + delta, LayerNorm(x + delta))``.  On the native path one kernel does both
-    (and one kernel the whole backward, including the gradient sum over the residual stream and -- with ``delta_bias`` -- the
-    bias gradient of the Linear that produced ``delta``)."""
-    if fuses_add_layer_norm(x):
+def add_layer_norm(x, delta, gamma, beta, eps=1e-6):
+    """Transformer residual step: returns ``(x + delta, LayerNorm(x + delta))``.  On the native path one kernel does both,
+    and one kernel the whole backward including the gradient sum over the residual stream."""
+    if x.is_cuda and not _force_torch() and x.shape[-1] % 8 == 0 and x.shape[-1] <= 1024:
         require_lib()
         from . import native
-        return native.add_layer_norm(x, delta, gamma, beta, eps, delta_bias)
+        return native.add_layer_norm(x, delta, gamma, beta, eps)
     s = x + delta
     return s, layer_norm(s, gamma, beta, eps)
 

@@ -69,7 +69,7 @@ _SIG = {
     "picd_layernorm_fwd": "pppppplifp",
     "picd_layernorm_bwd": "pppppppplip",
     "picd_add_layernorm_fwd": "pppppppplifp",
-    "picd_layernorm_bwd_add": "pppppppppplip",
+    "picd_layernorm_bwd_add": "ppppppppplip",
     "picd_small_linear_fwd": "ppppiiiiip",
     "picd_small_linear_bwd": "pppppppp" + "iiiiii" + "p",
     "picd_pack_s2d": "pp" + "i" * 11 + "p",
@@ -736,8 +736,7 @@ def _use_tc(M, N, K):
 
 class _LinearTC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, b, act, external_bias_grad=False):
-        ctx.external_bias_grad = bool(external_bias_grad)     # the consumer of this output reduces db (add_layer_norm)
+    def forward(ctx, x, w, b, act):
         K = w.shape[1]
         N = w.shape[0]
         x2 = x.reshape(-1, K)
@@ -784,7 +783,7 @@ class _LinearTC(torch.autograd.Function):
         dw = db = None
         if ctx.needs_input_grad[1]:
             tgt, routed = _grad_target(w)
-            if (not bias_done) and b is not None and ctx.needs_input_grad[2] and not ctx.external_bias_grad:
+            if (not bias_done) and b is not None and ctx.needs_input_grad[2]:
                 # bias gradient = column sums of dY: the wgrad kernel computes them with a ones-tile MMA (no extra pass)
                 btgt, b_routed = _grad_target(b)
                 call("picd_gemm_tn_f32_bias", dy2, x2, tgt, btgt, M, N, K)
@@ -800,14 +799,14 @@ class _LinearTC(torch.autograd.Function):
                 _mark_ready(b)
             else:
                 db = btgt
-        elif b is not None and ctx.needs_input_grad[2] and not ctx.external_bias_grad:
+        elif b is not None and ctx.needs_input_grad[2]:
             tgt, routed = _grad_target(b)
             call("picd_colsum", dy2, tgt, M, N)
             if routed:
                 _mark_ready(b)
             else:
                 db = tgt
-        return dx, dw, db, None, None
+        return dx, dw, db, None
 
 
 class _LinearSmall(torch.autograd.Function):
@@ -850,11 +849,11 @@ class _LinearSmall(torch.autograd.Function):
             (None if (b is None or b_routed) else bt), None
 
 
-def linear(x, w, b, act, external_bias_grad=False):
+def linear(x, w, b, act):
     N, K = w.shape
     M = x.numel() // K
     if _use_tc(M, N, K):
-        return _LinearTC.apply(x, w, b, act, external_bias_grad and act in (None, "none"))
+        return _LinearTC.apply(x, w, b, act)
     if act in (None, "none", "relu"):
         return _LinearSmall.apply(x, w, b, act)
     # swish / sigmoid / gelu on tiny tensors (squeeze-excite vectors): native linear, element-wise torch activation
@@ -1054,11 +1053,10 @@ def layer_norm(x, gamma, beta, eps):
 
 class _AddLayerNorm(torch.autograd.Function):
     """(s, y) = (x + delta, LayerNorm(x + delta)) in one kernel; the backward adds the gradient of ``s`` (the residual
-    stream) to the LayerNorm backward in one kernel as well and hands the SAME tensor to both inputs.  ``delta_bias``: bias
-    of the Linear that produced ``delta`` -- its gradient is the column sum of that tensor, reduced by the same kernel."""
+    stream) to the LayerNorm backward in one kernel as well and hands the SAME tensor to both inputs."""
 
     @staticmethod
-    def forward(ctx, x, delta, gamma, beta, eps, delta_bias):
+    def forward(ctx, x, delta, gamma, beta, eps):
         D = x.shape[-1]
         x2 = x.reshape(-1, D)
         d2 = delta.reshape(-1, D)
@@ -1072,12 +1070,12 @@ class _AddLayerNorm(torch.autograd.Function):
         stats = torch.empty(2, M, dtype=torch.float32, device=x.device)
         call("picd_add_layernorm_fwd", x2, d2, gamma, beta, ssum, y, stats[0], stats[1], M, D, float(eps))
         ctx.shape = x.shape
-        ctx.save_for_backward(ssum, gamma, beta, stats, delta_bias)
+        ctx.save_for_backward(ssum, gamma, beta, stats)
         return ssum.view(x.shape), y.view(x.shape)
 
     @staticmethod
     def backward(ctx, ds, dy):
-        ssum, gamma, beta, stats, delta_bias = ctx.saved_tensors
+        ssum, gamma, beta, stats = ctx.saved_tensors
         M, D = ssum.shape
         if dy is None:
             dy = torch.zeros_like(ssum)
@@ -1086,18 +1084,17 @@ class _AddLayerNorm(torch.autograd.Function):
         dx = torch.empty_like(ssum)
         gt, g_routed = _grad_target(gamma)
         bt, b_routed = _grad_target(beta)
-        ct, c_routed = (None, False) if delta_bias is None else _grad_target(delta_bias)
-        call("picd_layernorm_bwd_add", dy2, ssum, gamma, stats[0], stats[1], ds2, dx, gt, bt, ct, M, D)
-        for prm, routed in ((gamma, g_routed), (beta, b_routed), (delta_bias, c_routed)):
-            if routed:
-                _mark_ready(prm)
+        call("picd_layernorm_bwd_add", dy2, ssum, gamma, stats[0], stats[1], ds2, dx, gt, bt, M, D)
+        if g_routed:
+            _mark_ready(gamma)
+        if b_routed:
+            _mark_ready(beta)
         dxv = dx.view(ctx.shape)
-        return dxv, dxv, (None if g_routed else gt), (None if b_routed else bt), None, \
-            (None if (delta_bias is None or c_routed) else ct)
+        return dxv, dxv, (None if g_routed else gt), (None if b_routed else bt), None
 
 
-def add_layer_norm(x, delta, gamma, beta, eps, delta_bias=None):
-    return _AddLayerNorm.apply(x, delta, gamma, beta, eps, delta_bias)
+def add_layer_norm(x, delta, gamma, beta, eps):
+    return _AddLayerNorm.apply(x, delta, gamma, beta, eps)
 
 
 class _AttentionPacked(torch.autograd.Function):
