@@ -161,15 +161,16 @@ def run_b200(args):
                "h2d_bytes_per_step": host_loader.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e / args.steps}
 
-    # replica identity (what DDP guarantees, train.py:128), checked OUTSIDE the timed regions: every rank hashes its fp32
-    # masters (BN running statistics are rank-local between two forwards unless SyncBN is on, exactly as under DDP's
+    # replica identity (what DDP guarantees, train.py:128), checked OUTSIDE the timed regions: every rank hashes its
+    # weights (BN running statistics are rank-local between two forwards unless SyncBN is on, exactly as under DDP's
     # per-forward buffer broadcast) and the hashes are compared across ranks
     replicas_identical = None
     if world > 1:
         import hashlib
         import torch.distributed as dist
         torch.cuda.synchronize()
-        h = hashlib.sha1(dp.arena.master.detach().cpu().numpy().tobytes())
+        # the bf16 compute copies are what every rank trains with (the fp32 masters are sharded by slice owner)
+        h = hashlib.sha1(dp.arena.shadow.detach().view(torch.int16).cpu().numpy().tobytes())
         if args.sync_bn:
             for b in dp.module.buffers():
                 h.update(b.detach().cpu().numpy().tobytes())

@@ -42,10 +42,30 @@ def all_ok(flag: bool, device) -> bool:
     return bool(t.item())
 
 
-def check_fused_update(device, mode):
+def replicas_identical(dp, world):
+    """bf16 compute copies bit-identical on every rank, and -- after the collective gather of the sharded fp32 masters --
+    the masters too."""
+    dp.sync_masters()
+    torch.cuda.synchronize()
+    same = True
+    for flat in (dp.arena.shadow, dp.arena.master):
+        mine = flat.clone()
+        gathered = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(gathered, mine)
+        bits = torch.int16 if flat.dtype == torch.bfloat16 else torch.int32      # bit-for-bit, NaN-proof
+        same = same and all(torch.equal(gathered[0].view(bits), t.view(bits)) for t in gathered)
+    return same
+
+
+def check_fused_update(device, mode, wire="bf16"):
     from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
     rank, world = dist.get_rank(), dist.get_world_size()
     ok = True
+    os.environ["PICD_GRAD_WIRE"] = wire          # read when the communicator is created; the same on every rank
+    # bf16 wire: the reference below rounds the gradients the same way, but a gradient within one fp32 ulp of a bf16 rounding
+    # boundary can still land on the other side (0.4 % of that element), which Adam's normalisation amplifies for
+    # elements with tiny second moments (measured: SGD 1e-6 .. 5e-4, AdamW 2.5e-3 .. 4.6e-3)
+    tols = {"fp32": {"sgd": 2e-4, "adamw": 2e-4}, "bf16": {"sgd": 2e-3, "adamw": 1e-2}}
     for kind in ("sgd", "adamw"):
         torch.manual_seed(0)
         net = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.ReLU(), torch.nn.Linear(512, 1024),
@@ -57,7 +77,7 @@ def check_fused_update(device, mode):
         dp = FusedDataParallel(net, OptimizerSpec(kind=kind, lr=lr, momentum=0.9, weight_decay=0.01),
                                first_bucket_bytes=64 << 10, bucket_cap_bytes=1 << 20, comm=mode)
         if mode == "nvls" and not dp._impl.comm.has_nvls:
-            emit({"test": f"fused_update[{mode},{kind}]", "skipped": "no NVSwitch multicast mapping on this host", "ok": True})
+            emit({"test": f"fused_update[{mode},{kind},{wire}]", "skipped": "no NVSwitch multicast mapping on this host", "ok": True})
             del dp
             continue
         opt = (torch.optim.SGD(ref.parameters(), lr=lr, momentum=0.9, weight_decay=0.01) if kind == "sgd"
@@ -70,22 +90,25 @@ def check_fused_update(device, mode):
             opt.zero_grad()
             ref(x).square().mean().backward()
             for p in ref.parameters():
+                if wire == "bf16":       # the reference applies the wire format: every rank's gradient is rounded to bf16
+                    p.grad.copy_(p.grad.to(torch.bfloat16).float())
                 dist.all_reduce(p.grad)
+                if wire == "bf16" and dp._impl._mode(dp.arena.buckets[0]) >= 3:
+                    p.grad.copy_(p.grad.to(torch.bfloat16).float())      # the switch delivers its fp32 sum as bf16
                 p.grad /= world
             opt.step()
-        torch.cuda.synchronize()
+        identical = replicas_identical(dp, world)          # also gathers the sharded masters
         errs = [relerr(a, b) for a, b in zip(net.parameters(), ref.parameters())]
-        flat = dp.arena.master.clone()
-        gathered = [torch.empty_like(flat) for _ in range(world)]
-        dist.all_gather(gathered, flat)
-        identical = all(torch.equal(gathered[0], t) for t in gathered)
         sh_ok = relerr(dp.arena.shadow.float(), dp.arena.master) < 1e-2
         zero = dp.arena.grad.abs().max().item() == 0
-        good = max(errs) < 2e-4 and identical and sh_ok and zero
-        emit({"test": f"fused_update[{mode},{kind}]", "max_relerr": max(errs), "replicas_identical": identical,
-              "shadow_ok": sh_ok, "grad_zeroed": zero, "buckets": len(dp.arena.buckets), "ok": good})
+        tol = tols[wire][kind]
+        good = all_ok(max(errs) < tol and identical and sh_ok and zero, device)
+        emit({"test": f"fused_update[{mode},{kind},{wire}]", "max_relerr": max(errs), "tol": tol, "replicas_identical": identical,
+              "shadow_ok": sh_ok, "grad_zeroed": zero, "buckets": len(dp.arena.buckets),
+              "masters_sharded": dp.masters_sharded, "ok": good})
         ok &= good
         del dp
+    os.environ.pop("PICD_GRAD_WIRE", None)
     return ok
 
 
@@ -148,10 +171,7 @@ def check_training(device):
             loss.backward()
             dp.optimizer.step()
             losses.append(float(loss.item()))
-        flat = dp.arena.master.clone()
-        gathered = [torch.empty_like(flat) for _ in range(world)]
-        dist.all_gather(gathered, flat)
-        identical = all(torch.equal(gathered[0], t) for t in gathered)
+        identical = replicas_identical(dp, world)
         # BN running statistics: rank 0's copy is pushed to every peer by the step's last bucket kernel (DDP's per-forward
         # buffer broadcast); with SyncBN they are identical by construction
         bufs = dp._flat_buffers.clone()
@@ -164,6 +184,43 @@ def check_training(device):
         ok &= good
         del dp
     return ok
+
+
+def check_sharded_masters(device):
+    """PICD_SHARD_MASTERS=1 (slice owners keep their fp32 masters to themselves, only the bf16 copies travel) must produce,
+    after the collective gather, bit-for-bit the masters and compute copies of the replicated-master run.  Gradients are
+    written into the arena directly, so nothing in this check reads a parameter between the updates."""
+    from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec
+    rank, world = dist.get_rank(), dist.get_world_size()
+    results = {}
+    for shard in (False, True):
+        os.environ["PICD_SHARD_MASTERS"] = "1" if shard else "0"
+        holder = torch.nn.Module()
+        torch.manual_seed(5)
+        holder.w = torch.nn.Parameter(torch.randn(3 * (1 << 20) + 320, device=device) * 0.05)
+        dp = FusedDataParallel(holder, OptimizerSpec("adamw", lr=1e-3, weight_decay=0.01), first_bucket_bytes=1 << 20,
+                               bucket_cap_bytes=4 << 20, comm="two_shot", overlap=False)
+        for it in range(3):
+            g = torch.Generator(device="cpu").manual_seed(17 * it + rank)
+            dp.arena.grad[: holder.w.numel()].copy_(torch.randn(holder.w.numel(), generator=g).to(device) * 1e-2)
+            dp.finish_step()
+        stale_guard = False
+        if shard:
+            try:
+                dp.state_dict()
+            except RuntimeError:
+                stale_guard = True           # state_dict() refuses while the masters are stale
+        dp.sync_masters()
+        torch.cuda.synchronize()
+        results[shard] = (dp.arena.master.clone(), dp.arena.shadow.clone(), dp.masters_sharded, stale_guard, len(dp.arena.buckets))
+        del dp
+    os.environ.pop("PICD_SHARD_MASTERS", None)
+    (m0, s0, f0, _, nb), (m1, s1, f1, guard, _) = results[False], results[True]
+    same = bool(torch.equal(m0.view(torch.int32), m1.view(torch.int32)) and torch.equal(s0.view(torch.int16), s1.view(torch.int16)))
+    good = all_ok(same and (not f0) and f1 and guard, device)
+    emit({"test": "sharded_masters[two_shot,adamw]", "equal_to_replicated": same, "sharded": [f0, f1], "stale_guard": guard,
+          "buckets": nb, "ok": good})
+    return good
 
 
 def check_optimizer_checkpoint(device):
@@ -188,15 +245,18 @@ def check_optimizer_checkpoint(device):
 
     a = build()
     steps(a, 0, 3)
+    a.sync_masters()                                       # collective: the fp32 masters are sharded by slice owner
     weights = {k: v.detach().clone() for k, v in a.state_dict().items()}
     opt = a.optimizer.state_dict()                         # collective
     steps(a, 3, 6)
+    a.sync_masters()
     want = a.arena.master.clone()
     del a
     b = build()
     b.load_state_dict(weights)
     b.optimizer.load_state_dict(opt)
     steps(b, 3, 6)
+    b.sync_masters()
     same = all_ok(bool(torch.equal(b.arena.master, want)), device)
     nz = [float(t.abs().sum()) > 0 for t in opt["state"]]
     emit({"test": "optimizer_checkpoint[two_shot,adamw]", "resumed_equals_uninterrupted": same, "state_nonzero": nz,
@@ -230,10 +290,7 @@ def check_graph_training(device):
                 bsz = 8 if it == 6 else 16                      # step 6 is a ragged batch: runs eagerly in both arms
                 img, lab = synthetic_batch(bsz, 3, 64, 64, 7, 0, (it % 3) * world + rank, device, torch.bfloat16)
                 losses.append(float(step(img, lab).item()))
-            flat = dp.arena.master.clone()
-            gathered = [torch.empty_like(flat) for _ in range(world)]
-            dist.all_gather(gathered, flat)
-            identical = all(torch.equal(gathered[0], t) for t in gathered)
+            identical = replicas_identical(dp, world)
             bufs = dp._flat_buffers.clone()
             bg = [torch.empty_like(bufs) for _ in range(world)]
             dist.all_gather(bg, bufs)
@@ -260,9 +317,11 @@ def sweep(device):
         p = torch.nn.Parameter(torch.zeros(n, device=device))
         holder = torch.nn.Module()
         holder.w = p
-        for mode in ("one_shot", "two_shot", "nvls", "nvls_ld"):
+        for mode in ("one_shot", "two_shot", "nvls", "nvls_ld", "two_shot+shard", "nvls+shard"):
             if mode == "one_shot" and n * 4 > (64 << 20):
                 continue
+            os.environ["PICD_SHARD_MASTERS"] = "1" if mode.endswith("+shard") else "0"
+            mode = mode.split("+")[0]
             dp = FusedDataParallel(holder, OptimizerSpec("sgd", lr=0.01, momentum=0.9), first_bucket_bytes=1 << 40,
                                    bucket_cap_bytes=1 << 40, comm=mode, overlap=False)
             if mode.startswith("nvls") and not dp._impl.comm.has_nvls:
@@ -286,7 +345,8 @@ def sweep(device):
             ms = torch.tensor([a.elapsed_time(e) / iters], device=device)
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             bytes_ = dp.arena.total * 4
-            emit({"test": "sweep", "impl": f"p2p_{mode}", "bytes": bytes_, "ms": float(ms), "world": world,
+            emit({"test": "sweep", "impl": f"p2p_{mode}", "wire": "bf16" if dp._impl.comm.wire_bf16 else "fp32",
+                  "masters_sharded": dp.masters_sharded, "bytes": bytes_, "ms": float(ms), "world": world,
                   "busbw_GBs": 2 * (world - 1) / world * bytes_ / (float(ms) * 1e-3) / 1e9, "ok": True})
             del dp
         # NCCL baseline: all_reduce + /W + momentum SGD (foreach) + bf16 cast, what DDP + optimizer.step amount to
@@ -328,10 +388,13 @@ def main():
     ok = True
     if not args.skip_checks:
         for mode in ("one_shot", "two_shot", "nvls", "auto"):
-            ok &= check_fused_update(device, mode)
+            ok &= check_fused_update(device, mode, "bf16")
+        for mode in ("two_shot", "nvls"):
+            ok &= check_fused_update(device, mode, "fp32")       # full-precision exchange, replicated masters
         ok &= check_sync_bn(device)
         ok &= check_training(device)
         ok &= check_optimizer_checkpoint(device)
+        ok &= check_sharded_masters(device)
         ok &= check_graph_training(device)
     if args.sweep:
         sweep(device)

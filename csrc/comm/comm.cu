@@ -13,6 +13,10 @@
 //       NVLS        : two-shot through the NVSwitch multicast mapping of the slab (when the host provides one): the slice
 //                     owner pulls the in-switch reduced gradients with multimem.ld_reduce and broadcasts master + shadow with
 //                     multimem.st (mode 3), or keeps the unicast pushes (mode 4, faster above ~512 MB)
+//       bf16 wire   : (default) before the barrier-in every rank packs its fp32 gradients of the bucket to bf16 into a staging
+//                     region of its slab; peers read THAT (2 B per element instead of 4), and with sharded masters the owner
+//                     keeps its fp32 master slice to itself and pushes only the bf16 compute copy (2 B instead of 6):
+//                     2.5x fewer NVLink bytes per bucket
 //       barrier-out : once every peer has read my gradients and pushed my weights, re-zero my gradient bucket
 //   bn_finalize_sync_kernel        SyncBatchNorm statistics: publish (sum, sumsq, count), wait, sum all peers'
 //                                   slots in rank order, finalize scale/shift/running stats -- one launch, no NCCL
@@ -32,11 +36,13 @@ struct PeerTable {
     float* xchg[MAX_PEERS];          // exchange slots for small collectives
     unsigned* flags[MAX_PEERS];
     float* bufs[MAX_PEERS];          // module buffers (BatchNorm running statistics) kept identical to rank 0's, or nullptr
+    __nv_bfloat16* gbf[MAX_PEERS];   // bf16 staging copies of the gradient arenas (the wire format of the reduction), or nullptr
     // NVSwitch multicast (NVLS) views of the same regions, or nullptr: a multimem.ld_reduce on mc_grad returns the sum over all
     // ranks computed inside the switch, a multimem.st on mc_master / mc_shadow lands in every rank's copy
     float* mc_grad;
     float* mc_master;
     __nv_bfloat16* mc_shadow;
+    __nv_bfloat16* mc_gbf;
 };
 
 struct OptArgs {
@@ -64,6 +70,18 @@ __device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
     float4 v;
     asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+// in-switch sum of four bf16 values from every rank (accumulated in fp32 inside the switch, delivered as bf16)
+__device__ __forceinline__ uint2 multimem_ld_reduce_bf16x4(const __nv_bfloat16* mc) {
+    uint2 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0, %1}, [%2];"
+                 : "=r"(v.x), "=r"(v.y) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint2 ld_peer_u2(const void* p) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
     return v;
 }
 __device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
@@ -130,7 +148,9 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
                                                                      float* __restrict__ state1, OptArgs opt,
                                                                      int slot_in, int slot_out, unsigned epoch,
                                                                      unsigned* block_counter,
-                                                                     const float* __restrict__ dyn, long long bcast_n) {
+                                                                     const float* __restrict__ dyn, long long bcast_n,
+                                                                     int wire_bf16, int shard_master,
+                                                                     unsigned* pack_counter) {
     if (dyn != nullptr) {
         // step-varying scalars come from device memory so that a captured CUDA graph can be replayed step after step:
         // (lr, 1 - beta1^t, 1 - beta2^t, flag epoch as raw bits), rewritten by the host before each replay
@@ -139,7 +159,32 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
     }
     const unsigned* my_flags = pt.flags[rank];
     if (mode != 0) {
-        if (blockIdx.x == 0) signal_peers(pt, slot_in, rank, W, epoch);   // my gradients for this bucket are final
+        if (wire_bf16) {
+            // wire format: pack my fp32 gradients of this bucket to bf16 (what the peers will read); the LAST block of this
+            // grid to finish tells the peers (self-resetting ticket, like the barrier-out below)
+            const long long n8 = count >> 3;
+            const float* src = pt.grad[rank] + start;
+            __nv_bfloat16* dst = pt.gbf[rank] + start;
+            for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < n8;
+                 v += static_cast<long long>(gridDim.x) * blockDim.x) {
+                const float4 a = *reinterpret_cast<const float4*>(src + (v << 3));
+                const float4 b = *reinterpret_cast<const float4*>(src + (v << 3) + 4);
+                *reinterpret_cast<uint4*>(dst + (v << 3)) =
+                    make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+            }
+            __shared__ unsigned s_packed;
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const unsigned old = atomicAdd(pack_counter, 1u);
+                s_packed = (old + 1u == gridDim.x) ? 1u : 0u;
+                if (s_packed) atomicExch(pack_counter, 0u);
+            }
+            __syncthreads();
+            if (s_packed) signal_peers(pt, slot_in, rank, W, epoch);
+        } else if (blockIdx.x == 0) {
+            signal_peers(pt, slot_in, rank, W, epoch);                    // my gradients for this bucket are final
+        }
         wait_flags(my_flags, slot_in, W, epoch);                          // ... and so are everybody else's
     }
     long long lo = start, hi = start + count;
@@ -164,6 +209,23 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
             const long long i = lo + (v << 2);
             if (mode == 0) {
                 g[u] = *reinterpret_cast<const float4*>(pt.grad[rank] + i);
+            } else if (wire_bf16) {
+                if (mode >= 3) {
+                    const uint2 r = multimem_ld_reduce_bf16x4(pt.mc_gbf + i);  // the switch adds the W bf16 copies in fp32
+                    const float2 lo2 = unpack_bf16x2(r.x), hi2 = unpack_bf16x2(r.y);
+                    g[u] = make_float4(lo2.x, lo2.y, hi2.x, hi2.y);
+                } else {
+                    uint2 part[MAX_PEERS];
+#pragma unroll
+                    for (int p = 0; p < MAX_PEERS; ++p)
+                        if (p < W) part[p] = ld_peer_u2(pt.gbf[p] + i);       // 8 bytes per peer instead of 16
+#pragma unroll
+                    for (int p = 0; p < MAX_PEERS; ++p)                       // fixed rank order: bitwise reproducible
+                        if (p < W) {
+                            const float2 lo2 = unpack_bf16x2(part[p].x), hi2 = unpack_bf16x2(part[p].y);
+                            g[u].x += lo2.x; g[u].y += lo2.y; g[u].z += hi2.x; g[u].w += hi2.y;
+                        }
+                }
             } else if (mode >= 3) {
                 g[u] = multimem_ld_reduce_f4(pt.mc_grad + i);                 // the switch adds the W copies
             } else {
@@ -191,13 +253,16 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
             if (opt.kind != 0) *reinterpret_cast<float4*>(state1 + i) = s1[u];
             const uint2 sh = make_uint2(pack_bf16x2(w[u].x, w[u].y), pack_bf16x2(w[u].z, w[u].w));
             if (mode == 3) {
-                multimem_st_f4(pt.mc_master + i, w[u]);                       // one store, delivered to every rank
+                // one store, delivered to every rank; with sharded masters only the bf16 compute copy travels
+                if (shard_master) *reinterpret_cast<float4*>(pt.master[rank] + i) = w[u];
+                else multimem_st_f4(pt.mc_master + i, w[u]);
                 multimem_st_b64(pt.mc_shadow + i, sh);
             } else if (mode == 2 || mode == 4) {       // mode 4: in-switch reduction, unicast pushes
+                if (shard_master) *reinterpret_cast<float4*>(pt.master[rank] + i) = w[u];
 #pragma unroll
                 for (int p = 0; p < MAX_PEERS; ++p)
                     if (p < W) {
-                        *reinterpret_cast<float4*>(pt.master[p] + i) = w[u];     // push over NVLink (all-gather phase)
+                        if (!shard_master) *reinterpret_cast<float4*>(pt.master[p] + i) = w[u];     // push over NVLink (all-gather phase)
                         *reinterpret_cast<uint2*>(pt.shadow[p] + i) = sh;
                     }
             } else {
@@ -323,7 +388,10 @@ struct CommCtx {
     PeerTable pt;
     int rank, world;
     unsigned* counters;     // per-bucket block counters (device)
+    int num_buckets;
     long long bufs_n;       // floats in each rank's module-buffer region (0 = none registered)
+    int wire_bf16;          // peers read bf16 staging copies of the gradients (picd_comm_set_wire)
+    int shard_master;       // slice owners keep their fp32 master slices to themselves; only the bf16 copy is pushed
 };
 
 }  // namespace picd
@@ -375,8 +443,11 @@ extern "C" int picd_comm_create(int rank, int world, void* const* grad, void* co
     c->rank = rank;
     c->world = world;
     c->bufs_n = 0;
-    PICD_CUDA(cudaMalloc(&c->counters, sizeof(unsigned) * (num_buckets + 1)));
-    PICD_CUDA(cudaMemset(c->counters, 0, sizeof(unsigned) * (num_buckets + 1)));
+    c->wire_bf16 = 0;
+    c->shard_master = 0;
+    PICD_CUDA(cudaMalloc(&c->counters, sizeof(unsigned) * 2 * (num_buckets + 1)));      // [barrier-out | pack] tickets per bucket
+    PICD_CUDA(cudaMemset(c->counters, 0, sizeof(unsigned) * 2 * (num_buckets + 1)));
+    c->num_buckets = num_buckets;
     *ctx_out = c;
     return 0;
 }
@@ -395,6 +466,19 @@ extern "C" int picd_comm_set_buffers(void* ctx, void* const* bufs, long long n) 
     PICD_REQUIRE(n >= 0 && (n % 4) == 0, "comm_set_buffers: n=%lld must be a non-negative multiple of 4", n);
     for (int i = 0; i < c->world; ++i) c->pt.bufs[i] = static_cast<float*>(bufs[i]);
     c->bufs_n = n;
+    return 0;
+}
+// Wire format of the gradient exchange.  gbf: per-rank bf16 staging regions (same element offsets as the gradient arenas), mc_gbf
+// their NVSwitch multicast view or null; with them registered and wire_bf16 != 0 peers read 2 B per gradient element instead
+// of 4.  shard_master != 0: in the two-shot / NVLS modes the slice owner no longer pushes its fp32 master slice (peers' copies
+// of it go stale; the host gathers them when it needs a full state dict), only the bf16 compute copy: 2 B instead of 6.
+extern "C" int picd_comm_set_wire(void* ctx, void* const* gbf, void* mc_gbf, int wire_bf16, int shard_master) {
+    CommCtx* c = static_cast<CommCtx*>(ctx);
+    PICD_REQUIRE(!wire_bf16 || gbf != nullptr, "comm_set_wire: bf16 wire format needs the staging regions");
+    for (int i = 0; i < c->world; ++i) c->pt.gbf[i] = gbf ? static_cast<__nv_bfloat16*>(gbf[i]) : nullptr;
+    c->pt.mc_gbf = static_cast<__nv_bfloat16*>(mc_gbf);
+    c->wire_bf16 = wire_bf16;
+    c->shard_master = shard_master;
     return 0;
 }
 // Upper bound, in seconds, on how long a kernel spins for a peer's flag before it traps (default 600; env PICD_FLAG_TIMEOUT_S
@@ -431,6 +515,8 @@ static int fused_update_impl(void* ctx, int bucket, int mode, long long start, l
     o.weight_decay = weight_decay; o.bc1 = bc1; o.bc2 = bc2; o.nesterov = nesterov;
     o.grad_scale = 1.f / c->world;
     PICD_REQUIRE(mode < 3 || c->pt.mc_grad != nullptr, "fused_allreduce_update: NVLS mode without a multicast mapping");
+    PICD_REQUIRE(!c->wire_bf16 || count % 8 == 0, "fused_allreduce_update: bf16 wire format needs count %% 8 == 0 (%lld)", count);
+    PICD_REQUIRE(!(c->wire_bf16 && mode >= 3) || c->pt.mc_gbf != nullptr, "fused_allreduce_update: NVLS + bf16 wire without a multicast staging view");
     const long long work_vecs = (mode >= 2 ? count / c->world : count) / 4;
     long long want = (work_vecs + 511) / 512;
     // Peer kernels spin on flags, so the grid must be able to become co-resident: at most 2 CTAs of 512 threads per SM.
@@ -451,7 +537,9 @@ static int fused_update_impl(void* ctx, int bucket, int mode, long long start, l
     }
     fused_allreduce_update_kernel<<<blocks, 512, 0, stream>>>(c->pt, c->rank, c->world, mode, start, count, state0, state1, o,
                                                               2 * bucket, 2 * bucket + 1, epoch, c->counters + bucket, dyn,
-                                                              (bcast_buffers && c->world > 1) ? c->bufs_n : 0LL);
+                                                              (bcast_buffers && c->world > 1) ? c->bufs_n : 0LL,
+                                                              c->wire_bf16, c->shard_master,
+                                                              c->counters + c->num_buckets + 1 + bucket);
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -207,6 +207,10 @@ int picd_comm_set_multicast(void* ctx, void* mc_grad, void* mc_master, void* mc_
  * A bucket launch with bcast_buffers != 0 copies rank 0's region into every peer's between its two flag barriers: DDP's
  * per-forward buffer broadcast (torch/nn/parallel/distributed.py:2214-2257 via train.py:49,128) without a collective call. */
 int picd_comm_set_buffers(void* ctx, void* const* bufs, long long n);
+/* Wire format: gbf = per-rank bf16 staging regions of the gradient arenas (mc_gbf: their multicast view or NULL).  wire_bf16: peers
+ * read 2 B per gradient element (packed by the owner inside the bucket kernel) instead of 4; shard_master: slice owners keep
+ * their fp32 master slices local and push only the bf16 compute copy (2 B instead of 6) -- the host gathers masters on demand. */
+int picd_comm_set_wire(void* ctx, void* const* gbf, void* mc_gbf, int wire_bf16, int shard_master);
 /* Seconds a kernel may spin on a peer's flag before it traps (default 600); applies to the current device. */
 int picd_comm_set_flag_timeout(double seconds);
 int picd_comm_destroy(void* ctx);

@@ -119,6 +119,7 @@ class GraphedTrainStep:
         self.static_labels.copy_(labels, non_blocking=True)
         m._impl.sync_dyn(m.step_index + 1, self.replays)     # no H2D copy unless the host's view of (lr, step) moved
         self.graph.replay()
+        m._masters_stale = True
         m.step_index += 1
         self.optimizer.step_count += 1
         self.replays += 1

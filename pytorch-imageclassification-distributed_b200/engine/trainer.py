@@ -169,6 +169,8 @@ def fit(model, loss_fn, optimizer, scheduler, train_loader, val_loader, device, 
         loss = train_epoch(epoch, model, loss_fn, optimizer, train_loader, device, log_interval,
                            tracer, max_steps, printer, step_fn, progress)
         scheduler.step()                                          # train.py:166
+        if hasattr(model, "sync_masters"):
+            model.sync_masters()      # collective: sharded fp32 masters -> full copies before anything reads state_dict()
         acc = val_epoch(epoch, model, val_loader, device, printer, max_steps)
         # the optimizer state is sharded by slice owner on the peer-memory engine: assembling it is a collective, so
         # every rank takes part even though only rank 0 writes the file

@@ -306,6 +306,7 @@ class FusedDataParallel(nn.Module):
         self.rank = dist.get_rank(process_group) if is_dist() else 0
         self.overlap, self.comm = overlap, comm
         self.step_index = 0
+        self._masters_stale = False     # sharded masters: a step ran since the last sync_masters()
         self.capturing = False          # True while a CUDA graph of the step is being recorded (engine/graphed.py)
         try:
             device = next(module.parameters()).device
@@ -375,6 +376,35 @@ class FusedDataParallel(nn.Module):
                 f"(shape digest {box[0][1][:12]}, optimizer {box[0][2]}), rank(s) {bad} differ "
                 f"(e.g. rank {bad[0]}: {box[bad[0]][0]} parameters, digest {box[bad[0]][1][:12]}, optimizer "
                 f"{box[bad[0]][2]}).  All ranks must build the same network before FusedDataParallel wraps it.")
+
+    @property
+    def masters_sharded(self) -> bool:
+        impl = getattr(self, "_impl", None)
+        return bool(self.world > 1 and impl is not None and getattr(getattr(impl, "comm", None), "shard_master", False))
+
+    def sync_masters(self):
+        """COLLECTIVE.  With sharded masters (peer-memory engine, bf16 wire format) a rank holds the current fp32 master
+        only for the bucket slices it owns -- the bf16 compute copies are what the step keeps identical everywhere.  Before
+        anything reads ``parameter.data`` across the whole model (``state_dict()`` for a checkpoint, a comparison, a switch
+        to the library-op path) every rank calls this: the owners' slices are all-gathered in place."""
+        if not self.masters_sharded or not self._masters_stale:
+            return
+        impl = self._impl
+        torch.cuda.current_stream(self.device).wait_stream(impl.side)
+        for b in self.arena.buckets:
+            if impl._mode(b) < 2:
+                continue
+            per = b.numel // self.world
+            lo = b.start + per * self.rank
+            dist.all_gather_into_tensor(self.arena.master[b.start: b.end], self.arena.master[lo: lo + per].clone(),
+                                        group=self.group)
+        self._masters_stale = False
+
+    def state_dict(self, *args, **kw):
+        if self.masters_sharded and self._masters_stale:
+            raise RuntimeError("picd_b200: the fp32 masters are sharded by slice owner and have changed since the last "
+                               "gather; call model.sync_masters() on EVERY rank before state_dict()")
+        return super().state_dict(*args, **kw)
 
     def gather_sharded(self, flats):
         """Full copies of per-element buffers that the bucket kernels keep SHARDED by slice owner (optimizer state): for
@@ -455,6 +485,7 @@ class FusedDataParallel(nn.Module):
         self._impl.finish()
         self._reset_pending()
         self.step_index += 1
+        self._masters_stale = True
 
     # -- nn.Module plumbing -------------------------------------------------------------------
     def forward(self, *args, **kw):
@@ -472,6 +503,7 @@ class FusedDataParallel(nn.Module):
     def load_state_dict(self, state_dict, strict: bool = True, **kw):
         out = super().load_state_dict(state_dict, strict=strict, **kw)
         self.arena.refresh_shadow()
+        self._masters_stale = False      # every rank now holds the full, current masters
         return out
 
 

@@ -74,7 +74,9 @@ class SymmetricSlab:
         # module buffers (BatchNorm running statistics): rank 0's copy is pushed into the peers' by the step's last bucket kernel
         self.buffer_floats = (int(buffer_floats) + 3) // 4 * 4
         self.off_bufs = _align(self.off_flags + self.flag_words * 4)
-        self.nbytes = _align(self.off_bufs + self.buffer_floats * 4)
+        # bf16 staging copy of the gradient arena: the wire format of the reduction (peers read 2 B per element, not 4)
+        self.off_gbf = _align(self.off_bufs + self.buffer_floats * 4)
+        self.nbytes = _align(self.off_gbf + (total * 2 if world > 1 else 0))
         self.max_buckets = num_buckets_hint
         self.mc_base = 0          # NVSwitch multicast (NVLS) view of the slab, when the host can map one
         self._symm = None
@@ -179,6 +181,20 @@ class Comm:
             f3 = self.lib.picd_comm_set_buffers
             f3.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong]
             check(f3(ctx, slab.region_ptrs(slab.off_bufs), slab.buffer_floats), "picd_comm_set_buffers")
+        # wire format of the gradient exchange (PICD_GRAD_WIRE=fp32 restores full-precision exchange + replicated masters)
+        self.wire_bf16 = slab.world > 1 and os.environ.get("PICD_GRAD_WIRE", "bf16") != "fp32"
+        # Sharded masters (opt-in, PICD_SHARD_MASTERS=1): the slice owner keeps its fp32 master slice to itself and pushes only
+        # the bf16 compute copy -- 2 B per element on the wire instead of 6.  Safe only when EVERY forward read of a parameter
+        # goes through the native ops (which read the bf16 copies): a torch op applied to a parameter directly (nn.Linear,
+        # a position embedding added with `+`) reads the fp32 master, which is stale on the ranks that do not own its slice.
+        # Hence off by default, and never with the library-op A/B switch.
+        self.shard_master = self.wire_bf16 and os.environ.get("PICD_SHARD_MASTERS", "0") == "1" and \
+            os.environ.get("PICD_FORCE_TORCH", "0") != "1"
+        if slab.world > 1:
+            f5 = self.lib.picd_comm_set_wire
+            f5.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+            check(f5(ctx, slab.region_ptrs(slab.off_gbf), (slab.mc_base + slab.off_gbf) if slab.mc_base else None,
+                     int(self.wire_bf16), int(self.shard_master)), "picd_comm_set_wire")
         timeout_s = float(os.environ.get("PICD_FLAG_TIMEOUT_S", "600"))
         f4 = self.lib.picd_comm_set_flag_timeout
         f4.argtypes = [ctypes.c_double]
