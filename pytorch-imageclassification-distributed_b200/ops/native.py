@@ -582,8 +582,10 @@ class _ConvBnAct(torch.autograd.Function):
         if fork_ is not None and role == "deposit_res" and dres is not None:
             fork_.partner = dres
         acc = fork_.partner if (fork_ is not None and role == "accumulate") else None
+        # the fused BN-backward reduction needs this dgrad to produce the FINAL gradient of its input: any role but the one
+        # that adds into another branch's deposit ("deposit_res" only concerns the residual input, not x)
         dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1], accumulate_into=acc,
-                                src_bn=ctx.src_rec if fork_ is None else None)
+                                src_bn=ctx.src_rec if (fork_ is None or role == "deposit_res") else None)
         if fork_ is not None:
             if role == "deposit_dx" and dx is not None:
                 fork_.partner = dx
