@@ -309,25 +309,36 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(PeerTable p
 }
 
 // ---- small collectives over the exchange slots ----------------------------------------------------------
-// Publish `n` floats, wait for all peers, return the rank-ordered sum.  Single block.
+// PUSH exchange: every rank stores its `n` floats into sub-slot `rank` of the slot in EVERY peer's slab (fire-and-forget NVLink
+// stores), signals, waits for the W flags -- and then sums W sub-slots of its OWN slab.  The pull form (publish locally, peers
+// load remotely after the flags) paid one more NVLink round trip per exchange, 2 x 53 times per SyncBatchNorm step.
+// A slot half holds W sub-slots of `sub` floats; single block.
 __device__ __forceinline__ void xchg_publish_and_wait(const PeerTable& pt, int rank, int W, const float* in, int n,
-                                                      int in_replicas, long long slot_off, int flag_slot,
-                                                      unsigned epoch) {
-    float* mine = pt.xchg[rank] + slot_off;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                                                      int in_replicas, long long slot_off, int sub, int flag_slot,
+                                                      unsigned epoch, float extra, int extra_at) {
+    const long long mine = slot_off + static_cast<long long>(rank) * sub;
+    for (int i = threadIdx.x; i < n + (extra_at >= 0 ? 1 : 0); i += blockDim.x) {
         float acc = 0.f;                                   // fold the per-CTA-group replicas while publishing
-        for (int r = 0; r < in_replicas; ++r) acc += in[static_cast<size_t>(r) * n + i];
-        mine[i] = acc;
+        if (i < n) {
+            for (int r = 0; r < in_replicas; ++r) acc += in[static_cast<size_t>(r) * n + i];
+        } else {
+            acc = extra;                                   // one more scalar rides along (the local element count)
+        }
+        const int at = i < n ? i : extra_at;
+#pragma unroll
+        for (int p = 0; p < MAX_PEERS; ++p)
+            if (p < W) pt.xchg[p][mine + at] = acc;
     }
     __syncthreads();
     signal_peers(pt, flag_slot, rank, W, epoch);
     wait_flags(pt.flags[rank], flag_slot, W, epoch);
 }
-__device__ __forceinline__ float xchg_sum(const PeerTable& pt, int W, long long slot_off, int i) {
+__device__ __forceinline__ float xchg_sum(const PeerTable& pt, int rank, int W, long long slot_off, int sub, int i) {
     float acc = 0.f;
-    for (int p = 0; p < W; ++p) {
+    const float* base = pt.xchg[rank] + slot_off + i;
+    for (int p = 0; p < W; ++p) {                          // fixed rank order: every rank computes bit-identical sums
         float v;
-        asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(pt.xchg[p] + slot_off + i));
+        asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(base + static_cast<long long>(p) * sub));
         acc += v;
     }
     return acc;
@@ -346,10 +357,11 @@ __device__ __forceinline__ void apply_replay_delta(const unsigned* dyn_delta, in
 __global__ void __launch_bounds__(1024) p2p_allreduce_small_kernel(PeerTable pt, int rank, int W, const float* in,
                                                                    int in_replicas, float* out, int n,
                                                                    long long slot_off, int flag_slot, unsigned epoch,
-                                                                   const unsigned* dyn_delta, int slot_floats) {
+                                                                   const unsigned* dyn_delta, int slot_floats, int sub) {
+    pdl_sync();
     apply_replay_delta(dyn_delta, slot_floats, epoch, slot_off);
-    xchg_publish_and_wait(pt, rank, W, in, n, in_replicas, slot_off, flag_slot, epoch);
-    for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = xchg_sum(pt, W, slot_off, i);
+    xchg_publish_and_wait(pt, rank, W, in, n, in_replicas, slot_off, sub, flag_slot, epoch, 0.f, -1);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = xchg_sum(pt, rank, W, slot_off, sub, i);
 }
 
 // sums = local [sum(C), sumsq(C)], count = local element count.  Cross-replica merge + finalize in one launch.
@@ -359,16 +371,16 @@ __global__ void __launch_bounds__(1024) bn_finalize_sync_kernel(PeerTable pt, in
                                                                 float momentum, float eps, float* scale, float* shift,
                                                                 float* mean_out, float* invstd_out, float* total_count,
                                                                 int C, long long slot_off, int flag_slot,
-                                                                unsigned epoch, const unsigned* dyn_delta, int slot_floats) {
+                                                                unsigned epoch, const unsigned* dyn_delta, int slot_floats,
+                                                                int sub) {
+    pdl_sync();
     apply_replay_delta(dyn_delta, slot_floats, epoch, slot_off);
-    float* mine = pt.xchg[rank] + slot_off;
-    if (threadIdx.x == 0) mine[2 * C] = count;
-    xchg_publish_and_wait(pt, rank, W, sums, 2 * C, replicas, slot_off, flag_slot, epoch);
-    const float n = xchg_sum(pt, W, slot_off, 2 * C);
+    xchg_publish_and_wait(pt, rank, W, sums, 2 * C, replicas, slot_off, sub, flag_slot, epoch, count, 2 * C);
+    const float n = xchg_sum(pt, rank, W, slot_off, sub, 2 * C);
     if (threadIdx.x == 0) total_count[0] = n;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        const float mean = xchg_sum(pt, W, slot_off, c) / n;
-        float var = xchg_sum(pt, W, slot_off, C + c) / n - mean * mean;
+        const float mean = xchg_sum(pt, rank, W, slot_off, sub, c) / n;
+        float var = xchg_sum(pt, rank, W, slot_off, sub, C + c) / n - mean * mean;
         var = fmaxf(var, 0.f);
         const float invstd = rsqrtf(var + eps);
         const float sc = gamma[c] * invstd;
@@ -584,11 +596,14 @@ extern "C" int picd_dyn_advance(float* dyn, float beta1, float beta2, cudaStream
     return 0;
 }
 
+// slot_off: float offset of the slot HALF to use inside the exchange region; the half holds `world` sub-slots of `sub` floats
+// (sub >= n, a multiple of 4), so it spans world * sub floats.  Launched with programmatic stream serialization.
 extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n,
-                                        long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
+                                        long long slot_off, int flag_slot, unsigned epoch, int sub, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
-    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, in_replicas, out, n, slot_off, flag_slot,
-                                                       epoch, nullptr, 0);
+    PICD_REQUIRE(sub >= n, "p2p_allreduce_small: sub-slot of %d floats for a payload of %d", sub, n);
+    PICD_CUDA(launch_pdl<PDL_BN>(p2p_allreduce_small_kernel, dim3(1), dim3(1024), 0, stream, c->pt, c->rank, c->world, in,
+                                 in_replicas, out, n, slot_off, flag_slot, epoch, static_cast<const unsigned*>(nullptr), 0, sub));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -596,11 +611,13 @@ extern "C" int picd_p2p_allreduce_small(void* ctx, const float* in, int in_repli
 // time; the kernel adds *dyn_delta (device memory) and picks the half from the resulting parity.
 extern "C" int picd_p2p_allreduce_small_dyn(void* ctx, const float* in, int in_replicas, float* out, int n,
                                             long long slot_off, int flag_slot, unsigned epoch, const void* dyn_delta,
-                                            int slot_floats, cudaStream_t stream) {
+                                            int slot_floats, int sub, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
     PICD_REQUIRE(dyn_delta != nullptr, "p2p_allreduce_small_dyn: dyn_delta must point at a device word");
-    p2p_allreduce_small_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, in, in_replicas, out, n, slot_off, flag_slot,
-                                                       epoch, static_cast<const unsigned*>(dyn_delta), slot_floats);
+    PICD_REQUIRE(sub >= n, "p2p_allreduce_small_dyn: sub-slot of %d floats for a payload of %d", sub, n);
+    PICD_CUDA(launch_pdl<PDL_BN>(p2p_allreduce_small_kernel, dim3(1), dim3(1024), 0, stream, c->pt, c->rank, c->world, in,
+                                 in_replicas, out, n, slot_off, flag_slot, epoch, static_cast<const unsigned*>(dyn_delta),
+                                 slot_floats, sub));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -608,11 +625,12 @@ extern "C" int picd_p2p_allreduce_small_dyn(void* ctx, const float* in, int in_r
 extern "C" int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
                                      float* running_mean, float* running_var, float momentum, float eps, float* scale,
                                      float* shift, float* mean, float* invstd, float* total_count, int C,
-                                     long long slot_off, int flag_slot, unsigned epoch, cudaStream_t stream) {
+                                     long long slot_off, int flag_slot, unsigned epoch, int sub, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
-    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, replicas, count, gamma, beta, running_mean,
-                                                    running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
-                                                    slot_off, flag_slot, epoch, nullptr, 0);
+    PICD_REQUIRE(sub >= 2 * C + 1, "bn_finalize_sync: sub-slot of %d floats for %d channels", sub, C);
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_finalize_sync_kernel, dim3(1), dim3(1024), 0, stream, c->pt, c->rank, c->world, sums, replicas,
+                                 count, gamma, beta, running_mean, running_var, momentum, eps, scale, shift, mean, invstd,
+                                 total_count, C, slot_off, flag_slot, epoch, static_cast<const unsigned*>(nullptr), 0, sub));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -620,13 +638,14 @@ extern "C" int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int repli
                                          const float* beta, float* running_mean, float* running_var, float momentum,
                                          float eps, float* scale, float* shift, float* mean, float* invstd,
                                          float* total_count, int C, long long slot_off, int flag_slot, unsigned epoch,
-                                         const void* dyn_delta, int slot_floats, cudaStream_t stream) {
+                                         const void* dyn_delta, int slot_floats, int sub, cudaStream_t stream) {
     CommCtx* c = static_cast<CommCtx*>(ctx);
     PICD_REQUIRE(dyn_delta != nullptr, "bn_finalize_sync_dyn: dyn_delta must point at a device word");
-    bn_finalize_sync_kernel<<<1, 1024, 0, stream>>>(c->pt, c->rank, c->world, sums, replicas, count, gamma, beta, running_mean,
-                                                    running_var, momentum, eps, scale, shift, mean, invstd, total_count, C,
-                                                    slot_off, flag_slot, epoch, static_cast<const unsigned*>(dyn_delta),
-                                                    slot_floats);
+    PICD_REQUIRE(sub >= 2 * C + 1, "bn_finalize_sync_dyn: sub-slot of %d floats for %d channels", sub, C);
+    PICD_CUDA(launch_pdl<PDL_BN>(bn_finalize_sync_kernel, dim3(1), dim3(1024), 0, stream, c->pt, c->rank, c->world, sums, replicas,
+                                 count, gamma, beta, running_mean, running_var, momentum, eps, scale, shift, mean, invstd,
+                                 total_count, C, slot_off, flag_slot, epoch, static_cast<const unsigned*>(dyn_delta), slot_floats,
+                                 sub));
     PICD_LAUNCH_CHECK();
     return 0;
 }

@@ -227,20 +227,25 @@ int picd_fused_allreduce_update_dyn(void* ctx, int bucket, int mode, long long s
 /* First kernel of a captured step: increments dyn[3] (step / flag epoch, raw bits) and dyn[4] (replay index, raw bits) and
  * recomputes dyn[1], dyn[2] = 1 - beta^t on the device, so that a graph replay needs no host-to-device copy. */
 int picd_dyn_advance(float* dyn, float beta1, float beta2, cudaStream_t stream);
+/* Small collectives (SyncBatchNorm): PUSH exchange -- every rank stores its payload into sub-slot `rank` of the slot half at
+ * float offset slot_off in every peer's exchange region (the half spans world * sub floats, sub >= payload), signals, and sums
+ * the `world` sub-slots of its own slab. */
 int picd_p2p_allreduce_small(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
-                             int flag_slot, unsigned epoch, cudaStream_t stream);
+                             int flag_slot, unsigned epoch, int sub, cudaStream_t stream);
 int picd_bn_finalize_sync(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
                           float* running_mean, float* running_var, float momentum, float eps, float* scale,
                           float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
-                          int flag_slot, unsigned epoch, cudaStream_t stream);
+                          int flag_slot, unsigned epoch, int sub, cudaStream_t stream);
 /* Graph-replay variants of the two small collectives: slot_off = EVEN half of the double-buffered slot, epoch = the epoch
  * at capture time; the kernels add the device word *dyn_delta (steps since capture) and pick the half from the parity. */
 int picd_p2p_allreduce_small_dyn(void* ctx, const float* in, int in_replicas, float* out, int n, long long slot_off,
-                                 int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, cudaStream_t stream);
+                                 int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, int sub,
+                                 cudaStream_t stream);
 int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int replicas, float count, const float* gamma, const float* beta,
                               float* running_mean, float* running_var, float momentum, float eps, float* scale,
                               float* shift, float* mean, float* invstd, float* total_count, int C, long long slot_off,
-                              int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, cudaStream_t stream);
+                              int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, int sub,
+                              cudaStream_t stream);
 
 int picd_nvls_supported(void);   /* 1/0/-1: NVSwitch multicast available (probe only; the kernels use P2P loads/stores) */
 

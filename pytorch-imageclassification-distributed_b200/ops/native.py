@@ -458,14 +458,14 @@ def _bn_forward_coeffs(sums, count, gamma, beta, rm, rv, momentum, eps, sync_gro
     return coef, (total, None)
 
 
-def _bn_allreduce_bwd(sums2, sync_group, C):
+def _bn_allreduce_bwd(sums2, sync_group, C, key=None):
     """[STAT_REPLICAS, 2C] local sums -> the sums bn_bwd_apply should use (folded + all-reduced under SyncBN)."""
     if _sync_world(sync_group) <= 1:
         return sums2
     from ..parallel import native_comm
     comm = native_comm.current_comm()
     if comm is not None:
-        return comm.allreduce_small(sums2, 2 * C)
+        return comm.allreduce_small(sums2, 2 * C, key=key)
     import torch.distributed as dist
     out = sums2.view(-1, 2 * C).sum(0)
     dist.all_reduce(out, group=None if sync_group is True else sync_group)
@@ -544,7 +544,7 @@ def _bn_apply_bwd(ctx, dz, y, z, coef, gamma, beta, need_dres):
         call("picd_bn_bwd_reduce_mask", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, sums2, P, C)
     if rec is not None:
         rec.y = rec.coef = rec.sums = rec.dz = None
-    gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C)
+    gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C, key=gamma)
     gt, g_routed = _grad_target(gamma)
     bt, b_routed = _grad_target(beta)
     call("picd_bn_bwd_apply_mask_cnt", dz, y, zmask, rmask, coef[0], coef[1], coef[2], coef[3], act, gsums,

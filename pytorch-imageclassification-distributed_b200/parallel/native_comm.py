@@ -24,9 +24,11 @@ import torch.distributed as dist
 
 from ..ops._lib import check, require_lib
 
-SLOT_FLOATS = 2 * 2048 + 8          # (sum, sumsq) for up to 2048 channels + count
-N_SLOTS = 1024                      # small-collective slots (each double-buffered); eager and graph-captured
-                                    # launches use disjoint slots, so a ResNet-101 needs 104 + 192 + 2 x 104 of them
+SLOT_FLOATS = 2 * 2048 + 8          # largest payload: (sum, sumsq) for up to 2048 channels + count
+N_SLOTS = 1024                      # small-collective slots (flag words); eager and graph-captured launches use disjoint
+                                    # slots, so a ResNet-101 needs 4 x 104 of them
+XCHG_FLOATS = 16 << 20              # exchange region (64 MiB): a slot takes 2 halves x world sub-slots x its payload, handed
+                                    # out by a bump allocator (ResNet-101 at 8 ranks: 4 x 2 x 8 x 105k floats = 27 MiB)
 MAX_PEERS = 8
 TWO_SHOT_MIN_BYTES = 256 << 10      # below this a bucket is latency-bound: one-shot
 NVLS_MIN_BYTES = 4 << 20            # from here on the in-switch reduction (multimem.ld_reduce) replaces the W peer loads, if mapped
@@ -69,7 +71,7 @@ class SymmetricSlab:
         self.off_master = _align(self.off_grad + total * 4)
         self.off_shadow = _align(self.off_master + total * 4)
         self.off_xchg = _align(self.off_shadow + total * 2)
-        self.off_flags = _align(self.off_xchg + N_SLOTS * 2 * SLOT_FLOATS * 4)
+        self.off_flags = _align(self.off_xchg + XCHG_FLOATS * 4)
         self.flag_words = (2 * num_buckets_hint + N_SLOTS) * MAX_PEERS
         # module buffers (BatchNorm running statistics): rank 0's copy is pushed into the peers' by the step's last bucket kernel
         self.buffer_floats = (int(buffer_floats) + 3) // 4 * 4
@@ -204,6 +206,7 @@ class Comm:
         self._slots = {}
         self._slot_keys = []
         self._next_slot = 0
+        self._bump = 0                 # floats of the exchange region handed out so far
         self.graph_dyn = None          # device float[8] while a CUDA graph of the step is recorded (word 4 = replay delta)
         self._graph_slots = []         # slots owned by captured launches: their epochs advance once per replay
         self._f_upd = self.lib.picd_fused_allreduce_update
@@ -219,19 +222,19 @@ class Comm:
         self._f_small_dyn = self.lib.picd_p2p_allreduce_small_dyn
         self._f_small_dyn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p, ctypes.c_int,
-                                      ctypes.c_void_p]
+                                      ctypes.c_int, ctypes.c_void_p]
         self._f_bn_dyn = self.lib.picd_bn_finalize_sync_dyn
         self._f_bn_dyn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float] + [ctypes.c_void_p] * 4 +
                                    [ctypes.c_float, ctypes.c_float] + [ctypes.c_void_p] * 5 +
                                    [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p, ctypes.c_int,
-                                    ctypes.c_void_p])
+                                    ctypes.c_int, ctypes.c_void_p])
         self._f_small = self.lib.picd_p2p_allreduce_small
         self._f_small.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
-                                  ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
+                                  ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p]
         self._f_bn = self.lib.picd_bn_finalize_sync
         self._f_bn.argtypes = ([ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float] + [ctypes.c_void_p] * 4 +
                                [ctypes.c_float, ctypes.c_float] + [ctypes.c_void_p] * 5 +
-                               [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p])
+                               [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p])
         _current = self
 
     # -- gradient buckets ---------------------------------------------------------------------------
@@ -253,27 +256,37 @@ class Comm:
               "picd_fused_allreduce_update")
 
     # -- small collectives (SyncBN) ------------------------------------------------------------------
-    def _slot(self, key) -> int:
+    def _slot(self, key, n: int):
+        """(slot index, float offset of its even half, sub-slot floats) of the exchange slot of `key`; sized at first use for a
+        payload of n floats: 2 halves (epoch parity) x world sub-slots (one per pushing rank).  Every rank calls this in the
+        same order, so the layout agrees across the node."""
         k = (id(key), self.graph_dyn is not None)        # captured launches get slots of their own
         s = self._slots.get(k)
         if s is None:
-            s = self._next_slot
-            self._next_slot += 1
-            if s >= N_SLOTS:
+            sub = (n + 3) // 4 * 4
+            need = 2 * max(self.slab.world, 1) * sub
+            if self._next_slot >= N_SLOTS or self._bump + need > XCHG_FLOATS:
                 raise RuntimeError("picd_b200: out of small-collective slots")
+            s = (self._next_slot, self._bump, sub)
+            self._next_slot += 1
+            self._bump += need
             self._slots[k] = s
             self._slot_keys.append(key)          # keep the key alive so its id() stays unique
+        if s[2] < n:
+            raise RuntimeError("picd_b200: small-collective slot reused with a larger payload")
         return s
 
-    def _next(self, slot: int):
-        e = self._slot_epoch.get(slot, 0) + 1
-        self._slot_epoch[slot] = e
+    def _next(self, slot):
+        index, base, sub = slot
+        half = max(self.slab.world, 1) * sub
+        e = self._slot_epoch.get(index, 0) + 1
+        self._slot_epoch[index] = e
+        fslot = 2 * self.slab.max_buckets + index
         if self.graph_dyn is not None:
             # recorded launch: pass the EVEN half and the capture-time epoch; the kernel adds the replay delta itself
-            self._graph_slots.append(slot)
-            return e, slot * 2 * SLOT_FLOATS, 2 * self.slab.max_buckets + slot
-        off = (slot * 2 + (e & 1)) * SLOT_FLOATS
-        return e, off, 2 * self.slab.max_buckets + slot
+            self._graph_slots.append(index)
+            return e, base, fslot, half, sub
+        return e, base + (e & 1) * half, fslot, half, sub
 
     def begin_capture(self, dyn: torch.Tensor):
         self.graph_dyn, self._graph_slots = dyn, []
@@ -294,7 +307,7 @@ class Comm:
         C = gamma.numel()
         if 2 * C + 1 > SLOT_FLOATS:
             raise RuntimeError(f"picd_b200: SyncBN with {C} channels exceeds the exchange slot")
-        e, off, fslot = self._next(self._slot(gamma))
+        e, off, fslot, half, sub = self._next(self._slot(gamma, 2 * C + 1))
         total = torch.empty(1, dtype=torch.float32, device=sums.device)
         args = (self.ctx, sums.data_ptr(), sums.numel() // (2 * C), float(count), gamma.data_ptr(), beta.data_ptr(),
                 None if rm is None else rm.data_ptr(), None if rv is None else rv.data_ptr(),
@@ -302,9 +315,9 @@ class Comm:
                 coef[3].data_ptr(), total.data_ptr(), C, off, fslot, e & 0xFFFFFFFF)
         st = torch.cuda.current_stream().cuda_stream
         if self.graph_dyn is not None:
-            check(self._f_bn_dyn(*args, self._delta_ptr(), SLOT_FLOATS, st), "picd_bn_finalize_sync_dyn")
+            check(self._f_bn_dyn(*args, self._delta_ptr(), half, sub, st), "picd_bn_finalize_sync_dyn")
         else:
-            check(self._f_bn(*args, st), "picd_bn_finalize_sync")
+            check(self._f_bn(*args, sub, st), "picd_bn_finalize_sync")
         # `total` (device) is the exchanged GLOBAL count: the backward scales with it, so ranks may hold different batch
         # sizes (a ragged last batch through a non-padding loader); the host-side float is only an estimate for callers
         # that want a number without a sync
@@ -317,28 +330,38 @@ class Comm:
         replicas = vec.numel() // n
         if n > SLOT_FLOATS:
             raise RuntimeError("picd_b200: small all-reduce payload exceeds the exchange slot")
-        holder = key if key is not None else self
-        e, off, fslot = self._next(self._slot(_BwdKey.of(holder, n)))
+        holder = _BwdKey.of(key) if key is not None else _BwdKey.ring(n)
+        e, off, fslot, half, sub = self._next(self._slot(holder, n if key is not None else SLOT_FLOATS))
         out = torch.empty(n, dtype=vec.dtype, device=vec.device)
         st = torch.cuda.current_stream().cuda_stream
         if self.graph_dyn is not None:
             check(self._f_small_dyn(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF,
-                                    self._delta_ptr(), SLOT_FLOATS, st), "picd_p2p_allreduce_small_dyn")
+                                    self._delta_ptr(), half, sub, st), "picd_p2p_allreduce_small_dyn")
         else:
-            check(self._f_small(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF, st),
+            check(self._f_small(self.ctx, vec.data_ptr(), replicas, out.data_ptr(), n, off, fslot, e & 0xFFFFFFFF, sub, st),
                   "picd_p2p_allreduce_small")
         return out
 
 
 class _BwdKey:
-    """Slot identity for backward reductions: one per (call order position) -- every rank runs the same
-    sequence of BN backward calls per step, so a round-robin over positions is consistent across ranks."""
+    """Slot identity of a backward reduction.  With a `key` (the layer's gamma parameter) every layer owns a slot sized for
+    its payload; without one the caller gets a small ring of full-size slots indexed by call order (every rank runs the
+    same sequence of calls, so positions agree across ranks)."""
+    _by_key = {}
     _ring: List["_BwdKey"] = []
     _cursor = 0
-    RING = 192
+    RING = 16
 
     @classmethod
-    def of(cls, holder, n):
+    def of(cls, key):
+        k = cls._by_key.get(id(key))
+        if k is None:
+            k = cls._by_key[id(key)] = cls()
+            k.anchor = key                # keeps id(key) unique for the life of the process
+        return k
+
+    @classmethod
+    def ring(cls, n):
         if not cls._ring:
             cls._ring = [cls() for _ in range(cls.RING)]
         k = cls._ring[cls._cursor % cls.RING]
