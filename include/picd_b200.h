@@ -247,6 +247,19 @@ int picd_bn_finalize_sync_dyn(void* ctx, const float* sums, int replicas, float 
                               int flag_slot, unsigned epoch, const void* dyn_delta, int slot_floats, int sub,
                               cudaStream_t stream);
 
+/* The library's own symmetric slab on the CUDA VMM API (csrc/comm/vmm_slab.cu): a cuMemCreate allocation per rank exported as a
+ * POSIX fd (the host moves the fds between processes, e.g. SCM_RIGHTS), every peer's allocation mapped with cuMemMap, and an
+ * NVSwitch multicast object (cuMulticastCreate / AddDevice / BindMem) whose mapping the NVLS modes of the bucket kernel use.
+ * Protocol: every rank picd_vmm_create -> exchange fds -> picd_vmm_import_peer per peer; rank 0 picd_vmm_mc_create -> its fd to
+ * the others -> picd_vmm_mc_import; every rank picd_vmm_mc_add_device; barrier; every rank picd_vmm_mc_bind_map. */
+int picd_vmm_create(size_t bytes, int world, void** slab_out, void** base_out, int* fd_out, size_t* padded_bytes_out);
+int picd_vmm_import_peer(void* slab, int peer_rank, int fd, void** base_out);
+int picd_vmm_multicast_supported(void);
+int picd_vmm_mc_create(void* slab, int world, int* fd_out);
+int picd_vmm_mc_import(void* slab, int fd);
+int picd_vmm_mc_add_device(void* slab);
+int picd_vmm_mc_bind_map(void* slab, void** mc_base_out);
+int picd_vmm_destroy(void* slab);
 int picd_nvls_supported(void);   /* 1/0/-1: NVSwitch multicast available (probe only; the kernels use P2P loads/stores) */
 
 /* ---- runtime ---------------------------------------------------------------------------------------------- */

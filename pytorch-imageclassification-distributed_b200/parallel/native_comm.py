@@ -81,10 +81,15 @@ class SymmetricSlab:
         self.nbytes = _align(self.off_gbf + (total * 2 if world > 1 else 0))
         self.max_buckets = num_buckets_hint
         self.mc_base = 0          # NVSwitch multicast (NVLS) view of the slab, when the host can map one
-        self._symm = None
-        if world > 1 and os.environ.get("PICD_SYMM", "1") != "0":
-            self._try_symmetric_alloc()
-        if self._symm is None:
+        self._symm = None         # torch symmetric-memory allocation, if that is where the slab came from
+        self._vmm = None          # handle of the library's own VMM slab (csrc/comm/vmm_slab.cu), if that is
+        self.backing = "cudaMalloc+IPC"
+        mode = os.environ.get("PICD_SYMM", "own")
+        if world > 1 and mode not in ("0", "torch"):
+            self._try_vmm_alloc()             # own path: cuMemCreate + fd exchange + cuMulticast*
+        if world > 1 and self._vmm is None and mode != "0":
+            self._try_symmetric_alloc()       # torch's symmetric-memory allocator
+        if self._symm is None and self._vmm is None:
             base = ctypes.c_void_p()
             with torch.cuda.device(device):
                 self.lib.picd_slab_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
@@ -95,10 +100,146 @@ class SymmetricSlab:
         self.shadow = _view(self.base + self.off_shadow, total, "<i2", device, self).view(torch.bfloat16)
         self.state = [torch.zeros(total, dtype=torch.float32, device=device) for _ in range(n_state)]
         self.bufs = _view(self.base + self.off_bufs, self.buffer_floats, "<f4", device, self) if self.buffer_floats else None
-        if self._symm is None:
+        if self._symm is None and self._vmm is None:
             self.peer_bases: List[int] = [self.base] * max(world, 1)
             if world > 1:
                 self._exchange_handles()
+
+    # -- own VMM slab -------------------------------------------------------------------------------------------
+    def _agree(self, ok: bool) -> bool:
+        """True only if EVERY rank reports success (collective), so that all ranks take the same path."""
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return int(flag.item()) == 1
+
+    def _pass_fds(self, my_fd: int, owners) -> dict:
+        """Move POSIX file descriptors between the ranks of this node: for every `owner` rank in turn, the owner serves its
+        descriptor over a unix socket (SCM_RIGHTS) and every other rank connects and receives a descriptor of ITS OWN
+        process that refers to the same kernel object.  Returns {owner rank: local fd}.  Collective."""
+        import socket
+        import tempfile
+        import time
+        token = [None]
+        if self.rank == 0:
+            token[0] = f"{os.getpid()}_{int(time.time() * 1e6) & 0xFFFFFFFF:x}"
+        dist.broadcast_object_list(token, src=0)
+        got = {}
+        failed = False
+
+        def barrier():
+            dist.barrier(device_ids=[self.device.index]) if dist.get_backend() == "nccl" else dist.barrier()
+
+        for owner in owners:
+            path = os.path.join(tempfile.gettempdir(), f"picd_fd_{token[0]}_{owner}.sock")
+            srv = None
+            if self.rank == owner:
+                try:
+                    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                    srv.settimeout(30)
+                    srv.bind(path)
+                    srv.listen(self.world)
+                except OSError:
+                    failed, srv = True, None
+            barrier()                                        # the socket exists (or its owner has given up): peers may connect
+            try:                                             # both barriers run on every rank whatever happens in between
+                if self.rank == owner:
+                    if srv is not None:
+                        for _ in range(self.world - 1):
+                            conn, _ = srv.accept()
+                            socket.send_fds(conn, [b"f"], [my_fd])
+                            conn.close()
+                else:
+                    c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                    c.settimeout(30)
+                    c.connect(path)
+                    _, fds, _, _ = socket.recv_fds(c, 1, 1)
+                    c.close()
+                    got[owner] = fds[0]
+            except OSError:
+                failed = True
+            barrier()
+            if srv is not None:
+                srv.close()
+                try:
+                    os.unlink(path)
+                except OSError:
+                    pass
+        if failed:
+            for f in got.values():
+                os.close(f)
+            raise OSError("picd_b200: file-descriptor exchange over unix sockets failed")
+        return got
+
+    def _try_vmm_alloc(self):
+        """The library's own symmetric slab: a VMM allocation per rank exported as a POSIX fd, every peer's allocation mapped
+        into every process, and -- where the GPUs support it -- an NVSwitch multicast object over all of them whose mapping
+        is what the NVLS variant of the bucket kernel uses (multimem.ld_reduce / multimem.st).  Every step is followed by
+        an agreement round, so a failure on any rank sends ALL ranks on to the next allocator."""
+        lib = self.lib
+        if not hasattr(lib, "picd_vmm_create"):
+            return
+        lib.picd_vmm_create.argtypes = [ctypes.c_size_t, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p),
+                                        ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int),
+                                        ctypes.POINTER(ctypes.c_size_t)]
+        lib.picd_vmm_import_peer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+        lib.picd_vmm_mc_create.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        lib.picd_vmm_mc_import.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.picd_vmm_mc_add_device.argtypes = [ctypes.c_void_p]
+        lib.picd_vmm_mc_bind_map.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+        lib.picd_vmm_destroy.argtypes = [ctypes.c_void_p]
+        slab, base, fd, padded = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int(-1), ctypes.c_size_t(0)
+        with torch.cuda.device(self.device):
+            ok = lib.picd_vmm_create(self.nbytes, self.world, ctypes.byref(slab), ctypes.byref(base), ctypes.byref(fd),
+                                     ctypes.byref(padded)) == 0
+            if not self._agree(ok):
+                if ok:
+                    lib.picd_vmm_destroy(slab)
+                return
+            bases = [0] * self.world
+            bases[self.rank] = base.value
+            try:
+                fds = self._pass_fds(fd.value, range(self.world))
+                ok = True
+                for r, pfd in fds.items():
+                    p = ctypes.c_void_p()
+                    ok = ok and lib.picd_vmm_import_peer(slab, r, pfd, ctypes.byref(p)) == 0
+                    os.close(pfd)
+                    bases[r] = p.value or 0
+            except Exception:      # noqa: BLE001 -- no unix sockets / fd passing in this container
+                ok = False
+            os.close(fd.value)
+            if not self._agree(ok):
+                lib.picd_vmm_destroy(slab)
+                return
+            # multicast view (NVLS); optional: without it the slab still serves the P2P variants
+            mc_base = 0
+            want_mc = os.environ.get("PICD_NVLS", "1") != "0" and lib.picd_vmm_multicast_supported() == 1
+            if self._agree(want_mc):
+                mfd = ctypes.c_int(-1)
+                ok = True
+                if self.rank == 0:
+                    ok = lib.picd_vmm_mc_create(slab, self.world, ctypes.byref(mfd)) == 0
+                if self._agree(ok):
+                    try:
+                        got = self._pass_fds(mfd.value, [0])
+                        if self.rank != 0:
+                            ok = lib.picd_vmm_mc_import(slab, got[0]) == 0
+                            os.close(got[0])
+                        else:
+                            os.close(mfd.value)
+                    except Exception:      # noqa: BLE001
+                        ok = False
+                    ok = ok and lib.picd_vmm_mc_add_device(slab) == 0
+                    if self._agree(ok):            # every device is a member before anybody binds
+                        p = ctypes.c_void_p()
+                        ok = lib.picd_vmm_mc_bind_map(slab, ctypes.byref(p)) == 0
+                        if self._agree(ok):
+                            mc_base = p.value
+            self._vmm = slab
+            self.base = base.value
+            self.peer_bases = bases
+            self.mc_base = mc_base or 0
+            self.backing = "own VMM slab" + (" + multicast" if mc_base else "")
 
     def _try_symmetric_alloc(self):
         """Allocate the slab from torch's symmetric-memory allocator: besides the peer mappings (what the CUDA-IPC path
@@ -127,6 +268,7 @@ class SymmetricSlab:
         self.base = t.data_ptr()
         self.peer_bases = bases
         self.mc_base = int(h.multicast_ptr) if os.environ.get("PICD_NVLS", "1") != "0" else 0
+        self.backing = "torch symmetric memory" + (" + multicast" if self.mc_base else "")
 
     def _exchange_handles(self):
         nb = self.lib.picd_ipc_handle_bytes()
