@@ -59,6 +59,65 @@ def _view(ptr: int, n: int, typestr: str, device, owner) -> torch.Tensor:
     return torch.as_tensor(_DevMem(ptr, (n,), typestr, owner), device=device)
 
 
+def pass_fds(rank: int, world: int, my_fd: int, owners, device=None) -> dict:
+    """Move POSIX file descriptors between the ranks of this node: for every `owner` rank in turn, the owner serves its
+    descriptor over a unix socket (SCM_RIGHTS) and every other rank connects and receives a descriptor of ITS OWN
+    process that refers to the same kernel object.  Returns {owner rank: local fd}.  Collective."""
+    import socket
+    import tempfile
+    import time
+    token = [None]
+    if rank == 0:
+        token[0] = f"{os.getpid()}_{int(time.time() * 1e6) & 0xFFFFFFFF:x}"
+    dist.broadcast_object_list(token, src=0)
+    got = {}
+    failed = False
+
+    def barrier():
+        dist.barrier(device_ids=[device.index]) if (device is not None and dist.get_backend() == "nccl") else dist.barrier()
+
+    for owner in owners:
+        path = os.path.join(tempfile.gettempdir(), f"picd_fd_{token[0]}_{owner}.sock")
+        srv = None
+        if rank == owner:
+            try:
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.settimeout(30)
+                srv.bind(path)
+                srv.listen(world)
+            except OSError:
+                failed, srv = True, None
+        barrier()                                        # the socket exists (or its owner has given up): peers may connect
+        try:                                             # both barriers run on every rank whatever happens in between
+            if rank == owner:
+                if srv is not None:
+                    for _ in range(world - 1):
+                        conn, _ = srv.accept()
+                        socket.send_fds(conn, [b"f"], [my_fd])
+                        conn.close()
+            else:
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.settimeout(30)
+                c.connect(path)
+                _, fds, _, _ = socket.recv_fds(c, 1, 1)
+                c.close()
+                got[owner] = fds[0]
+        except OSError:
+            failed = True
+        barrier()
+        if srv is not None:
+            srv.close()
+            try:
+                os.unlink(path)
+            except OSError:
+                pass
+    if failed:
+        for f in got.values():
+            os.close(f)
+        raise OSError("picd_b200: file-descriptor exchange over unix sockets failed")
+    return got
+
+
 class SymmetricSlab:
     def __init__(self, total: int, n_state: int, device: torch.device, world: int, rank: int,
                  num_buckets_hint: int = 256, buffer_floats: int = 0):
@@ -113,62 +172,7 @@ class SymmetricSlab:
         return int(flag.item()) == 1
 
     def _pass_fds(self, my_fd: int, owners) -> dict:
-        """Move POSIX file descriptors between the ranks of this node: for every `owner` rank in turn, the owner serves its
-        descriptor over a unix socket (SCM_RIGHTS) and every other rank connects and receives a descriptor of ITS OWN
-        process that refers to the same kernel object.  Returns {owner rank: local fd}.  Collective."""
-        import socket
-        import tempfile
-        import time
-        token = [None]
-        if self.rank == 0:
-            token[0] = f"{os.getpid()}_{int(time.time() * 1e6) & 0xFFFFFFFF:x}"
-        dist.broadcast_object_list(token, src=0)
-        got = {}
-        failed = False
-
-        def barrier():
-            dist.barrier(device_ids=[self.device.index]) if dist.get_backend() == "nccl" else dist.barrier()
-
-        for owner in owners:
-            path = os.path.join(tempfile.gettempdir(), f"picd_fd_{token[0]}_{owner}.sock")
-            srv = None
-            if self.rank == owner:
-                try:
-                    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                    srv.settimeout(30)
-                    srv.bind(path)
-                    srv.listen(self.world)
-                except OSError:
-                    failed, srv = True, None
-            barrier()                                        # the socket exists (or its owner has given up): peers may connect
-            try:                                             # both barriers run on every rank whatever happens in between
-                if self.rank == owner:
-                    if srv is not None:
-                        for _ in range(self.world - 1):
-                            conn, _ = srv.accept()
-                            socket.send_fds(conn, [b"f"], [my_fd])
-                            conn.close()
-                else:
-                    c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                    c.settimeout(30)
-                    c.connect(path)
-                    _, fds, _, _ = socket.recv_fds(c, 1, 1)
-                    c.close()
-                    got[owner] = fds[0]
-            except OSError:
-                failed = True
-            barrier()
-            if srv is not None:
-                srv.close()
-                try:
-                    os.unlink(path)
-                except OSError:
-                    pass
-        if failed:
-            for f in got.values():
-                os.close(f)
-            raise OSError("picd_b200: file-descriptor exchange over unix sockets failed")
-        return got
+        return pass_fds(self.rank, self.world, my_fd, owners, self.device)
 
     def _try_vmm_alloc(self):
         """The library's own symmetric slab: a VMM allocation per rank exported as a POSIX fd, every peer's allocation mapped

@@ -68,6 +68,21 @@ except RuntimeError as e:
 sd = dp.optimizer.state_dict()
 assert len(sd["state"]) == 2 and all(t.numel() == dp.arena.total for t in sd["state"])
 dp.optimizer.load_state_dict(sd)
+
+# descriptor exchange used by the VMM slab (native_comm.pass_fds): every rank ends up with descriptors of ITS OWN process
+# that refer to the other ranks' kernel objects (memfd here; a cuMemCreate handle on the GPU box)
+from picd_b200.parallel.native_comm import pass_fds  # noqa: E402
+
+mine = os.memfd_create(f"picd_test_{rank}")
+os.write(mine, f"rank{rank}".encode())
+fds = pass_fds(rank, world, mine, range(world))
+assert sorted(fds) == [r for r in range(world) if r != rank], fds
+for r, fd in fds.items():
+    assert os.pread(fd, 16, 0) == f"rank{r}".encode()
+    os.close(fd)
+one = pass_fds(rank, world, mine, [0])              # the multicast handle travels from rank 0 only
+assert (rank == 0 and one == {}) or (rank != 0 and os.pread(one[0], 16, 0) == b"rank0")
+os.close(mine)
 barrier()
 if rank == 0:
     print("DIST_WORKER_OK")
