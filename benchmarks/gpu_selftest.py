@@ -477,6 +477,74 @@ def group_conv():
                     ok &= check(tag + f".dgrad_bnreduce[relu={relu}].sum_g", sums[:Cin], gm.sum((0, 2, 3)), 1e-2, g)
                     ok &= check(tag + f".dgrad_bnreduce[relu={relu}].sum_g_xhat", sums[Cin:],
                                 (gm * (yf - mu) * istd).sum((0, 2, 3)), 1e-2, g)
+    ok &= stem_checks()
+    return ok
+
+
+def _stem_run(mode, x, w0, g0, b0, stride, pad, r):
+    """max_pool(relu(BN(conv(x)))) and its gradients: 'fused' (csrc/ops/stem.cu), 'unfused' (native conv_bn_act + pool2d) or
+    'oracle' (torch, fp32)."""
+    import torch
+    import torch.nn.functional as F
+    from picd_b200.ops import native
+    C = w0.shape[0]
+    w, gam, bet = w0.clone().requires_grad_(), g0.clone().requires_grad_(), b0.clone().requires_grad_()
+    rm, rv = torch.zeros(C, device=x.device), torch.ones(C, device=x.device)
+    first = x.shape[1] % 8 != 0
+    if mode == "oracle":
+        xi = x.float()
+        if not first:
+            xi.requires_grad_()
+        # the same op in fp32 with the two storage roundings (conv output, activation) made explicit as straight-through
+        # casts: a max-pool over bf16 values has ties an unrounded oracle would break differently
+        def ste(t):
+            return t + (t.to(torch.bfloat16).float() - t).detach()
+        y = F.conv2d(xi, w.to(torch.bfloat16).float(), None, stride, pad)
+        z = ste(F.relu(F.batch_norm(ste(y), rm, rv, gam, bet, True, 0.1, 1e-5)))
+        out = F.max_pool2d(z, 3, 2, 1)
+    else:
+        xi = x.clone()
+        if not first:
+            xi.requires_grad_()
+        kw = dict(stride=stride, padding=pad, training=True, momentum=0.1, eps=1e-5, sync_group=False)
+        if mode == "fused":
+            out = native.conv_bn_relu_maxpool(xi, w, gam, bet, rm, rv, **kw)
+        else:
+            z = native.conv_bn_act(xi, w, gam, bet, rm, rv, act="relu", residual=None, **kw)
+            out = native.pool2d(z, 3, 2, 1, mode="max")
+    out.backward(r.to(out.dtype))
+    return {"out": out.detach().float(), "dw": w.grad.float(), "dgamma": gam.grad.float(), "dbeta": bet.grad.float(),
+            "dx": None if first else xi.grad.float(), "rm": rm, "rv": rv}
+
+
+def stem_checks():
+    """Fused stem == the two separate native ops (same arg-max rule, so the pooled output is bit-identical and the gradients
+    differ only by the bf16 rounding of the dz tensor the fused form never writes) and == the fp32 oracle."""
+    import torch
+    dev = torch.device("cuda")
+    ok = True
+    g = "conv"
+    #        N  Cin  H    W   Cout R  stride pad
+    cases = [(4, 16, 30, 30, 64, 3, 1, 1), (2, 3, 64, 64, 64, 7, 2, 3), (3, 8, 29, 31, 32, 3, 1, 1), (2, 16, 18, 18, 128, 3, 1, 1)]
+    for N, Cin, H, W, C, R, stride, pad in cases:
+        torch.manual_seed(5)
+        x = torch.randn(N, Cin, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w0 = (torch.randn(C, Cin, R, R, device=dev) / (Cin * R * R) ** 0.5).contiguous(memory_format=torch.channels_last)
+        g0, b0 = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev) * 0.2
+        OH = ((H + 2 * pad - R) // stride + 1 + 2 - 3) // 2 + 1
+        OW = ((W + 2 * pad - R) // stride + 1 + 2 - 3) // 2 + 1
+        r = torch.randn(N, C, OH, OW, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        res = {m: _stem_run(m, x, w0, g0, b0, stride, pad, r) for m in ("fused", "unfused", "oracle")}
+        tag = f"stem{[N, Cin, H, W, C, R, stride, pad]}"
+        ok &= emit_ok({"group": g, "test": tag + ".out_identical_to_unfused",
+                       "ok": bool(torch.equal(res["fused"]["out"], res["unfused"]["out"]))})
+        ok &= check(tag + ".out", res["fused"]["out"], res["oracle"]["out"], 2e-2, g)
+        for k in ("dw", "dgamma", "dbeta", "rm", "rv"):
+            ok &= check(tag + f".{k}", res["fused"][k], res["oracle"][k], 3e-2, g)
+            ok &= check(tag + f".{k}.vs_unfused", res["fused"][k], res["unfused"][k], 1e-2, g)
+        if res["fused"]["dx"] is not None:
+            ok &= check_sparse(tag + ".dx", res["fused"]["dx"], res["oracle"]["dx"], 4e-2, g, max_bad_frac=2e-3)
+            ok &= check(tag + ".dx.vs_unfused", res["fused"]["dx"], res["unfused"]["dx"], 1.5e-2, g)
     return ok
 
 

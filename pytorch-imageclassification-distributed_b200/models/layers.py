@@ -127,6 +127,17 @@ def conv_bn_act(x, conv: Conv2d, bn: BatchNorm2d, act: Optional[str] = "relu", r
         sync_group=bn.sync_group, grad_fork=grad_fork)
 
 
+def conv_bn_relu_maxpool(x, conv: Conv2d, bn: BatchNorm2d):
+    """Stem ``max_pool2d(relu(BN(conv(x))), 3, 2, 1)`` as one op (ops.conv_bn_relu_maxpool)."""
+    if conv.groups != 1:
+        return ops.max_pool2d(conv_bn_act(x, conv, bn, "relu"), 3, 2, 1)
+    if bn.training:
+        _count_batch(bn)
+    return ops.conv_bn_relu_maxpool(x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, stride=conv.stride,
+                                    padding=conv.padding, training=bn.training, momentum=bn.momentum, eps=bn.eps,
+                                    sync_group=bn.sync_group)
+
+
 class Linear(nn.Module):
     def __init__(self, in_features, out_features, bias=True, act: Optional[str] = None):
         super().__init__()

@@ -13,7 +13,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from .layers import BatchNorm2d, Conv2d, Linear, conv_bn_act, prepare_input
+from .layers import BatchNorm2d, Conv2d, Linear, conv_bn_act, conv_bn_relu_maxpool, prepare_input
 
 
 class BasicBlock(nn.Module):
@@ -92,9 +92,10 @@ class ResNet(nn.Module):
 
     def forward(self, x):
         x = prepare_input(x)
-        x = conv_bn_act(x, self.conv1, self.bn1, "relu")
-        if not self.small_input:
-            x = ops.max_pool2d(x, 3, 2, 1)
+        if self.small_input:
+            x = conv_bn_act(x, self.conv1, self.bn1, "relu")
+        else:
+            x = conv_bn_relu_maxpool(x, self.conv1, self.bn1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)
         return self.fc(x)

@@ -103,6 +103,19 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride=1, paddi
                            eps=eps, act=act, residual=residual, sync_group=sync_group)
 
 
+def conv_bn_relu_maxpool(x, w, gamma, beta, running_mean, running_var, *, stride=1, padding=0, training=True, momentum=0.1,
+                         eps=1e-5, sync_group=False):
+    """Classifier stem ``max_pool2d(relu(BN(conv(x))), 3, 2, 1)`` (torchvision resnet.py `conv1 -> bn1 -> relu -> maxpool`).
+    Native path: the normalised activation is never materialised (csrc/ops/stem.cu)."""
+    if use_native(x):
+        from . import native
+        return native.conv_bn_relu_maxpool(x, w, gamma, beta, running_mean, running_var, stride=stride, padding=padding,
+                                           training=training, momentum=momentum, eps=eps, sync_group=sync_group)
+    z = conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride, padding=padding, training=training,
+                    momentum=momentum, eps=eps, act="relu", sync_group=sync_group)
+    return max_pool2d(z, 3, 2, 1)
+
+
 def conv2d(x, w, bias=None, stride=1, padding=0, groups=1):
     if use_native(x) and groups == 1:
         from . import native

@@ -55,6 +55,9 @@ _SIG = {
     "picd_bn_bwd_reduce": "pppppppiplip",
     "picd_bn_bwd_apply": "pppppppi" + "pif" + "pi" + "pp" + "pp" + "lip",
     "picd_bn_bwd_eval": "pppppipplip",
+    "picd_bn_relu_maxpool_fwd": "ppppp" + "iiiiii" + "p",
+    "picd_bn_relu_maxpool_bwd_reduce": "pppppppp" + "iiiiii" + "p",
+    "picd_bn_relu_maxpool_bwd_apply": "ppppppp" + "pifp" + "pi" + "pp" + "p" + "iiiiii" + "p",
     "picd_pool_fwd": "ppp" + "i" * 11 + "p",
     "picd_pool_bwd": "ppp" + "i" * 11 + "p",
     "picd_gap_fwd": "ppiiip",
@@ -607,6 +610,79 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, *, stride, padding
     if cfg.rec is not None:
         out._bn_rec = cfg.rec
     return out
+
+
+# --------------------------------------------------------------------------- stem: conv + BN + ReLU + 3x3/s2 max-pool
+_FUSE_STEM = os.environ.get("PICD_FUSE_STEM", "1") != "0"               # A/B switch
+
+
+class _ConvBnReluPool(torch.autograd.Function):
+    """ResNet / DenseNet stem (reference: nn/classifier.py:36-37 -> torchvision `conv1, bn1, relu, maxpool`): the normalised
+    112x112 activation -- the largest tensor of the network -- is never written.  Forward pools relu(BN(y)) straight from the
+    conv output; backward regenerates the pooled gradient per input pixel from (dpool, arg-max bytes) inside both BatchNorm
+    backward kernels (csrc/ops/stem.cu)."""
+
+    @staticmethod
+    def forward(ctx, x, w, gamma, beta, cfg: _BNCfg):
+        C = w.shape[0]
+        stats = stat_buffer(C, x.device) if cfg.training else None
+        y, info = _conv_forward(x, w, cfg.stride, cfg.padding, stats, None, None)
+        count = y.numel() // C
+        total_dev = None
+        if cfg.training:
+            coef, (total, total_dev) = _bn_forward_coeffs(stats, count, gamma, beta, cfg.rm, cfg.rv, cfg.momentum, cfg.eps,
+                                                          cfg.sync_group)
+        else:
+            coef = torch.empty(4, C, dtype=torch.float32, device=y.device)
+            call("picd_bn_eval_coeffs", gamma, beta, cfg.rm, cfg.rv, float(cfg.eps), coef[0], coef[1], C)
+            total = float(count)
+        N, _, H, W = y.shape
+        OH, OW = _out_size(H, 3, 2, 1), _out_size(W, 3, 2, 1)
+        out = empty_nhwc(N, C, OH, OW, y.device)
+        arg = torch.empty((N, OH, OW, C), dtype=torch.uint8, device=y.device)
+        call("picd_bn_relu_maxpool_fwd", y, coef[0], coef[1], out, arg, N, H, W, C, OH, OW)
+        ctx.info, ctx.geom = info, (N, H, W, C, OH, OW)
+        ctx.bn_total, ctx.bn_total_dev, ctx.bn_sync = total, total_dev, cfg.sync_group
+        ctx.save_for_backward(w, gamma, beta, y, arg, coef)
+        return out
+
+    @staticmethod
+    def backward(ctx, dpool):
+        w, gamma, beta, y, arg, coef = ctx.saved_tensors
+        N, H, W, C, OH, OW = ctx.geom
+        need = ctx.needs_input_grad
+        dpool = nhwc(dpool)
+        sums2 = stat_buffer(C, y.device)
+        call("picd_bn_relu_maxpool_bwd_reduce", dpool, arg, y, coef[0], coef[1], coef[2], coef[3], sums2, N, H, W, C, OH, OW)
+        gsums = _bn_allreduce_bwd(sums2, ctx.bn_sync, C, key=gamma)
+        gt, g_routed = _grad_target(gamma)
+        bt, b_routed = _grad_target(beta)
+        dy = torch.empty_like(y)
+        call("picd_bn_relu_maxpool_bwd_apply", dpool, arg, y, coef[0], coef[1], coef[2], coef[3], gsums,
+             gsums.numel() // (2 * C), 1.0 / ctx.bn_total, ctx.bn_total_dev, sums2, STAT_REPLICAS, gt, bt, dy, N, H, W, C, OH, OW)
+        if g_routed:
+            _mark_ready(gamma)
+        if b_routed:
+            _mark_ready(beta)
+        dx, dw = _conv_backward(ctx.info, dy, w, need[0], need[1])
+        return dx, dw, (None if g_routed else gt), (None if b_routed else bt), None
+
+
+def conv_bn_relu_maxpool(x, w, gamma, beta, running_mean, running_var, *, stride, padding, training, momentum, eps,
+                         sync_group):
+    """max_pool2d(relu(BN(conv(x))), 3, 2, 1).  One fused chain in training mode and under no_grad; an eval-mode BatchNorm
+    that still needs gradients (frozen statistics) takes the two separate ops."""
+    C = w.shape[0]
+    fusable = _FUSE_STEM and C % 8 == 0 and 256 % (C // 8) == 0 and (training or not torch.is_grad_enabled())
+    if not fusable:
+        z = conv_bn_act(x, w, gamma, beta, running_mean, running_var, stride=stride, padding=padding, training=training,
+                        momentum=momentum, eps=eps, act="relu", residual=None, sync_group=sync_group)
+        return pool2d(z, 3, 2, 1, mode="max")
+    cfg = _BNCfg()
+    cfg.stride, cfg.padding, cfg.training, cfg.momentum, cfg.eps = stride, padding, training, momentum, eps
+    cfg.act, cfg.rm, cfg.rv, cfg.sync_group = "relu", running_mean, running_var, sync_group
+    cfg.fork = cfg.fork_role = cfg.rec = cfg.src_rec = None
+    return _ConvBnReluPool.apply(x, w, gamma, beta, cfg)
 
 
 class _BnAct(torch.autograd.Function):
