@@ -258,6 +258,20 @@ __device__ __forceinline__ void tma_load_4d_pair_warp(void* dst, const CUtensorM
         "r"(c3)
         : "memory");
 }
+// Same, with the box delivered to the same shared-memory offset of every CTA in `mask` (cluster ranks); each delivery credits
+// the leader of the pair it lands in.  TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
+// from another GPU's memory hung the GPU: callers check that the tensor map's buffer belongs to the current device.
+__device__ __forceinline__ void tma_load_3d_pair_mc_warp(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                                         uint32_t mask) {
+    asm volatile(
+        "{\n\t.reg .pred e;\n\t.reg .b16 cm;\n\t"
+        "cvt.u16.u32 cm, %6;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], cm;\n\t}"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & PEER_BIT_MASK), "r"(c0), "r"(c1), "r"(c2),
+        "r"(mask)
+        : "memory");
+}
 // arrive on the mbarrier at this offset in the LEADER CTA of the pair (works from either CTA)
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & PEER_BIT_MASK) : "memory");

@@ -27,6 +27,7 @@
 #include "../common/picd_common.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -65,6 +66,14 @@ struct ConvGemmParams {
     int half_w;           // columns drained per staging pass: 128 (deep operand ring) or 256 (short-K tiles, one pass)
     int cluster;          // 1: launched as CTA pairs (clusters of 2, cta_group::2): each CTA loads its own half of every B tile
     int reduce_add;       // 1: the output tile is ADDED to the destination (TMA reduce) instead of overwriting it
+    int quad;             // pairs only, K-major B, free schedule: clusters of FOUR CTAs = two pairs on vertically adjacent 256-row
+                          // tiles of the same column tile.  The pairs need the same B tile: each CTA fetches a QUARTER of it and
+                          // TMA-multicasts that quarter to its twin in the other pair (tensor map over this GPU's memory), so a
+                          // k-iteration pulls 16 + 8 KB instead of 16 + 16 KB per CTA through L2.
+    int nbw;              // free schedule: column tiles are walked in blocks of nbw (all row tiles of a block before the next block),
+                          // so a block's B rows stay in L2 while the A rows stream past once per block
+    int free_sched;       // pairs only, no per-channel statistics: pair-tiles are dealt round-robin over ALL pairs (the column
+                          // tile of a CTA changes from tile to tile), so every SM pair works whatever numN is
     // halo mode (3x3, stride 1): one activation box with a one-row halo above and below is loaded per (k-chunk, dw) and
     // the three dh taps read it through descriptors shifted by whole pixel rows -> 3 instead of 9 A loads per k-chunk.
     // taps[] is then ordered [dw][dh] with dh = -1, 0, +1.
@@ -145,7 +154,8 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     if (threadIdx.x == 0) {
         for (int i = 0; i < stages; ++i) {
             mbar_init(&bars->full[i], 1);
-            mbar_init(&bars->empty[i], 1);                    // pair: the leader's commit arrives once in each CTA
+            mbar_init(&bars->empty[i], (kCluster && p.quad) ? 2 : 1);   // pair: the leader's commit arrives once in each CTA;
+                                                                        // quad: a stage is free when BOTH pairs have consumed it
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bars->tfull[i], 1);
@@ -177,12 +187,35 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
     const int crank = kCluster ? static_cast<int>(uniform_u32(cluster_ctarank())) : 0;
     // tile walk: (non-cluster) CTA b owns column tile b % numN and pixel tiles b/numN, +grid_m, ...
     //            (cluster)     cluster c owns column tile c % numN; its two CTAs take pixel tiles 2j and 2j+1 in lockstep
-    const int unit = kCluster ? (blockIdx.x >> 1) : blockIdx.x;
-    const int units = kCluster ? (gridDim.x >> 1) : gridDim.x;
-    const int n_tile = unit % numN;
+    const bool quad = kCluster && p.quad != 0;
+    const int csh = quad ? 2 : 1;            // log2(cluster size)
+    const int unit = kCluster ? (blockIdx.x >> csh) : blockIdx.x;
+    const int units = kCluster ? (gridDim.x >> csh) : gridDim.x;
+    const int prank = crank & 1;             // rank inside the CTA pair (0 = the pair's leader)
+    const bool free_s = kCluster && p.free_sched != 0;
+    int n_tile = unit % numN;                // (free schedule: the column tile of the CURRENT tile, set by tile_at)
     const int grid_m = kCluster ? 2 * (units / numN) : units / numN;
     const int m_first = kCluster ? 2 * (unit / numN) + crank : unit / numN;
     const int m_limit = kCluster ? p.num_m_tiles + crank : p.num_m_tiles;   // the pair iterates while its EVEN tile exists
+    // i-th tile of this CTA: sets n_tile and m, false when the walk is over.  Free schedule: pair-tile t = unit + i * units
+    // with the column tile fastest, so concurrently running pairs share their A rows through L2.
+    auto tile_at = [&](int i, int& m) -> bool {
+        if (free_s) {
+            const int t = unit + i * units;
+            const int mgroups = (p.num_m_tiles + (1 << csh) - 1) >> csh;      // row groups (pairs / quads of 128-row tiles)
+            if (t >= mgroups * numN) return false;
+            const int per_block = p.nbw * mgroups;
+            const int blk = t / per_block;
+            const int r = t - blk * per_block;
+            const int w = min(p.nbw, numN - blk * p.nbw);                     // the last block may be narrower
+            const int mg = r / w;
+            n_tile = blk * p.nbw + (r - mg * w);
+            m = (mg << csh) + crank;
+            return true;
+        }
+        m = m_first + i * grid_m;
+        return m < m_limit;
+    };
     const int k_iters = p.halo ? 3 * p.kchunks : p.ntaps * p.kchunks;
     float* sBias = reinterpret_cast<float*>(smem + SMEM_BIAS_OFF);
     if (kBiasAct) {
@@ -228,7 +261,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                 mbar_arrive_expect_tx_warp(&bars->bres, 9 * b_tap);
                 for (int t = 0; t < 9; ++t) load_b_tap(sBres + t * b_tap, &bars->bres, 0, p.taps[t].btap);
             }
-            for (int m = m_first; m < m_limit; m += grid_m) {
+            for (int ti = 0, m = 0; tile_at(ti, m); ++ti) {
                 const int tw = m % p.tiles_w;
                 const int th = (m / p.tiles_w) % p.tiles_h;
                 const int tn = m / (p.tiles_w * p.tiles_h);
@@ -259,15 +292,22 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                         if (kCluster) {
                             // pair: the leader's barrier collects the bytes of BOTH CTAs; this CTA fetches its own pixel
                             // rows and weight rows [crank * BN/2, +BN/2) into its own shared memory
-                            if (crank == 0) mbar_arrive_expect_tx_warp(&bars->full[stage], 2 * tx_bytes);
+                            if (prank == 0) mbar_arrive_expect_tx_warp(&bars->full[stage], 2 * tx_bytes);
                             tma_load_4d_pair_warp(sA + stage * a_stage, &p.amap[tp.amap], &bars->full[stage], kc * KCHUNK,
                                                   w0 + tp.dw, h0 + tp.dh, n0);
-                            if (!p.b_mn) {
+                            if (quad) {
+                                // this CTA's quarter of the B tile, delivered to itself and to its twin (same pair rank) in
+                                // the other pair; each delivery credits the leader of the pair it lands in
+                                const int twin = crank >> 1;
+                                tma_load_3d_pair_mc_warp(dstB + twin * (b_tap >> 1), &p.bmap, &bars->full[stage], kc * KCHUNK,
+                                                         tp.btap, n_tile * BN + prank * (BN >> 1) + twin * (BN >> 2),
+                                                         0x5u << prank);
+                            } else if (!p.b_mn) {
                                 tma_load_3d_pair_warp(dstB, &p.bmap, &bars->full[stage], kc * KCHUNK, tp.btap,
-                                                      n_tile * BN + crank * (BN >> 1));
+                                                      n_tile * BN + prank * (BN >> 1));
                             } else {                     // MN-major: this CTA's half of the columns, in 64-column boxes
                                 for (int j = 0; j < BN / 128; ++j) {
-                                    int c0 = n_tile * BN + crank * (BN >> 1) + j * 64;
+                                    int c0 = n_tile * BN + prank * (BN >> 1) + j * 64;
                                     if (c0 >= p.Cout) c0 = 0;   // never request a fully out-of-range box
                                     tma_load_3d_pair_warp(dstB + j * 8192, &p.bmap, &bars->full[stage], c0, tp.btap, kc * KCHUNK);
                                 }
@@ -308,7 +348,7 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
         const uint32_t b_tap_lo = static_cast<uint32_t>(b_tap) >> 4;
         const uint32_t row_lo = (static_cast<uint32_t>(bw) * 128u) >> 4;   // one pixel row of the halo box
         if (p.halo && p.b_resident) { mbar_wait(&bars->bres, 0); tc_fence_after(); }
-        for (int m = m_first; m < m_limit && (!kCluster || crank == 0); m += grid_m) {     // pair: only the leader issues
+        for (int ti = 0, m = 0; tile_at(ti, m) && (!kCluster || prank == 0); ++ti) {     // pair: only the leader issues
             mbar_wait(&bars->tempty[acc], accphase ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * 256;
@@ -335,11 +375,12 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
                         else umma_bf16_warp(tmem_d, adesc0 + k * 2, bdesc0 + k * b_kstep, idesc, (it | k) != 0);
                     }
                 }
-                if (kCluster) umma_commit_pair_warp(&bars->empty[stage], 3);   // frees the stage in both CTAs
+                if (kCluster) umma_commit_pair_warp(&bars->empty[stage], quad ? 0xFu : 3u);   // frees the stage in both CTAs (quad:
+                                                                                                // one of two arrivals, in all four)
                 else umma_commit_warp(&bars->empty[stage]);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
-            if (kCluster) umma_commit_pair_warp(&bars->tfull[acc], 3);         // both CTAs' accumulator rows are complete
+            if (kCluster) umma_commit_pair_warp(&bars->tfull[acc], 3u << (crank & 2));   // both CTAs' accumulator rows are complete
             else umma_commit_warp(&bars->tfull[acc]);
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
@@ -432,12 +473,20 @@ __global__ void __launch_bounds__(320, 1) conv_gemm_kernel(const __grid_constant
             }
         };
 
-        for (int m = m_first; m < m_limit; m += grid_m) {
+        for (int ti = 0, m = 0; tile_at(ti, m); ++ti) {
             const int tw = m % p.tiles_w;
             const int th = (m / p.tiles_w) % p.tiles_h;
             const int tn = m / (p.tiles_w * p.tiles_h);
             const int w0 = tw * bw, h0 = th * bh, n0 = tn * bn;
             const bool tile_ok = m < p.num_m_tiles;          // the odd CTA of the last pair may have no tile of its own
+            if (kBiasAct && free_s) {
+                // the column tile moved: restage its bias slice.  Every reader of the old slice is past the barrier that closed the
+                // previous tile's last pass; the first barrier of the pass below publishes the new one.
+                for (int i = tid_e; i < BN; i += 256) {
+                    const int c = n_tile * BN + i;
+                    sBias[i] = (p.bias != nullptr && c < p.Cout) ? p.bias[c] : 0.f;
+                }
+            }
             const bool valid = tile_ok && (w0 + iw < p.W) && (h0 + ih < p.H) && (n0 + in_ < p.N);
             const uint32_t vmask = valid ? 0xffffffffu : 0u;     // rows hanging over the tensor edge are stored as 0
             mbar_wait(&bars->tfull[acc], accphase);
@@ -898,6 +947,23 @@ static bool want_cluster(int k_iters, int num_m_tiles, int BN, bool b_mn) {
     return k_iters >= 12 && BN >= 192;
 }
 
+// Clusters of four (two pairs sharing their B tile by TMA multicast, see ConvGemmParams::quad): for plain GEMM-shaped launches
+// that already want pairs.  The multicast load reads the weight operand, which must live in THIS GPU's memory.
+static bool want_quad(const void* b_operand, int BN, int num_m_tiles, int k_iters) {
+    static const int mode = [] { const char* e = getenv("PICD_QUAD"); return e == nullptr ? -1 : atoi(e); }();
+    if (mode == 0 || (BN % 32) != 0 || num_m_tiles < 8) return false;
+    // Opt-in (PICD_QUAD=1).  Measured on 8192^3 with the blocked tile walk: 1464 TFLOP/s against 1560 for plain pairs -- only 33
+    // clusters of four are co-resident on the 148 SMs (132 CTAs), which costs more than the 25 % fewer L2 -> SM bytes buy; on
+    // the ViT shapes (K = 768 / 3072, 197 row tiles) four CTAs in lockstep lose 4-6 % to two.
+    (void)k_iters;
+    if (mode != 1) return false;
+    cudaPointerAttributes at{};
+    int dev = -1;
+    if (cudaPointerGetAttributes(&at, b_operand) != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (at.type != cudaMemoryTypeDevice || at.device != dev) return false;
+    return true;
+}
+
 // halo mode keeps three weight taps per stage, so its column tiles are capped at 128 channels
 static int num_n_tiles_halo(int C, int* BN) {
     const int numN = ceil_div(C, 128);
@@ -952,14 +1018,69 @@ static int launch_conv_gemm(ConvGemmParams& p, int Cout_gemm, cudaStream_t strea
         int nclusters = std::max(p.numN, (sms / 2) / p.numN * p.numN);
         const long long pairs = 1LL * ((p.num_m_tiles + 1) / 2) * p.numN;
         if (nclusters > pairs) nclusters = static_cast<int>(std::max<long long>(p.numN, pairs / p.numN * p.numN));
+        // plain GEMMs (no per-channel statistics tied to a fixed column tile): when the column-tile count does not divide the
+        // SM pairs (8192 columns: 32 tiles -> 64 of 74 pairs), deal the pair-tiles round-robin over every pair instead
+        static const bool free_ok = [] { const char* e = getenv("PICD_FREE_SCHED"); return e == nullptr || atoi(e) != 0; }();
+        p.free_sched = 0;
+        int csize = 2;
+        if (p.quad) {
+            static const int max_quads = [] {
+                cudaLaunchConfig_t q{};
+                q.gridDim = dim3(4 * (num_sms() / 4)); q.blockDim = dim3(320); q.dynamicSmemBytes = MAX_DYN_SMEM;
+                cudaLaunchAttribute a[1];
+                a[0].id = cudaLaunchAttributeClusterDimension;
+                a[0].val.clusterDim.x = 4; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
+                q.attrs = a; q.numAttrs = 1;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, conv_gemm_kernel<false, true>, &q) != cudaSuccess) { cudaGetLastError(); n = 0; }
+                return n;
+            }();
+            const long long quads = 1LL * ((p.num_m_tiles + 3) / 4) * p.numN;
+            const int cap = std::min(sms / 4, max_quads);
+            static bool told = false;
+            if (!told && getenv("PICD_DEBUG") != nullptr) {
+                fprintf(stderr, "[picd] conv_gemm quad mode: %d clusters of 4 co-resident (device), using %d\n", max_quads, cap);
+                told = true;
+            }
+            PICD_REQUIRE(cap >= 1, "conv_gemm: no cluster of four CTAs fits this device (%d)", cap);
+            p.free_sched = 1;
+            csize = 4;
+            nclusters = static_cast<int>(std::min<long long>(cap, quads));
+        } else if (free_ok && p.stats == nullptr && !p.bn_reduce && pairs > sms / 2) {
+            const long long rounds_fixed = (pairs + nclusters - 1) / nclusters;
+            const long long rounds_free = (pairs + sms / 2 - 1) / (sms / 2);
+            // (a pair that cannot be co-resident would run as a second wave: never ask for more clusters than the device places)
+            static const int max_pairs = [] {
+                cudaLaunchConfig_t q{};
+                q.gridDim = dim3(2 * (num_sms() / 2)); q.blockDim = dim3(320); q.dynamicSmemBytes = MAX_DYN_SMEM;
+                cudaLaunchAttribute a[1];
+                a[0].id = cudaLaunchAttributeClusterDimension;
+                a[0].val.clusterDim.x = 2; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
+                q.attrs = a; q.numAttrs = 1;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, conv_gemm_kernel<false, true>, &q) != cudaSuccess) { cudaGetLastError(); n = 0; }
+                return n;
+            }();
+            const int cap = std::min(sms / 2, max_pairs);
+            if (cap > nclusters && (pairs + cap - 1) / cap < rounds_fixed) { p.free_sched = 1; nclusters = cap; }
+            (void)rounds_free;
+        }
+        if (p.free_sched) {
+            // column block = what keeps its B rows (BN x K bf16 each) within ~32 MB of the 126 MB L2 (8192^3: blocks of 8 column
+            // tiles 1560 TFLOP/s, 16: 1522, 4: 1535, all 32 i.e. no blocking: 1419; DRAM reads drop from 2.1 GB to ~0.7 GB)
+            const long long tile_bytes = 2LL * p.BN * p.ntaps * p.kchunks * KCHUNK;
+            p.nbw = static_cast<int>(std::max<long long>(1, std::min<long long>(p.numN, (32LL << 20) / tile_bytes)));
+            static const int forced_nbw = [] { const char* e = getenv("PICD_NBW"); return e == nullptr ? 0 : atoi(e); }();
+            if (forced_nbw > 0) p.nbw = std::min(forced_nbw, p.numN);
+        }
         cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(2 * nclusters);
+        cfg.gridDim = dim3(csize * nclusters);
         cfg.blockDim = dim3(320);
         cfg.dynamicSmemBytes = MAX_DYN_SMEM;
         cfg.stream = stream;
         cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        attr[0].val.clusterDim.x = csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
@@ -1024,7 +1145,9 @@ extern "C" int picd_conv_fprop(const void* x, const void* w, void* y, float* sta
         int BN;
         if (halo) num_n_tiles_halo(Cout, &BN); else num_n_tiles(Cout, &BN);
         p.cluster = (!halo && want_cluster(R * S * ceil_div(Cin, KCHUNK), g.tiles_w * g.tiles_h * g.tiles_n, BN, false)) ? 1 : 0;
-        uint32_t box[3] = {64, 1, (uint32_t)(p.cluster ? BN / 2 : BN)};     // cluster: each CTA fetches half the rows
+        p.quad = (p.cluster && stats == nullptr && want_quad(w, BN, g.tiles_w * g.tiles_h * g.tiles_n, R * S * ceil_div(Cin, KCHUNK))) ? 1 : 0;
+        uint32_t box[3] = {64, 1, (uint32_t)(p.quad ? BN / 4 : p.cluster ? BN / 2 : BN)};   // pair: each CTA fetches half the rows,
+                                                                                             // quad: a quarter (and multicasts it)
         if (make_tensor_map(&p.bmap, w, 2, 3, dims, strides, box, true)) return 3;
     }
     if (make_act_map(&p.dmap, y, N, OH, OW, Cout, 1, 0, 0, bw, bh, g.bn)) return 3;
