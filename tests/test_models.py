@@ -127,3 +127,32 @@ def test_cpu_fallbacks_of_small_ops():
     assert fk is None and len(parts) == 3 and all(p is x for p in parts)
     x1, x2, fk2 = ops.fork(x)
     assert fk2 is None and x1 is x and x2 is x
+
+
+def test_stem_op_cpu_equals_separate_ops():
+    """ops.conv_bn_relu_maxpool (the ResNet stem as one op) on CPU == conv -> BN -> ReLU -> max_pool2d, values and gradients,
+    and moves the running statistics the same way."""
+    import torch
+    import torch.nn.functional as F
+    from picd_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 33, 33)
+    w = torch.randn(16, 3, 7, 7) * 0.1
+    g, b = torch.rand(16) + 0.5, torch.randn(16) * 0.1
+
+    def run(fused):
+        ps = [t.clone().requires_grad_() for t in (w, g, b)]
+        rm, rv = torch.zeros(16), torch.ones(16)
+        if fused:
+            out = ops.conv_bn_relu_maxpool(x, ps[0], ps[1], ps[2], rm, rv, stride=2, padding=3, training=True)
+        else:
+            y = F.conv2d(x, ps[0], None, 2, 3)
+            out = F.max_pool2d(F.relu(F.batch_norm(y, rm, rv, ps[1], ps[2], True, 0.1, 1e-5)), 3, 2, 1)
+        out.square().sum().backward()
+        return out.detach(), [p.grad for p in ps], rm, rv
+
+    o1, g1, rm1, rv1 = run(True)
+    o2, g2, rm2, rv2 = run(False)
+    assert o1.shape == (2, 16, 9, 9)
+    assert torch.allclose(o1, o2, atol=1e-5) and all(torch.allclose(a, c, atol=1e-4, rtol=1e-4) for a, c in zip(g1, g2))
+    assert torch.allclose(rm1, rm2, atol=1e-6) and torch.allclose(rv1, rv2, atol=1e-6)
