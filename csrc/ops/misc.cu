@@ -514,24 +514,25 @@ __device__ __forceinline__ void ld8f(const float* p, float (&o)[8]) {
     o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
 }
 constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
+// gamma / beta are staged in shared memory once per block and read back with 128-bit loads per row: as 2 x 8 x V registers
+// per thread they cost an SM its third and fourth resident block, and latency hiding is all these kernels need.
 template <int V>
-__global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                                                            const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                            long long M, int D, float eps,
-                                                            const __nv_bfloat16* __restrict__ res,
-                                                            __nv_bfloat16* __restrict__ sum_out) {
+__global__ void __launch_bounds__(256, 3) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                                                               float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                               long long M, int D, float eps,
+                                                               const __nv_bfloat16* __restrict__ res,
+                                                               __nv_bfloat16* __restrict__ sum_out) {
     // res / sum_out (both or neither): the transformer's residual add fused in -- the row normalised is s = bf16(x + res),
     // which is also written to sum_out (the residual stream); one pass instead of an add kernel followed by this one
+    __shared__ __align__(16) float sgb[2][V * 256];
+    for (int j = threadIdx.x; j < V * 256; j += blockDim.x) {       // parameters do not depend on the previous kernel
+        sgb[0][j] = j < D ? gamma[j] : 0.f;
+        sgb[1][j] = j < D ? beta[j] : 0.f;
+    }
+    __syncthreads();
     pdl_sync();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float gm[V][8], bt[V][8];
-#pragma unroll
-    for (int i = 0; i < V; ++i) {
-        const int j = lane * 8 + i * 256;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { gm[i][k] = (j + k < D) ? gamma[j + k] : 0.f; bt[i][k] = (j + k < D) ? beta[j + k] : 0.f; }
-    }
     const float inv_d = 1.f / D;
     const long long nwarps = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
     for (long long row = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp) * 2; row < M; row += nwarps * 2) {
@@ -544,6 +545,14 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
                 raw[r][i] = (row + r < M && j < D) ? *reinterpret_cast<const uint4*>(x + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
             }
         if (res != nullptr) {
+            uint4 rr[2][V];
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int i = 0; i < V; ++i) {
+                    const int j = lane * 8 + i * 256;
+                    rr[r][i] = (row + r < M && j < D) ? *reinterpret_cast<const uint4*>(res + (row + r) * D + j) : make_uint4(0, 0, 0, 0);
+                }
 #pragma unroll
             for (int r = 0; r < 2; ++r)
 #pragma unroll
@@ -552,7 +561,7 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
                     if (row + r < M && j < D) {
                         float a[8], b[8];
                         unpack8(raw[r][i], a);
-                        unpack8(*reinterpret_cast<const uint4*>(res + (row + r) * D + j), b);
+                        unpack8(rr[r][i], b);
 #pragma unroll
                         for (int k = 0; k < 8; ++k) a[k] += b[k];
                         raw[r][i] = pack8(a);               // the bf16-rounded sum is what gets normalised (and re-read by the backward)
@@ -563,13 +572,13 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             if (row + r >= M) break;
-            float f[V][8];
             float s = 0.f, q = 0.f;
 #pragma unroll
             for (int i = 0; i < V; ++i) {
-                unpack8(raw[r][i], f[i]);
+                float f[8];
+                unpack8(raw[r][i], f);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) { s += f[i][k]; q += f[i][k] * f[i][k]; }
+                for (int k = 0; k < 8; ++k) { s += f[k]; q += f[k] * f[k]; }
             }
             s = warp_sum(s); q = warp_sum(q);
             const float mean = s * inv_d;
@@ -579,20 +588,24 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const __nv_bfloat16*
             for (int i = 0; i < V; ++i) {
                 const int j = lane * 8 + i * 256;
                 if (j < D) {
+                    float f[8], gm[8], bt[8];
+                    unpack8(raw[r][i], f);
+                    ld8f(&sgb[0][j], gm);
+                    ld8f(&sgb[1][j], bt);
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) f[i][k] = (f[i][k] - mean) * rstd * gm[i][k] + bt[i][k];
-                    *reinterpret_cast<uint4*>(y + (row + r) * D + j) = pack8(f[i]);
+                    for (int k = 0; k < 8; ++k) f[k] = (f[k] - mean) * rstd * gm[k] + bt[k];
+                    *reinterpret_cast<uint4*>(y + (row + r) * D + j) = pack8(f);
                 }
             }
         }
     }
 }
 // dx and (atomically accumulated) dgamma/dbeta.  A lane owns the same columns (lane*8 + 256*i) for every row its warp
-// handles, so the parameter-gradient partials live in registers; they are folded across the block's warps through shared
-// memory once at the end (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).  Two rows per iteration: the
-// loads of the second row are in flight while the first one reduces.
+// handles; the parameter-gradient partials of a warp live in ITS slice of shared memory (128-bit read-modify-write per row, no
+// other warp touches it) instead of 2 x 8 x V registers per thread, and are folded across the block's warps once at the end
+// (one fp32 atomic per column per block).  D <= 1024 (ViT-B: 768).
 template <int V>
-__global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+__global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                                                const float* __restrict__ gamma, const float* __restrict__ mean,
                                                                const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -600,17 +613,24 @@ __global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat
                                                                const __nv_bfloat16* __restrict__ add_in) {
     // add_in (nullable): gradient arriving over the residual stream; the kernel writes dx = LayerNorm-backward + add_in, i.e. the
     // gradient sum autograd would otherwise compute with a separate add kernel.
-    // Register diet (two blocks per SM instead of one at 199 registers): a row is read TWICE -- pass A accumulates the two row
-    // sums and the parameter-gradient partials on the fly, pass B re-reads dy / x (L1 hits: a row is 3 KB) and writes dx -- so
-    // that no per-row array survives between the passes; gamma is re-read from L1 as well.
-    extern __shared__ float sm[];   // [warps][2][V*256]: every warp parks its partial sums, no shared-memory atomics
-    pdl_sync();
+    // A row is read TWICE: pass A accumulates the two row sums and the parameter-gradient partials on the fly, pass B re-reads
+    // dy / x (L1 hits: a row is 3 KB) and writes dx, so that no per-row array survives between the passes; the residual-stream
+    // gradient is requested in pass A already (its DRAM latency would otherwise be exposed a second time per row).
+    extern __shared__ __align__(16) float sm[];   // [warps][2][V*256] partial dgamma / dbeta, then [V*256] gamma
+    constexpr int W2 = V * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    float pg[V][8], pb[V][8];
+    float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
+    float* sgamma = sm + static_cast<size_t>(nw) * 2 * W2;
+    for (int j = threadIdx.x; j < W2; j += blockDim.x) sgamma[j] = j < D ? gamma[j] : 0.f;
 #pragma unroll
-    for (int i = 0; i < V; ++i)
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { pg[i][k] = 0.f; pb[i][k] = 0.f; }
+    for (int i = 0; i < V; ++i) {
+        const int j = lane * 8 + i * 256;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(mine + j) = z; *reinterpret_cast<float4*>(mine + j + 4) = z;
+        *reinterpret_cast<float4*>(mine + W2 + j) = z; *reinterpret_cast<float4*>(mine + W2 + j + 4) = z;
+    }
+    __syncthreads();
+    pdl_sync();
     const float inv_d = 1.f / D;
     const long long r0 = static_cast<long long>(blockIdx.x) * rows_per_block;
     long long r1 = r0 + rows_per_block;
@@ -618,22 +638,34 @@ __global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat
     for (long long row = r0 + warp; row < r1; row += nw) {
         const float mu = mean[row], rs = rstd[row];
         float a = 0.f, b = 0.f;
+        uint4 ad[V];
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            const int j = lane * 8 + i * 256;
+            ad[i] = (add_in != nullptr && j < D) ? *reinterpret_cast<const uint4*>(add_in + row * D + j) : make_uint4(0, 0, 0, 0);
+        }
 #pragma unroll
         for (int i = 0; i < V; ++i) {
             const int j = lane * 8 + i * 256;
             if (j < D) {
-                float g[8], f[8], gm[8];
+                float g[8], f[8], gm[8], pg[8], pb[8];
                 unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
                 unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
-                ld8f(gamma + j, gm);
+                ld8f(sgamma + j, gm);
+                ld8f(mine + j, pg);
+                ld8f(mine + W2 + j, pb);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const float xh = (f[k] - mu) * rs;
                     const float gg = g[k] * gm[k];
                     a += gg; b = fmaf(gg, xh, b);
-                    pg[i][k] = fmaf(g[k], xh, pg[i][k]);
-                    pb[i][k] += g[k];
+                    pg[k] = fmaf(g[k], xh, pg[k]);
+                    pb[k] += g[k];
                 }
+                *reinterpret_cast<float4*>(mine + j) = make_float4(pg[0], pg[1], pg[2], pg[3]);
+                *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[4], pg[5], pg[6], pg[7]);
+                *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[0], pb[1], pb[2], pb[3]);
+                *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[4], pb[5], pb[6], pb[7]);
             }
         }
         a = warp_sum(a) * inv_d; b = warp_sum(b) * inv_d;
@@ -641,34 +673,18 @@ __global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat
         for (int i = 0; i < V; ++i) {
             const int j = lane * 8 + i * 256;
             if (j < D) {
-                float g[8], f[8], gm[8], o[8];
+                float g[8], f[8], gm[8], o[8], adf[8];
                 unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
                 unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
-                ld8f(gamma + j, gm);
+                ld8f(sgamma + j, gm);
+                unpack8(ad[i], adf);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) o[k] = rs * (g[k] * gm[k] - a - (f[k] - mu) * rs * b);
-                if (add_in != nullptr) {
-                    float ad[8];
-                    unpack8(*reinterpret_cast<const uint4*>(add_in + row * D + j), ad);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) o[k] += ad[k];
-                }
+                for (int k = 0; k < 8; ++k) o[k] = rs * (g[k] * gm[k] - a - (f[k] - mu) * rs * b) + adf[k];
                 *reinterpret_cast<uint4*>(dx + row * D + j) = pack8(o);
             }
         }
     }
-    // fold the block's warps: warp w writes its partials to sm[w], then every thread sums a few columns over the warps and
-    // issues one global atomic per column (the former version did 2 x 8 x V shared-memory atomics per thread, 8-way contended)
-    constexpr int W2 = V * 256;
-    float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
-#pragma unroll
-    for (int i = 0; i < V; ++i) {
-        const int j = lane * 8 + i * 256;
-        *reinterpret_cast<float4*>(mine + j) = make_float4(pg[i][0], pg[i][1], pg[i][2], pg[i][3]);
-        *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
-        *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
-        *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
-    }
+    // fold the block's warps: every thread sums a few columns over the warps and issues one global atomic per column
     __syncthreads();
     for (int j = threadIdx.x; j < D; j += blockDim.x) {
         float a = 0.f, b = 0.f;
@@ -1053,8 +1069,8 @@ extern "C" int picd_add_layernorm_fwd(const void* x, const void* res, const floa
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
     PICD_REQUIRE((res == nullptr) == (sum_out == nullptr), "add_layernorm: res and sum_out go together");
     const int V = (D + 255) / 256;
-    long long blocks = std::min<long long>((M + 15) / 16, 8LL * num_sms());
-    if (blocks < 1) blocks = 1;
+    long long blocks = std::min<long long>((M + 15) / 16, 3LL * num_sms());     // resident blocks only: the parameter staging
+    if (blocks < 1) blocks = 1;                                                 // is paid once per block
 #define PICD_LN_FWD(VV)                                                                                              \
     PICD_CUDA(launch_pdl<PDL_ROWWISE>(layernorm_fwd_kernel<VV>, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st,            \
                          static_cast<const bf16*>(x), gamma, beta, static_cast<bf16*>(y), mean, rstd, M, D, eps,     \
@@ -1074,18 +1090,19 @@ extern "C" int picd_layernorm_bwd_add(const void* dy, const void* x, const float
                                       cudaStream_t st) {
     PICD_REQUIRE(D % 8 == 0 && D <= 256 * LN_MAX_VECS, "layernorm: D=%d must be a multiple of 8 and <= 1024", D);
     static bool attr_set = false;
-    if (!attr_set) {       // V = 4 parks 8 warps x 2 x 1024 floats = 64 KB
-        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    if (!attr_set) {       // V = 4 parks 8 warps x 2 x 1024 floats + gamma = 68 KB
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
+        PICD_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
         attr_set = true;
     }
-    long long blocks = 2LL * num_sms();
+    long long blocks = 3LL * num_sms();
     long long rpb = (M + blocks - 1) / blocks;
     if (rpb < 16) rpb = 16;
     blocks = (M + rpb - 1) / rpb;
     const int V = (D + 255) / 256;
 #define PICD_LN_BWD(VV)                                                                                                   \
     PICD_CUDA(launch_pdl<PDL_ROWWISE>(layernorm_bwd_kernel<VV>, dim3(static_cast<unsigned>(blocks)), dim3(256),                         \
-        8 * 2 * VV * 256 * sizeof(float), st,                                                                             \
+        (8 * 2 + 1) * VV * 256 * sizeof(float), st,                                                                             \
         static_cast<const bf16*>(dy), static_cast<const bf16*>(x), gamma, mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, \
         M, D, static_cast<int>(rpb), static_cast<const bf16*>(add_in)))
     if (V == 1) PICD_LN_BWD(1); else if (V == 2) PICD_LN_BWD(2); else if (V == 3) PICD_LN_BWD(3); else PICD_LN_BWD(4);
