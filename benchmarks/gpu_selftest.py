@@ -186,6 +186,9 @@ def group_basic():
     y.backward(torch.ones_like(y))
     ok &= check("gap.fwd", y, x.float().mean((2, 3)), 1e-2, g)
     ok &= check("gap.bwd", xn.grad, torch.full_like(x, 1 / 49.0), 1e-2, g)
+    for (N, C, H, W) in [(3, 144, 40, 40), (2, 32, 75, 75), (5, 8, 33, 31)]:       # pixel-split variant (few samples x channels)
+        x = (torch.randn(N, C, H, W, device=dev) + 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        ok &= check(f"gap_split[{N},{C},{H},{W}].fwd", native.global_avg_pool(x), x.float().mean((2, 3)), 1e-2, g)
 
     # cross entropy
     lg = torch.randn(37, 7, device=dev, requires_grad=True)
@@ -278,6 +281,23 @@ def group_basic():
         ok &= check(f"fused_update[{kind}].weight", lin.weight, refm.weight, 1e-4, g)
         ok &= check(f"fused_update[{kind}].shadow", lin.weight._shadow, refm.weight, 1e-2, g)
         ok &= emit_ok({"group": g, "test": f"fused_update[{kind}].grad_zeroed", "ok": bool(dp.arena.grad.abs().max().item() == 0)})
+    # squeeze-excite gate (+ stochastic-depth mask): out = x * s[n, c] * m[n]
+    for (N, C, H, W, masked) in [(4, 144, 19, 19, False), (3, 32, 75, 75, True), (5, 1392, 10, 10, True), (2, 8, 7, 9, False)]:
+        torch.manual_seed(N + C)
+        x = torch.randn(N, C, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        sg = torch.rand(N, C, device=dev).to(torch.bfloat16)
+        m = ((torch.rand(N, device=dev) < 0.7).float() / 0.7) if masked else None
+        xn, sn = x.clone().requires_grad_(), sg.clone().requires_grad_()
+        out = ops.channel_scale(xn, sn, m)
+        dy = torch.randn_like(out)
+        out.backward(dy)
+        xr, sr = x.float().requires_grad_(), sg.float().requires_grad_()
+        outr = xr * sr[:, :, None, None] * (1.0 if m is None else m.view(-1, 1, 1, 1))
+        outr.backward(dy.float())
+        tag = f"channel_scale[{N},{C},{H},{W},mask={masked}]"
+        ok &= check(tag + ".fwd", out, outr, 1e-2, g)
+        ok &= check(tag + ".dx", xn.grad, xr.grad, 1e-2, g)
+        ok &= check(tag + ".ds", sn.grad, sr.grad, 1.5e-2, g)
     return ok
 
 

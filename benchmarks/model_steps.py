@@ -17,8 +17,11 @@ from picd_b200.parallel.engine import FusedDataParallel, OptimizerSpec  # noqa: 
 
 dev = torch.device("cuda")
 out = []
+ONLY = set(sys.argv[1:])        # optional: model names to run
 for name, batch, size, opt in [("resnet18", 256, 224, "sgd"), ("resnet50", 256, 224, "sgd"), ("resnet101", 128, 224, "sgd"),
                                ("inceptionv3", 128, 299, "adam"), ("efficientnet-b3", 64, 300, "sgd"), ("vit_b_16", 128, 224, "adamw")]:
+    if ONLY and name not in ONLY:
+        continue
     try:
         torch.manual_seed(0)
         m = Classifier(name, 7, image_size=size).to(dev)

@@ -255,6 +255,53 @@ __global__ void __launch_bounds__(256) gap_fwd_kernel(const __nv_bfloat16* __res
     }
 }
 
+// Few samples x few channels over many pixels (EfficientNet's early squeeze-excite layers: 64 x 144 channels over 150 x 150): the
+// kernel above would run on N * ceil(C / 256) blocks only.  Here the pixels of a sample are split over blockIdx.z as well; partial
+// sums meet in an fp32 scratch [N, C] (zeroed by the caller), gap_finish_kernel scales and rounds.
+__global__ void __launch_bounds__(256) gap_fwd_part_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ acc_out, int HW, int C,
+                                                           int rows_per_block) {
+    pdl_sync();
+    const int vecs = C >> 3;
+    const int n = blockIdx.y;
+    const int tx_count = vecs < 32 ? vecs : 32;
+    const int ty_count = 256 / tx_count;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    __shared__ float red[256 * 8];
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (ty < ty_count && cv < vecs) {
+        const int p0 = blockIdx.z * rows_per_block;
+        const int p1 = min(p0 + rows_per_block, HW);
+        for (int p = p0 + ty; p < p1; p += 2 * ty_count) {          // two rows in flight
+            const __nv_bfloat16* src = x + (static_cast<long long>(n) * HW + p) * C + cv * 8;
+            const uint4 a = *reinterpret_cast<const uint4*>(src);
+            const bool two = p + ty_count < p1;
+            const uint4 b = two ? *reinterpret_cast<const uint4*>(src + static_cast<long long>(ty_count) * C) : make_uint4(0, 0, 0, 0);
+            float f[8], g[8];
+            unpack8(a, f); unpack8(b, g);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += f[k] + g[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) red[threadIdx.x * 8 + k] = acc[k];
+    __syncthreads();
+    if (ty == 0 && cv < vecs) {
+        float t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] += red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(acc_out + static_cast<long long>(n) * C + cv * 8 + k, t[k]);
+    }
+}
+__global__ void __launch_bounds__(256) gap_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, int total,
+                                                         float inv) {
+    pdl_sync();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < total) out[i] = __float2bfloat16(acc[i] * inv);
+}
+
 __global__ void __launch_bounds__(256) gap_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
                                                       long long total_vecs, int HW, int C) {
     const int vecs = C >> 3;
@@ -268,6 +315,84 @@ __global__ void __launch_bounds__(256) gap_bwd_kernel(const __nv_bfloat16* __res
 #pragma unroll
         for (int k = 0; k < 8; ++k) g[k] *= inv;
         *reinterpret_cast<uint4*>(dx + i * 8) = pack8(g);
+    }
+}
+
+// ------------------------------------------------------------------------------------ per-(sample, channel) scaling
+// out[n, p, c] = x[n, p, c] * s[n, c] * m[n]: the squeeze-excite gate of the MBConv blocks (reference: nn/classifier.py ->
+// efficientnet_pytorch `x = torch.sigmoid(x_squeezed) * x`) with the stochastic-depth sample mask m (nullable) folded in.
+// Backward in ONE pass over (dy, x): dx = dy * s * m and ds[n, c] += m * sum_p dy * x (fp32 atomics; a block owns one sample,
+// <= 32 channel vectors and one chunk of the pixels).
+__global__ void __launch_bounds__(256) channel_scale_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ s,
+                                                                const float* __restrict__ m, __nv_bfloat16* __restrict__ out,
+                                                                long long total_vecs, int HW, int C) {
+    pdl_sync();
+    const int vecs = C >> 3;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total_vecs; i += step) {
+        const int cv = static_cast<int>(i % vecs);
+        const long long n = i / (static_cast<long long>(vecs) * HW);
+        float f[8], g[8];
+        unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+        unpack8(*reinterpret_cast<const uint4*>(s + n * C + cv * 8), g);
+        const float mk = m != nullptr ? m[n] : 1.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] *= g[k] * mk;
+        *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
+    }
+}
+
+__global__ void __launch_bounds__(256) channel_scale_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                                const __nv_bfloat16* __restrict__ s, const float* __restrict__ m,
+                                                                __nv_bfloat16* __restrict__ dx, float* __restrict__ ds, int HW, int C,
+                                                                int rows_per_block) {
+    pdl_sync();
+    const int vecs = C >> 3;
+    const int n = blockIdx.y;
+    const int tx_count = vecs < 32 ? vecs : 32;
+    const int ty_count = 256 / tx_count;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    __shared__ float red[256 * 8];
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const float mk = m != nullptr ? m[n] : 1.f;
+    if (ty < ty_count && cv < vecs) {
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(s + static_cast<long long>(n) * C + cv * 8), g);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= mk;
+        const int p0 = blockIdx.z * rows_per_block;
+        const int p1 = min(p0 + rows_per_block, HW);
+        for (int p = p0 + ty; p < p1; p += 2 * ty_count) {          // two rows in flight
+            const long long o0 = (static_cast<long long>(n) * HW + p) * C + cv * 8;
+            const bool two = p + ty_count < p1;
+            const long long o1 = o0 + static_cast<long long>(ty_count) * C;
+            const uint4 d0 = *reinterpret_cast<const uint4*>(dy + o0), x0 = *reinterpret_cast<const uint4*>(x + o0);
+            uint4 d1 = make_uint4(0, 0, 0, 0), x1 = make_uint4(0, 0, 0, 0);
+            if (two) { d1 = *reinterpret_cast<const uint4*>(dy + o1); x1 = *reinterpret_cast<const uint4*>(x + o1); }
+            float a[8], b[8], o[8];
+            unpack8(d0, a); unpack8(x0, b);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { acc[k] = fmaf(a[k], b[k], acc[k]); o[k] = a[k] * g[k]; }
+            *reinterpret_cast<uint4*>(dx + o0) = pack8(o);
+            if (two) {
+                unpack8(d1, a); unpack8(x1, b);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { acc[k] = fmaf(a[k], b[k], acc[k]); o[k] = a[k] * g[k]; }
+                *reinterpret_cast<uint4*>(dx + o1) = pack8(o);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) red[threadIdx.x * 8 + k] = acc[k];
+    __syncthreads();
+    if (ty == 0 && cv < vecs) {
+        float t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] += red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(ds + static_cast<long long>(n) * C + cv * 8 + k, t[k] * mk);
     }
 }
 
@@ -730,12 +855,19 @@ __global__ void __launch_bounds__(256) small_linear_dpre_kernel(const void* __re
 }
 __global__ void __launch_bounds__(256) small_linear_dx_kernel(const float* __restrict__ dpre, const float* __restrict__ w,
                                                               __nv_bfloat16* __restrict__ dx, int M, int N, int K) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= M * K) return;
-    const int m = i / K, k = i % K;
+    // eight lanes share one output element and split the reduction over n (squeeze-excite layers: M * K is a few thousand
+    // outputs over N up to ~1400 -- one thread per output was a 1400-step dependent chain on 15 blocks)
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = t >> 3, sub = t & 7;
+    const bool live = i < M * K;
+    const int m = live ? i / K : 0, k = live ? i % K : 0;
     float acc = 0.f;
-    for (int n = 0; n < N; ++n) acc += dpre[m * N + n] * w[static_cast<long long>(n) * K + k];
-    dx[i] = __float2bfloat16(acc);
+    if (live)
+        for (int n = sub; n < N; n += 8) acc = fmaf(dpre[m * N + n], w[static_cast<long long>(n) * K + k], acc);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (live && sub == 0) dx[i] = __float2bfloat16(acc);
 }
 __global__ void __launch_bounds__(256) small_linear_dw_kernel(const float* __restrict__ dpre, const __nv_bfloat16* __restrict__ x,
                                                               float* __restrict__ dw, float* __restrict__ db, int M, int N,
@@ -965,9 +1097,57 @@ extern "C" int picd_gap_fwd(const void* x, void* out, int N, int HW, int C, cuda
     PICD_LAUNCH_CHECK();
     return 0;
 }
+// Same result as picd_gap_fwd with the pixels of a sample split over blocks; scratch = fp32 [N, C], ZEROED by the caller.
+// Returns through `use_split` semantics on the Python side: worth it when N * ceil(C / 256) blocks would leave SMs idle.
+extern "C" int picd_gap_fwd_split(const void* x, float* scratch, void* out, int N, int HW, int C, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "gap_fwd: C=%d must be a multiple of 8", C);
+    const int vecs = C / 8;
+    const int tx_count = vecs < 32 ? vecs : 32;
+    const int ty_count = 256 / tx_count;
+    const int xblocks = (vecs + tx_count - 1) / tx_count;
+    int z = std::max(1, (4 * num_sms() + N * xblocks - 1) / (N * xblocks));
+    z = std::min(z, std::max(1, HW / (2 * ty_count)));
+    const int rpb = (HW + z - 1) / z;
+    z = (HW + rpb - 1) / rpb;
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(gap_fwd_part_kernel, dim3(xblocks, N, z), dim3(256), 0, st, static_cast<const bf16*>(x), scratch, HW,
+                                      C, rpb));
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(gap_finish_kernel, dim3((N * C + 255) / 256), dim3(256), 0, st, static_cast<const float*>(scratch),
+                                      static_cast<bf16*>(out), N * C, 1.f / HW));
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
 extern "C" int picd_gap_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t st) {
     const long long total = 1LL * N * HW * (C / 8);
     gap_bwd_kernel<<<grid_for(total), 256, 0, st>>>(static_cast<const bf16*>(dy), static_cast<bf16*>(dx), total, HW, C);
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+
+// out = x * s[n, c] * m[n] (x, out [N, HW, C] bf16; s [N, C] bf16; m [N] fp32 or null)
+extern "C" int picd_channel_scale_fwd(const void* x, const void* s, const float* m, void* out, int N, int HW, int C, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "channel_scale: C=%d must be a multiple of 8", C);
+    const long long total = static_cast<long long>(N) * HW * (C / 8);
+    const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 16LL * num_sms()));
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(channel_scale_fwd_kernel, dim3(blocks), dim3(256), 0, st, static_cast<const bf16*>(x),
+                                      static_cast<const bf16*>(s), m, static_cast<bf16*>(out), total, HW, C));
+    PICD_LAUNCH_CHECK();
+    return 0;
+}
+// dx = dy * s * m;  ds[n, c] += m[n] * sum_p dy * x   (ds fp32 [N, C], zeroed by the caller)
+extern "C" int picd_channel_scale_bwd(const void* dy, const void* x, const void* s, const float* m, void* dx, float* ds, int N,
+                                      int HW, int C, cudaStream_t st) {
+    PICD_REQUIRE(C % 8 == 0, "channel_scale: C=%d must be a multiple of 8", C);
+    const int vecs = C / 8;
+    const int tx_count = vecs < 32 ? vecs : 32;
+    const int ty_count = 256 / tx_count;
+    const int xblocks = (vecs + tx_count - 1) / tx_count;
+    // enough blocks to fill the GPU: split the pixels of a sample when N * channel slabs alone are too few
+    int z = std::max(1, (4 * num_sms() + N * xblocks - 1) / (N * xblocks));
+    z = std::min(z, std::max(1, HW / (2 * ty_count)));
+    const int rpb = (HW + z - 1) / z;
+    z = (HW + rpb - 1) / rpb;
+    PICD_CUDA(launch_pdl<PDL_ROWWISE>(channel_scale_bwd_kernel, dim3(xblocks, N, z), dim3(256), 0, st, static_cast<const bf16*>(dy),
+                                      static_cast<const bf16*>(x), static_cast<const bf16*>(s), m, static_cast<bf16*>(dx), ds, HW, C, rpb));
     PICD_LAUNCH_CHECK();
     return 0;
 }
@@ -1127,7 +1307,7 @@ extern "C" int picd_small_linear_bwd(const void* dy, const void* y, const void* 
                                      cudaStream_t st) {
     small_linear_dpre_kernel<<<(M * N + 255) / 256, 256, 0, st>>>(dy, y, dpre_scratch, M * N, act, dy_fp32, y_fp32);
     if (dx != nullptr)
-        small_linear_dx_kernel<<<(M * K + 255) / 256, 256, 0, st>>>(dpre_scratch, w, static_cast<bf16*>(dx), M, N, K);
+        small_linear_dx_kernel<<<(M * K * 8 + 255) / 256, 256, 0, st>>>(dpre_scratch, w, static_cast<bf16*>(dx), M, N, K);
     const int work = N * K > N ? N * K : N;
     small_linear_dw_kernel<<<(work + 255) / 256, 256, 0, st>>>(dpre_scratch, static_cast<const bf16*>(x), dw, db, M, N, K);
     PICD_LAUNCH_CHECK();
@@ -1261,7 +1441,7 @@ extern "C" int picd_small_linear_bwd_noalloc(const void* dy, const void* y, cons
     if (int rc = small_linear_noalloc_scratch(&scratch)) return rc;
     small_linear_dpre_kernel<<<(M * N + 255) / 256, 256, 0, st>>>(dy, y, scratch, M * N, act, dy_fp32, y_fp32);
     if (dx != nullptr)
-        small_linear_dx_kernel<<<(M * K + 255) / 256, 256, 0, st>>>(scratch, w, static_cast<bf16*>(dx), M, N, K);
+        small_linear_dx_kernel<<<(M * K * 8 + 255) / 256, 256, 0, st>>>(scratch, w, static_cast<bf16*>(dx), M, N, K);
     const int work = N * K > N ? N * K : N;
     small_linear_dw_kernel<<<(work + 255) / 256, 256, 0, st>>>(scratch, static_cast<const bf16*>(x), dw, db, M, N, K);
     PICD_LAUNCH_CHECK();

@@ -132,7 +132,13 @@ int picd_pool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, i
 int picd_pool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W, int C, int OH, int OW, int kh,
                   int kw, int stride, int pad, int mode, cudaStream_t stream);
 int picd_gap_fwd(const void* x, void* out, int N, int HW, int C, cudaStream_t stream);
+/* picd_gap_fwd with the pixels of a sample split over blocks (few samples x channels, many pixels); scratch fp32 [N, C], zeroed */
+int picd_gap_fwd_split(const void* x, float* scratch, void* out, int N, int HW, int C, cudaStream_t stream);
 int picd_gap_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);
+/* out = x * s[n, c] * m[n]  (squeeze-excite gate + stochastic-depth mask; m nullable); backward in one pass, ds fp32 zeroed by caller */
+int picd_channel_scale_fwd(const void* x, const void* s, const float* m, void* out, int N, int HW, int C, cudaStream_t stream);
+int picd_channel_scale_bwd(const void* dy, const void* x, const void* s, const float* m, void* dx, float* ds, int N, int HW, int C,
+                           cudaStream_t stream);
 /* class-weighted softmax cross-entropy (train.py:157-158): loss[0] and d loss/d logits in one launch */
 int picd_cross_entropy(const float* logits, const long long* labels, const float* weight, float* loss,
                        float* dlogits, int B, int nc, cudaStream_t stream);

@@ -90,14 +90,13 @@ class MBConv(nn.Module):
         s = ops.global_avg_pool(x)
         s = ops.linear(s, self._se_reduce.weight.flatten(1), self._se_reduce.bias, "swish")
         s = ops.linear(s, self._se_expand.weight.flatten(1), self._se_expand.bias, "sigmoid")
-        x = x * s.to(x.dtype)[:, :, None, None]
-        residual = None
+        residual, mask = None, None
         if self.skip:
             residual = inp
-            if self.training and self.drop_connect > 0:   # stochastic depth on the branch
+            if self.training and self.drop_connect > 0:   # stochastic depth on the branch: folded into the gate kernel
                 keep = 1.0 - self.drop_connect
-                mask = (torch.rand(x.shape[0], 1, 1, 1, device=x.device) < keep).to(x.dtype) / keep
-                x = x * mask
+                mask = (torch.rand(x.shape[0], device=x.device) < keep).float() / keep
+        x = ops.channel_scale(x, s, mask)
         return conv_bn_act(x, self._project_conv, self._bn2, None, residual=residual)
 
 

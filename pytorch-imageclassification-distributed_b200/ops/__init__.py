@@ -183,6 +183,18 @@ def avg_pool2d(x, kernel_size, stride, padding=0, count_include_pad=True, grad_f
     return ref.avg_pool2d(x, kernel_size, stride, padding, count_include_pad)
 
 
+def channel_scale(x, s, sample_mask=None):
+    """``x * s[:, :, None, None]`` (squeeze-excite gate, s = [N, C]) times an optional per-sample factor ``sample_mask`` [N]
+    (stochastic depth: mask / keep_prob).  Native path: one kernel forward, one backward (dx and the [N, C] gate gradient)."""
+    if use_native(x) and x.dim() == 4 and x.shape[1] % 8 == 0:
+        from . import native
+        return native.channel_scale(x, s, sample_mask)
+    out = x * s.to(x.dtype)[:, :, None, None]
+    if sample_mask is not None:
+        out = out * sample_mask.to(x.dtype).view(-1, 1, 1, 1)
+    return out
+
+
 def global_avg_pool(x):
     if use_native(x):
         from . import native

@@ -60,7 +60,10 @@ _SIG = {
     "picd_bn_relu_maxpool_bwd_apply": "ppppppp" + "pifp" + "pi" + "pp" + "p" + "iiiiii" + "p",
     "picd_pool_fwd": "ppp" + "i" * 11 + "p",
     "picd_pool_bwd": "ppp" + "i" * 11 + "p",
+    "picd_channel_scale_fwd": "ppppiiip",
+    "picd_channel_scale_bwd": "ppppppiiip",
     "picd_gap_fwd": "ppiiip",
+    "picd_gap_fwd_split": "pppiiip",
     "picd_gap_bwd": "ppiiip",
     "picd_cross_entropy": "pppppiip",
     "picd_act_fwd": "ppplii" + "p",
@@ -100,6 +103,18 @@ def _fn(name: str):
 
 def _p(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
+
+
+_sm_counts = {}
+
+
+def _sm_count(device) -> int:
+    d = torch.device(device)
+    idx = d.index if d.index is not None else torch.cuda.current_device()
+    n = _sm_counts.get(idx)
+    if n is None:
+        n = _sm_counts[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return n
 
 
 def _stream():
@@ -977,7 +992,11 @@ class _GlobalAvgPool(torch.autograd.Function):
         x = nhwc(x)
         N, C, H, W = x.shape
         out = torch.empty((N, C), dtype=torch.bfloat16, device=x.device)
-        call("picd_gap_fwd", x, out, N, H * W, C)
+        if N * ((C // 8 + 31) // 32) < 2 * _sm_count(x.device) and H * W >= 1024:
+            # few samples x channels over many pixels: split the pixels over blocks as well (fp32 scratch + finish kernel)
+            call("picd_gap_fwd_split", x, torch.zeros((N, C), dtype=torch.float32, device=x.device), out, N, H * W, C)
+        else:
+            call("picd_gap_fwd", x, out, N, H * W, C)
         ctx.geom = (N, C, H, W)
         return out
 
@@ -993,6 +1012,36 @@ def global_avg_pool(x):
     if x.shape[1] % 8 != 0:
         return ref.global_avg_pool(x)
     return _GlobalAvgPool.apply(x)
+
+
+class _ChannelScale(torch.autograd.Function):
+    """out = x * s[n, c] * m[n] (squeeze-excite gate, optional stochastic-depth sample mask); csrc/ops/misc.cu."""
+
+    @staticmethod
+    def forward(ctx, x, s, m):
+        x = nhwc(x)
+        N, C, H, W = x.shape
+        sb = s.to(torch.bfloat16).contiguous()
+        mf = None if m is None else m.float().contiguous()
+        out = empty_nhwc(N, C, H, W, x.device)
+        call("picd_channel_scale_fwd", x, sb, mf, out, N, H * W, C)
+        ctx.save_for_backward(x, sb, mf)
+        ctx.s_dtype = s.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, sb, mf = ctx.saved_tensors
+        N, C, H, W = x.shape
+        dy = nhwc(dy)
+        dx = empty_nhwc(N, C, H, W, x.device)
+        ds = torch.zeros((N, C), dtype=torch.float32, device=x.device)
+        call("picd_channel_scale_bwd", dy, x, sb, mf, dx, ds, N, H * W, C)
+        return dx, ds.to(ctx.s_dtype), None
+
+
+def channel_scale(x, s, sample_mask=None):
+    return _ChannelScale.apply(x, s, sample_mask)
 
 
 # --------------------------------------------------------------------------- loss
