@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     if (q0 >= p.S) return;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1);
+        mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1); mbar_init(&bars->mma2, 1);
         fence_mbar_init();
         tma_prefetch_desc(&p.qkv_map);
     }
@@ -109,12 +109,15 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     const int row_base = b * p.S;
 
     if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
-        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 5);
+        // two barriers: S = Q K^T starts as soon as Q and K (48 of the 80 KB) have landed; V (bars->mma2 doubles as its load
+        // barrier here) is only needed after the softmax
+        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 3);
         tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
         tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
         tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
-        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
+        mbar_arrive_expect_tx_warp(&bars->mma2, 16384 * 2);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->mma2, 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->mma2, 2 * HD + h * ATT_D, row_base + 128);
         mbar_wait(&bars->load, 0);
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
@@ -128,7 +131,9 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     mbar_wait(&bars->mma0, 0);
     tc_fence_after();
-    const int nchunks = (p.n_keys + 31) >> 5;
+    // a warp whose 32 query rows all lie beyond the sequence (second tile of S = 197: rows 96..127) skips both softmax passes:
+    // its P rows stay whatever the Q / K bytes were, which only reaches output rows that are never stored
+    const int nchunks = (q0 + (warp & 3) * 32 < p.S) ? (p.n_keys + 31) >> 5 : 0;
     float mx = -INFINITY;
     for (int g = half; g < nchunks; g += 2) {
         uint32_t v[32];
@@ -176,6 +181,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     __syncthreads();
     l = s_red[row] + s_red[128 + row];
     if (warp == 0) {      // whole warp, one elected lane issues (picd_common.cuh)
+        mbar_wait(&bars->mma2, 0);           // V has landed (long ago)
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
         const int ksteps = p.n_keys >> 4;
@@ -220,7 +226,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 // dQ = dS K lands in the same columns again.  256 TMEM columns and 98 KB of shared memory per CTA: two CTAs per SM hide
 // each other's latency chain.
 struct AttDqBars {
-    uint64_t load, mma0, mma1, mma2;
+    uint64_t load, mma0, mma1, mma2, load2;
     uint32_t tmem_base;
 };
 __device__ __forceinline__ void store_row_chunk32_bits(uint32_t tile_u32, int row, int col0, const uint32_t (&f)[32]) {
@@ -257,6 +263,7 @@ __global__ void __launch_bounds__(256, 2) attn_bwd_dq_kernel(const __grid_consta
 
     if (threadIdx.x == 0) {
         mbar_init(&bars->load, 1); mbar_init(&bars->mma0, 1); mbar_init(&bars->mma1, 1); mbar_init(&bars->mma2, 1);
+        mbar_init(&bars->load2, 1);
         fence_mbar_init();
         tma_prefetch_desc(&p.qkv_map); tma_prefetch_desc(&p.do_map);
     }
@@ -269,13 +276,15 @@ __global__ void __launch_bounds__(256, 2) attn_bwd_dq_kernel(const __grid_consta
     const int HD = p.H * ATT_D;
 
     if (warp == 0) {          // whole warp, one elected lane issues
-        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 6);
+        // two barriers: S = Q K^T starts when Q and K (48 of the 96 KB) have landed; dO and V are needed for dP only
+        mbar_arrive_expect_tx_warp(&bars->load, 16384 * 3);
         tma_load_2d_warp(sQ, &p.qkv_map, &bars->load, h * ATT_D, row_base + q0);
         tma_load_2d_warp(sK, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base);
         tma_load_2d_warp(sK + 16384, &p.qkv_map, &bars->load, HD + h * ATT_D, row_base + 128);
-        tma_load_2d_warp(sdO, &p.do_map, &bars->load, h * ATT_D, row_base + q0);
-        tma_load_2d_warp(sV, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base);
-        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load, 2 * HD + h * ATT_D, row_base + 128);
+        mbar_arrive_expect_tx_warp(&bars->load2, 16384 * 3);
+        tma_load_2d_warp(sdO, &p.do_map, &bars->load2, h * ATT_D, row_base + q0);
+        tma_load_2d_warp(sV, &p.qkv_map, &bars->load2, 2 * HD + h * ATT_D, row_base);
+        tma_load_2d_warp(sV + 16384, &p.qkv_map, &bars->load2, 2 * HD + h * ATT_D, row_base + 128);
         mbar_wait(&bars->load, 0);
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
@@ -303,7 +312,9 @@ __global__ void __launch_bounds__(256, 2) attn_bwd_dq_kernel(const __grid_consta
     }
     const float lse = qvalid ? p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + q] : 0.f;
     const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    const int nchunks = (p.n_keys + 31) >> 5;
+    // (a warp whose 32 query rows all lie beyond the sequence skips both phases: dQ rows do not depend on one another and
+    //  those rows are never stored)
+    const int nchunks = (q0 + (warp & 3) * 32 < p.S) ? (p.n_keys + 31) >> 5 : 0;
 
     // ---- phase 1: P = exp2(S * c - lse), packed to bf16 and kept in registers
     uint32_t pk[4][16];
@@ -334,6 +345,7 @@ __global__ void __launch_bounds__(256, 2) attn_bwd_dq_kernel(const __grid_consta
     tc_fence_before();
     __syncthreads();                     // every S column has been read: the dP MMA may overwrite them
     if (warp == 0) {
+        mbar_wait(&bars->load2, 0);      // dO and V have landed
         tc_fence_after();
         const uint32_t idesc = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
 #pragma unroll
