@@ -149,7 +149,7 @@ def group_basic():
     # depthwise convolution (EfficientNet), symmetric and TF-"same" asymmetric padding
     for (N, C, H, K, stride, pad) in [(2, 32, 17, 3, 1, (1, 1, 1, 1)), (2, 96, 16, 3, 2, (0, 0, 1, 1)), (2, 144, 15, 5, 2, (2, 2, 2, 2)),
                                       (3, 40, 9, 5, 1, (2, 2, 2, 2)), (2, 288, 19, 5, 2, (1, 1, 2, 2)), (2, 8, 33, 7, 1, (3, 3, 3, 3)),
-                                      (4, 528, 10, 3, 1, (1, 1, 1, 1))]:
+                                      (4, 528, 10, 3, 1, (1, 1, 1, 1)), (2, 48, 21, 5, 1, (1, 2, 3, 2)), (1, 16, 6, 3, 1, (0, 1, 2, 1))]:
         x = torch.randn(N, C, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         w = (torch.randn(C, 1, K, K, device=dev) / K).requires_grad_()
         xn = x.clone().requires_grad_()
@@ -781,10 +781,22 @@ def group_model():
         ct, kt = _min_cos(g0, g2)
         mean_cn = sum(float(torch.nn.functional.cosine_similarity(g1[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g1) / max(1, len(g2))
         mean_ct = sum(float(torch.nn.functional.cosine_similarity(g0[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g0) / max(1, len(g2))
-        good = (not missing) and mean_cn >= mean_ct - 0.05 and cn >= min(0.9, ct - 0.2)
+        # per parameter: wherever the LIBRARY bf16 path still finds the fp32 direction (cosine >= 0.5), the native path must be
+        # within 0.25 of it.  Parameters whose bf16 gradient is rounding noise for the library as well (the first blocks' BN biases:
+        # cosine around zero either way) carry no signal and made a plain minimum flip between runs.
+        cos = torch.nn.functional.cosine_similarity
+        worst_gap, worst_param = 0.0, None
+        for k in g2:
+            if k in g1 and k in g0:
+                c0 = float(cos(g0[k].flatten(), g2[k].flatten(), dim=0))
+                c1 = float(cos(g1[k].flatten(), g2[k].flatten(), dim=0))
+                if c0 >= 0.5 and c0 - c1 > worst_gap:
+                    worst_gap, worst_param = c0 - c1, k
+        good = (not missing) and mean_cn >= mean_ct - 0.05 and worst_gap <= 0.25
         emit({"group": g, "test": f"{name}.grads_vs_fp32", "native_min_cos": cn, "native_min_param": kn,
               "torch_bf16_min_cos": ct, "torch_bf16_min_param": kt, "native_mean_cos": mean_cn,
-              "torch_bf16_mean_cos": mean_ct, "missing": missing[:5], "ok": good})
+              "torch_bf16_mean_cos": mean_ct, "worst_gap_where_bf16_is_meaningful": worst_gap, "worst_gap_param": worst_param,
+              "missing": missing[:5], "ok": good})
         ok &= good
     return ok
 

@@ -316,6 +316,148 @@ __global__ void __launch_bounds__(256) dw_wgrad_rows_kernel(const __nv_bfloat16*
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Stride-1 STRIP kernels (every 3x3 / 5x5 stride-1 depthwise layer): a thread owns FOUR consecutive output pixels of a row for
+// its 8 channels.  Per filter row it loads the K + 3 input vectors those four outputs need ONCE (the row kernels above loaded
+// and unpacked K per output, 2.5x as many for K = 5) and all loads of a filter row are issued together.  dgrad is the same
+// kernel on dy with the filter flipped (kFlip) and the complementary padding.
+template <int K, bool kFlip>
+__global__ void __launch_bounds__(256, 2) dw_conv_strip_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wt,
+                                                               __nv_bfloat16* __restrict__ y, int NR, int H, int W, int C, int OH,
+                                                               int OW, int pad_t, int pad_l, int tx_count, int ty_count,
+                                                               int rows_per_block) {
+    extern __shared__ float dw_sw[];           // [K*K][tx_count*8]
+    const int vecs = C >> 3, cw = tx_count * 8;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    for (int i = threadIdx.x; i < K * K * cw; i += blockDim.x) {
+        const int tap = i / cw, c = blockIdx.x * cw + (i - tap * cw);
+        const int src_tap = kFlip ? (K * K - 1 - tap) : tap;
+        dw_sw[i] = c < C ? wt[static_cast<size_t>(src_tap) * C + c] : 0.f;
+    }
+    __syncthreads();
+    if (ty >= ty_count || cv >= vecs) return;
+    const float* swc = dw_sw + tx * 8;
+    const int row0 = blockIdx.y * rows_per_block;
+    const int nrows = min(rows_per_block, NR - row0);
+    const int nstrips = (OW + 3) >> 2;
+    for (int it = ty; it < nrows * nstrips; it += ty_count) {       // (row, strip) pairs of the block, flattened
+        const int lr = it / nstrips, st = it - lr * nstrips;
+        const int row = row0 + lr;
+        const int n = row / OH, oh = row - n * OH;
+        const int ow0 = st << 2;
+        const __nv_bfloat16* xn = x + static_cast<size_t>(n) * H * W * C + cv * 8;
+        float acc[4][8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[j][k] = 0.f;
+#pragma unroll
+        for (int r = 0; r < K; ++r) {
+            const int ih = oh - pad_t + r;
+            if (ih < 0 || ih >= H) continue;
+            const __nv_bfloat16* xr = xn + static_cast<size_t>(ih) * W * C;
+            uint4 raw[K + 3];
+#pragma unroll
+            for (int j = 0; j < K + 3; ++j) {
+                const int iw = ow0 - pad_l + j;
+                raw[j] = (iw >= 0 && iw < W) ? *reinterpret_cast<const uint4*>(xr + static_cast<size_t>(iw) * C) : make_uint4(0, 0, 0, 0);
+            }
+            float f[K + 3][8];
+#pragma unroll
+            for (int j = 0; j < K + 3; ++j) dw_unpack8(raw[j], f[j]);
+#pragma unroll
+            for (int q = 0; q < K; ++q) {
+                const float4 w0 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw);
+                const float4 w1 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw + 4);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    acc[j][0] = fmaf(f[j + q][0], w0.x, acc[j][0]); acc[j][1] = fmaf(f[j + q][1], w0.y, acc[j][1]);
+                    acc[j][2] = fmaf(f[j + q][2], w0.z, acc[j][2]); acc[j][3] = fmaf(f[j + q][3], w0.w, acc[j][3]);
+                    acc[j][4] = fmaf(f[j + q][4], w1.x, acc[j][4]); acc[j][5] = fmaf(f[j + q][5], w1.y, acc[j][5]);
+                    acc[j][6] = fmaf(f[j + q][6], w1.z, acc[j][6]); acc[j][7] = fmaf(f[j + q][7], w1.w, acc[j][7]);
+                }
+            }
+        }
+        __nv_bfloat16* yr = y + static_cast<size_t>(row) * OW * C + cv * 8;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (ow0 + j < OW) *reinterpret_cast<uint4*>(yr + static_cast<size_t>(ow0 + j) * C) = dw_pack8(acc[j]);
+    }
+}
+
+// wgrad, stride 1: blockIdx.z = filter row r; a thread takes strips of four output pixels: 4 dy + (K + 3) x vectors feed
+// 4 * K * 8 FMAs (the row kernel: 1 + K vectors per K * 8 FMAs).
+template <int K>
+__global__ void __launch_bounds__(256, 2) dw_wgrad_strip_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                                                float* __restrict__ dwt, int NR, int H, int W, int C, int OH, int OW,
+                                                                int pad_t, int pad_l, int tx_count, int ty_count, int rows_per_block) {
+    extern __shared__ float dw_red[];          // [ty_count][tx_count][8]
+    const int vecs = C >> 3;
+    const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
+    const int cv = blockIdx.x * tx_count + tx;
+    const int r = blockIdx.z;
+    float acc[K][8];
+#pragma unroll
+    for (int q = 0; q < K; ++q)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[q][k] = 0.f;
+    const bool active = ty < ty_count && cv < vecs;
+    if (active) {
+        const int row0 = blockIdx.y * rows_per_block;
+        const int nrows = min(rows_per_block, NR - row0);
+        const int nstrips = (OW + 3) >> 2;
+        for (int it = ty; it < nrows * nstrips; it += ty_count) {
+            const int lr = it / nstrips, st = it - lr * nstrips;
+            const int row = row0 + lr;                                   // row = n * OH + oh
+            const int n = row / OH, oh = row - n * OH;
+            const int ih = oh - pad_t + r;
+            if (ih < 0 || ih >= H) continue;
+            const int ow0 = st << 2;
+            const __nv_bfloat16* xr = x + (static_cast<size_t>(n) * H + ih) * W * C + cv * 8;
+            const __nv_bfloat16* gr = dy + static_cast<size_t>(row) * OW * C + cv * 8;
+            uint4 graw[4], xraw[K + 3];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                graw[j] = (ow0 + j < OW) ? *reinterpret_cast<const uint4*>(gr + static_cast<size_t>(ow0 + j) * C) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int j = 0; j < K + 3; ++j) {
+                const int iw = ow0 - pad_l + j;
+                xraw[j] = (iw >= 0 && iw < W) ? *reinterpret_cast<const uint4*>(xr + static_cast<size_t>(iw) * C) : make_uint4(0, 0, 0, 0);
+            }
+            float f[K + 3][8];
+#pragma unroll
+            for (int j = 0; j < K + 3; ++j) dw_unpack8(xraw[j], f[j]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float g[8];
+                dw_unpack8(graw[j], g);
+#pragma unroll
+                for (int q = 0; q < K; ++q)
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[q][k] = fmaf(g[k], f[j + q][k], acc[q][k]);
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+        __syncthreads();
+        if (ty < ty_count) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dw_red[(ty * tx_count + tx) * 8 + k] = acc[q][k];
+        }
+        __syncthreads();
+        if (active && ty == 0) {
+            float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int yy = 0; yy < ty_count; ++yy)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += dw_red[(yy * tx_count + tx) * 8 + k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(dwt + static_cast<size_t>(r * K + q) * C + cv * 8 + k, s[k]);
+        }
+    }
+}
+
 struct DwShape { int tx, ty, gx, gy, rpb; };
 // thread block = tx channel vectors x ty pixel lanes; blockIdx.y strips of rows sized for ~`waves` blocks per SM
 static DwShape dw_shape(int C, int rows, int waves, int gz) {
@@ -348,6 +490,18 @@ using namespace picd;
 extern "C" int picd_depthwise_fprop(const void* x, const float* wt, void* y, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    static const bool strips = [] { const char* e = getenv("PICD_DW_STRIPS"); return e == nullptr || atoi(e) != 0; }();
+#define PICD_DW_FPROP_STRIP(KK)                                                                                        \
+    if (strips && K == KK && stride == 1) {                                                                              \
+        const DwShape d = dw_shape(C, N * OH, 8, 1);                                                                      \
+        dw_conv_strip_kernel<KK, false><<<dim3(d.gx, d.gy), 256, KK * KK * d.tx * 8 * sizeof(float), st>>>(                \
+            static_cast<const __nv_bfloat16*>(x), wt, static_cast<__nv_bfloat16*>(y), N * OH, H, W, C, OH, OW, pad_t, pad_l, \
+            d.tx, d.ty, d.rpb);                                                                                           \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_FPROP_STRIP(3) PICD_DW_FPROP_STRIP(5)
+#undef PICD_DW_FPROP_STRIP
 #define PICD_DW_FPROP(KK, SS)                                                                                          \
     if (K == KK && stride == SS) {                                                                                       \
         const DwShape d = dw_shape(C, N * OH, 8, 1);                                                                      \
@@ -368,6 +522,20 @@ extern "C" int picd_depthwise_fprop(const void* x, const float* wt, void* y, int
 extern "C" int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    static const bool strips = [] { const char* e = getenv("PICD_DW_STRIPS"); return e == nullptr || atoi(e) != 0; }();
+    // stride 1: dx = dy convolved with the flipped filter under the complementary padding; "input" of that convolution is dy
+    // [OH, OW], its output dx [H, W]
+#define PICD_DW_DGRAD_STRIP(KK)                                                                                        \
+    if (strips && K == KK && stride == 1) {                                                                              \
+        const DwShape d = dw_shape(C, N * H, 8, 1);                                                                       \
+        dw_conv_strip_kernel<KK, true><<<dim3(d.gx, d.gy), 256, KK * KK * d.tx * 8 * sizeof(float), st>>>(                 \
+            static_cast<const __nv_bfloat16*>(dy), wt, static_cast<__nv_bfloat16*>(dx), N * H, OH, OW, C, H, W,            \
+            KK - 1 - pad_t, KK - 1 - pad_l, d.tx, d.ty, d.rpb);                                                           \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_DGRAD_STRIP(3) PICD_DW_DGRAD_STRIP(5)
+#undef PICD_DW_DGRAD_STRIP
 #define PICD_DW_DGRAD(KK, SS)                                                                                          \
     if (K == KK && stride == SS) {                                                                                       \
         const DwShape d = dw_shape(C, N * H, 8, 1);                                                                       \
@@ -389,6 +557,18 @@ extern "C" int picd_depthwise_dgrad(const void* dy, const float* wt, void* dx, i
 extern "C" int picd_depthwise_wgrad(const void* x, const void* dy, float* dwt, int N, int H, int W, int C, int OH, int OW, int K,
                                     int stride, int pad_t, int pad_l, cudaStream_t st) {
     PICD_REQUIRE(C % 8 == 0, "depthwise: C=%d must be a multiple of 8", C);
+    static const bool strips = [] { const char* e = getenv("PICD_DW_STRIPS"); return e == nullptr || atoi(e) != 0; }();
+#define PICD_DW_WGRAD_STRIP(KK)                                                                                        \
+    if (strips && K == KK && stride == 1) {                                                                              \
+        const DwShape d = dw_shape(C, N * OH, 4, KK);                                                                     \
+        dw_wgrad_strip_kernel<KK><<<dim3(d.gx, d.gy, KK), 256, d.tx * d.ty * 8 * sizeof(float), st>>>(                     \
+            static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dwt, N * OH, H, W, C, OH, OW, pad_t,  \
+            pad_l, d.tx, d.ty, d.rpb);                                                                                    \
+        PICD_LAUNCH_CHECK();                                                                                              \
+        return 0;                                                                                                         \
+    }
+    PICD_DW_WGRAD_STRIP(3) PICD_DW_WGRAD_STRIP(5)
+#undef PICD_DW_WGRAD_STRIP
 #define PICD_DW_WGRAD(KK, SS)                                                                                          \
     if (K == KK && stride == SS) {                                                                                       \
         const DwShape d = dw_shape(C, N * OH, 4, KK);                                                                     \
