@@ -330,14 +330,17 @@ __global__ void __launch_bounds__(256, 2) dw_conv_strip_kernel(const __nv_bfloat
     const int vecs = C >> 3, cw = tx_count * 8;
     const int tx = threadIdx.x % tx_count, ty = threadIdx.x / tx_count;
     const int cv = blockIdx.x * tx_count + tx;
+    // shared weights as [tap][half][tx][4]: a thread's two float4 loads per tap then sit 16 bytes from its neighbour's (the
+    // [tap][tx][8] layout put them 32 bytes apart: a 2-way bank conflict on every load)
+    const int hw = cw >> 1;
     for (int i = threadIdx.x; i < K * K * cw; i += blockDim.x) {
-        const int tap = i / cw, c = blockIdx.x * cw + (i - tap * cw);
+        const int tap = i / cw, cl = i - tap * cw, c = blockIdx.x * cw + cl;
         const int src_tap = kFlip ? (K * K - 1 - tap) : tap;
-        dw_sw[i] = c < C ? wt[static_cast<size_t>(src_tap) * C + c] : 0.f;
+        dw_sw[tap * cw + ((cl >> 2) & 1) * hw + (cl >> 3) * 4 + (cl & 3)] = c < C ? wt[static_cast<size_t>(src_tap) * C + c] : 0.f;
     }
     __syncthreads();
     if (ty >= ty_count || cv >= vecs) return;
-    const float* swc = dw_sw + tx * 8;
+    const float* swc = dw_sw + tx * 4;
     const int row0 = blockIdx.y * rows_per_block;
     const int nrows = min(rows_per_block, NR - row0);
     const int nstrips = (OW + 3) >> 2;
@@ -369,7 +372,7 @@ __global__ void __launch_bounds__(256, 2) dw_conv_strip_kernel(const __nv_bfloat
 #pragma unroll
             for (int q = 0; q < K; ++q) {
                 const float4 w0 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw);
-                const float4 w1 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw + 4);
+                const float4 w1 = *reinterpret_cast<const float4*>(swc + (r * K + q) * cw + hw);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     acc[j][0] = fmaf(f[j + q][0], w0.x, acc[j][0]); acc[j][1] = fmaf(f[j + q][1], w0.y, acc[j][1]);

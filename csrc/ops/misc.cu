@@ -638,7 +638,20 @@ __device__ __forceinline__ void ld8f(const float* p, float (&o)[8]) {
     const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
     o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
 }
+// the same eight values in the permuted layout: halves 128 floats apart
+__device__ __forceinline__ void ld8f_split(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 128);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+__device__ __forceinline__ void st8f_split(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 128) = make_float4(v[4], v[5], v[6], v[7]);
+}
 constexpr int LN_MAX_VECS = 4;     // D <= 4 * 256
+// Shared-memory position of column j: a lane owns columns lane*8 .. lane*8+7 of every 256-column chunk and reads them as two
+// float4; stored in place those sit 32 bytes from the neighbour lane's (2-way bank conflict on every access).  The permutation
+// puts the first halves of all lanes side by side, then the second halves: [chunk][half][lane][4].
+__device__ __forceinline__ int ln_perm(int j) { return (j & ~255) | (((j >> 2) & 1) << 7) | (((j & 255) >> 3) << 2) | (j & 3); }
 // gamma / beta are staged in shared memory once per block and read back with 128-bit loads per row: as 2 x 8 x V registers
 // per thread they cost an SM its third and fourth resident block, and latency hiding is all these kernels need.
 template <int V>
@@ -652,8 +665,8 @@ __global__ void __launch_bounds__(256, 3) layernorm_fwd_kernel(const __nv_bfloat
     // which is also written to sum_out (the residual stream); one pass instead of an add kernel followed by this one
     __shared__ __align__(16) float sgb[2][V * 256];
     for (int j = threadIdx.x; j < V * 256; j += blockDim.x) {       // parameters do not depend on the previous kernel
-        sgb[0][j] = j < D ? gamma[j] : 0.f;
-        sgb[1][j] = j < D ? beta[j] : 0.f;
+        sgb[0][ln_perm(j)] = j < D ? gamma[j] : 0.f;
+        sgb[1][ln_perm(j)] = j < D ? beta[j] : 0.f;
     }
     __syncthreads();
     pdl_sync();
@@ -715,8 +728,8 @@ __global__ void __launch_bounds__(256, 3) layernorm_fwd_kernel(const __nv_bfloat
                 if (j < D) {
                     float f[8], gm[8], bt[8];
                     unpack8(raw[r][i], f);
-                    ld8f(&sgb[0][j], gm);
-                    ld8f(&sgb[1][j], bt);
+                    ld8f_split(&sgb[0][ln_perm(j)], gm);
+                    ld8f_split(&sgb[1][ln_perm(j)], bt);
 #pragma unroll
                     for (int k = 0; k < 8; ++k) f[k] = (f[k] - mean) * rstd * gm[k] + bt[k];
                     *reinterpret_cast<uint4*>(y + (row + r) * D + j) = pack8(f);
@@ -746,13 +759,13 @@ __global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     float* mine = sm + static_cast<size_t>(warp) * 2 * W2;
     float* sgamma = sm + static_cast<size_t>(nw) * 2 * W2;
-    for (int j = threadIdx.x; j < W2; j += blockDim.x) sgamma[j] = j < D ? gamma[j] : 0.f;
+    for (int j = threadIdx.x; j < W2; j += blockDim.x) sgamma[ln_perm(j)] = j < D ? gamma[j] : 0.f;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int j = lane * 8 + i * 256;
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        *reinterpret_cast<float4*>(mine + j) = z; *reinterpret_cast<float4*>(mine + j + 4) = z;
-        *reinterpret_cast<float4*>(mine + W2 + j) = z; *reinterpret_cast<float4*>(mine + W2 + j + 4) = z;
+        const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        st8f_split(mine + ln_perm(j), z);
+        st8f_split(mine + W2 + ln_perm(j), z);
     }
     __syncthreads();
     pdl_sync();
@@ -776,9 +789,9 @@ __global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat
                 float g[8], f[8], gm[8], pg[8], pb[8];
                 unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
                 unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
-                ld8f(sgamma + j, gm);
-                ld8f(mine + j, pg);
-                ld8f(mine + W2 + j, pb);
+                ld8f_split(sgamma + ln_perm(j), gm);
+                ld8f_split(mine + ln_perm(j), pg);
+                ld8f_split(mine + W2 + ln_perm(j), pb);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const float xh = (f[k] - mu) * rs;
@@ -787,10 +800,8 @@ __global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat
                     pg[k] = fmaf(g[k], xh, pg[k]);
                     pb[k] += g[k];
                 }
-                *reinterpret_cast<float4*>(mine + j) = make_float4(pg[0], pg[1], pg[2], pg[3]);
-                *reinterpret_cast<float4*>(mine + j + 4) = make_float4(pg[4], pg[5], pg[6], pg[7]);
-                *reinterpret_cast<float4*>(mine + W2 + j) = make_float4(pb[0], pb[1], pb[2], pb[3]);
-                *reinterpret_cast<float4*>(mine + W2 + j + 4) = make_float4(pb[4], pb[5], pb[6], pb[7]);
+                st8f_split(mine + ln_perm(j), pg);
+                st8f_split(mine + W2 + ln_perm(j), pb);
             }
         }
         a = warp_sum(a) * inv_d; b = warp_sum(b) * inv_d;
@@ -801,7 +812,7 @@ __global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat
                 float g[8], f[8], gm[8], o[8], adf[8];
                 unpack8(*reinterpret_cast<const uint4*>(dy + row * D + j), g);
                 unpack8(*reinterpret_cast<const uint4*>(x + row * D + j), f);
-                ld8f(sgamma + j, gm);
+                ld8f_split(sgamma + ln_perm(j), gm);
                 unpack8(ad[i], adf);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) o[k] = rs * (g[k] * gm[k] - a - (f[k] - mu) * rs * b) + adf[k];
@@ -813,9 +824,10 @@ __global__ void __launch_bounds__(256, 3) layernorm_bwd_kernel(const __nv_bfloat
     __syncthreads();
     for (int j = threadIdx.x; j < D; j += blockDim.x) {
         float a = 0.f, b = 0.f;
+        const int pj = ln_perm(j);
         for (int w = 0; w < nw; ++w) {
-            a += sm[static_cast<size_t>(w) * 2 * W2 + j];
-            b += sm[static_cast<size_t>(w) * 2 * W2 + W2 + j];
+            a += sm[static_cast<size_t>(w) * 2 * W2 + pj];
+            b += sm[static_cast<size_t>(w) * 2 * W2 + W2 + pj];
         }
         atomicAdd(dgamma + j, a);
         atomicAdd(dbeta + j, b);
