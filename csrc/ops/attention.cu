@@ -13,6 +13,7 @@
 #include "../common/picd_common.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace picd {
@@ -215,6 +216,209 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+// ------------------------------------------------------------------------------------------------ forward, pipelined
+// One PERSISTENT CTA per SM walks (batch, head, query tile) items: a TMA warp keeps the loads of the next two items in flight
+// (two Q | K | V buffers), an MMA warp issues S = Q K^T and O = P V for both, and TWO softmax teams of eight warps take
+// alternate items, each with its own shared-memory buffer, its own 256 TMEM columns and its own named barrier -- while one team
+// waits (for its scores, for its P V product) the other one runs its exponentials.  This is the overlap the one-item-per-CTA
+// kernel above gets from a second resident CTA, without that kernel's per-item set-up, TMEM allocation and exposed first load
+// (a third of its stall samples in ncu).
+struct AttPipeBars {
+    uint64_t qk_full[2], v_full[2], s_full[2], p_part[2][4], o_full[2], t_free[2];     // p_part: P columns [64 i, 64 i + 64) are written
+    uint32_t tmem_base;
+};
+constexpr int ATTP_TEAM_WARPS = 8;
+#ifndef ATTP_PART_CHUNKS
+#define ATTP_PART_CHUNKS 8          // 32-column chunks per P part: 2 = four parts of 64 columns, 4 = two of 128, 8 = one
+#endif
+constexpr int ATTP_PV_WARP = 2 + 2 * ATTP_TEAM_WARPS;            // the last warp issues the O = P V chain
+constexpr int ATTP_THREADS = 32 * (ATTP_PV_WARP + 1);
+constexpr int ATTP_HEADER = 8192;                // barriers (256 B) | row partials [team][max / sum][half][128] at +1024
+constexpr int ATTP_BUF = 65536 + 32768;          // P (over Q | K) + V
+
+__global__ void __launch_bounds__(ATTP_THREADS, 1) attn_fwd_pipe_kernel(const __grid_constant__ AttnParams p) {
+    extern __shared__ uint8_t att_raw[];
+    uint8_t* smem = att_align(att_raw);
+    AttPipeBars* bars = reinterpret_cast<AttPipeBars*>(smem);
+    const int warp = uniform_warp_id(), lane = threadIdx.x & 31;
+    const int n_tiles = (p.S + ATT_TILE - 1) / ATT_TILE;
+    const int total = p.B * p.H * n_tiles;
+    const int n_items = static_cast<int>(blockIdx.x) < total ? (total - static_cast<int>(blockIdx.x) + gridDim.x - 1) / gridDim.x : 0;
+    const int HD = p.H * ATT_D;
+
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&bars->qk_full[b], 1); mbar_init(&bars->v_full[b], 1); mbar_init(&bars->s_full[b], 1);
+            for (int i = 0; i < 4; ++i) mbar_init(&bars->p_part[b][i], 1);
+            mbar_init(&bars->o_full[b], 1); mbar_init(&bars->t_free[b], ATTP_TEAM_WARPS);
+        }
+        fence_mbar_init();
+        tma_prefetch_desc(&p.qkv_map);
+    }
+    if (warp == 1) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = uniform_u32(bars->tmem_base);
+    pdl_sync();
+
+    auto decode = [&](int k, int& bb, int& h, int& q0) {
+        const int it = blockIdx.x + k * gridDim.x;
+        const int mt = it % n_tiles, bh = it / n_tiles;
+        h = bh % p.H; bb = bh / p.H; q0 = mt * ATT_TILE;
+    };
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        for (int k = 0; k < n_items; ++k) {
+            const int b = k & 1;
+            int bb, h, q0;
+            decode(k, bb, h, q0);
+            const int row_base = bb * p.S;
+            uint8_t* buf = smem + ATTP_HEADER + b * ATTP_BUF;
+            if (k >= 2) mbar_wait(&bars->o_full[b], ((k >> 1) - 1) & 1);     // P V of item k - 2 has consumed this buffer
+            mbar_arrive_expect_tx_warp(&bars->qk_full[b], 16384 * 3);
+            tma_load_2d_warp(buf, &p.qkv_map, &bars->qk_full[b], h * ATT_D, row_base + q0);
+            tma_load_2d_warp(buf + 16384, &p.qkv_map, &bars->qk_full[b], HD + h * ATT_D, row_base);
+            tma_load_2d_warp(buf + 32768, &p.qkv_map, &bars->qk_full[b], HD + h * ATT_D, row_base + 128);
+            mbar_arrive_expect_tx_warp(&bars->v_full[b], 16384 * 2);
+            tma_load_2d_warp(buf + 65536, &p.qkv_map, &bars->v_full[b], 2 * HD + h * ATT_D, row_base);
+            tma_load_2d_warp(buf + 65536 + 16384, &p.qkv_map, &bars->v_full[b], 2 * HD + h * ATT_D, row_base + 128);
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer 1: S = Q K^T, item after item
+        // (two issuing warps, one per chain: a single in-order issuer let an S waiting for its operands hold up a ready P V and
+        //  vice versa; one warp polling both chains cost more issue slots than it saved)
+        const uint32_t idesc_s = make_idesc_bf16(ATT_TILE, p.n_keys, 0, 0);
+        for (int k = 0; k < n_items; ++k) {
+            const int b = k & 1;
+            const uint32_t buf = smem_u32(smem + ATTP_HEADER + b * ATTP_BUF);
+            mbar_wait(&bars->qk_full[b], (k >> 1) & 1);
+            if (k >= 2) mbar_wait(&bars->t_free[b], ((k >> 1) - 1) & 1);       // O of item k - 2 has left these TMEM columns
+            tc_fence_after();
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                umma_bf16_warp(tmem + b * 256, desc_kmajor(buf, j), desc_kmajor(buf + 16384, j), idesc_s, j != 0);
+            umma_commit_warp(&bars->s_full[b]);
+        }
+    } else if (warp == ATTP_PV_WARP) {
+        // ------------------------------------------------------------------ MMA issuer 2: O = P V
+        const uint32_t idesc_o = make_idesc_bf16(ATT_TILE, ATT_D, 0, 1);
+        const int ksteps = p.n_keys >> 4;
+        for (int k = 0; k < n_items; ++k) {
+            const int b = k & 1;
+            const uint32_t par = (k >> 1) & 1;
+            const uint32_t buf = smem_u32(smem + ATTP_HEADER + b * ATTP_BUF);
+            mbar_wait(&bars->v_full[b], par);
+            mbar_wait(&bars->p_part[b][0], par);
+            tc_fence_after();
+            for (int kk = 0; kk < ksteps; ++kk)           // O overwrites the first 64 columns of the item's own scores (read by now)
+                umma_bf16_warp(tmem + b * 256, desc_kmajor(buf, kk), desc_mnmajor(buf + 65536, kk), idesc_o, kk != 0);
+            umma_commit_warp(&bars->o_full[b]);
+        }
+    } else {
+        // ------------------------------------------------------------------ softmax + read-out: two teams of 8 warps
+        const int team = (warp - 2) >> 3;            // items k = team, team + 2, ... ; buffer / TMEM half b = team
+        const int half = ((warp - 2) >> 2) & 1;      // which half of the score columns (chunks half, half + 2, ...)
+        const int q = warp & 3;                      // TMEM lane quarter this warp may touch
+        const int row = q * 32 + lane;
+        const int b = team;
+        float* s_max = reinterpret_cast<float*>(smem + 1024) + team * 512;      // [half][128]
+        float* s_sum = s_max + 256;
+        const uint32_t t_row = tmem + b * 256 + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t sP_u32 = smem_u32(smem + ATTP_HEADER + b * ATTP_BUF);
+        const uint32_t bar_id = 1 + team;
+        for (int k = team; k < n_items; k += 2) {
+            int bb, h, q0;
+            decode(k, bb, h, q0);
+            const uint32_t par = (k >> 1) & 1;
+            // a warp whose 32 query rows all lie beyond the sequence skips both passes (its P rows only reach unstored rows)
+            const int nchunks = (q0 + q * 32 < p.S) ? (p.n_keys + 31) >> 5 : 0;
+            mbar_wait(&bars->s_full[b], par);
+            tc_fence_after();
+            float mx = -INFINITY;
+            for (int g = half; g < nchunks; g += 2) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + g * 32, v);
+                tmem_ld_wait();
+                if (g * 32 + 32 <= p.S) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (g * 32 + i < p.S) mx = fmaxf(mx, __uint_as_float(v[i]));
+                }
+            }
+            s_max[half * 128 + row] = mx;
+            named_barrier_sync(bar_id, 32 * ATTP_TEAM_WARPS);
+            mx = fmaxf(s_max[row], s_max[128 + row]);
+            const float m2 = mx * p.scale_log2e;
+            float l = 0.f;
+            const int nparts = (((p.n_keys + 31) >> 5) + ATTP_PART_CHUNKS - 1) / ATTP_PART_CHUNKS;
+            for (int i = 0; i < nparts; ++i) {                   // part i = ATTP_PART_CHUNKS chunks, split between the two halves
+              for (int g = ATTP_PART_CHUNKS * i + half; g < ATTP_PART_CHUNKS * (i + 1); g += 2) {
+                if (g < nchunks) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + g * 32, v);
+                    tmem_ld_wait();
+                    float f[32];
+                    if (g * 32 + 32 <= p.S) {
+#pragma unroll
+                        for (int ii = 0; ii < 32; ++ii) {
+                            f[ii] = fast_exp2(fmaf(__uint_as_float(v[ii]), p.scale_log2e, -m2));
+                            l += f[ii];
+                        }
+                    } else {
+#pragma unroll
+                        for (int ii = 0; ii < 32; ++ii) {
+                            f[ii] = (g * 32 + ii < p.S) ? fast_exp2(fmaf(__uint_as_float(v[ii]), p.scale_log2e, -m2)) : 0.f;
+                            l += f[ii];
+                        }
+                    }
+                    store_row_chunk32(sP_u32, row, g * 32, f);       // over Q / K: S = Q K^T has completed (s_full)
+                }
+              }
+                if (i == nparts - 1) s_sum[half * 128 + row] = l;
+                tc_fence_before();
+                fence_proxy_async_smem();
+                named_barrier_sync(bar_id, 32 * ATTP_TEAM_WARPS);     // this part of P is written, its S columns are read
+                if (((warp - 2) & 7) == 0 && lane == 0) mbar_arrive(&bars->p_part[b][i]);
+            }
+            l = s_sum[row] + s_sum[128 + row];
+            const int qq = q0 + row;
+            if (half == 0 && qq < p.S) p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + qq] = m2 + log2f(l);
+            // ---- read-out (the other team computes meanwhile)
+            mbar_wait(&bars->o_full[b], par);
+            tc_fence_after();
+            {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + half * 32, v);          // each half stores 32 of the 64 output columns
+                tmem_ld_wait();
+                if (qq < p.S) {
+                    const float inv_l = 1.f / l;
+                    uint4* dst = reinterpret_cast<uint4*>(p.o + static_cast<size_t>(bb * p.S + qq) * HD + h * ATT_D + half * 32);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        uint4 w;
+                        w.x = pack_bf16x2(__uint_as_float(v[8 * c + 0]) * inv_l, __uint_as_float(v[8 * c + 1]) * inv_l);
+                        w.y = pack_bf16x2(__uint_as_float(v[8 * c + 2]) * inv_l, __uint_as_float(v[8 * c + 3]) * inv_l);
+                        w.z = pack_bf16x2(__uint_as_float(v[8 * c + 4]) * inv_l, __uint_as_float(v[8 * c + 5]) * inv_l);
+                        w.w = pack_bf16x2(__uint_as_float(v[8 * c + 6]) * inv_l, __uint_as_float(v[8 * c + 7]) * inv_l);
+                        dst[c] = w;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->t_free[b]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------------ backward: dQ (+ delta)
@@ -602,10 +806,20 @@ extern "C" int picd_attention_fwd(const void* qkv, void* o, float* lse, int B, i
     p.o = static_cast<__nv_bfloat16*>(o);
     p.lse = lse;
     const int smem = 2048 + 65536 + 32768 + 1024;       // 99 KB: two CTAs per SM
+    const int smem_pipe = ATTP_HEADER + 2 * ATTP_BUF + 1024;
     static bool attr = false;
     if (!attr) {
         PICD_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        PICD_CUDA(cudaFuncSetAttribute(attn_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pipe));
         attr = true;
+    }
+    // default: the persistent two-team kernel (B256 S197 H12: 0.140 -> 0.124 ms; library SDPA 0.104); PICD_ATTN_PIPE=0 = one item per CTA
+    static const bool pipe = [] { const char* e = getenv("PICD_ATTN_PIPE"); return e == nullptr || atoi(e) != 0; }();
+    if (pipe) {
+        const int total = B * H * ((S + ATT_TILE - 1) / ATT_TILE);
+        PICD_CUDA(launch_pdl<PDL_ATTN>(attn_fwd_pipe_kernel, dim3(std::min(total, num_sms())), dim3(ATTP_THREADS), smem_pipe, stream, p));
+        PICD_LAUNCH_CHECK();
+        return 0;
     }
     PICD_CUDA(launch_pdl<PDL_ATTN>(attn_fwd_kernel, dim3(B * H * 2), dim3(256), smem, stream, p));
     PICD_LAUNCH_CHECK();
