@@ -565,6 +565,16 @@ def stem_checks():
         for k in ("dw", "dgamma", "dbeta", "rm", "rv"):
             ok &= check(tag + f".{k}", res["fused"][k], res["oracle"][k], 3e-2, g)
             ok &= check(tag + f".{k}.vs_unfused", res["fused"][k], res["unfused"][k], 1e-2, g)
+        # eval mode under no_grad (validation epochs): running statistics, the same single pass
+        from picd_b200.ops import native
+        rm = torch.randn(C, device=dev) * 0.1
+        rv = torch.rand(C, device=dev) + 0.5
+        with torch.no_grad():
+            kw = dict(stride=stride, padding=pad, training=False, momentum=0.1, eps=1e-5, sync_group=False)
+            ev_f = native.conv_bn_relu_maxpool(x, w0, g0, b0, rm.clone(), rv.clone(), **kw)
+            ev_u = native.pool2d(native.conv_bn_act(x, w0, g0, b0, rm.clone(), rv.clone(), act="relu", residual=None, **kw), 3, 2, 1,
+                                 mode="max")
+        ok &= emit_ok({"group": g, "test": tag + ".eval_identical_to_unfused", "ok": bool(torch.equal(ev_f, ev_u))})
         if res["fused"]["dx"] is not None:
             ok &= check_sparse(tag + ".dx", res["fused"]["dx"], res["oracle"]["dx"], 4e-2, g, max_bad_frac=2e-3)
             ok &= check(tag + ".dx.vs_unfused", res["fused"]["dx"], res["unfused"]["dx"], 1.5e-2, g)

@@ -156,3 +156,31 @@ def test_stem_op_cpu_equals_separate_ops():
     assert o1.shape == (2, 16, 9, 9)
     assert torch.allclose(o1, o2, atol=1e-5) and all(torch.allclose(a, c, atol=1e-4, rtol=1e-4) for a, c in zip(g1, g2))
     assert torch.allclose(rm1, rm2, atol=1e-6) and torch.allclose(rv1, rv2, atol=1e-6)
+
+
+def test_channel_scale_cpu_fallback_and_stem_eval_mode():
+    """ops.channel_scale on CPU == x * s[:, :, None, None] * mask (values and gradients); the stem op in eval mode uses the
+    running statistics like the separate ops."""
+    import torch
+    import torch.nn.functional as F
+    from picd_b200 import ops
+    torch.manual_seed(1)
+    x = torch.randn(3, 8, 5, 4, requires_grad=True)
+    s = torch.rand(3, 8, requires_grad=True)
+    m = torch.tensor([1.25, 0.0, 1.25])
+    out = ops.channel_scale(x, s, m)
+    out.sum().backward()
+    xr, sr = x.detach().clone().requires_grad_(), s.detach().clone().requires_grad_()
+    ref = xr * sr[:, :, None, None] * m.view(-1, 1, 1, 1)
+    ref.sum().backward()
+    assert torch.allclose(out, ref) and torch.allclose(x.grad, xr.grad) and torch.allclose(s.grad, sr.grad)
+    assert torch.equal(ops.channel_scale(x, s), x * s[:, :, None, None])
+    # stem, eval mode
+    w = torch.randn(16, 3, 7, 7) * 0.1
+    g, b = torch.rand(16) + 0.5, torch.randn(16) * 0.1
+    rm, rv = torch.randn(16) * 0.1, torch.rand(16) + 0.5
+    img = torch.randn(2, 3, 33, 33)
+    with torch.no_grad():
+        got = ops.conv_bn_relu_maxpool(img, w, g, b, rm.clone(), rv.clone(), stride=2, padding=3, training=False)
+        want = F.max_pool2d(F.relu(F.batch_norm(F.conv2d(img, w, None, 2, 3), rm, rv, g, b, False, 0.1, 1e-5)), 3, 2, 1)
+    assert torch.allclose(got, want, atol=1e-5)
