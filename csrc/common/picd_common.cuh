@@ -441,12 +441,20 @@ __device__ __forceinline__ float gelu_fwd(float x) {
     const float tail = gelu_tail(x, e);
     return fmaf(-fabsf(x), tail, fmaxf(x, 0.f));
 }
+// sigmoid from one ex2.approx and one rcp.approx (an IEEE division costs ~10 instructions; the saturating ends come out right:
+// ex2 -> inf gives rcp -> 0, ex2 -> 0 gives 1)
+__device__ __forceinline__ float fast_sigmoid(float x) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return r;
+}
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_RELU: return fmaxf(x, 0.f);
         case ACT_GELU: return gelu_fwd(x);
-        case ACT_SWISH: return x / (1.f + __expf(-x));
-        case ACT_SIGMOID: return 1.f / (1.f + __expf(-x));
+        case ACT_SWISH: return x * fast_sigmoid(x);
+        case ACT_SIGMOID: return fast_sigmoid(x);
         default: return x;
     }
 }
@@ -460,11 +468,11 @@ __device__ __forceinline__ float act_grad(float x, int act) {
             return fmaf(x * 0.3989422804014327f, e, c);
         }
         case ACT_SWISH: {
-            float s = 1.f / (1.f + __expf(-x));
-            return s * (1.f + x * (1.f - s));
+            const float s = fast_sigmoid(x);
+            return s * fmaf(x, 1.f - s, 1.f);
         }
         case ACT_SIGMOID: {
-            float s = 1.f / (1.f + __expf(-x));
+            const float s = fast_sigmoid(x);
             return s * (1.f - s);
         }
         default: return 1.f;
