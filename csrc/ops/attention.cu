@@ -220,19 +220,16 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 
 // ------------------------------------------------------------------------------------------------ forward, pipelined
 // One PERSISTENT CTA per SM walks (batch, head, query tile) items: a TMA warp keeps the loads of the next two items in flight
-// (two Q | K | V buffers), an MMA warp issues S = Q K^T and O = P V for both, and TWO softmax teams of eight warps take
+// (two Q | K | V buffers), one warp issues the S = Q K^T chain and another the O = P V chain, and TWO softmax teams of eight warps take
 // alternate items, each with its own shared-memory buffer, its own 256 TMEM columns and its own named barrier -- while one team
 // waits (for its scores, for its P V product) the other one runs its exponentials.  This is the overlap the one-item-per-CTA
 // kernel above gets from a second resident CTA, without that kernel's per-item set-up, TMEM allocation and exposed first load
 // (a third of its stall samples in ncu).
 struct AttPipeBars {
-    uint64_t qk_full[2], v_full[2], s_full[2], p_part[2][4], o_full[2], t_free[2];     // p_part: P columns [64 i, 64 i + 64) are written
+    uint64_t qk_full[2], v_full[2], s_full[2], p_full[2], o_full[2], t_free[2];
     uint32_t tmem_base;
 };
 constexpr int ATTP_TEAM_WARPS = 8;
-#ifndef ATTP_PART_CHUNKS
-#define ATTP_PART_CHUNKS 8          // 32-column chunks per P part: 2 = four parts of 64 columns, 4 = two of 128, 8 = one
-#endif
 constexpr int ATTP_PV_WARP = 2 + 2 * ATTP_TEAM_WARPS;            // the last warp issues the O = P V chain
 constexpr int ATTP_THREADS = 32 * (ATTP_PV_WARP + 1);
 constexpr int ATTP_HEADER = 8192;                // barriers (256 B) | row partials [team][max / sum][half][128] at +1024
@@ -251,8 +248,7 @@ __global__ void __launch_bounds__(ATTP_THREADS, 1) attn_fwd_pipe_kernel(const __
     if (threadIdx.x == 0) {
         for (int b = 0; b < 2; ++b) {
             mbar_init(&bars->qk_full[b], 1); mbar_init(&bars->v_full[b], 1); mbar_init(&bars->s_full[b], 1);
-            for (int i = 0; i < 4; ++i) mbar_init(&bars->p_part[b][i], 1);
-            mbar_init(&bars->o_full[b], 1); mbar_init(&bars->t_free[b], ATTP_TEAM_WARPS);
+            mbar_init(&bars->p_full[b], 1); mbar_init(&bars->o_full[b], 1); mbar_init(&bars->t_free[b], ATTP_TEAM_WARPS);
         }
         fence_mbar_init();
         tma_prefetch_desc(&p.qkv_map);
@@ -312,7 +308,7 @@ __global__ void __launch_bounds__(ATTP_THREADS, 1) attn_fwd_pipe_kernel(const __
             const uint32_t par = (k >> 1) & 1;
             const uint32_t buf = smem_u32(smem + ATTP_HEADER + b * ATTP_BUF);
             mbar_wait(&bars->v_full[b], par);
-            mbar_wait(&bars->p_part[b][0], par);
+            mbar_wait(&bars->p_full[b], par);
             tc_fence_after();
             for (int kk = 0; kk < ksteps; ++kk)           // O overwrites the first 64 columns of the item's own scores (read by now)
                 umma_bf16_warp(tmem + b * 256, desc_kmajor(buf, kk), desc_mnmajor(buf + 65536, kk), idesc_o, kk != 0);
@@ -357,36 +353,31 @@ __global__ void __launch_bounds__(ATTP_THREADS, 1) attn_fwd_pipe_kernel(const __
             mx = fmaxf(s_max[row], s_max[128 + row]);
             const float m2 = mx * p.scale_log2e;
             float l = 0.f;
-            const int nparts = (((p.n_keys + 31) >> 5) + ATTP_PART_CHUNKS - 1) / ATTP_PART_CHUNKS;
-            for (int i = 0; i < nparts; ++i) {                   // part i = ATTP_PART_CHUNKS chunks, split between the two halves
-              for (int g = ATTP_PART_CHUNKS * i + half; g < ATTP_PART_CHUNKS * (i + 1); g += 2) {
-                if (g < nchunks) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_row + g * 32, v);
-                    tmem_ld_wait();
-                    float f[32];
-                    if (g * 32 + 32 <= p.S) {
+            for (int g = half; g < nchunks; g += 2) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_row + g * 32, v);
+                tmem_ld_wait();
+                float f[32];
+                if (g * 32 + 32 <= p.S) {
 #pragma unroll
-                        for (int ii = 0; ii < 32; ++ii) {
-                            f[ii] = fast_exp2(fmaf(__uint_as_float(v[ii]), p.scale_log2e, -m2));
-                            l += f[ii];
-                        }
-                    } else {
-#pragma unroll
-                        for (int ii = 0; ii < 32; ++ii) {
-                            f[ii] = (g * 32 + ii < p.S) ? fast_exp2(fmaf(__uint_as_float(v[ii]), p.scale_log2e, -m2)) : 0.f;
-                            l += f[ii];
-                        }
+                    for (int i = 0; i < 32; ++i) {
+                        f[i] = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -m2));
+                        l += f[i];
                     }
-                    store_row_chunk32(sP_u32, row, g * 32, f);       // over Q / K: S = Q K^T has completed (s_full)
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        f[i] = (g * 32 + i < p.S) ? fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -m2)) : 0.f;
+                        l += f[i];
+                    }
                 }
-              }
-                if (i == nparts - 1) s_sum[half * 128 + row] = l;
-                tc_fence_before();
-                fence_proxy_async_smem();
-                named_barrier_sync(bar_id, 32 * ATTP_TEAM_WARPS);     // this part of P is written, its S columns are read
-                if (((warp - 2) & 7) == 0 && lane == 0) mbar_arrive(&bars->p_part[b][i]);
+                store_row_chunk32(sP_u32, row, g * 32, f);       // over Q / K: S = Q K^T has completed (s_full)
             }
+            s_sum[half * 128 + row] = l;
+            tc_fence_before();
+            fence_proxy_async_smem();
+            named_barrier_sync(bar_id, 32 * ATTP_TEAM_WARPS);     // every P chunk is written and every S column read
+            if (((warp - 2) & 7) == 0 && lane == 0) mbar_arrive(&bars->p_full[b]);
             l = s_sum[row] + s_sum[128 + row];
             const int qq = q0 + row;
             if (half == 0 && qq < p.S) p.lse[(static_cast<size_t>(bb) * p.H + h) * p.S + qq] = m2 + log2f(l);
