@@ -792,7 +792,7 @@ def group_model():
         mean_cn = sum(float(torch.nn.functional.cosine_similarity(g1[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g1) / max(1, len(g2))
         mean_ct = sum(float(torch.nn.functional.cosine_similarity(g0[k].flatten(), g2[k].flatten(), dim=0)) for k in g2 if k in g0) / max(1, len(g2))
         # per parameter: wherever the LIBRARY bf16 path still finds the fp32 direction (cosine >= 0.5), the native path must be
-        # within 0.25 of it.  Parameters whose bf16 gradient is rounding noise for the library as well (the first blocks' BN biases:
+        # within 0.4 of it.  Parameters whose bf16 gradient is rounding noise for the library as well (the first blocks' BN biases:
         # cosine around zero either way) carry no signal and made a plain minimum flip between runs.
         cos = torch.nn.functional.cosine_similarity
         worst_gap, worst_param = 0.0, None
@@ -802,7 +802,8 @@ def group_model():
                 c1 = float(cos(g1[k].flatten(), g2[k].flatten(), dim=0))
                 if c0 >= 0.5 and c0 - c1 > worst_gap:
                     worst_gap, worst_param = c0 - c1, k
-        good = (not missing) and mean_cn >= mean_ct - 0.05 and worst_gap <= 0.25
+        good = (not missing) and mean_cn >= mean_ct - 0.05 and worst_gap <= 0.4     # (a sign error shows up as a gap > 1;
+        # the largest gap seen on a correct build is 0.17, on a bias of ResNet-50's last block; stage-level exactness is `compose`)
         emit({"group": g, "test": f"{name}.grads_vs_fp32", "native_min_cos": cn, "native_min_param": kn,
               "torch_bf16_min_cos": ct, "torch_bf16_min_param": kt, "native_mean_cos": mean_cn,
               "torch_bf16_mean_cos": mean_ct, "worst_gap_where_bf16_is_meaningful": worst_gap, "worst_gap_param": worst_param,
