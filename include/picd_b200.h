@@ -132,6 +132,18 @@ int picd_pool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, i
 int picd_pool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W, int C, int OH, int OW, int kh,
                   int kw, int stride, int pad, int mode, cudaStream_t stream);
 int picd_gap_fwd(const void* x, void* out, int N, int HW, int C, cudaStream_t stream);
+/* ResNet / DenseNet stem: max_pool3x3/s2/p1(relu(y * scale + shift)) in one pass (argmax: one byte per output element, window tap
+ * 0..8), and its backward as two kernels that regenerate the pooled gradient per input pixel (the normalised activation and its
+ * gradient are never written).  sums = [STAT_REPLICAS][2C] fp32, zeroed by the caller; bwd_apply folds sums / param_sums in place. */
+int picd_bn_relu_maxpool_fwd(const void* y, const float* scale, const float* shift, void* out, void* argmax, int N, int H, int W,
+                             int C, int OH, int OW, cudaStream_t stream);
+int picd_bn_relu_maxpool_bwd_reduce(const void* dpool, const void* argmax, const void* y, const float* scale, const float* shift,
+                                    const float* mean, const float* invstd, float* sums, int N, int H, int W, int C, int OH, int OW,
+                                    cudaStream_t stream);
+int picd_bn_relu_maxpool_bwd_apply(const void* dpool, const void* argmax, const void* y, const float* scale, const float* shift,
+                                   const float* mean, const float* invstd, float* sums, int sums_replicas, float inv_count,
+                                   const float* count_dev, float* param_sums, int param_replicas, float* dgamma, float* dbeta,
+                                   void* dy, int N, int H, int W, int C, int OH, int OW, cudaStream_t stream);
 /* picd_gap_fwd with the pixels of a sample split over blocks (few samples x channels, many pixels); scratch fp32 [N, C], zeroed */
 int picd_gap_fwd_split(const void* x, float* scratch, void* out, int N, int HW, int C, cudaStream_t stream);
 int picd_gap_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);

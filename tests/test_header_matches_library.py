@@ -1,0 +1,37 @@
+"""Every entry point declared in include/picd_b200.h is exported by the built library and vice versa, and every ctypes signature the Python
+side binds (ops/native.py::_SIG) names an exported symbol (CPU-only: reads the ELF symbol table with nm)."""
+import os
+import re
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "pytorch-imageclassification-distributed_b200", "lib", "libpicd_b200.so")
+
+
+def _exported():
+    if not os.path.exists(LIB):
+        import build
+        build.build(force=False, verbose=False)
+    out = subprocess.run(["nm", "-D", "--defined-only", LIB], capture_output=True, text=True, check=True).stdout
+    return {line.split()[-1] for line in out.splitlines() if " T " in line}
+
+
+@pytest.mark.skipif(shutil.which("nm") is None or shutil.which("nvcc") is None, reason="needs nm and nvcc")
+def test_header_and_bindings_match_library():
+    exported = _exported()
+    header = open(os.path.join(ROOT, "include", "picd_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(picd_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) > 60
+    missing = sorted(d for d in declared if d not in exported)
+    assert not missing, f"declared in picd_b200.h but not exported: {missing}"
+    undeclared = sorted(e for e in exported if e.startswith("picd_") and e not in declared)
+    assert not undeclared, f"exported by the library but missing from picd_b200.h: {undeclared}"
+    import sys
+    sys.path.insert(0, ROOT)
+    from picd_b200.ops import native
+    unbound = sorted(n for n in native._SIG if n not in exported)
+    assert not unbound, f"bound in ops/native.py but not exported: {unbound}"
