@@ -35,3 +35,13 @@ def test_header_and_bindings_match_library():
     from picd_b200.ops import native
     unbound = sorted(n for n in native._SIG if n not in exported)
     assert not unbound, f"bound in ops/native.py but not exported: {unbound}"
+
+
+@pytest.mark.skipif(shutil.which("gcc") is None or not os.path.exists("/usr/local/cuda/include/cuda_runtime.h"),
+                    reason="needs gcc and the CUDA headers")
+def test_public_header_is_plain_c_and_cpp():
+    """Non-Python hosts link the same library: the header must parse as C and as C++."""
+    hdr = os.path.join(ROOT, "include", "picd_b200.h")
+    for lang, cc in (("c", "gcc"), ("c++", "g++")):
+        r = subprocess.run([cc, "-I/usr/local/cuda/include", "-x", lang, "-fsyntax-only", hdr], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
