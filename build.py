@@ -37,7 +37,7 @@ def headers():
 def _compile(src: str, obj: str, verbose: bool) -> None:
     cmd = [NVCC, *ARCH, *FLAGS, "-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
     if src.endswith(".cpp"):
-        cmd = [NVCC, "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-x", "c++", "-c", src, "-o", obj]
+        cmd = [NVCC, "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-x", "c++", "-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
     if verbose:
         print(" ".join(cmd), flush=True)
     subprocess.run(cmd, check=True)

@@ -11,6 +11,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "picd_b200.h"      // the public prototypes: every definition in this library is checked against them by the compiler
+
 namespace picd {
 
 // ------------------------------------------------------------------------------------ host

@@ -8,6 +8,8 @@
 // split a bucket into `world` slices of whole 16-byte vectors, which must work for 3, 5, 6 or 7 ranks as well.
 #include <cstdint>
 
+#include "picd_b200.h"      // the public prototype of picd_plan_buckets, checked against the definition below
+
 static inline int64_t round_up(int64_t n, int64_t a) { return a <= 1 ? n : (n + a - 1) / a * a; }
 
 extern "C" int picd_plan_buckets(const int64_t* padded_sizes, int n_params, int64_t first_bytes, int64_t cap_bytes,

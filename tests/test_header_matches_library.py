@@ -45,3 +45,40 @@ def test_public_header_is_plain_c_and_cpp():
     for lang, cc in (("c", "gcc"), ("c++", "g++")):
         r = subprocess.run([cc, "-I/usr/local/cuda/include", "-x", lang, "-fsyntax-only", hdr], capture_output=True, text=True)
         assert r.returncode == 0, r.stderr[-2000:]
+
+
+def _prototypes():
+    header = open(os.path.join(ROOT, "include", "picd_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    header = re.sub(r"//[^\n]*", "", header)
+    protos = {}
+    for m in re.finditer(r"\b(picd_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        params = [p.strip() for p in m.group(2).replace("\n", " ").split(",")]
+        protos[m.group(1)] = [] if params in ([""], ["void"]) else params
+    return protos
+
+
+def _kind(param: str) -> str:
+    if "*" in param or "cudaStream_t" in param:
+        return "p"
+    t = param.rsplit(" ", 1)[0] if " " in param else param
+    t = t.replace("const", "").strip()
+    return {"int": "i", "float": "f", "long long": "l", "unsigned": "u", "unsigned int": "u", "size_t": "z", "uint32_t": "u"}.get(t, "?")
+
+
+def test_ctypes_signatures_match_the_c_prototypes():
+    """ops/native.py binds the library through hand-written signature strings: each must agree with the prototype in the public
+    header in arity and in the class of every argument (pointer / int / float / long long / unsigned / size_t)."""
+    import sys
+    sys.path.insert(0, ROOT)
+    from picd_b200.ops import native
+    protos = _prototypes()
+    bad = []
+    for name, sig in native._SIG.items():
+        if name not in protos:
+            bad.append(f"{name}: no prototype in picd_b200.h")
+            continue
+        kinds = "".join(_kind(p) for p in protos[name])
+        if kinds != sig:
+            bad.append(f"{name}: header {kinds} != binding {sig}")
+    assert not bad, "\n".join(bad)
